@@ -1,0 +1,933 @@
+// =====================================================================================
+//  fempar_oracle.cpp  --  TEST INFRASTRUCTURE ONLY (parity oracle + timed CPU baseline)
+//
+//  A from-scratch CPU restatement (C++17, no GPU, no BLAS) of the FEMPAR hot path named
+//  by BASELINE.json:north_star.  The reference itself (Fortran 2003/2008 + FPL/FLAP
+//  submodules that are absent from /root/reference) cannot be compiled in this image, so
+//  this file follows the reference's algorithms step by step and cites, for every
+//  function, the reference file:line it restates.  Paths are relative to
+//  /root/reference/Sources/Lib unless stated.
+//
+//  PARITY PIN: validated against the only numeric golden data the reference holds for
+//  this path -- Tutorials/tutorial_01_poisson_sharp_circular_wave/convergence_plot/
+//  uniform_mesh_error_order_{1,2,4} (tests/test_oracle_golden.py) -- and against the
+//  par_test_poisson acceptance criterion (all error norms < 1e-4 for u = x+y+z).
+//  The DOF numbering / CSR graph have no fixture upstream: for them this restatement IS
+//  the pin, argued by the citations below ("parity unpinned" in the strict sense for the
+//  ORDER of the DOFs).
+//
+//  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+//  legs may load this library.  The product (fempar_b200/) never does.
+// =====================================================================================
+#include <algorithm>
+#include <array>
+#include <cassert>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <numeric>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace fo {
+
+typedef long long i64;
+
+// ---------------------------------------------------------------------------
+// polytope_t (hypercube only): n-faces sorted by (dimension, bit code)
+//   Integration/ReferenceFE/sbm_polytope.i90:175-227 (create + sort_n_faces)
+//   code = free_bits << d | anchor_bits ; "n_face_dir_is_fixed" returns the FREE bit
+//   (sbm_polytope.i90:342-349), "n_face_dir_coordinate" the anchor bit (:352-359).
+// ---------------------------------------------------------------------------
+struct Polytope {
+  int d = 0;
+  std::vector<int> code;          // sorted n-face codes; last one is the cell itself
+  std::vector<int> index_of_code; // ijk_to_index (1-based, 0 = none)
+  void create(int dims) {
+    d = dims;
+    code.clear();
+    for (int fr = 0; fr < (1 << d); ++fr)
+      for (int an = 0; an < (1 << d); ++an)
+        if ((fr & an) == 0) code.push_back((fr << d) | an);
+    std::stable_sort(code.begin(), code.end(), [&](int a, int b) {
+      int da = __builtin_popcount(a >> d), db = __builtin_popcount(b >> d);
+      if (da != db) return da < db;
+      return a < b;
+    });
+    index_of_code.assign(((1 << d) - 1) * (1 << d) + 1, 0);
+    for (size_t i = 0; i < code.size(); ++i) index_of_code[code[i]] = int(i) + 1;
+  }
+  int num_n_faces() const { return int(code.size()); }
+  int free_bits(int f) const { return code[f] >> d; }
+  int anchor(int f) const { return code[f] & ((1 << d) - 1); }
+  int dim(int f) const { return __builtin_popcount(free_bits(f)); }
+  int is_free(int f, int dir) const { return (free_bits(f) >> dir) & 1; }
+  int coord(int f, int dir) const { return (anchor(f) >> dir) & 1; }
+};
+
+// ijk <-> spatial numbering, Geometry/Tools/uniform_hex_mesh_generator.f90:783-815 (0-based here)
+static inline i64 ijk_to_lex(int d, const int* n, const int* ijk) {
+  i64 r = 0, prev = 1;
+  for (int k = 0; k < d; ++k) { r += prev * ijk[k]; prev *= n[k]; }
+  return r;
+}
+static inline void lex_to_ijk(int d, const int* n, i64 j, int* ijk) {
+  for (int k = 0; k < d; ++k) { ijk[k] = int(j % n[k]); j /= n[k]; }
+  for (int k = d; k < 3; ++k) ijk[k] = 0;
+}
+
+// ---------------------------------------------------------------------------
+// uniform_hex_mesh_t%generate_part_local_mesh
+//   Geometry/Tools/uniform_hex_mesh_generator.f90:145-647
+// ---------------------------------------------------------------------------
+struct Mesh {
+  int d = 3;
+  int N[3] = {1, 1, 1}, P[3] = {1, 1, 1}, pijk[3] = {0, 0, 0};
+  bool par = false;
+  int part_id = 1;
+  int nloc[3] = {1, 1, 1}, ntot[3] = {1, 1, 1}, L[3] = {0, 0, 0}, R[3] = {0, 0, 0}, first[3] = {0, 0, 0};
+  int n_local = 0, n_ghost = 0, n_itfc = 0, n_cells = 0;
+  Polytope poly;
+  int nvef = 0;       // n-faces per cell without the cell itself (26 in 3-D)
+  int ntypes = 0;
+  std::vector<std::array<int, 3>> tot_x_dir, glob_x_dir;
+  std::vector<int> tot_off;    // 0-based first vef id of each type (size ntypes+1)
+  std::vector<i64> glob_off;   // 1-based like the reference (num_global_n_faces)
+  std::vector<int> type_first_face; // polytope n-face (0-based) defining each type
+  int n_vefs = 0, n_vertices = 0;
+  std::vector<int> perm, lex_of;   // lex (total box, 0-based) -> local cell id (0-based) and inverse
+  std::vector<int> lst_vefs;       // [n_cells * nvef] local vef ids, 0-based
+  std::vector<int> vef_bid;        // boundary id per vef: 1..3^d-1 on the boundary, 3^d interior
+  std::vector<i64> cells_gid, vefs_gid; // 1-based global ids
+  std::vector<int> cells_part;     // 1-based part ids
+  std::vector<double> vcoord;      // [n_vertices*3]
+  std::vector<char> vef_ghost;     // vef touches no local cell
+  double dom[3][2] = {{0, 1}, {0, 1}, {0, 1}};
+
+  void create(int dims, const int* Nc, const int* Pp, int part /*1-based; <=0: serial*/) {
+    d = dims;
+    for (int k = 0; k < 3; ++k) { N[k] = k < d ? Nc[k] : 1; P[k] = 1; pijk[k] = 0; }
+    par = part > 0;
+    part_id = par ? part : 1;
+    poly.create(d);
+    nvef = poly.num_n_faces() - 1;
+    if (par) {
+      for (int k = 0; k < d; ++k) P[k] = Pp[k];
+      lex_to_ijk(d, P, part - 1, pijk);      // :263-268
+    }
+    for (int k = 0; k < 3; ++k) { L[k] = R[k] = 0; }
+    for (int k = 0; k < d; ++k) {            // :269-276 (non periodic)
+      L[k] = R[k] = 1;
+      if (pijk[k] == 0) L[k] = 0;
+      if (pijk[k] == P[k] - 1) R[k] = 0;
+    }
+    if (!par) for (int k = 0; k < 3; ++k) L[k] = R[k] = 0;
+    n_local = 1;
+    for (int k = 0; k < 3; ++k) { nloc[k] = 1; ntot[k] = 1; first[k] = 0; }
+    for (int k = 0; k < d; ++k) {            // :281-291
+      nloc[k] = N[k] / P[k];
+      first[k] = pijk[k] * nloc[k];
+      n_local *= nloc[k];
+      ntot[k] = nloc[k] + L[k] + R[k];
+      first[k] -= L[k];
+    }
+    n_cells = 1;
+    for (int k = 0; k < d; ++k) n_cells *= ntot[k];
+    n_ghost = n_cells - n_local;
+    // number of interface cells, :303-315
+    n_itfc = 1;
+    for (int k = 0; k < d; ++k) {
+      if (nloc[k] > L[k] + R[k]) n_itfc *= (nloc[k] - L[k] - R[k]);
+      else { n_itfc = 0; break; }
+    }
+    n_itfc = n_local - n_itfc;
+    // cell permutation interior -> interface (filled backwards) -> ghost (filled backwards), :316-351
+    perm.assign(n_cells, -1);
+    {
+      int ighost = 0, ilocal = 0, iitfc = 0, ijk[3];
+      for (int ic = 0; ic < n_cells; ++ic) {
+        lex_to_ijk(d, ntot, ic, ijk);
+        int p1 = 0; // 1-based like the reference, 0 = unset
+        for (int k = 0; k < d; ++k)
+          if ((L[k] == 1 && ijk[k] == 0) || (R[k] == 1 && ijk[k] == ntot[k] - 1)) {
+            p1 = n_local + n_ghost - ighost; ++ighost; break;
+          }
+        if (p1 == 0)
+          for (int k = 0; k < d; ++k)
+            if ((L[k] == 1 && ijk[k] == 1) || (R[k] == 1 && ijk[k] == ntot[k] - 2)) {
+              p1 = n_local - iitfc; ++iitfc; break;
+            }
+        if (p1 == 0) { ++ilocal; p1 = ilocal; }
+        perm[ic] = p1 - 1;
+      }
+      assert(ilocal == n_local - n_itfc && iitfc == n_itfc && ighost == n_ghost);
+    }
+    lex_of.assign(n_cells, -1);
+    for (int ic = 0; ic < n_cells; ++ic) lex_of[perm[ic]] = ic;
+    // n-face types, :371-430
+    ntypes = 0; tot_x_dir.clear(); glob_x_dir.clear(); type_first_face.clear();
+    for (int f = 0; f < poly.num_n_faces(); ++f)
+      if (poly.dim(f) < d && poly.anchor(f) == 0) {
+        std::array<int, 3> t = {1, 1, 1}, g = {1, 1, 1};
+        for (int k = 0; k < d; ++k) {
+          g[k] = N[k] + 1 - poly.is_free(f, k);
+          t[k] = ntot[k] + 1 - poly.is_free(f, k);
+        }
+        tot_x_dir.push_back(t); glob_x_dir.push_back(g); type_first_face.push_back(f);
+        ++ntypes;
+      }
+    tot_off.assign(ntypes + 1, 0); glob_off.assign(ntypes + 1, 1);
+    for (int t = 0; t < ntypes; ++t) {
+      i64 gt = 1; int tt = 1;
+      for (int k = 0; k < d; ++k) { gt *= glob_x_dir[t][k]; tt *= tot_x_dir[t][k]; }
+      tot_off[t + 1] = tot_off[t] + tt;
+      glob_off[t + 1] = glob_off[t] + gt;
+    }
+    n_vefs = tot_off[ntypes];
+    n_vertices = tot_off[1];
+    // cell -> vef list, :445-466
+    lst_vefs.assign(size_t(n_cells) * nvef, -1);
+    for (int ic = 0; ic < n_cells; ++ic) {
+      int ijk[3], fijk[3];
+      lex_to_ijk(d, ntot, ic, ijk);
+      int itype = -1;
+      for (int f = 0; f < nvef; ++f) {
+        if (poly.anchor(f) == 0) ++itype;
+        for (int k = 0; k < d; ++k) fijk[k] = (ijk[k] + poly.coord(f, k)) % tot_x_dir[itype][k];
+        lst_vefs[size_t(perm[ic]) * nvef + f] = tot_off[itype] + int(ijk_to_lex(d, tot_x_dir[itype].data(), fijk));
+      }
+    }
+    // cells gids / parts, :468-489
+    cells_gid.assign(n_cells, 0); cells_part.assign(n_cells, 1);
+    for (int ic = 0; ic < n_cells; ++ic) {
+      int ijk[3], mp[3] = {0, 0, 0}, g[3] = {0, 0, 0};
+      lex_to_ijk(d, ntot, ic, ijk);
+      for (int k = 0; k < d; ++k) {
+        if (L[k] == 1 && ijk[k] == 0) mp[k] = pijk[k] - 1;
+        else if (R[k] == 1 && ijk[k] == ntot[k] - 1) mp[k] = pijk[k] + 1;
+        else mp[k] = pijk[k];
+        g[k] = first[k] + ijk[k];
+      }
+      cells_part[perm[ic]] = 1 + int(ijk_to_lex(d, P, mp));
+      cells_gid[perm[ic]] = 1 + ijk_to_lex(d, N, g);
+    }
+    // vef gids, coordinates, boundary ids, :581-635
+    vefs_gid.assign(n_vefs, 0); vef_bid.assign(n_vefs, -1); vcoord.assign(size_t(n_vertices) * 3, 0.0);
+    for (int t = 0; t < ntypes; ++t) {
+      int f = type_first_face[t];
+      for (int v = tot_off[t]; v < tot_off[t + 1]; ++v) {
+        int fijk[3];
+        lex_to_ijk(d, tot_x_dir[t].data(), v - tot_off[t], fijk);
+        for (int k = 0; k < d; ++k) fijk[k] += first[k];
+        vefs_gid[v] = glob_off[t] + ijk_to_lex(d, glob_x_dir[t].data(), fijk);
+        if (t == 0)
+          for (int k = 0; k < d; ++k) {
+            double c = double(fijk[k]) / double(N[k]);
+            vcoord[size_t(v) * 3 + k] = (dom[k][1] - dom[k][0]) * c + dom[k][0];
+          }
+        int index = 0;
+        for (int k = 0; k < d; ++k) {
+          if (poly.is_free(f, k) == 0 && fijk[k] == 0) { /* bit stays 0 */ }
+          else if (poly.is_free(f, k) == 0 && fijk[k] == glob_x_dir[t][k] - 1) index |= (1 << k);
+          else index |= (1 << (d + k));
+        }
+        vef_bid[v] = poly.index_of_code[index];
+      }
+    }
+    // a vef is ghost iff no local cell touches it (bst_vef_iterator is_ghost semantics)
+    vef_ghost.assign(n_vefs, 1);
+    for (int c = 0; c < n_local; ++c)
+      for (int f = 0; f < nvef; ++f) vef_ghost[lst_vefs[size_t(c) * nvef + f]] = 0;
+  }
+  bool vef_at_boundary(int v) const { return vef_bid[v] != poly.num_n_faces(); }
+  // vertex coordinates of local cell c (2^d vertices, polytope order = x fastest)
+  void cell_vertices(int c, double* X /*[2^d][3]*/) const {
+    for (int a = 0; a < (1 << d); ++a) {
+      int v = lst_vefs[size_t(c) * nvef + a];
+      for (int k = 0; k < 3; ++k) X[a * 3 + k] = vcoord[size_t(v) * 3 + k];
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------
+// 1-D Lagrange basis on equispaced nodes of [-1,1]   (sbm_polynomial.i90:60-108)
+// Gauss-Legendre rule on [-1,1]                      (sbm_quadrature.i90:767-823)
+// ---------------------------------------------------------------------------
+static void lagrange_1d(int p, double x, double* val, double* der) {
+  std::vector<double> xn(p + 1);
+  for (int k = 0; k <= p; ++k) xn[k] = p == 0 ? 0.0 : -1.0 + 2.0 * k / p;
+  for (int k = 0; k <= p; ++k) {
+    double v = 1.0;
+    for (int m = 0; m <= p; ++m) if (m != k) v *= (x - xn[m]) / (xn[k] - xn[m]);
+    double dsum = 0.0;
+    for (int n = 0; n <= p; ++n) {
+      if (n == k) continue;
+      double t = 1.0 / (xn[k] - xn[n]);
+      for (int m = 0; m <= p; ++m) if (m != k && m != n) t *= (x - xn[m]) / (xn[k] - xn[m]);
+      dsum += t;
+    }
+    val[k] = v; der[k] = dsum;
+  }
+}
+static void gauss_legendre(int n, double* x, double* w) {
+  for (int i = 0; i < n; ++i) {
+    double z = std::cos(M_PI * (i + 0.75) / (n + 0.5)), pp = 0;
+    for (int it = 0; it < 100; ++it) {
+      double p1 = 1.0, p2 = 0.0;
+      for (int j = 1; j <= n; ++j) { double p3 = p2; p2 = p1; p1 = ((2.0 * j - 1.0) * z * p2 - (j - 1.0) * p3) / j; }
+      pp = n * (z * p1 - p2) / (z * z - 1.0);
+      double dz = p1 / pp; z -= dz;
+      if (std::fabs(dz) < 1e-16) break;
+    }
+    { double p1 = 1.0, p2 = 0.0;
+      for (int j = 1; j <= n; ++j) { double p3 = p2; p2 = p1; p1 = ((2.0 * j - 1.0) * z * p2 - (j - 1.0) * p3) / j; }
+      pp = n * (z * p1 - p2) / (z * z - 1.0); }
+    x[n - 1 - i] = z; w[n - 1 - i] = 2.0 / ((1.0 - z * z) * pp * pp);
+  }
+  for (int i = 0; i < n / 2; ++i) { // symmetrise
+    double xa = 0.5 * (x[n - 1 - i] - x[i]); x[i] = -xa; x[n - 1 - i] = xa;
+    double wa = 0.5 * (w[i] + w[n - 1 - i]); w[i] = w[n - 1 - i] = wa;
+  }
+  if (n % 2) x[n / 2] = 0.0;
+}
+
+// ---------------------------------------------------------------------------
+// Reference FE: hex Lagrangian of order p with ncomp components.
+//   node / shape index = i + j(p+1) + k(p+1)^2 (sbm_polytope.i90:882-893,
+//   sbm_hex_lagrangian_reference_fe.i90:301-316); vector fields = component-major
+//   blocks (sbm_lagrangian_reference_fe.i90:1141-1149); own DOFs of an n-face = its
+//   interior lattice nodes, lowest free direction fastest (sbm_polytope.i90:731-880),
+//   for ncomp>1 [comp1 nodes.., comp2 nodes..] (sbm_lagrangian_reference_fe.i90:1250-1286).
+//   Quadrature: p+1 GL points per direction (sbm_lagrangian_reference_fe.i90:1414-1423),
+//   x index fastest, weight = product.
+// ---------------------------------------------------------------------------
+struct RefFE {
+  int d, p, ncomp, n1, nnode, ndofs, nq;
+  std::vector<std::vector<int>> own;   // per n-face (incl. cell): cell-local dof ids (0-based)
+  std::vector<double> qx, qw;          // qx[nq*3], qw[nq]
+  std::vector<double> phi;             // [nq][nnode]
+  std::vector<double> dphi;            // [nq][nnode][3]  (reference gradients)
+  std::vector<double> gphi, gdphi;     // geometry (order 1) basis at the q-points: [nq][2^d], [nq][2^d][3]
+  std::vector<double> node_ref;        // reference coordinates of the nodes [nnode*3] in [-1,1]
+  std::vector<double> gphi_nodes;      // geometry basis at the FE nodes [nnode][2^d]
+  void create(const Polytope& poly, int order, int ncomponents) {
+    d = poly.d; p = order; ncomp = ncomponents; n1 = p + 1;
+    nnode = 1; for (int k = 0; k < d; ++k) nnode *= n1;
+    ndofs = nnode * ncomp;
+    own.assign(poly.num_n_faces(), {});
+    for (int f = 0; f < poly.num_n_faces(); ++f) {
+      std::vector<int> nodes;
+      int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+      for (int k = 0; k < d; ++k) {
+        if (poly.is_free(f, k)) { lo[k] = 1; hi[k] = p - 1; }
+        else { lo[k] = hi[k] = poly.coord(f, k) * p; }
+      }
+      for (int k2 = lo[2]; k2 <= hi[2]; ++k2)
+        for (int k1 = lo[1]; k1 <= hi[1]; ++k1)
+          for (int k0 = lo[0]; k0 <= hi[0]; ++k0) nodes.push_back(k0 + n1 * (k1 + (d > 2 ? n1 * k2 : 0)));
+      for (int c = 0; c < ncomp; ++c)
+        for (int nd : nodes) own[f].push_back(c * nnode + nd);
+    }
+    int nq1 = p + 1;
+    std::vector<double> x1(nq1), w1(nq1);
+    gauss_legendre(nq1, x1.data(), w1.data());
+    nq = 1; for (int k = 0; k < d; ++k) nq *= nq1;
+    qx.assign(size_t(nq) * 3, 0.0); qw.assign(nq, 0.0);
+    int nqd[3] = {nq1, nq1, d > 2 ? nq1 : 1}, nnd[3] = {n1, n1, d > 2 ? n1 : 1};
+    for (int q = 0; q < nq; ++q) {
+      int qi[3]; lex_to_ijk(d, nqd, q, qi);
+      double w = 1.0;
+      for (int k = 0; k < d; ++k) { qx[q * 3 + k] = x1[qi[k]]; w *= w1[qi[k]]; }
+      qw[q] = w;
+    }
+    auto tabulate = [&](int ord, const double* pts, int npts, std::vector<double>& v, std::vector<double>* dv) {
+      int m1 = ord + 1, nn = 1; for (int k = 0; k < d; ++k) nn *= m1;
+      int mm[3] = {m1, m1, d > 2 ? m1 : 1};
+      v.assign(size_t(npts) * nn, 0.0);
+      if (dv) dv->assign(size_t(npts) * nn * 3, 0.0);
+      std::vector<double> l(3 * m1, 1.0), dl(3 * m1, 0.0);
+      for (int q = 0; q < npts; ++q) {
+        for (int k = 0; k < d; ++k) lagrange_1d(ord, pts[q * 3 + k], &l[k * m1], &dl[k * m1]);
+        for (int a = 0; a < nn; ++a) {
+          int ai[3]; lex_to_ijk(d, mm, a, ai);
+          double val = 1.0;
+          for (int k = 0; k < d; ++k) val *= l[k * m1 + ai[k]];
+          v[size_t(q) * nn + a] = val;
+          if (dv)
+            for (int k = 0; k < d; ++k) {
+              double g = 1.0;
+              for (int k2 = 0; k2 < d; ++k2) g *= (k2 == k) ? dl[k2 * m1 + ai[k2]] : l[k2 * m1 + ai[k2]];
+              (*dv)[(size_t(q) * nn + a) * 3 + k] = g;
+            }
+        }
+      }
+    };
+    tabulate(p, qx.data(), nq, phi, &dphi);
+    tabulate(1, qx.data(), nq, gphi, &gdphi);
+    node_ref.assign(size_t(nnode) * 3, 0.0);
+    for (int a = 0; a < nnode; ++a) {
+      int ai[3]; lex_to_ijk(d, nnd, a, ai);
+      for (int k = 0; k < d; ++k) node_ref[a * 3 + k] = -1.0 + 2.0 * ai[k] / p;
+    }
+    tabulate(1, node_ref.data(), nnode, gphi_nodes, nullptr);
+  }
+};
+
+// ---------------------------------------------------------------------------
+// analytic data ("functions")
+// ---------------------------------------------------------------------------
+enum { FUNC_ZERO = 0, FUNC_LINEAR = 1, FUNC_SHARP_WAVE = 2 };
+struct Func {
+  int kind = FUNC_LINEAR, d = 3;
+  double alpha = 200.0, r = 0.7, c[3] = {-0.05, -0.05, -0.05};
+  // exact solution / boundary function
+  double u(const double* x) const {
+    if (kind == FUNC_LINEAR) { double s = 0; for (int k = 0; k < d; ++k) s += x[k]; return s; } // par_test_poisson_analytical_functions.f90:71-124
+    if (kind == FUNC_SHARP_WAVE) { // tutorial_01_..._modules.f90:462-484
+      double t = 0; for (int k = 0; k < d; ++k) t += (x[k] - c[k]) * (x[k] - c[k]);
+      return std::atan(alpha * (std::sqrt(t) - r));
+    }
+    return 0.0;
+  }
+  void grad_u(const double* x, double* g) const {
+    g[0] = g[1] = g[2] = 0.0;
+    if (kind == FUNC_LINEAR) { for (int k = 0; k < d; ++k) g[k] = 1.0; return; }
+    if (kind == FUNC_SHARP_WAVE) { // tutorial_01_..._modules.f90:486-527
+      double t1 = 0; for (int k = 0; k < d; ++k) t1 += (x[k] - c[k]) * (x[k] - c[k]);
+      double s = std::sqrt(t1), t2 = s - r, den = s * (alpha * alpha * t2 * t2 + 1.0);
+      for (int k = 0; k < d; ++k) g[k] = alpha * (x[k] - c[k]) / den;
+    }
+  }
+  double f(const double* x) const { // source term
+    if (kind != FUNC_SHARP_WAVE) return 0.0;
+    // tutorial_01_..._modules.f90:395-458
+    double a = alpha, a2 = a * a, a3 = a2 * a, t1 = 0, dx2[3];
+    for (int k = 0; k < d; ++k) { dx2[k] = (x[k] - c[k]) * (x[k] - c[k]); t1 += dx2[k]; }
+    double s = std::sqrt(t1), t2 = s - r, t22 = t2 * t2;
+    double den1 = s * (a2 * t22 + 1.0), den2 = std::pow(t1, 1.5) * (a2 * t22 + 1.0),
+           den3 = t1 * (a2 * t22 + 1.0) * (a2 * t22 + 1.0);
+    double res = 0;
+    for (int k = 0; k < d; ++k) res -= a / den1 - (a * dx2[k]) / den2 - (2.0 * a3 * dx2[k] * t2) / den3;
+    return res;
+  }
+};
+
+enum { KIND_POISSON = 0, KIND_VECTOR_LAPLACIAN = 1, KIND_ELASTICITY = 2 };
+
+// ---------------------------------------------------------------------------
+// The FE space + linear system of one part (or of the serial problem)
+// ---------------------------------------------------------------------------
+struct Space {
+  Mesh m;
+  RefFE fe;
+  unsigned dir_mask = 0xFFFFFFFFu;     // bit (b-1) set => boundary id b carries a strong Dirichlet condition
+  std::vector<int> gids;               // lst_dofs_gids [n_cells*ndofs], 1-based signed (fe_space.f90:636-637)
+  int n_dirichlet = 0, n_free = 0, n_free_ghost = 0;
+  // linear system
+  bool sym_storage = false;
+  std::vector<i64> irp;                // 0-based offsets here, size n+1 (exported 1-based on request)
+  std::vector<int> ja;                 // 1-based column ids like the reference
+  std::vector<double> val, rhs, fixed;
+  std::vector<double> dinv;            // Jacobi inverse diagonal
+  // par data (filled by par layer)
+  std::vector<double> weight;
+  double t_integrate = 0, t_pattern = 0;
+
+  bool vef_dirichlet(int v) const {
+    int b = m.vef_bid[v];
+    if (b == m.poly.num_n_faces()) return false;
+    return (dir_mask >> (b - 1)) & 1u;
+  }
+
+  void create(int d, const int* N, const int* P, int part, int order, int ncomp, unsigned mask) {
+    m.create(d, N, P, part);
+    fe.create(m.poly, order, ncomp);
+    dir_mask = mask;
+    gids.assign(size_t(m.n_cells) * fe.ndofs, 0);
+    setup_strong_dirichlet();
+    list_dofs();
+  }
+
+  // serial_fe_space_set_up_strong_dirichlet_bcs  Integration/FESpace/sbm_serial_fe_space.i90:525-651
+  //   + ..._on_vef_and_field :653-709, generate_own_dofs_vef_component_wise sbm_fe_cell_iterator.i90:686-732,
+  //   fetch_own_dofs_vef_from_source_fe :803-856 (identity permutation on an oriented structured mesh)
+  void setup_strong_dirichlet() {
+    const int nvef = m.nvef, nd = fe.ndofs;
+    n_dirichlet = 0;
+    std::vector<int> vis_cell(m.n_vefs, -1), vis_ivef(m.n_vefs, -1);
+    for (int c = 0; c < m.n_cells; ++c)          // the cell iterator runs over local AND ghost cells
+      for (int f = 0; f < nvef; ++f) {
+        int v = m.lst_vefs[size_t(c) * nvef + f];
+        if (!vef_dirichlet(v)) continue;         // vef%get_set_id() /= 0 and the condition flags every component
+        int prev = n_dirichlet;
+        if (vis_cell[v] == -1) {
+          for (int l : fe.own[f]) {
+            int& g = gids[size_t(c) * nd + l];
+            if (g >= 0) { ++n_dirichlet; g = -n_dirichlet; }
+          }
+        }
+        if (vis_cell[v] != -1) {
+          int sc = vis_cell[v], sf = vis_ivef[v];
+          for (size_t i = 0; i < fe.own[f].size(); ++i)
+            gids[size_t(c) * nd + fe.own[f][i]] = gids[size_t(sc) * nd + fe.own[sf][i]];
+        }
+        if (vis_cell[v] == -1 && prev < n_dirichlet) { vis_cell[v] = c; vis_ivef[v] = f; }
+      }
+  }
+
+  // serial_fe_space_list_dofs  Integration/FESpace/sbm_serial_fe_space.i90:2623-2875
+  //   generate_own_dofs_cell sbm_fe_cell_iterator.i90:410-454 ; generate_own_dofs_vef :507-544
+  void list_dofs() {
+    const int nvef = m.nvef, nd = fe.ndofs;
+    std::vector<int> own_cell(m.n_vefs, -1), own_ivef(m.n_vefs, -1);
+    int cur = 0;
+    for (int c = 0; c < m.n_cells; ++c) {        // first loop: every cell, local ones first
+      bool local = c < m.n_local;
+      if (local)
+        for (int l : fe.own[nvef]) gids[size_t(c) * nd + l] = ++cur;   // interior DOFs, unconditional
+      for (int f = 0; f < nvef; ++f) {
+        int v = m.lst_vefs[size_t(c) * nvef + f];
+        if (m.vef_ghost[v]) continue;
+        if (own_cell[v] == -1) {
+          if (local) {
+            int prev = cur;
+            for (int l : fe.own[f]) {
+              int& g = gids[size_t(c) * nd + l];
+              if (g >= 0) g = ++cur;
+            }
+            if (prev < cur) { own_cell[v] = c; own_ivef[v] = f; }
+          }
+        } else {
+          int sc = own_cell[v], sf = own_ivef[v];
+          for (size_t i = 0; i < fe.own[f].size(); ++i)
+            gids[size_t(c) * nd + fe.own[f][i]] = gids[size_t(sc) * nd + fe.own[sf][i]];
+        }
+      }
+    }
+    n_free = cur;
+    int gcur = cur;
+    for (int c = m.n_local; c < m.n_cells; ++c) { // second loop: ghost cells, :2812-2859
+      for (int l : fe.own[nvef]) gids[size_t(c) * nd + l] = ++gcur;
+      for (int f = 0; f < nvef; ++f) {
+        int v = m.lst_vefs[size_t(c) * nvef + f];
+        if (!m.vef_ghost[v]) continue;
+        if (own_cell[v] == -1) {
+          int prev = gcur;
+          for (int l : fe.own[f]) {
+            int& g = gids[size_t(c) * nd + l];
+            if (g >= 0) g = ++gcur;
+          }
+          if (prev < gcur) { own_cell[v] = c; own_ivef[v] = f; }
+        } else {
+          int sc = own_cell[v], sf = own_ivef[v];
+          for (size_t i = 0; i < fe.own[f].size(); ++i)
+            gids[size_t(c) * nd + fe.own[f][i]] = gids[size_t(sc) * nd + fe.own[sf][i]];
+        }
+      }
+    }
+    n_free_ghost = gcur - cur;
+  }
+
+  // physical coordinates of the FE nodes of a cell through the order-1 geometry map
+  void node_coords(int c, double* xn /*[nnode][3]*/) const {
+    double X[8 * 3]; m.cell_vertices(c, X);
+    int nv = 1 << m.d;
+    for (int a = 0; a < fe.nnode; ++a)
+      for (int k = 0; k < 3; ++k) {
+        double s = 0; for (int v = 0; v < nv; ++v) s += fe.gphi_nodes[size_t(a) * nv + v] * X[v * 3 + k];
+        xn[a * 3 + k] = s;
+      }
+  }
+
+  // interpolate_dirichlet_values: fixed_dof_values(-gid) = g(x_node)  sbm_serial_fe_space.i90:997-1176
+  void interpolate_dirichlet(const Func& fn) {
+    fixed.assign(n_dirichlet, 0.0);
+    std::vector<double> xn(size_t(fe.nnode) * 3);
+    for (int c = 0; c < m.n_cells; ++c) {
+      bool any = false;
+      for (int l = 0; l < fe.ndofs; ++l) if (gids[size_t(c) * fe.ndofs + l] < 0) { any = true; break; }
+      if (!any) continue;
+      node_coords(c, xn.data());
+      for (int l = 0; l < fe.ndofs; ++l) {
+        int g = gids[size_t(c) * fe.ndofs + l];
+        if (g < 0) fixed[-g - 1] = fn.u(&xn[size_t(l % fe.nnode) * 3]);
+      }
+    }
+  }
+
+  // cell_map_update + apply_cell_map_to_interpolation for one cell:
+  //   J(q) = sum_a x_a (x) grad N_a(q)  (sbm_cell_map.i90:272-296), invmtx (sbm_cell_integrator.i90:448-561),
+  //   grad phi = J^-T grad_ref phi   (sbm_lagrangian_reference_fe.i90:1333-1347)
+  void cell_geometry(int c, double* detj /*[nq]*/, double* grad /*[nq][nnode][3]*/, double* xq /*[nq][3]*/) const {
+    const int d = m.d, nv = 1 << d;
+    double X[8 * 3]; m.cell_vertices(c, X);
+    for (int q = 0; q < fe.nq; ++q) {
+      double J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+      for (int k = 0; k < 3; ++k) xq[q * 3 + k] = 0.0;
+      for (int a = 0; a < nv; ++a) {
+        for (int i = 0; i < d; ++i)
+          for (int j = 0; j < d; ++j) J[i][j] += X[a * 3 + j] * fe.gdphi[(size_t(q) * nv + a) * 3 + i]; // J(i,j)= d x_j / d xi_i
+        for (int k = 0; k < 3; ++k) xq[q * 3 + k] += fe.gphi[size_t(q) * nv + a] * X[a * 3 + k];
+      }
+      double inv[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, det;
+      if (d == 2) {
+        det = J[0][0] * J[1][1] - J[0][1] * J[1][0];
+        inv[0][0] = J[1][1] / det; inv[1][1] = J[0][0] / det; inv[0][1] = -J[0][1] / det; inv[1][0] = -J[1][0] / det;
+      } else {
+        double c00 = J[1][1] * J[2][2] - J[1][2] * J[2][1], c01 = J[1][2] * J[2][0] - J[1][0] * J[2][2],
+               c02 = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+        det = J[0][0] * c00 + J[0][1] * c01 + J[0][2] * c02;
+        inv[0][0] = c00 / det; inv[1][0] = c01 / det; inv[2][0] = c02 / det;
+        inv[0][1] = (J[0][2] * J[2][1] - J[0][1] * J[2][2]) / det;
+        inv[1][1] = (J[0][0] * J[2][2] - J[0][2] * J[2][0]) / det;
+        inv[2][1] = (J[0][1] * J[2][0] - J[0][0] * J[2][1]) / det;
+        inv[0][2] = (J[0][1] * J[1][2] - J[0][2] * J[1][1]) / det;
+        inv[1][2] = (J[0][2] * J[1][0] - J[0][0] * J[1][2]) / det;
+        inv[2][2] = (J[0][0] * J[1][1] - J[0][1] * J[1][0]) / det;
+      }
+      detj[q] = std::fabs(det);
+      // with J(i,j) = d x_j/d xi_i : grad_x phi = J^{-1} grad_xi phi
+      for (int a = 0; a < fe.nnode; ++a)
+        for (int i = 0; i < 3; ++i) {
+          double s = 0;
+          for (int j = 0; j < d; ++j) s += inv[i][j] * fe.dphi[(size_t(q) * fe.nnode + a) * 3 + j];
+          grad[(size_t(q) * fe.nnode + a) * 3 + i] = i < d ? s : 0.0;
+        }
+    }
+  }
+
+  // the user integrands:
+  //  Poisson   Tutorials/tutorial_01_.../modules/tutorial_01_..._modules.f90:71-137 and
+  //            Tests/Par/par_test_poisson/modules/par_test_poisson_discrete_integration.f90:62-142
+  //  vector Laplacian  Tests/Serial/test_poisson/modules/vector_poisson_discrete_integration.f90:62-140
+  //  elasticity  Tests/Par/par_test_pb_bddc_linear_elasticity/modules/sbm_irreducible_discrete_integration.i90:93-125
+  void element(int c, int kind, const Func& fn, const double* mat /*lambda,mu*/, double* elmat /*col-major nd x nd*/, double* elvec,
+               double* detj, double* grad, double* xq) const {
+    const int nd = fe.ndofs, nn = fe.nnode;
+    cell_geometry(c, detj, grad, xq);
+    std::fill(elmat, elmat + size_t(nd) * nd, 0.0);
+    std::fill(elvec, elvec + nd, 0.0);
+    for (int q = 0; q < fe.nq; ++q) {
+      double factor = detj[q] * fe.qw[q];
+      const double* g = &grad[size_t(q) * nn * 3];
+      if (kind == KIND_POISSON) {
+        for (int i = 0; i < nd; ++i)
+          for (int j = 0; j < nd; ++j)
+            elmat[i + size_t(j) * nd] += factor * (g[j * 3] * g[i * 3] + g[j * 3 + 1] * g[i * 3 + 1] + g[j * 3 + 2] * g[i * 3 + 2]);
+        double f = fn.f(&xq[q * 3]);
+        for (int i = 0; i < nd; ++i) elvec[i] += factor * f * fe.phi[size_t(q) * nn + i];
+      } else if (kind == KIND_VECTOR_LAPLACIAN) {
+        for (int i = 0; i < nd; ++i)
+          for (int j = 0; j < nd; ++j) {
+            int ci = i / nn, cj = j / nn, ni = i % nn, nj = j % nn;
+            double dc = (ci == cj) ? (g[nj * 3] * g[ni * 3] + g[nj * 3 + 1] * g[ni * 3 + 1] + g[nj * 3 + 2] * g[ni * 3 + 2]) : 0.0;
+            elmat[i + size_t(j) * nd] += factor * dc;
+          }
+        // source term is zero in vector_poisson_analytical_functions.f90:69-82
+      } else { // isotropic linear elasticity: sigma = lambda tr(eps) I + 2 mu eps
+        double lambda = mat[0], mu = mat[1];
+        for (int i = 0; i < nd; ++i)
+          for (int j = 0; j < nd; ++j) {
+            int ci = i / nn, cj = j / nn, ni = i % nn, nj = j % nn;
+            // eps(phi_j e_cj) : sigma(phi_i e_ci)
+            double gi[3] = {g[ni * 3], g[ni * 3 + 1], g[ni * 3 + 2]}, gj[3] = {g[nj * 3], g[nj * 3 + 1], g[nj * 3 + 2]};
+            double dotg = gi[0] * gj[0] + gi[1] * gj[1] + gi[2] * gj[2];
+            double v = lambda * gi[ci] * gj[cj] + mu * ((ci == cj ? dotg : 0.0) + gi[cj] * gj[ci]);
+            elmat[i + size_t(j) * nd] += factor * v;
+          }
+      }
+    }
+  }
+
+  // fe_cell_iterator_impose_strong_dirichlet_bcs_conforming  sbm_fe_cell_iterator.i90:1610-1637
+  void impose_dirichlet(int c, const double* elmat, double* elvec) const {
+    const int nd = fe.ndofs;
+    for (int j = 0; j < nd; ++j) {
+      int g = gids[size_t(c) * nd + j];
+      if (g < 0) {
+        double gv = fixed[-g - 1];
+        for (int i = 0; i < nd; ++i) elvec[i] -= elmat[i + size_t(j) * nd] * gv;
+      }
+    }
+  }
+
+  // Assembly.  route 0 = reference-faithful COO append -> stable sort -> sum duplicates in insertion order
+  //   (base_sparse_matrix.f90:3469-3513, 4479-4628; csr_sparse_matrix.f90:416-479);
+  // route 1 = direct: graph first, then accumulate in the same cell order (bitwise identical sums,
+  //   needed beyond the int32/COO memory limits).
+  // Matrix rows/cols are the LOCAL free dofs 1..n_free; gids > n_free (ghost-only) are dropped
+  // (base_sparse_matrix.f90:3469-3513 filters ia/ja outside 1..n), Dirichlet (<1) dropped.
+  void assemble(int kind, const Func& fn, const double* mat, bool sym, int route) {
+    sym_storage = sym;
+    const int nd = fe.ndofs, n = n_free;
+    interpolate_dirichlet(fn);
+    rhs.assign(n, 0.0);
+    std::vector<double> elmat(size_t(nd) * nd), elvec(nd), detj(fe.nq), grad(size_t(fe.nq) * fe.nnode * 3), xq(size_t(fe.nq) * 3);
+    if (route == 0) {
+      std::vector<int> ci, cj; std::vector<double> cv;
+      for (int c = 0; c < m.n_local; ++c) {
+        element(c, kind, fn, mat, elmat.data(), elvec.data(), detj.data(), grad.data(), xq.data());
+        impose_dirichlet(c, elmat.data(), elvec.data());
+        const int* g = &gids[size_t(c) * nd];
+        for (int j = 0; j < nd; ++j) {         // coo append: loops j (columns) outer, i inner
+          if (g[j] < 1 || g[j] > n) continue;
+          for (int i = 0; i < nd; ++i) {
+            if (g[i] < 1 || g[i] > n) continue;
+            if (sym && g[i] > g[j]) continue;
+            ci.push_back(g[i]); cj.push_back(g[j]); cv.push_back(elmat[i + size_t(j) * nd]);
+          }
+        }
+        for (int i = 0; i < nd; ++i) if (g[i] >= 1 && g[i] <= n) rhs[g[i] - 1] += elvec[i]; // serial_scalar_array.f90:247-262
+      }
+      std::vector<size_t> idx(ci.size());
+      std::iota(idx.begin(), idx.end(), size_t(0));
+      std::stable_sort(idx.begin(), idx.end(), [&](size_t a, size_t b) {
+        if (ci[a] != ci[b]) return ci[a] < ci[b];
+        return cj[a] < cj[b];
+      });
+      irp.assign(n + 1, 0); ja.clear(); val.clear();
+      int lr = -1, lc = -1;
+      for (size_t k : idx) {
+        if (ci[k] == lr && cj[k] == lc) { val.back() += cv[k]; continue; }
+        lr = ci[k]; lc = cj[k];
+        ja.push_back(lc); val.push_back(cv[k]); irp[lr]++;
+      }
+      for (int i = 0; i < n; ++i) irp[i + 1] += irp[i];
+    } else {
+      build_pattern(sym);
+      std::fill(val.begin(), val.end(), 0.0);
+      for (int c = 0; c < m.n_local; ++c) {
+        element(c, kind, fn, mat, elmat.data(), elvec.data(), detj.data(), grad.data(), xq.data());
+        impose_dirichlet(c, elmat.data(), elvec.data());
+        const int* g = &gids[size_t(c) * nd];
+        for (int i = 0; i < nd; ++i) {
+          if (g[i] < 1 || g[i] > n) continue;
+          const int* rb = &ja[irp[g[i] - 1]]; const int* re = &ja[irp[g[i]]];
+          for (int j = 0; j < nd; ++j) {
+            if (g[j] < 1 || g[j] > n) continue;
+            if (sym && g[i] > g[j]) continue;
+            const int* it = std::lower_bound(rb, re, g[j]);
+            val[it - &ja[0]] += elmat[i + size_t(j) * nd];
+          }
+          rhs[g[i] - 1] += elvec[i];
+        }
+      }
+    }
+  }
+
+  void build_pattern(bool sym) {
+    sym_storage = sym;
+    const int nd = fe.ndofs, n = n_free;
+    // dof -> cells adjacency
+    std::vector<i64> dptr(n + 1, 0);
+    for (int c = 0; c < m.n_local; ++c)
+      for (int l = 0; l < nd; ++l) { int g = gids[size_t(c) * nd + l]; if (g >= 1 && g <= n) dptr[g]++; }
+    for (int i = 0; i < n; ++i) dptr[i + 1] += dptr[i];
+    std::vector<int> dcell(dptr[n]); std::vector<i64> pos(dptr.begin(), dptr.end() - 1);
+    for (int c = 0; c < m.n_local; ++c)
+      for (int l = 0; l < nd; ++l) { int g = gids[size_t(c) * nd + l]; if (g >= 1 && g <= n) dcell[pos[g - 1]++] = c; }
+    irp.assign(n + 1, 0);
+    std::vector<int> tmp;
+    for (int pass = 0; pass < 2; ++pass) {
+      for (int r = 0; r < n; ++r) {
+        tmp.clear();
+        for (i64 k = dptr[r]; k < dptr[r + 1]; ++k) {
+          const int* g = &gids[size_t(dcell[k]) * nd];
+          for (int l = 0; l < nd; ++l) if (g[l] >= 1 && g[l] <= n && (!sym || g[l] >= r + 1)) tmp.push_back(g[l]);
+        }
+        std::sort(tmp.begin(), tmp.end());
+        tmp.erase(std::unique(tmp.begin(), tmp.end()), tmp.end());
+        if (pass == 0) irp[r + 1] = irp[r] + i64(tmp.size());
+        else std::copy(tmp.begin(), tmp.end(), ja.begin() + irp[r]);
+      }
+      if (pass == 0) { ja.assign(irp[n], 0); val.assign(irp[n], 0.0); }
+    }
+  }
+
+  // csr matvec / matvec_symmetric_storage   LinearAlgebra/SparseMatrix/csr_sparse_matrix.f90:545-568,597-623
+  void spmv(const double* x, double* y) const {
+    const int n = n_free;
+    if (!sym_storage) {
+#pragma omp parallel for schedule(static)
+      for (int i = 0; i < n; ++i) {
+        double s = 0.0;
+        for (i64 k = irp[i]; k < irp[i + 1]; ++k) s += val[k] * x[ja[k] - 1];
+        y[i] = s;
+      }
+    } else {
+      std::fill(y, y + n, 0.0);
+      for (int i = 0; i < n; ++i) {
+        i64 k0 = irp[i];
+        if (k0 == irp[i + 1]) continue;
+        // the diagonal is the first stored entry of each row
+        y[i] += val[k0] * x[ja[k0] - 1];
+        for (i64 k = k0 + 1; k < irp[i + 1]; ++k) {
+          y[i] += val[k] * x[ja[k] - 1];
+          y[ja[k] - 1] += val[k] * x[i];
+        }
+      }
+    }
+  }
+
+  // csr extract_diagonal (csr_sparse_matrix.f90:4231-4256) + entrywise_invert (jacobi_preconditioner.f90:371-386)
+  void jacobi_setup() {
+    const int n = n_free;
+    dinv.assign(n, 0.0);
+    for (int i = 0; i < n; ++i) {
+      const int* rb = &ja[irp[i]]; const int* re = &ja[irp[i + 1]];
+      const int* it = std::lower_bound(rb, re, i + 1);
+      if (it != re && *it == i + 1) dinv[i] = val[it - &ja[0]];
+    }
+    for (int i = 0; i < n; ++i) dinv[i] = 1.0 / dinv[i];
+  }
+
+  static double dot(const double* a, const double* b, int n) { double s = 0; for (int i = 0; i < n; ++i) s += a[i] * b[i]; return s; }
+
+  // cg_solve_body  LinearAlgebra/IterativeLinearSolver/cg.f90:101-238; stopping criteria :279-407
+  //  stop: 0 = res_res (default for CG), 1 = res_rhs
+  int cg(int prec /*0 identity, 1 jacobi*/, double rtol, double atol, int maxit, int stop, const double* b, double* x,
+         int* iters, int* converged, double* err, double* hist, double* t_spmv_acc) {
+    const int n = n_free;
+    std::vector<double> r(n), z(n), p(n), Ap(n);
+    auto applyM = [&](const double* in, double* out) {
+      if (prec == 1) for (int i = 0; i < n; ++i) out[i] = dinv[i] * in[i];
+      else std::copy(in, in + n, out);
+    };
+    std::fill(x, x + n, 0.0);                       // x <- initial_solution (zero)
+    spmv(x, r.data());                              // r = A x
+    for (int i = 0; i < n; ++i) r[i] = b[i] - r[i]; // r = b - r
+    applyM(r.data(), z.data());
+    double r_z = dot(r.data(), z.data(), n);
+    p = z;
+    double tol = (stop == 1 ? rtol * std::sqrt(dot(b, b, n)) : rtol * std::sqrt(dot(r.data(), r.data(), n))) + atol;
+    int it = 0; bool conv = false; double e = 0;
+    for (;;) {
+      ++it;
+      spmv(p.data(), Ap.data());
+      double App = dot(Ap.data(), p.data(), n);
+      double alpha = (App != 0.0) ? r_z / App : 0.0;
+      for (int i = 0; i < n; ++i) x[i] += alpha * p[i];
+      for (int i = 0; i < n; ++i) r[i] -= alpha * Ap[i];
+      e = std::sqrt(dot(r.data(), r.data(), n));
+      if (hist) hist[it - 1] = e;
+      conv = e <= tol;
+      if (conv || it >= maxit) break;
+      applyM(r.data(), z.data());
+      double beta = 1.0 / r_z;
+      r_z = dot(r.data(), z.data(), n);
+      beta *= r_z;
+      for (int i = 0; i < n; ++i) p[i] = z[i] + beta * p[i];
+    }
+    *iters = it; *converged = conv ? 1 : 0; *err = e;
+    (void)t_spmv_acc;
+    return 0;
+  }
+
+  // energy-norm error sqrt(sum_K int |grad(u - u_h)|^2)  tutorial_01_..._modules.f90:611-661; also L2
+  void errors(const double* x, const Func& fn, double* h1semi, double* l2) const {
+    const int nd = fe.ndofs, nn = fe.nnode;
+    std::vector<double> detj(fe.nq), grad(size_t(fe.nq) * nn * 3), xq(size_t(fe.nq) * 3), ul(nd);
+    double e1 = 0, e0 = 0;
+    for (int c = 0; c < m.n_local; ++c) {
+      cell_geometry(c, detj.data(), grad.data(), xq.data());
+      for (int l = 0; l < nd; ++l) {
+        int g = gids[size_t(c) * nd + l];
+        ul[l] = g > 0 ? x[g - 1] : fixed[-g - 1];
+      }
+      double loc = 0;
+      for (int q = 0; q < fe.nq; ++q) {
+        double factor = detj[q] * fe.qw[q], gu[3], uh = 0, gh[3] = {0, 0, 0};
+        fn.grad_u(&xq[q * 3], gu);
+        for (int a = 0; a < nn; ++a) {
+          uh += ul[a] * fe.phi[size_t(q) * nn + a];
+          for (int k = 0; k < 3; ++k) gh[k] += ul[a] * grad[(size_t(q) * nn + a) * 3 + k];
+        }
+        double dd = 0; for (int k = 0; k < 3; ++k) dd += (gu[k] - gh[k]) * (gu[k] - gh[k]);
+        loc += factor * dd;
+        double du = fn.u(&xq[q * 3]) - uh; e0 += factor * du * du;
+      }
+      e1 += loc;
+    }
+    *h1semi = std::sqrt(e1); *l2 = std::sqrt(e0);
+  }
+};
+
+} // namespace fo
+
+// =====================================================================================
+// flat C API for ctypes
+// =====================================================================================
+using fo::Space; using fo::Func; using fo::i64;
+static Func make_func(int d, int kind, const double* prm) {
+  Func f; f.kind = kind; f.d = d;
+  if (prm) { f.alpha = prm[0]; f.r = prm[1]; f.c[0] = prm[2]; f.c[1] = prm[3]; f.c[2] = prm[4]; }
+  return f;
+}
+extern "C" {
+void* fo_create(int d, const int* N, const int* P, int part_id, int order, int ncomp, unsigned dir_mask) {
+  Space* s = new Space(); s->create(d, N, P, part_id, order, ncomp, dir_mask); return s;
+}
+void fo_destroy(void* h) { delete (Space*)h; }
+int fo_num_cells(void* h) { return ((Space*)h)->m.n_cells; }
+int fo_num_local_cells(void* h) { return ((Space*)h)->m.n_local; }
+int fo_num_itfc_cells(void* h) { return ((Space*)h)->m.n_itfc; }
+int fo_num_vefs(void* h) { return ((Space*)h)->m.n_vefs; }
+int fo_ndofs_per_cell(void* h) { return ((Space*)h)->fe.ndofs; }
+int fo_num_free(void* h) { return ((Space*)h)->n_free; }
+int fo_num_free_ghost(void* h) { return ((Space*)h)->n_free_ghost; }
+int fo_num_dirichlet(void* h) { return ((Space*)h)->n_dirichlet; }
+const int* fo_lst_dofs_gids(void* h) { return ((Space*)h)->gids.data(); }
+const int* fo_lst_vefs(void* h) { return ((Space*)h)->m.lst_vefs.data(); }
+const int* fo_vef_bid(void* h) { return ((Space*)h)->m.vef_bid.data(); }
+const i64* fo_cells_gid(void* h) { return ((Space*)h)->m.cells_gid.data(); }
+const int* fo_cells_part(void* h) { return ((Space*)h)->m.cells_part.data(); }
+const i64* fo_vefs_gid(void* h) { return ((Space*)h)->m.vefs_gid.data(); }
+int fo_assemble(void* h, int kind, int func, const double* fprm, const double* mat, int sym, int route) {
+  Space* s = (Space*)h; Func f = make_func(s->m.d, func, fprm);
+  s->assemble(kind, f, mat, sym != 0, route); return 0;
+}
+int fo_build_pattern(void* h, int sym) { ((Space*)h)->build_pattern(sym != 0); return 0; }
+i64 fo_nnz(void* h) { return i64(((Space*)h)->ja.size()); }
+const i64* fo_irp(void* h) { return ((Space*)h)->irp.data(); }      // 0-based offsets (reference irp = this + 1)
+const int* fo_ja(void* h) { return ((Space*)h)->ja.data(); }        // 1-based
+const double* fo_val(void* h) { return ((Space*)h)->val.data(); }
+const double* fo_rhs(void* h) { return ((Space*)h)->rhs.data(); }
+const double* fo_fixed(void* h) { return ((Space*)h)->fixed.data(); }
+int fo_spmv(void* h, const double* x, double* y) { ((Space*)h)->spmv(x, y); return 0; }
+int fo_jacobi_setup(void* h) { ((Space*)h)->jacobi_setup(); return 0; }
+const double* fo_dinv(void* h) { return ((Space*)h)->dinv.data(); }
+int fo_cg(void* h, int prec, double rtol, double atol, int maxit, int stop, const double* b, double* x, int* iters,
+          int* converged, double* err, double* hist) {
+  return ((Space*)h)->cg(prec, rtol, atol, maxit, stop, b, x, iters, converged, err, hist, nullptr);
+}
+int fo_errors(void* h, const double* x, int func, const double* fprm, double* h1semi, double* l2) {
+  Space* s = (Space*)h; Func f = make_func(s->m.d, func, fprm);
+  s->errors(x, f, h1semi, l2); return 0;
+}
+// element matrix of one cell (column-major nd x nd) and element vector, before Dirichlet elimination
+int fo_element(void* h, int cell, int kind, int func, const double* fprm, const double* mat, double* elmat, double* elvec) {
+  Space* s = (Space*)h; Func f = make_func(s->m.d, func, fprm);
+  std::vector<double> detj(s->fe.nq), grad(size_t(s->fe.nq) * s->fe.nnode * 3), xq(size_t(s->fe.nq) * 3);
+  s->element(cell, kind, f, mat, elmat, elvec, detj.data(), grad.data(), xq.data());
+  return 0;
+}
+int fo_ref_tables(void* h, double* qw, double* phi, double* dphi) {
+  Space* s = (Space*)h;
+  std::copy(s->fe.qw.begin(), s->fe.qw.end(), qw);
+  std::copy(s->fe.phi.begin(), s->fe.phi.end(), phi);
+  std::copy(s->fe.dphi.begin(), s->fe.dphi.end(), dphi);
+  return 0;
+}
+int fo_nq(void* h) { return ((Space*)h)->fe.nq; }
+int fo_num_threads() {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+}
