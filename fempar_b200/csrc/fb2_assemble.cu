@@ -1,0 +1,433 @@
+// Batched per-cell Galerkin integration + scatter into the device-built CSR matrix and RHS
+// (replaces the serial cell loop of the user discrete_integration_t plugins and
+//  fe_cell_iterator%assembly -> sparse_assembler -> coo append -> sort_and_compress:
+//  sbm_fe_affine_operator.i90:15-34, sbm_fe_cell_iterator.i90:1610-1637,1818-1879,
+//  base_sparse_matrix.f90:3469-3513).
+#include "fb2_internal.h"
+
+struct CellGeom {  // structured-part geometry needed to rebuild vertex coordinates of a cell
+  int N[3], ntot[3], nloc[3], L[3], first[3];
+  int n_local;
+};
+static CellGeom make_geom(const fb2_space_s* s) {
+  CellGeom g;
+  for (int k = 0; k < 3; ++k) {
+    g.N[k] = s->m.N[k]; g.ntot[k] = s->m.ntot[k]; g.nloc[k] = s->m.nloc[k]; g.L[k] = s->m.L[k]; g.first[k] = s->m.first[k];
+  }
+  g.n_local = s->m.n_local;
+  return g;
+}
+
+struct FuncPrm { int kind; double alpha, r, c[3]; };
+
+__device__ __forceinline__ double func_u(const FuncPrm& f, const double* x) {
+  if (f.kind == FB2_FUNC_LINEAR) return x[0] + x[1] + x[2];
+  if (f.kind == FB2_FUNC_SHARP_WAVE) {
+    double t = (x[0] - f.c[0]) * (x[0] - f.c[0]) + (x[1] - f.c[1]) * (x[1] - f.c[1]) + (x[2] - f.c[2]) * (x[2] - f.c[2]);
+    return atan(f.alpha * (sqrt(t) - f.r));
+  }
+  return 0.0;
+}
+__device__ __forceinline__ void func_grad(const FuncPrm& f, const double* x, double* g) {
+  g[0] = g[1] = g[2] = 0.0;
+  if (f.kind == FB2_FUNC_LINEAR) { g[0] = g[1] = g[2] = 1.0; return; }
+  if (f.kind == FB2_FUNC_SHARP_WAVE) {
+    double t1 = (x[0] - f.c[0]) * (x[0] - f.c[0]) + (x[1] - f.c[1]) * (x[1] - f.c[1]) + (x[2] - f.c[2]) * (x[2] - f.c[2]);
+    double s = sqrt(t1), t2 = s - f.r, den = s * (f.alpha * f.alpha * t2 * t2 + 1.0);
+    for (int k = 0; k < 3; ++k) g[k] = f.alpha * (x[k] - f.c[k]) / den;
+  }
+}
+__device__ __forceinline__ double func_f(const FuncPrm& f, const double* x) {
+  if (f.kind != FB2_FUNC_SHARP_WAVE) return 0.0;
+  double a = f.alpha, a2 = a * a, a3 = a2 * a, dx2[3], t1 = 0.0;
+  for (int k = 0; k < 3; ++k) { dx2[k] = (x[k] - f.c[k]) * (x[k] - f.c[k]); t1 += dx2[k]; }
+  double s = sqrt(t1), t2 = s - f.r, t22 = t2 * t2, w = a2 * t22 + 1.0;
+  double den1 = s * w, den2 = t1 * s * w, den3 = t1 * w * w, res = 0.0;
+  for (int k = 0; k < 3; ++k) res -= a / den1 - (a * dx2[k]) / den2 - (2.0 * a3 * dx2[k] * t2) / den3;
+  return res;
+}
+static FuncPrm make_func(int func, const double* prm) {
+  FuncPrm f;
+  f.kind = func; f.alpha = 200.0; f.r = 0.7; f.c[0] = f.c[1] = f.c[2] = -0.05;
+  if (prm) { f.alpha = prm[0]; f.r = prm[1]; f.c[0] = prm[2]; f.c[1] = prm[3]; f.c[2] = prm[4]; }
+  return f;
+}
+
+// vertex coordinates of the cell at total-box position ijk (unit cube; uniform_hex_mesh_generator.f90:608-635)
+__device__ __forceinline__ void cell_vertices(const CellGeom& g, const int* ijk, double X[8][3]) {
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) X[a][k] = (double)(g.first[k] + ijk[k] + ((a >> k) & 1)) / (double)g.N[k];
+}
+
+// J(q) = sum_a x_a (x) gradN_a(q), inverse, |det| (sbm_cell_map.i90:272-296, sbm_cell_integrator.i90:448-561)
+__device__ __forceinline__ void jacobian_at(const double X[8][3], const double* __restrict__ gd /*[8][3]*/, double inv[3][3],
+                                            double& det) {
+  double J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) J[i][j] += X[a][j] * gd[a * 3 + i];  // J[i][j] = d x_j / d xi_i
+  double c00 = J[1][1] * J[2][2] - J[1][2] * J[2][1], c01 = J[1][2] * J[2][0] - J[1][0] * J[2][2],
+         c02 = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+  det = J[0][0] * c00 + J[0][1] * c01 + J[0][2] * c02;
+  double id = 1.0 / det;
+  inv[0][0] = c00 * id; inv[1][0] = c01 * id; inv[2][0] = c02 * id;
+  inv[0][1] = (J[0][2] * J[2][1] - J[0][1] * J[2][2]) * id;
+  inv[1][1] = (J[0][0] * J[2][2] - J[0][2] * J[2][0]) * id;
+  inv[2][1] = (J[0][1] * J[2][0] - J[0][0] * J[2][1]) * id;
+  inv[0][2] = (J[0][1] * J[1][2] - J[0][2] * J[1][1]) * id;
+  inv[1][2] = (J[0][2] * J[1][0] - J[0][0] * J[1][2]) * id;
+  inv[2][2] = (J[0][0] * J[1][1] - J[0][1] * J[1][0]) * id;
+  det = fabs(det);
+}
+
+struct AsmArgs {
+  CellGeom g;
+  int p, nn, ncomp, nd, nq;
+  const int* perm;       // lex -> local cell id (nullptr: identity)
+  const int* gids;
+  const double* fixed;
+  const double *qw, *phi, *dphi, *gphi, *gdphi;
+  const i64* irp;
+  const int* ja;
+  double* val;
+  double* rhs;
+  i64 n_free;
+  int kind, sym, color;  // color < 0: atomic scatter over all cells; 0..7: plain read-modify-write on one colour class
+  FuncPrm fn;
+  double lambda, mu;
+};
+
+__device__ __forceinline__ i64 find_slot(const int* __restrict__ ja, i64 lo, i64 hi, int col) {
+  while (lo < hi) {
+    i64 mid = (lo + hi) >> 1;
+    if (ja[mid] < col) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+template <bool ATOMIC>
+__device__ __forceinline__ void add_entry(const AsmArgs& A, int gi, int gj, double v, double gfix_j, double* elvec_i) {
+  if (gi <= 0 || gi > A.n_free) return;
+  if (gj < 0) { atomicAdd(elvec_i, -v * gfix_j); return; }   // strong Dirichlet column -> RHS
+  if (gj == 0 || gj > A.n_free) return;
+  if (A.sym && gi > gj) return;
+  i64 slot = find_slot(A.ja, A.irp[gi - 1], A.irp[gi], gj);
+  if (ATOMIC) atomicAdd(&A.val[slot], v); else A.val[slot] += v;
+}
+
+// Generic kernel: one warp per cell, lanes over the (i,j) node pairs; reference tables in shared memory.
+template <bool ATOMIC>
+__global__ void __launch_bounds__(128) k_assemble_generic(AsmArgs A, int cells_in_launch) {
+  extern __shared__ double sm[];
+  const int nq = A.nq, nn = A.nn, nd = A.nd;
+  double* s_dphi = sm;                      // [nq][nn][3]
+  double* s_phi = s_dphi + nq * nn * 3;     // [nq][nn]
+  double* s_qw = s_phi + nq * nn;           // [nq]
+  double* s_gphi = s_qw + nq;               // [nq][8]
+  double* s_gdphi = s_gphi + nq * 8;        // [nq][8][3]
+  double* s_warp = s_gdphi + nq * 24;
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per_warp = nq * 17 + 2 * nd + ((nd + 1) / 2);   // D[6] Jinv[9] wdet fw | gfix elvec | gid(int, nd)
+  double* w_D = s_warp + (size_t)w * per_warp;  // [nq][6]
+  double* w_Ji = w_D + nq * 6;                  // [nq][9]
+  double* w_wd = w_Ji + nq * 9;                 // [nq]
+  double* w_fw = w_wd + nq;                     // [nq]
+  double* w_gfix = w_fw + nq;                   // [nd]
+  double* w_elvec = w_gfix + nd;                // [nd]
+  int* w_gid = (int*)(w_elvec + nd);            // [nd]
+  for (int i = threadIdx.x; i < nq * nn * 3; i += blockDim.x) s_dphi[i] = A.dphi[i];
+  for (int i = threadIdx.x; i < nq * nn; i += blockDim.x) s_phi[i] = A.phi[i];
+  for (int i = threadIdx.x; i < nq; i += blockDim.x) s_qw[i] = A.qw[i];
+  for (int i = threadIdx.x; i < nq * 8; i += blockDim.x) s_gphi[i] = A.gphi[i];
+  for (int i = threadIdx.x; i < nq * 24; i += blockDim.x) s_gdphi[i] = A.gdphi[i];
+  __syncthreads();
+
+  // colour classes: cells with the same parity of (i,j,k) share no DOF
+  int cdim[3], coff[3];
+  for (int k = 0; k < 3; ++k) {
+    coff[k] = A.color < 0 ? 0 : (A.color >> k) & 1;
+    cdim[k] = A.color < 0 ? A.g.nloc[k] : (A.g.nloc[k] - coff[k] + 1) / 2;
+  }
+  for (int ci = blockIdx.x * warps + w; ci < cells_in_launch; ci += gridDim.x * warps) {
+    int ijk[3];
+    {
+      int r = ci;
+      ijk[0] = r % cdim[0]; r /= cdim[0];
+      ijk[1] = r % cdim[1]; ijk[2] = r / cdim[1];
+      for (int k = 0; k < 3; ++k) ijk[k] = (A.color < 0 ? ijk[k] : 2 * ijk[k] + coff[k]) + A.g.L[k];
+    }
+    int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
+    int c = A.perm ? A.perm[lex] : lex;
+    double X[8][3];
+    cell_vertices(A.g, ijk, X);
+    // geometry at the quadrature points (lanes over q)
+    for (int q = lane; q < nq; q += 32) {
+      double inv[3][3], det;
+      jacobian_at(X, s_gdphi + q * 24, inv, det);
+      double wd = det * s_qw[q];
+      // D = wd * Jinv Jinv^T  where grad_x = Jinv * grad_xi (Jinv[i][j] = d xi_j / d x_i)
+      double D[6];
+      D[0] = inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0];
+      D[1] = inv[0][0] * inv[0][1] + inv[1][0] * inv[1][1] + inv[2][0] * inv[2][1];
+      D[2] = inv[0][0] * inv[0][2] + inv[1][0] * inv[1][2] + inv[2][0] * inv[2][2];
+      D[3] = inv[0][1] * inv[0][1] + inv[1][1] * inv[1][1] + inv[2][1] * inv[2][1];
+      D[4] = inv[0][1] * inv[0][2] + inv[1][1] * inv[1][2] + inv[2][1] * inv[2][2];
+      D[5] = inv[0][2] * inv[0][2] + inv[1][2] * inv[1][2] + inv[2][2] * inv[2][2];
+      for (int k = 0; k < 6; ++k) w_D[q * 6 + k] = wd * D[k];
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) w_Ji[q * 9 + i * 3 + j] = inv[i][j];
+      w_wd[q] = wd;
+      double xq[3] = {0, 0, 0};
+      for (int a = 0; a < 8; ++a)
+        for (int k = 0; k < 3; ++k) xq[k] += s_gphi[q * 8 + a] * X[a][k];
+      w_fw[q] = (A.kind == FB2_KIND_POISSON) ? wd * func_f(A.fn, xq) : 0.0;
+    }
+    for (int l = lane; l < nd; l += 32) {
+      int g = A.gids[(i64)c * nd + l];
+      w_gid[l] = g;
+      w_gfix[l] = g < 0 ? A.fixed[-g - 1] : 0.0;
+      w_elvec[l] = 0.0;
+    }
+    __syncwarp();
+    // element vector: sum_q f(x_q) w detJ phi_i(q)
+    if (A.kind == FB2_KIND_POISSON)
+      for (int i = lane; i < nn; i += 32) {
+        double s = 0.0;
+        for (int q = 0; q < nq; ++q) s += w_fw[q] * s_phi[q * nn + i];
+        w_elvec[i] = s;
+      }
+    __syncwarp();
+    // element matrix entries, node pairs (ni, nj)
+    for (int e = lane; e < nn * nn; e += 32) {
+      int ni = e % nn, nj = e / nn;
+      if (A.kind != FB2_KIND_ELASTICITY) {
+        double s = 0.0;
+        for (int q = 0; q < nq; ++q) {
+          const double* gi = s_dphi + (q * nn + ni) * 3;
+          const double* gj = s_dphi + (q * nn + nj) * 3;
+          const double* D = w_D + q * 6;
+          double t0 = D[0] * gj[0] + D[1] * gj[1] + D[2] * gj[2];
+          double t1 = D[1] * gj[0] + D[3] * gj[1] + D[4] * gj[2];
+          double t2 = D[2] * gj[0] + D[4] * gj[1] + D[5] * gj[2];
+          s += gi[0] * t0 + gi[1] * t1 + gi[2] * t2;
+        }
+        for (int cc = 0; cc < A.ncomp; ++cc) {
+          int i = cc * nn + ni, j = cc * nn + nj;
+          add_entry<ATOMIC>(A, w_gid[i], w_gid[j], s, w_gfix[j], &w_elvec[i]);
+        }
+      } else {
+        double acc[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+        for (int q = 0; q < nq; ++q) {
+          const double* ri = s_dphi + (q * nn + ni) * 3;
+          const double* rj = s_dphi + (q * nn + nj) * 3;
+          const double* Ji = w_Ji + q * 9;
+          double gi[3], gj[3];
+          for (int k = 0; k < 3; ++k) {
+            gi[k] = Ji[k * 3] * ri[0] + Ji[k * 3 + 1] * ri[1] + Ji[k * 3 + 2] * ri[2];
+            gj[k] = Ji[k * 3] * rj[0] + Ji[k * 3 + 1] * rj[1] + Ji[k * 3 + 2] * rj[2];
+          }
+          double dotg = gi[0] * gj[0] + gi[1] * gj[1] + gi[2] * gj[2], wd = w_wd[q];
+          for (int ci2 = 0; ci2 < 3; ++ci2)
+            for (int cj = 0; cj < 3; ++cj)
+              acc[ci2][cj] += wd * (A.lambda * gi[ci2] * gj[cj] + A.mu * ((ci2 == cj ? dotg : 0.0) + gi[cj] * gj[ci2]));
+        }
+        for (int ci2 = 0; ci2 < 3; ++ci2)
+          for (int cj = 0; cj < 3; ++cj) {
+            int i = ci2 * nn + ni, j = cj * nn + nj;
+            add_entry<ATOMIC>(A, w_gid[i], w_gid[j], acc[ci2][cj], w_gfix[j], &w_elvec[i]);
+          }
+      }
+    }
+    __syncwarp();
+    for (int i = lane; i < nd; i += 32) {
+      int g = w_gid[i];
+      double v = w_elvec[i];
+      if (g > 0 && g <= A.n_free && v != 0.0) {
+        if (ATOMIC) atomicAdd(&A.rhs[g - 1], v); else A.rhs[g - 1] += v;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+static size_t generic_smem_bytes(const fb2_space_s* s, int warps) {
+  int nq = s->rt.nq, nn = s->rt.nnode, nd = s->rt.ndofs;
+  size_t per_warp = (size_t)nq * 17 + 2 * nd + ((nd + 1) / 2);
+  return sizeof(double) * ((size_t)nq * nn * 4 + nq + nq * 32 + per_warp * warps);
+}
+
+int fb2_assemble_q2_fast(fb2_matrix_t A, fb2_vector_t rhs, const AsmArgs& args);  // fb2_assemble_q2.cu
+
+extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind, int func, const double* func_params,
+                                      const double* mat_params, int scatter_variant) {
+  FB2_CHECK(A && rhs, "null handle");
+  fb2_space_s* s = A->s;
+  FB2_CHECK(rhs->n == A->n, "rhs size mismatch");
+  FB2_CHECK(kind == FB2_KIND_POISSON ? s->rt.ncomp == 1 : s->rt.ncomp == 3, "operator kind does not match the field type");
+  cudaStream_t st = fb2_stream();
+  // fe_affine_operator%compute starts from a zeroed matrix/array (sbm_fe_operator.i90:136-137; force_compute zeroes too)
+  AsmArgs a;
+  a.g = make_geom(s);
+  a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = s->rt.ncomp; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
+  a.perm = s->d_perm; a.gids = s->d_gids; a.fixed = s->d_fixed;
+  a.qw = s->d_qw; a.phi = s->d_phi; a.dphi = s->d_dphi; a.gphi = s->d_gphi; a.gdphi = s->d_gdphi;
+  a.irp = A->d_irp; a.ja = A->d_ja; a.val = A->d_val; a.rhs = rhs->d; a.n_free = A->n;
+  a.kind = kind; a.sym = A->sym; a.fn = make_func(func, func_params);
+  a.lambda = mat_params ? mat_params[0] : 0.0; a.mu = mat_params ? mat_params[1] : 1.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  FB2_CUDA(cudaMemsetAsync(A->d_val, 0, sizeof(double) * (size_t)A->nnz, st));
+  FB2_CUDA(cudaMemsetAsync(rhs->d, 0, sizeof(double) * (size_t)rhs->n, st));
+  const int warps = 4, threads = warps * 32;
+  size_t smem = generic_smem_bytes(s, warps);
+  FB2_CHECK(smem <= 227 * 1024, "reference tables do not fit in shared memory for this order");
+  FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int bps = (int)(227 * 1024 / smem); if (bps < 1) bps = 1; if (bps > 8) bps = 8;
+  if (scatter_variant == FB2_SCATTER_ATOMIC) {
+    a.color = -1;
+    int ncell = s->m.n_local;
+    int blocks = fb2_num_sms() * bps;
+    if ((i64)blocks * warps > ncell) blocks = (ncell + warps - 1) / warps;
+    k_assemble_generic<true><<<blocks, threads, smem, st>>>(a, ncell);
+  } else {
+    for (int color = 0; color < 8; ++color) {
+      a.color = color;
+      int ncell = 1;
+      for (int k = 0; k < 3; ++k) ncell *= (s->m.nloc[k] - ((color >> k) & 1) + 1) / 2;
+      if (ncell == 0) continue;
+      int blocks = fb2_num_sms() * bps;
+      if ((i64)blocks * warps > ncell) blocks = (ncell + warps - 1) / warps;
+      k_assemble_generic<false><<<blocks, threads, smem, st>>>(a, ncell);
+    }
+  }
+  FB2_CUDA(cudaGetLastError());
+  cudaEventRecord(e1, st);
+  FB2_CUDA(cudaStreamSynchronize(st));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  fb2_record_phase("integrate", ms);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  // par: assemble the RHS across parts (par_sparse_assembler.f90:171-176)
+  if (s->imp && fb2_comm_active()) FB2_TRY(fb2_import_exchange(s->imp, rhs->d));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// strong Dirichlet values by nodal interpolation (sbm_serial_fe_space.i90:997-1176)
+// ------------------------------------------------------------------------------------------
+__global__ void k_interp_dirichlet(CellGeom g, int p, int nn, int nd, int n_cells, const int* __restrict__ lex_of,
+                                   const int* __restrict__ gids, FuncPrm fn, double* fixed) {
+  i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (i64)n_cells * nd) return;
+  int c = (int)(tid / nd), l = (int)(tid % nd);
+  int gid = gids[tid];
+  if (gid >= 0) return;
+  int lex = lex_of ? lex_of[c] : c;
+  int ijk[3] = {lex % g.ntot[0], (lex / g.ntot[0]) % g.ntot[1], lex / (g.ntot[0] * g.ntot[1])};
+  int node = l % nn, n1 = p + 1;
+  int in[3] = {node % n1, (node / n1) % n1, node / (n1 * n1)};
+  double x[3];
+  for (int k = 0; k < 3; ++k) {
+    double x0 = (double)(g.first[k] + ijk[k]) / (double)g.N[k], x1 = (double)(g.first[k] + ijk[k] + 1) / (double)g.N[k];
+    double sfrac = (double)in[k] / (double)p;
+    x[k] = (1.0 - sfrac) * x0 + sfrac * x1;
+  }
+  fixed[-gid - 1] = func_u(fn, x);
+}
+
+extern "C" int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const double* func_params) {
+  if (s->n_dirichlet == 0) return 0;
+  i64 total = (i64)s->m.n_cells * s->rt.ndofs;
+  k_interp_dirichlet<<<(unsigned)((total + 255) / 256), 256, 0, fb2_stream()>>>(
+      make_geom(s), s->rt.p, s->rt.nnode, s->rt.ndofs, s->m.n_cells, s->d_lex_of, s->d_gids, make_func(func, func_params),
+      s->d_fixed);
+  FB2_CUDA(cudaGetLastError());
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// error norms (tutorial_01_..._modules.f90:611-661; ErrorNorms/): warp per cell, lanes over q
+// ------------------------------------------------------------------------------------------
+__global__ void k_error_norms(AsmArgs A, const double* __restrict__ x, int ncells, double* out /*[2]*/) {
+  extern __shared__ double sm[];
+  const int nq = A.nq, nn = A.nn;
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double* w_u = sm + (size_t)w * nn;
+  double e1 = 0.0, e0 = 0.0;
+  for (int ci = blockIdx.x * warps + w; ci < ncells; ci += gridDim.x * warps) {
+    int ijk[3] = {ci % A.g.nloc[0] + A.g.L[0], (ci / A.g.nloc[0]) % A.g.nloc[1] + A.g.L[1],
+                  ci / (A.g.nloc[0] * A.g.nloc[1]) + A.g.L[2]};
+    int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
+    int c = A.perm ? A.perm[lex] : lex;
+    for (int l = lane; l < nn; l += 32) {
+      int g = A.gids[(i64)c * A.nd + l];
+      w_u[l] = g > 0 ? x[g - 1] : (g < 0 ? A.fixed[-g - 1] : 0.0);
+    }
+    __syncwarp();
+    double X[8][3];
+    cell_vertices(A.g, ijk, X);
+    for (int q = lane; q < nq; q += 32) {
+      double inv[3][3], det;
+      jacobian_at(X, A.gdphi + q * 24, inv, det);
+      double wd = det * A.qw[q], xq[3] = {0, 0, 0}, uh = 0.0, gr[3] = {0, 0, 0};
+      for (int a = 0; a < 8; ++a)
+        for (int k = 0; k < 3; ++k) xq[k] += A.gphi[q * 8 + a] * X[a][k];
+      for (int a = 0; a < nn; ++a) {
+        uh += w_u[a] * A.phi[q * nn + a];
+        for (int k = 0; k < 3; ++k) gr[k] += w_u[a] * A.dphi[(q * nn + a) * 3 + k];
+      }
+      double gu[3], d2 = 0.0;
+      func_grad(A.fn, xq, gu);
+      for (int i = 0; i < 3; ++i) {
+        double gh = inv[i][0] * gr[0] + inv[i][1] * gr[1] + inv[i][2] * gr[2];
+        d2 += (gu[i] - gh) * (gu[i] - gh);
+      }
+      e1 += wd * d2;
+      double du = func_u(A.fn, xq) - uh;
+      e0 += wd * du * du;
+    }
+    __syncwarp();
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    e1 += __shfl_down_sync(0xffffffffu, e1, o);
+    e0 += __shfl_down_sync(0xffffffffu, e0, o);
+  }
+  if (lane == 0) { atomicAdd(&out[0], e1); atomicAdd(&out[1], e0); }
+}
+
+extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double* h1_seminorm,
+                               double* l2_norm) {
+  FB2_CHECK(s->rt.ncomp == 1, "error norms are implemented for scalar fields");
+  AsmArgs a;
+  a.g = make_geom(s);
+  a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = 1; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
+  a.perm = s->d_perm; a.gids = s->d_gids; a.fixed = s->d_fixed;
+  a.qw = s->d_qw; a.phi = s->d_phi; a.dphi = s->d_dphi; a.gphi = s->d_gphi; a.gdphi = s->d_gdphi;
+  a.fn = make_func(func, func_params);
+  double* d_out = fb2_scratch_partials();
+  cudaStream_t st = fb2_stream();
+  FB2_CUDA(cudaMemsetAsync(d_out, 0, 2 * sizeof(double), st));
+  int warps = 4, blocks = fb2_num_sms() * 8;
+  k_error_norms<<<blocks, warps * 32, warps * a.nn * sizeof(double), st>>>(a, x->d, s->m.n_local, d_out);
+  FB2_CUDA(cudaGetLastError());
+  double h[2];
+  FB2_CUDA(cudaMemcpyAsync(h, d_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  FB2_CUDA(cudaStreamSynchronize(st));
+  if (fb2_comm_active()) {
+    // local cells partition the mesh: plain sum over parts
+    FB2_CUDA(cudaMemcpy(d_out, h, 2 * sizeof(double), cudaMemcpyHostToDevice));
+    FB2_TRY(fb2_allreduce_sum(d_out, 2));
+    FB2_CUDA(cudaMemcpy(h, d_out, 2 * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+  *h1_seminorm = sqrt(h[0]);
+  *l2_norm = sqrt(h[1]);
+  return 0;
+}

@@ -1,0 +1,120 @@
+// Distributed layer: execution_context_t on NCCL (mpi_context.f90:384-474,522-639) and the device
+// dof_import_t (dof_import.f90:49-213) used by par_scalar_array%comm() (par_scalar_array.f90:498-533).
+#include <nccl.h>
+#include <string.h>
+#include <algorithm>
+#include <map>
+#include "fb2_internal.h"
+
+static ncclComm_t g_comm = nullptr;
+static int g_rank = 0, g_nranks = 1;
+
+#define FB2_NCCL(call)                                                                            \
+  do {                                                                                            \
+    ncclResult_t r_ = (call);                                                                     \
+    if (r_ != ncclSuccess) {                                                                      \
+      fb2_set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, ncclGetErrorString(r_));  \
+      return 3;                                                                                   \
+    }                                                                                             \
+  } while (0)
+
+int fb2_comm_active() { return g_comm != nullptr; }
+int fb2_comm_nranks() { return g_nranks; }
+int fb2_comm_rank() { return g_rank; }
+
+extern "C" int fb2_comm_unique_id(void* id128) {
+  ncclUniqueId id;
+  FB2_NCCL(ncclGetUniqueId(&id));
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+  memcpy(id128, &id, 128);
+  return 0;
+}
+extern "C" int fb2_comm_init(int rank, int nranks, const void* id128) {
+  FB2_CHECK(fb2_stream() != nullptr, "fb2_init must be called before fb2_comm_init");
+  ncclUniqueId id;
+  memcpy(&id, id128, 128);
+  FB2_NCCL(ncclCommInitRank(&g_comm, nranks, id, rank));
+  g_rank = rank; g_nranks = nranks;
+  return 0;
+}
+extern "C" int fb2_comm_finalize(void) {
+  if (g_comm) { ncclCommDestroy(g_comm); g_comm = nullptr; }
+  g_rank = 0; g_nranks = 1;
+  return 0;
+}
+
+// environment%l1_sum_scalar_rp -> mpi_allreduce(MPI_IN_PLACE, ., mpi_sum)  (mpi_context.f90:384)
+int fb2_allreduce_sum(double* d_buf, int count) {
+  if (!g_comm) return 0;
+  FB2_NCCL(ncclAllReduce(d_buf, d_buf, count, ncclDouble, ncclSum, g_comm, fb2_stream()));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// dof_import on the device
+// ------------------------------------------------------------------------------------------
+struct fb2_import_s {
+  int num_rcv = 0, num_snd = 0;
+  std::vector<int> list_rcv, rcv_ptrs, list_snd, snd_ptrs;   // part ids 1-based, ptrs 0-based offsets
+  int *d_pack_idx = nullptr, *d_unpack_idx = nullptr;        // 0-based local dof ids
+  double *d_snd_buf = nullptr, *d_rcv_buf = nullptr;
+  double* d_weight = nullptr;
+  i64 n_pack = 0, n_unpack = 0;
+};
+const double* fb2_import_weight(fb2_import_s* imp) { return imp->d_weight; }
+void fb2_import_destroy(fb2_import_s* imp) {
+  if (!imp) return;
+  cudaFree(imp->d_pack_idx); cudaFree(imp->d_unpack_idx); cudaFree(imp->d_snd_buf); cudaFree(imp->d_rcv_buf);
+  cudaFree(imp->d_weight);
+  delete imp;
+}
+
+// pack_rp / unpack_rp of mpi_context.f90:522-639
+__global__ void k_pack(const double* __restrict__ x, const int* __restrict__ idx, int lo, int hi, double* buf) {
+  int i = lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < hi) buf[i] = x[idx[i]];
+}
+__global__ void k_unpack(double* __restrict__ x, const int* __restrict__ idx, int lo, int hi, const double* buf, int add) {
+  int i = lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < hi) { if (add) x[idx[i]] += buf[i]; else x[idx[i]] = buf[i]; }
+}
+
+// one neighbours exchange.  forward: pack_idx -> snd neighbours, unpack into unpack_idx (add or overwrite);
+// reverse: roles of the two lists swapped (stage 2 of comm()).
+static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add) {
+  cudaStream_t s = fb2_stream();
+  const std::vector<int>& sl = reverse ? imp->list_rcv : imp->list_snd;
+  const std::vector<int>& sp = reverse ? imp->rcv_ptrs : imp->snd_ptrs;
+  const std::vector<int>& rl = reverse ? imp->list_snd : imp->list_rcv;
+  const std::vector<int>& rp = reverse ? imp->snd_ptrs : imp->rcv_ptrs;
+  const int* sidx = reverse ? imp->d_unpack_idx : imp->d_pack_idx;
+  const int* ridx = reverse ? imp->d_pack_idx : imp->d_unpack_idx;
+  int ns = sp.empty() ? 0 : sp.back(), nr = rp.empty() ? 0 : rp.back();
+  if (ns > 0) k_pack<<<(ns + 255) / 256, 256, 0, s>>>(x, sidx, 0, ns, imp->d_snd_buf);
+  FB2_NCCL(ncclGroupStart());
+  for (size_t i = 0; i < rl.size(); ++i)
+    if (rp[i + 1] > rp[i]) FB2_NCCL(ncclRecv(imp->d_rcv_buf + rp[i], rp[i + 1] - rp[i], ncclDouble, rl[i] - 1, g_comm, s));
+  for (size_t i = 0; i < sl.size(); ++i)
+    if (sp[i + 1] > sp[i]) FB2_NCCL(ncclSend(imp->d_snd_buf + sp[i], sp[i + 1] - sp[i], ncclDouble, sl[i] - 1, g_comm, s));
+  FB2_NCCL(ncclGroupEnd());
+  // unpack neighbour by neighbour IN LIST ORDER so that additions happen in the reference's order
+  if (nr > 0) k_unpack<<<(nr + 255) / 256, 256, 0, s>>>(x, ridx, 0, nr, imp->d_rcv_buf, add ? 1 : 0);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// par_scalar_array_comm (par_scalar_array.f90:498-533):
+//  stage 1: non-owners send their partial sums, the owner receives and adds   (rcv side = owner)
+//  stage 2: the owner sends the total, non-owners receive and overwrite
+int fb2_import_exchange(fb2_import_s* imp, double* d_vec) {
+  if (!g_comm || !imp) return 0;
+  FB2_TRY(exchange_stage(imp, d_vec, false, true));
+  FB2_TRY(exchange_stage(imp, d_vec, true, false));
+  return 0;
+}
+
+int fb2_build_par_layer(fb2_space_s* s) {
+  (void)s;
+  fb2_set_error("par layer (dof_import) not built yet");
+  return 4;
+}

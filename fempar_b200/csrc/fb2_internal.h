@@ -1,0 +1,122 @@
+// Internal declarations of libfempar_b200 (not part of the C-ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/fempar_b200.h"
+
+typedef long long i64;
+
+void fb2_set_error(const char* fmt, ...);
+#define FB2_CUDA(call)                                                                           \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess) {                                                                     \
+      fb2_set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      return 1;                                                                                  \
+    }                                                                                            \
+  } while (0)
+#define FB2_CHECK(cond, msg)                                       \
+  do {                                                             \
+    if (!(cond)) {                                                 \
+      fb2_set_error("%s:%d: %s", __FILE__, __LINE__, msg);         \
+      return 2;                                                    \
+    }                                                              \
+  } while (0)
+#define FB2_TRY(expr)          \
+  do {                         \
+    int rc_ = (expr);          \
+    if (rc_ != 0) return rc_;  \
+  } while (0)
+
+cudaStream_t fb2_stream();
+int fb2_num_sms();
+void fb2_record_phase(const char* name, double ms);
+
+template <class T>
+int fb2_dalloc(T** p, size_t n) {
+  *p = nullptr;
+  if (n == 0) n = 1;
+  cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+  if (e != cudaSuccess) {
+    fb2_set_error("cudaMalloc of %zu bytes failed: %s", n * sizeof(T), cudaGetErrorString(e));
+    return 1;
+  }
+  return 0;
+}
+
+// --- structured local mesh of one part (uniform_hex_mesh_generator.f90:145-647) ---
+struct MeshDesc {
+  int N[3], P[3], pijk[3];
+  int nloc[3], ntot[3], L[3], R[3], first[3];
+  int n_local, n_cells, n_itfc;
+  int par;  // 1: cell permutation interior -> interface -> ghost is active
+};
+
+// --- reference-FE tables shared by host and device (filled on the host once per space) ---
+struct RefTables {
+  int p, n1, nnode, ncomp, ndofs, nq;
+  int m_face[27];          // own nodes (per component) of each n-face, hex polytope order, [26] = cell
+  int face_of_code[64];    // polytope index (0-based) from code = free<<3|anchor
+  int code_of_face[27];
+};
+
+struct fb2_space_s {
+  MeshDesc m;
+  RefTables rt;
+  uint32_t dir_mask;
+  int part_id;
+  // device arrays
+  int* d_perm = nullptr;     // lex (total box) -> local cell id; nullptr when identity
+  int* d_lex_of = nullptr;   // local cell id -> lex
+  int* d_gids = nullptr;     // lst_dofs_gids [n_cells * ndofs]
+  int* d_node_dof = nullptr; // [ncomp][lattice of the LOCAL cell box] -> gid
+  int* d_dof_node = nullptr; // [n_free] -> comp * lattice_size + lattice node
+  double* d_fixed = nullptr; // fixed_dof_values [n_dirichlet]
+  // reference tables on device
+  double* d_qw = nullptr;    // [nq]
+  double* d_phi = nullptr;   // [nq][nnode]
+  double* d_dphi = nullptr;  // [nq][nnode][3]
+  double* d_gphi = nullptr;  // geometry (Q1) basis at q-points [nq][8]
+  double* d_gdphi = nullptr; // [nq][8][3]
+  std::vector<double> h_qw, h_phi, h_dphi, h_gphi, h_gdphi;
+  i64 n_free = 0, n_dirichlet = 0, n_free_ghost = 0;
+  i64 n_interior = 0, n_interface = 0;
+  int Mlat[3];               // lattice nodes per direction of the local cell box
+  i64 lat_size = 0;
+  // par layer (dof_import_t, dof_import.f90:49-90)
+  struct fb2_import_s* imp = nullptr;
+};
+
+struct fb2_matrix_s {
+  fb2_space_s* s = nullptr;
+  int sym = 0;
+  i64 n = 0, nnz = 0;
+  i64* d_irp = nullptr;   // 0-based offsets, n+1
+  int* d_ja = nullptr;    // 1-based columns
+  double* d_val = nullptr;
+};
+
+struct fb2_vector_s {
+  i64 n = 0;
+  double* d = nullptr;
+  fb2_space_s* s = nullptr;
+};
+
+// reductions
+int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, double* d_result /*device*/);
+double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x 4
+#define FB2_MAX_PARTIALS 4096
+
+// comm layer
+struct fb2_import_s;
+int fb2_comm_active();
+int fb2_comm_nranks();
+int fb2_comm_rank();
+int fb2_allreduce_sum(double* d_buf, int count);           // in place, device buffer
+int fb2_import_exchange(fb2_import_s* imp, double* d_vec); // par_scalar_array%comm()
+const double* fb2_import_weight(fb2_import_s* imp);
+void fb2_import_destroy(fb2_import_s* imp);
+int fb2_build_par_layer(fb2_space_s* s);                   // interface detection + dof_import + I-then-G renumbering

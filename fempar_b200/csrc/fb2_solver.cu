@@ -1,0 +1,541 @@
+// CSR SpMV, BLAS-1 vector kernels, Jacobi and the preconditioned CG iteration on the device.
+// Reference semantics: csr_sparse_matrix.f90:545-672 (matvec), serial_scalar_array.f90:282-419,556-588
+// (dot/axpby/nrm2/copy/scal/entrywise_*), par_scalar_array.f90:303-350 (weighted dot + all-reduce),
+// jacobi_preconditioner.f90:356-412, cg.f90:101-238,279-407.
+#include <math.h>
+#include "fb2_internal.h"
+
+// ------------------------------------------------------------------------------------------
+// deterministic reductions: per-block partials (fixed grid), then one block sums them in order
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+// sums `v` over the block in a fixed order; result valid on thread 0
+__device__ __forceinline__ double block_sum(double v, double* s_red /*[32]*/) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) s_red[w] = v;
+  __syncthreads();
+  double r = 0.0;
+  if (threadIdx.x == 0)
+    for (int i = 0; i < nw; ++i) r += s_red[i];
+  return r;
+}
+
+// out[k] = sum_i partials[k*stride + i], i < nparts, fixed order; one block
+__global__ void k_reduce_partials(const double* __restrict__ partials, int nparts, int stride, int nvals, double* out) {
+  __shared__ double s_red[32];
+  for (int k = 0; k < nvals; ++k) {
+    double v = 0.0;
+    for (int i = threadIdx.x; i < nparts; i += blockDim.x) v += partials[k * stride + i];
+    double r = block_sum(v, s_red);
+    if (threadIdx.x == 0) out[k] = r;
+    __syncthreads();
+  }
+}
+
+__global__ void k_dot(const double* __restrict__ x, const double* __restrict__ y, const double* __restrict__ w, i64 n,
+                      double* partials) {
+  __shared__ double s_red[32];
+  double acc = 0.0;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x)
+    acc += (w ? w[i] : 1.0) * x[i] * y[i];
+  double r = block_sum(acc, s_red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = r;
+}
+
+static int reduce_grid(i64 n) {
+  i64 b = (n + 1023) / 1024;
+  i64 cap = (i64)fb2_num_sms() * 8;
+  if (cap > FB2_MAX_PARTIALS) cap = FB2_MAX_PARTIALS;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+// d_result (device) = sum w x y over the local entries; the caller all-reduces when par
+int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, double* d_result) {
+  int g = reduce_grid(n);
+  double* part = fb2_scratch_partials();
+  k_dot<<<g, 256, 0, fb2_stream()>>>(x, y, w, n, part);
+  k_reduce_partials<<<1, 256, 0, fb2_stream()>>>(part, g, 0, 1, d_result);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// SpMV: warp per row, 4 independent 32-wide passes in flight per warp, coalesced val/ja streams
+// ------------------------------------------------------------------------------------------
+struct CgState {
+  double rz, App, rr, rz_new, tol, alpha, beta, err;
+  int iter, converged, done, maxit;
+};
+
+template <bool FUSE_DOT>
+__global__ void __launch_bounds__(256) k_spmv(i64 n, const i64* __restrict__ irp, const int* __restrict__ ja,
+                                              const double* __restrict__ val, const double* __restrict__ x,
+                                              double* __restrict__ y, double* partials, const CgState* st) {
+  __shared__ double s_red[32];
+  if (st && st->done) return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  double dacc = 0.0;
+  for (i64 row = (i64)blockIdx.x * warps + w; row < n; row += (i64)gridDim.x * warps) {
+    const i64 start = irp[row], end = irp[row + 1];
+    double acc = 0.0;
+    for (i64 e = start + lane; e < end; e += 128) {
+      const i64 e1 = e + 32, e2 = e + 64, e3 = e + 96;
+      double v0 = val[e];
+      int c0 = ja[e];
+      double v1 = 0.0, v2 = 0.0, v3 = 0.0;
+      int c1 = 1, c2 = 1, c3 = 1;
+      if (e1 < end) { v1 = val[e1]; c1 = ja[e1]; }
+      if (e2 < end) { v2 = val[e2]; c2 = ja[e2]; }
+      if (e3 < end) { v3 = val[e3]; c3 = ja[e3]; }
+      acc += v0 * x[c0 - 1];
+      acc += v1 * x[c1 - 1];
+      acc += v2 * x[c2 - 1];
+      acc += v3 * x[c3 - 1];
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      y[row] = acc;
+      if (FUSE_DOT) dacc += acc * x[row];
+    }
+  }
+  if (FUSE_DOT) {
+    double r = block_sum(dacc, s_red);
+    if (threadIdx.x == 0) partials[blockIdx.x] = r;
+  }
+}
+
+// symmetric storage (upper triangle, diagonal first in each row): y = (U + U^T - D) x, csr_sparse_matrix.f90:597-623
+__global__ void k_spmv_sym(i64 n, const i64* __restrict__ irp, const int* __restrict__ ja, const double* __restrict__ val,
+                           const double* __restrict__ x, double* __restrict__ y) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  for (i64 row = (i64)blockIdx.x * warps + w; row < n; row += (i64)gridDim.x * warps) {
+    const i64 start = irp[row], end = irp[row + 1];
+    const double xr = x[row];
+    double acc = 0.0;
+    for (i64 e = start + lane; e < end; e += 32) {
+      int c = ja[e] - 1;
+      double v = val[e];
+      acc += v * x[c];
+      if (c != row) atomicAdd(&y[c], v * xr);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) atomicAdd(&y[row], acc);
+  }
+}
+
+static int spmv_grid(i64 n, int warps_per_block) {
+  i64 b = (n + warps_per_block - 1) / warps_per_block;
+  i64 cap = (i64)fb2_num_sms() * (2048 / (warps_per_block * 32));
+  if (cap > FB2_MAX_PARTIALS) cap = FB2_MAX_PARTIALS;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+// y = A x on the local rows (no halo exchange)
+static int spmv_local(fb2_matrix_t A, const double* x, double* y, bool fuse_dot, const CgState* st, int* grid_out) {
+  cudaStream_t s = fb2_stream();
+  if (A->sym) {
+    FB2_CUDA(cudaMemsetAsync(y, 0, sizeof(double) * (size_t)A->n, s));
+    k_spmv_sym<<<spmv_grid(A->n, 8), 256, 0, s>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y);
+    if (grid_out) *grid_out = 0;
+  } else {
+    int g = spmv_grid(A->n, 8);
+    if (fuse_dot) k_spmv<true><<<g, 256, 0, s>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, fb2_scratch_partials(), st);
+    else k_spmv<false><<<g, 256, 0, s>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, nullptr, st);
+    if (grid_out) *grid_out = g;
+  }
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int fb2_spmv(fb2_matrix_t A, fb2_vector_t x, fb2_vector_t y) {
+  FB2_CHECK(A && x && y && x->n == A->n && y->n == A->n, "fb2_spmv: size mismatch");
+  cudaStream_t st = fb2_stream();
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  FB2_TRY(spmv_local(A, x->d, y->d, false, nullptr, nullptr));
+  cudaEventRecord(e1, st);
+  if (A->s->imp && fb2_comm_active()) FB2_TRY(fb2_import_exchange(A->s->imp, y->d));
+  FB2_CUDA(cudaStreamSynchronize(st));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  fb2_record_phase("spmv", ms);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// vector kernels
+// ------------------------------------------------------------------------------------------
+__global__ void k_init(double* x, double a, i64 n) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) x[i] = a;
+}
+__global__ void k_scal(double* d, double a, const double* s, i64 n) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) d[i] = a * s[i];
+}
+// op1 = alpha*op2 + beta*op1 (serial_scalar_array.f90:366-402: beta==0 -> copy+scal, no read of op1)
+__global__ void k_axpby(double* op1, double a, const double* op2, double b, i64 n) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x)
+    op1[i] = (b == 0.0) ? a * op2[i] : a * op2[i] + b * op1[i];
+}
+__global__ void k_ew_product(double* z, const double* x, const double* y, i64 n) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) z[i] = x[i] * y[i];
+}
+__global__ void k_ew_invert(double* v, i64 n) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) v[i] = 1.0 / v[i];
+}
+static int vec_grid(i64 n) {
+  i64 b = (n + 255) / 256, cap = (i64)fb2_num_sms() * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+extern "C" int fb2_vec_create_n(fb2_vector_t* out, int64_t n) {
+  fb2_vector_s* v = new fb2_vector_s();
+  v->n = n;
+  FB2_TRY(fb2_dalloc(&v->d, (size_t)n));
+  FB2_CUDA(cudaMemset(v->d, 0, sizeof(double) * (size_t)(n ? n : 1)));
+  *out = v;
+  return 0;
+}
+extern "C" int fb2_vec_create(fb2_vector_t* out, fb2_space_t s) {
+  FB2_TRY(fb2_vec_create_n(out, s->n_free));
+  (*out)->s = s;
+  return 0;
+}
+extern "C" int fb2_vec_destroy(fb2_vector_t v) {
+  if (!v) return 0;
+  cudaFree(v->d);
+  delete v;
+  return 0;
+}
+extern "C" int fb2_vec_size(fb2_vector_t v, int64_t* n) { *n = v->n; return 0; }
+extern "C" void* fb2_vec_device_ptr(fb2_vector_t v) { return v->d; }
+extern "C" int fb2_vec_set(fb2_vector_t v, const double* h) {
+  FB2_CUDA(cudaMemcpyAsync(v->d, h, sizeof(double) * (size_t)v->n, cudaMemcpyHostToDevice, fb2_stream()));
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  return 0;
+}
+extern "C" int fb2_vec_get(fb2_vector_t v, double* h) {
+  FB2_CUDA(cudaMemcpyAsync(h, v->d, sizeof(double) * (size_t)v->n, cudaMemcpyDeviceToHost, fb2_stream()));
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  return 0;
+}
+extern "C" int fb2_vec_init(fb2_vector_t v, double a) {
+  k_init<<<vec_grid(v->n), 256, 0, fb2_stream()>>>(v->d, a, v->n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int fb2_vec_copy(fb2_vector_t dst, fb2_vector_t src) {
+  FB2_CHECK(dst->n == src->n, "size mismatch");
+  FB2_CUDA(cudaMemcpyAsync(dst->d, src->d, sizeof(double) * (size_t)dst->n, cudaMemcpyDeviceToDevice, fb2_stream()));
+  return 0;
+}
+extern "C" int fb2_vec_scal(fb2_vector_t dst, double a, fb2_vector_t src) {
+  FB2_CHECK(dst->n == src->n, "size mismatch");
+  k_scal<<<vec_grid(dst->n), 256, 0, fb2_stream()>>>(dst->d, a, src->d, dst->n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int fb2_vec_axpby(fb2_vector_t op1, double alpha, fb2_vector_t op2, double beta) {
+  FB2_CHECK(op1->n == op2->n, "size mismatch");
+  k_axpby<<<vec_grid(op1->n), 256, 0, fb2_stream()>>>(op1->d, alpha, op2->d, beta, op1->n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+static const double* weight_of(fb2_vector_t v) {
+  return (v->s && v->s->imp && fb2_comm_active()) ? fb2_import_weight(v->s->imp) : nullptr;
+}
+extern "C" int fb2_vec_dot(fb2_vector_t x, fb2_vector_t y, double* result) {
+  FB2_CHECK(x->n == y->n, "size mismatch");
+  double* d_res = fb2_scratch_partials() + FB2_MAX_PARTIALS * 3;
+  FB2_TRY(fb2_dot_device(x->d, y->d, weight_of(x), x->n, d_res));
+  if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(d_res, 1));
+  FB2_CUDA(cudaMemcpyAsync(result, d_res, sizeof(double), cudaMemcpyDeviceToHost, fb2_stream()));
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  return 0;
+}
+extern "C" int fb2_vec_nrm2(fb2_vector_t x, double* result) {
+  FB2_TRY(fb2_vec_dot(x, x, result));
+  *result = sqrt(*result);
+  return 0;
+}
+extern "C" int fb2_vec_entrywise_product(fb2_vector_t z, fb2_vector_t x, fb2_vector_t y) {
+  FB2_CHECK(z->n == x->n && z->n == y->n, "size mismatch");
+  k_ew_product<<<vec_grid(z->n), 256, 0, fb2_stream()>>>(z->d, x->d, y->d, z->n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int fb2_vec_entrywise_invert(fb2_vector_t v) {
+  k_ew_invert<<<vec_grid(v->n), 256, 0, fb2_stream()>>>(v->d, v->n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int fb2_vec_comm(fb2_vector_t v) {
+  if (v->s && v->s->imp && fb2_comm_active()) FB2_TRY(fb2_import_exchange(v->s->imp, v->d));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Jacobi
+// ------------------------------------------------------------------------------------------
+__global__ void k_extract_diag(i64 n, const i64* __restrict__ irp, const int* __restrict__ ja, const double* __restrict__ val,
+                               double* d) {
+  i64 r = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  i64 lo = irp[r], hi = irp[r + 1];
+  const i64 end = hi;
+  int col = (int)(r + 1);
+  while (lo < hi) {
+    i64 mid = (lo + hi) >> 1;
+    if (ja[mid] < col) lo = mid + 1; else hi = mid;
+  }
+  d[r] = (lo < end && ja[lo] == col) ? val[lo] : 0.0;
+}
+extern "C" int fb2_extract_diagonal(fb2_matrix_t A, fb2_vector_t d) {
+  FB2_CHECK(d->n == A->n, "size mismatch");
+  if (A->n) k_extract_diag<<<(unsigned)((A->n + 255) / 256), 256, 0, fb2_stream()>>>(A->n, A->d_irp, A->d_ja, A->d_val, d->d);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int fb2_jacobi_setup(fb2_matrix_t A, fb2_vector_t dinv) {
+  FB2_TRY(fb2_extract_diagonal(A, dinv));
+  if (A->s->imp && fb2_comm_active()) FB2_TRY(fb2_import_exchange(A->s->imp, dinv->d));
+  FB2_TRY(fb2_vec_entrywise_invert(dinv));
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// fused PCG kernels (scalars stay on the device; every kernel is a no-op once st->done is set,
+// so the host may enqueue iterations ahead and still report the reference's exact iteration count)
+// ------------------------------------------------------------------------------------------
+// x += alpha p ; r -= alpha Ap ; partials of <r,r>_w and <r, dinv r>_w
+__global__ void __launch_bounds__(256) k_cg_update_xr(i64 n, CgState* st, const double* __restrict__ p,
+                                                      const double* __restrict__ Ap, const double* __restrict__ dinv,
+                                                      const double* __restrict__ w, double* __restrict__ x,
+                                                      double* __restrict__ r, double* partials, int stride) {
+  __shared__ double s_red[32];
+  if (st->done) return;
+  const double App = st->App;
+  const double alpha = (App != 0.0) ? st->rz / App : 0.0;   // cg.f90:195-199
+  double a_rr = 0.0, a_rz = 0.0;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
+    x[i] += alpha * p[i];
+    double ri = r[i] - alpha * Ap[i];
+    r[i] = ri;
+    double wi = w ? w[i] : 1.0;
+    a_rr += wi * ri * ri;
+    a_rz += wi * ri * (dinv ? dinv[i] * ri : ri);
+  }
+  double s1 = block_sum(a_rr, s_red);
+  double s2 = block_sum(a_rz, s_red);
+  if (threadIdx.x == 0) { partials[blockIdx.x] = s1; partials[stride + blockIdx.x] = s2; }
+}
+// convergence bookkeeping: cg.f90:208-226 and update_convergence_data_and_evaluate_stopping_criteria :331-407
+__global__ void k_cg_scalars(CgState* st, double* hist) {
+  if (st->done) return;
+  st->iter += 1;
+  double e = sqrt(st->rr);
+  st->err = e;
+  if (hist) hist[st->iter - 1] = e;
+  bool conv = e <= st->tol;
+  st->converged = conv ? 1 : 0;
+  if (conv || st->iter >= st->maxit) { st->done = 1; return; }
+  st->beta = st->rz_new / st->rz;
+  st->rz = st->rz_new;
+}
+// p = dinv r + beta p
+__global__ void __launch_bounds__(256) k_cg_update_p(i64 n, const CgState* st, const double* __restrict__ r,
+                                                     const double* __restrict__ dinv, double* __restrict__ p) {
+  if (st->done) return;
+  const double beta = st->beta;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x)
+    p[i] = (dinv ? dinv[i] * r[i] : r[i]) + beta * p[i];
+}
+__global__ void k_cg_init_state(CgState* st, double rz, double tol, int maxit) {
+  st->rz = rz; st->App = 0; st->rr = 0; st->rz_new = 0; st->tol = tol; st->alpha = 0; st->beta = 0; st->err = 0;
+  st->iter = 0; st->converged = 0; st->done = 0; st->maxit = maxit;
+}
+
+struct CgWork {
+  i64 n = 0;
+  double *r = nullptr, *p = nullptr, *Ap = nullptr, *hist = nullptr;
+  CgState* st = nullptr;
+  int hist_cap = 0;
+};
+static CgWork g_work;
+static int cg_workspace(i64 n, int hist_len) {
+  if (g_work.n != n) {
+    cudaFree(g_work.r); cudaFree(g_work.p); cudaFree(g_work.Ap);
+    FB2_TRY(fb2_dalloc(&g_work.r, (size_t)n)); FB2_TRY(fb2_dalloc(&g_work.p, (size_t)n)); FB2_TRY(fb2_dalloc(&g_work.Ap, (size_t)n));
+    g_work.n = n;
+  }
+  if (!g_work.st) FB2_TRY(fb2_dalloc(&g_work.st, 1));
+  if (hist_len > g_work.hist_cap) {
+    cudaFree(g_work.hist);
+    FB2_TRY(fb2_dalloc(&g_work.hist, (size_t)hist_len));
+    g_work.hist_cap = hist_len;
+  }
+  return 0;
+}
+extern "C" int fb2_pcg_free_workspace(void) {
+  cudaFree(g_work.r); cudaFree(g_work.p); cudaFree(g_work.Ap); cudaFree(g_work.hist); cudaFree(g_work.st);
+  g_work = CgWork();
+  return 0;
+}
+
+// one PCG iteration enqueued on the stream
+static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double* w, double* x, bool par, double* hist,
+                                cudaEvent_t ev_spmv0, cudaEvent_t ev_spmv1) {
+  cudaStream_t s = fb2_stream();
+  CgWork& W = g_work;
+  double* part = fb2_scratch_partials();
+  const i64 n = A->n;
+  int g = 0;
+  if (ev_spmv0) cudaEventRecord(ev_spmv0, s);
+  if (!par && !A->sym) {
+    FB2_TRY(spmv_local(A, W.p, W.Ap, true, W.st, &g));                       // Ap = A p, partial <Ap,p> fused
+    if (ev_spmv1) cudaEventRecord(ev_spmv1, s);
+    k_reduce_partials<<<1, 256, 0, s>>>(part, g, 0, 1, &W.st->App);
+  } else {
+    FB2_TRY(spmv_local(A, W.p, W.Ap, false, A->sym ? nullptr : W.st, &g));
+    if (ev_spmv1) cudaEventRecord(ev_spmv1, s);
+    if (par) FB2_TRY(fb2_import_exchange(A->s->imp, W.Ap));                  // par_sparse_matrix.f90:757-758
+    FB2_TRY(fb2_dot_device(W.Ap, W.p, w, n, &W.st->App));
+    if (par) FB2_TRY(fb2_allreduce_sum(&W.st->App, 1));
+  }
+  int g2 = reduce_grid(n);
+  k_cg_update_xr<<<g2, 256, 0, s>>>(n, W.st, W.p, W.Ap, dinv, w, x, W.r, part, FB2_MAX_PARTIALS);
+  k_reduce_partials<<<1, 256, 0, s>>>(part, g2, FB2_MAX_PARTIALS, 2, &W.st->rr);   // rr, rz_new are adjacent
+  if (par) FB2_TRY(fb2_allreduce_sum(&W.st->rr, 2));
+  k_cg_scalars<<<1, 1, 0, s>>>(W.st, hist);
+  k_cg_update_p<<<vec_grid(n), 256, 0, s>>>(n, W.st, W.r, dinv, W.p);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const double* b, double* x, bool par, double rtol,
+                    double atol, int maxit, int stop) {
+  cudaStream_t s = fb2_stream();
+  CgWork& W = g_work;
+  const i64 n = A->n;
+  // x <- 0 ; r = A x ; r = b - r   (cg.f90:142,158-162)
+  k_init<<<vec_grid(n), 256, 0, s>>>(x, 0.0, n);
+  FB2_TRY(spmv_local(A, x, W.r, false, nullptr, nullptr));
+  if (par) FB2_TRY(fb2_import_exchange(A->s->imp, W.r));
+  k_axpby<<<vec_grid(n), 256, 0, s>>>(W.r, 1.0, b, -1.0, n);
+  // z = M^-1 r ; p = z ; r_z = <r,z>
+  if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, dinv, W.r, n);
+  else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 3;
+  FB2_TRY(fb2_dot_device(W.r, W.p, w, n, d_tmp));
+  FB2_TRY(fb2_dot_device(stop == FB2_STOP_RES_RHS ? b : W.r, stop == FB2_STOP_RES_RHS ? b : W.r, w, n, d_tmp + 1));
+  if (par) FB2_TRY(fb2_allreduce_sum(d_tmp, 2));
+  double h[2];
+  FB2_CUDA(cudaMemcpyAsync(h, d_tmp, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  FB2_CUDA(cudaStreamSynchronize(s));
+  double tol = rtol * sqrt(h[1]) + atol;   // init_convergence_data, cg.f90:279-321
+  k_cg_init_state<<<1, 1, 0, s>>>(W.st, h[0], tol, maxit);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, const fb2_ils_params_t* prm,
+                             int* num_iterations, int* did_converge, double* error_estimate, double* history) {
+  FB2_CHECK(A && b && x && prm, "null argument");
+  FB2_CHECK(b->n == A->n && x->n == A->n && (!dinv || dinv->n == A->n), "size mismatch");
+  FB2_CHECK(prm->stopping_criterium == FB2_STOP_RES_RES || prm->stopping_criterium == FB2_STOP_RES_RHS,
+            "stopping criterium not supported by the device CG");
+  const int maxit = prm->max_num_iterations;
+  const bool par = A->s->imp && fb2_comm_active();
+  const double* w = par ? fb2_import_weight(A->s->imp) : nullptr;
+  const bool track = history != nullptr;
+  FB2_TRY(cg_workspace(A->n, track ? maxit : 0));
+  cudaStream_t s = fb2_stream();
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, s);
+  FB2_TRY(cg_setup(A, dinv ? dinv->d : nullptr, w, b->d, x->d, par, prm->rtol, prm->atol, maxit, prm->stopping_criterium));
+  int every = prm->check_every > 0 ? prm->check_every : 8;
+  CgState h;
+  memset(&h, 0, sizeof(h));
+  int launched = 0;
+  while (launched < maxit) {
+    int chunk = every;
+    if (launched + chunk > maxit) chunk = maxit - launched;
+    for (int k = 0; k < chunk; ++k)
+      FB2_TRY(cg_enqueue_iteration(A, dinv ? dinv->d : nullptr, w, x->d, par, track ? g_work.hist : nullptr, nullptr, nullptr));
+    launched += chunk;
+    FB2_CUDA(cudaMemcpyAsync(&h, g_work.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
+    FB2_CUDA(cudaStreamSynchronize(s));
+    if (h.done) break;
+  }
+  cudaEventRecord(e1, s);
+  FB2_CUDA(cudaStreamSynchronize(s));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  fb2_record_phase("pcg", ms);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  *num_iterations = h.iter;
+  *did_converge = h.converged;
+  *error_estimate = h.err;
+  if (track && h.iter > 0) FB2_CUDA(cudaMemcpy(history, g_work.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+extern "C" int fb2_pcg_solve_host(fb2_matrix_t A, fb2_vector_t dinv, const double* b_host, double* x_host,
+                                  const fb2_ils_params_t* prm, int* num_iterations, int* did_converge, double* error_estimate,
+                                  double* history) {
+  static fb2_vector_t vb = nullptr, vx = nullptr;
+  if (!vb || vb->n != A->n) {
+    if (vb) { fb2_vec_destroy(vb); fb2_vec_destroy(vx); }
+    FB2_TRY(fb2_vec_create_n(&vb, A->n));
+    FB2_TRY(fb2_vec_create_n(&vx, A->n));
+    vb->s = A->s; vx->s = A->s;
+  }
+  FB2_TRY(fb2_vec_set(vb, b_host));
+  FB2_TRY(fb2_pcg_solve(A, dinv, vb, vx, prm, num_iterations, did_converge, error_estimate, history));
+  FB2_TRY(fb2_vec_get(vx, x_host));
+  return 0;
+}
+
+extern "C" int fb2_pcg_iterate(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, int n_iterations,
+                               double* ms_total, double* ms_spmv) {
+  FB2_CHECK(A && b && x && n_iterations > 0, "bad argument");
+  const bool par = A->s->imp && fb2_comm_active();
+  const double* w = par ? fb2_import_weight(A->s->imp) : nullptr;
+  FB2_TRY(cg_workspace(A->n, 0));
+  cudaStream_t s = fb2_stream();
+  // tolerance -1: never converges, so exactly n_iterations full iterations run
+  FB2_TRY(cg_setup(A, dinv ? dinv->d : nullptr, w, b->d, x->d, par, 0.0, -1.0, n_iterations + 1, FB2_STOP_RES_RES));
+  std::vector<cudaEvent_t> ev(2 * (size_t)n_iterations + 2);
+  for (auto& e : ev) cudaEventCreate(&e);
+  cudaEventRecord(ev[2 * n_iterations], s);
+  for (int k = 0; k < n_iterations; ++k)
+    FB2_TRY(cg_enqueue_iteration(A, dinv ? dinv->d : nullptr, w, x->d, par, nullptr, ev[2 * k], ev[2 * k + 1]));
+  cudaEventRecord(ev[2 * n_iterations + 1], s);
+  FB2_CUDA(cudaStreamSynchronize(s));
+  float ms = 0, acc = 0;
+  cudaEventElapsedTime(&ms, ev[2 * n_iterations], ev[2 * n_iterations + 1]);
+  for (int k = 0; k < n_iterations; ++k) {
+    float m1 = 0;
+    cudaEventElapsedTime(&m1, ev[2 * k], ev[2 * k + 1]);
+    acc += m1;
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  if (ms_total) *ms_total = ms;
+  if (ms_spmv) *ms_spmv = acc;
+  return 0;
+}

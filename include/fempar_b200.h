@@ -1,0 +1,148 @@
+/*
+ * fempar_b200.h -- C-ABI of libfempar_b200.so, the B200 (sm_100a) implementation of FEMPAR's
+ * data-parallel hot path: FE-space numbering, CSR graph, batched Galerkin integration + assembly,
+ * SpMV, BLAS-1 vector kernels, Jacobi and the (preconditioned) CG iteration, serial and in the
+ * par_* sub-domain layout (NCCL halo exchange + all-reduce).
+ *
+ * Every entry point is what a Fortran `bind(C)` interface (ISO_C_BINDING) of the FEMPAR type
+ * extension named beside it would bind; INTEGRATION.md shows those interfaces.  Plain pointers
+ * and sizes only; no torch / C++ types.  Reference file:line citations are relative to
+ * /root/reference/Sources/Lib.
+ *
+ * Conventions:
+ *   - all functions return int: 0 = ok, !=0 = error (text in fb2_last_error_string()); the
+ *     Fortran shim does `check(ierr==0)` like debug.i90's check macro;
+ *   - indices are Fortran 1-based where the reference's are (ja, DOF ids, part ids, irp on export);
+ *   - DOF ids are signed int32: >0 free DOF, <0 strong-Dirichlet DOF (-id indexes fixed_dof_values);
+ *   - reals are IEEE double; logicals are int;
+ *   - host arrays passed in are borrowed for the call only; handles own device memory;
+ *   - one host thread per handle; one CUDA device per process (rank).
+ *   - there is NO CPU fallback: without a CUDA device every call fails with an error.
+ */
+#ifndef FEMPAR_B200_H
+#define FEMPAR_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fb2_space_s* fb2_space_t;   /* serial_fe_space_t / par_fe_space_t on a uniform_hex_mesh_t  */
+typedef struct fb2_matrix_s* fb2_matrix_t; /* csr_sparse_matrix_t / par_sparse_matrix_t                   */
+typedef struct fb2_vector_s* fb2_vector_t; /* serial_scalar_array_t / par_scalar_array_t                  */
+
+/* operator kinds = the user discrete_integration_t plugins on this path (discrete_integration.f90:44-75) */
+enum {
+  FB2_KIND_POISSON = 0,          /* tutorial_01 ..._modules.f90:71-137, par_test_poisson_discrete_integration.f90:62-142 */
+  FB2_KIND_VECTOR_LAPLACIAN = 1, /* Tests/Serial/test_poisson/modules/vector_poisson_discrete_integration.f90:62-140     */
+  FB2_KIND_ELASTICITY = 2        /* par_test_pb_bddc_linear_elasticity/.../sbm_irreducible_discrete_integration.i90:93-125 */
+};
+/* analytic data (source term + boundary function) evaluated on the device */
+enum {
+  FB2_FUNC_ZERO = 0,
+  FB2_FUNC_LINEAR = 1,     /* u = x+y+z, f = 0: par_test_poisson_analytical_functions.f90:71-124 */
+  FB2_FUNC_SHARP_WAVE = 2  /* tutorial_01 ..._modules.f90:395-527; params = alpha, r, cx, cy, cz */
+};
+/* scatter variants of the assembly (north_star: atomic vs conflict-free, chosen by ncu) */
+enum { FB2_SCATTER_ATOMIC = 0, FB2_SCATTER_COLORED = 1 };
+/* iterative_solver_parameters.f90:76-83 stopping criteria supported by the CG path */
+enum { FB2_STOP_RES_RES = 0, FB2_STOP_RES_RHS = 1 };
+
+/* ILS_* parameter-list keys (iterative_solver_parameters.f90:167-183) */
+typedef struct {
+  double rtol;              /* ILS_RTOL, default 1e-6 */
+  double atol;              /* ILS_ATOL, default 0    */
+  int max_num_iterations;   /* ILS_MAX_NUM_ITERATIONS, default 1000 */
+  int stopping_criterium;   /* ILS_STOPPING_CRITERIUM, default RES_RES for CG */
+  int track_convergence_history; /* ILS_TRACK_CONVERGENCE_HISTORY */
+  int check_every;          /* device iterations between host polls of the convergence flag (>=1) */
+} fb2_ils_params_t;
+
+/* ---- runtime ---------------------------------------------------------------------------- */
+int fb2_init(int device);                       /* cudaSetDevice + constant tables; FEMPAR_INIT analogue (fempar.f90:126-133) */
+const char* fb2_last_error_string(void);
+int fb2_device_synchronize(void);
+int fb2_version(void);
+/* elapsed device time (ms) of the last timed region inside the named phase: "pattern", "integrate", "spmv", "pcg" */
+int fb2_last_phase_ms(const char* phase, double* ms);
+
+/* ---- distributed context: execution_context_t on NCCL (mpi_context.f90:384-474,522-639) -- */
+int fb2_comm_unique_id(void* id128);            /* fills a 128-byte ncclUniqueId on the root */
+int fb2_comm_init(int rank, int nranks, const void* id128);
+int fb2_comm_finalize(void);
+
+/* ---- FE space: uniform_hex_mesh_generator.f90:145-647 + sbm_serial_fe_space.i90:525-715,2623-2875 ---- */
+/* part_id: 0 = serial triangulation; 1..prod(num_parts) = this rank's sub-domain (par_triangulation_t).  */
+int fb2_fe_space_create(fb2_space_t* out, const int num_cells[3], const int num_parts[3], int part_id, int order,
+                        int num_components, uint32_t dirichlet_boundary_mask);
+int fb2_fe_space_destroy(fb2_space_t s);
+/* sizes[0..7] = num_cells(local+ghost), num_local_cells, dofs_per_cell, num_free_dofs, num_dirichlet_dofs,
+ *               num_free_ghost_dofs, num_interior_dofs (par, after I-then-G renumbering), num_interface_dofs */
+int fb2_fe_space_get_sizes(fb2_space_t s, int64_t sizes[8]);
+/* lst_dofs_gids (fe_space.f90:636-637): [num_cells * dofs_per_cell] signed 1-based ids, cell-major */
+int fb2_fe_space_get_lst_dofs_gids(fb2_space_t s, int32_t* host_out);
+int fb2_fe_space_get_cells_gids(fb2_space_t s, int64_t* host_out, int32_t* host_mypart_out);
+/* fixed_dof_values(1..num_dirichlet) = g(x_node): interpolate_dirichlet_values, sbm_serial_fe_space.i90:997-1176 */
+int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const double* func_params);
+int fb2_fe_space_get_fixed_values(fb2_space_t s, double* host_out);
+int fb2_fe_space_set_fixed_values(fb2_space_t s, const double* host_in);
+
+/* ---- matrix: csr_sparse_matrix.f90:44-50 ; graph = what coo sort_and_compress would produce ---------- */
+int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_storage);
+int fb2_csr_destroy(fb2_matrix_t A);
+int fb2_csr_get_sizes(fb2_matrix_t A, int64_t* num_rows, int64_t* nnz);
+/* irp is exported 1-based (irp(1)=1) as int64; ja 1-based int32, ascending per row */
+int fb2_csr_get_pattern(fb2_matrix_t A, int64_t* irp_host, int32_t* ja_host);
+int fb2_csr_get_values(fb2_matrix_t A, double* val_host);
+int fb2_csr_set_values(fb2_matrix_t A, const double* val_host);
+/* fe_affine_operator%compute: integrate + assemble matrix and RHS (sbm_fe_affine_operator.i90:15-34).
+ * func selects source term / boundary function; mat_params = {lambda, mu} for elasticity.           */
+int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind, int func, const double* func_params,
+                           const double* mat_params, int scatter_variant);
+/* y = A x : csr apply_body (csr_sparse_matrix.f90:626-672); par: + comm() (par_sparse_matrix.f90:739-762) */
+int fb2_spmv(fb2_matrix_t A, fb2_vector_t x, fb2_vector_t y);
+int fb2_extract_diagonal(fb2_matrix_t A, fb2_vector_t d);   /* csr_sparse_matrix.f90:4231-4256 */
+
+/* ---- vectors: vector_t TBPs (vector.f90:36-52) on serial_scalar_array.f90:213-419,556-588 ---- */
+int fb2_vec_create(fb2_vector_t* out, fb2_space_t s);     /* length = num_free_dofs of the space */
+int fb2_vec_create_n(fb2_vector_t* out, int64_t n);
+int fb2_vec_destroy(fb2_vector_t v);
+int fb2_vec_size(fb2_vector_t v, int64_t* n);
+int fb2_vec_set(fb2_vector_t v, const double* host_in);    /* insert_subvector / H2D */
+int fb2_vec_get(fb2_vector_t v, double* host_out);         /* extract_subvector / D2H */
+void* fb2_vec_device_ptr(fb2_vector_t v);
+int fb2_vec_init(fb2_vector_t v, double alpha);
+int fb2_vec_copy(fb2_vector_t dst, fb2_vector_t src);
+int fb2_vec_scal(fb2_vector_t dst, double alpha, fb2_vector_t src);      /* dst = alpha*src */
+int fb2_vec_axpby(fb2_vector_t op1, double alpha, fb2_vector_t op2, double beta); /* op1 = alpha*op2 + beta*op1 */
+int fb2_vec_dot(fb2_vector_t x, fb2_vector_t y, double* result);        /* par: weighted + all-reduce */
+int fb2_vec_nrm2(fb2_vector_t x, double* result);
+int fb2_vec_entrywise_product(fb2_vector_t z, fb2_vector_t x, fb2_vector_t y); /* z = x .* y */
+int fb2_vec_entrywise_invert(fb2_vector_t v);
+int fb2_vec_comm(fb2_vector_t v);                          /* par_scalar_array%comm, par_scalar_array.f90:498-533 */
+
+/* ---- Jacobi (jacobi_preconditioner.f90:356-412) and CG (cg.f90:101-238) ---------------------- */
+/* dinv = 1 ./ comm(diag(A)) */
+int fb2_jacobi_setup(fb2_matrix_t A, fb2_vector_t dinv);
+/* Solve A x = b with x0 = 0.  dinv == NULL -> identity preconditioner.  history may be NULL; else
+ * must hold max_num_iterations doubles.  num_iterations counts loop SpMVs exactly like cg.f90.      */
+int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, const fb2_ils_params_t* params,
+                  int* num_iterations, int* did_converge, double* error_estimate, double* history);
+/* the same through HOST buffers (what iterative_linear_solver%apply sees from Fortran arrays):
+ * H2D of b, solve, D2H of x inside the call. */
+int fb2_pcg_solve_host(fb2_matrix_t A, fb2_vector_t dinv, const double* b_host, double* x_host,
+                       const fb2_ils_params_t* params, int* num_iterations, int* did_converge,
+                       double* error_estimate, double* history);
+/* fixed-iteration variant used by benchmarks: runs exactly n PCG iterations (no convergence exit) and
+ * reports device time per phase */
+int fb2_pcg_iterate(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, int n_iterations,
+                    double* ms_total, double* ms_spmv);
+
+/* ---- error norms: sqrt(sum_K int |grad(u-u_h)|^2), sqrt(int (u-u_h)^2) ----- */
+int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double* h1_seminorm,
+                    double* l2_norm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

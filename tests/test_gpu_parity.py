@@ -1,0 +1,222 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the CPU oracle on identical meshes.
+
+Bars (BASELINE.json north_star): DOF numbering, irp, ja bit-exact; matrix entries and RHS within
+1e-12 relative; CG iteration count within +-1 and same convergence flag.
+"""
+import numpy as np
+import pytest
+
+from oracle.oracle import (OracleSpace, KIND_POISSON, KIND_VECTOR_LAPLACIAN, KIND_ELASTICITY, FUNC_LINEAR,
+                           FUNC_SHARP_WAVE)
+
+pytestmark = pytest.mark.gpu
+
+WAVE = [200.0, 0.7, -0.05, -0.05, -0.05]
+VAL_RTOL = 1e-12
+
+
+def _close(a, b, rtol=VAL_RTOL):
+    scale = max(np.max(np.abs(b)), 1e-300) if b.size else 1.0
+    return np.max(np.abs(a - b)) <= rtol * scale if b.size else True
+
+
+CASES = [((4, 4, 4), 1, 1), ((10, 10, 10), 1, 1), ((5, 4, 3), 2, 1), ((6, 6, 6), 2, 1), ((3, 4, 2), 3, 1),
+         ((1, 1, 1), 2, 1), ((2, 1, 3), 1, 1), ((4, 3, 3), 2, 3), ((3, 3, 3), 1, 3), ((2, 2, 2), 4, 1)]
+
+
+@pytest.mark.parametrize("N,p,ncomp", CASES)
+def test_dof_numbering_bit_exact(fb2, N, p, ncomp):
+    s = fb2.FeSpace(N, order=p, num_components=ncomp)
+    o = OracleSpace(N, order=p, ncomp=ncomp)
+    assert s.num_free_dofs == o.num_free
+    assert s.num_dirichlet_dofs == o.num_dirichlet
+    assert np.array_equal(s.get_lst_dofs_gids(), o.lst_dofs_gids())
+
+
+@pytest.mark.parametrize("N,p,ncomp", CASES)
+@pytest.mark.parametrize("sym", [False, True])
+def test_csr_graph_bit_exact(fb2, N, p, ncomp, sym):
+    s = fb2.FeSpace(N, order=p, num_components=ncomp)
+    A = fb2.SparseMatrix(s, symmetric_storage=sym)
+    o = OracleSpace(N, order=p, ncomp=ncomp)
+    o.build_pattern(sym=sym)
+    irp, ja = A.get_pattern()
+    assert A.nnz == o.nnz
+    assert np.array_equal(irp - 1, o.irp())
+    assert np.array_equal(ja, o.ja())
+
+
+def test_csr_graph_matches_reference_faithful_coo_route(fb2):
+    """route 0 of the oracle = COO append -> stable sort -> compress, as the reference does it."""
+    N, p = (5, 5, 5), 2
+    s = fb2.FeSpace(N, order=p)
+    o = OracleSpace(N, order=p)
+    for sym in (False, True):
+        A = fb2.SparseMatrix(s, symmetric_storage=sym)
+        o.assemble(KIND_POISSON, FUNC_LINEAR, sym=sym, route=0)
+        irp, ja = A.get_pattern()
+        assert np.array_equal(irp - 1, o.irp()) and np.array_equal(ja, o.ja())
+
+
+def _assemble(fb2, N, p, ncomp, kind, func, prm, mat, scatter, sym=False):
+    s = fb2.FeSpace(N, order=p, num_components=ncomp)
+    op = fb2.FeAffineOperator()
+    op.create(fb2.csr_format, [sym], [True], [1], s, fb2.DiscreteIntegration(kind, func, prm, mat, scatter))
+    op.compute()
+    return s, op
+
+
+@pytest.mark.parametrize("N,p", [((4, 4, 4), 1), ((10, 10, 10), 1), ((5, 4, 3), 2), ((6, 6, 6), 2), ((3, 3, 2), 3)])
+@pytest.mark.parametrize("func,prm", [(FUNC_LINEAR, None), (FUNC_SHARP_WAVE, WAVE)])
+@pytest.mark.parametrize("scatter", [0, 1])
+def test_poisson_assembly_matches_oracle(fb2, N, p, func, prm, scatter):
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, func, prm, None, scatter)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, func, prm, route=1)
+    assert _close(s.get_fixed_dof_values(), o.fixed())
+    assert _close(op.get_matrix().get_values(), o.val())
+    assert _close(op.get_translation().get_entries(), o.rhs())
+
+
+def test_poisson_assembly_symmetric_storage(fb2):
+    N, p = (5, 5, 5), 2
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0, sym=True)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, sym=True, route=0)
+    assert _close(op.get_matrix().get_values(), o.val())
+    assert _close(op.get_translation().get_entries(), o.rhs())
+    # symmetric-storage SpMV (csr_sparse_matrix.f90:597-623)
+    x = np.random.default_rng(0).standard_normal(s.num_free_dofs)
+    vx, vy = s.create_dof_values(), s.create_dof_values()
+    vx.set_entries(x)
+    op.get_matrix().apply(vx, vy)
+    assert _close(vy.get_entries(), o.spmv(x), 1e-12)
+
+
+@pytest.mark.parametrize("kind,okind,mat", [(1, KIND_VECTOR_LAPLACIAN, None), (2, KIND_ELASTICITY, [5.0 / 18.0, 5.0 / 12.0])])
+def test_vector_assembly_matches_oracle(fb2, kind, okind, mat):
+    N, p = (4, 3, 3), 2
+    s, op = _assemble(fb2, N, p, 3, kind, FUNC_LINEAR, None, mat, 0)
+    o = OracleSpace(N, order=p, ncomp=3)
+    o.assemble(okind, FUNC_LINEAR, mat=mat, route=1)
+    assert _close(op.get_matrix().get_values(), o.val())
+    assert _close(op.get_translation().get_entries(), o.rhs())
+
+
+@pytest.mark.parametrize("N,p", [((10, 10, 10), 1), ((6, 6, 6), 2), ((3, 3, 3), 3)])
+def test_spmv_and_blas1_match_oracle(fb2, N, p):
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    n = s.num_free_dofs
+    rng = np.random.default_rng(0)
+    x, y = rng.standard_normal(n), rng.standard_normal(n)
+    vx, vy, vz = s.create_dof_values(), s.create_dof_values(), s.create_dof_values()
+    vx.set_entries(x)
+    op.get_matrix().apply(vx, vz)
+    ref = o.spmv(x)
+    assert np.max(np.abs(vz.get_entries() - ref)) <= 1e-13 * np.max(np.abs(ref))
+    vy.set_entries(y)
+    assert abs(vx.dot(vy) - float(x @ y)) <= 1e-12 * np.sqrt(float(x @ x) * float(y @ y))
+    assert abs(vx.nrm2() - np.linalg.norm(x)) <= 1e-13 * np.linalg.norm(x)
+    vy.axpby(2.5, vx, -0.5)
+    assert np.allclose(vy.get_entries(), 2.5 * x - 0.5 * y, rtol=1e-15, atol=1e-15)
+    vy.axpby(3.0, vx, 0.0)
+    assert np.array_equal(vy.get_entries(), 3.0 * x)
+    vz.entrywise_product(vx, vy)
+    assert np.array_equal(vz.get_entries(), x * (3.0 * x))
+    vz.scal(-2.0, vx)
+    assert np.array_equal(vz.get_entries(), -2.0 * x)
+    vz.copy(vx)
+    vz.entrywise_invert()
+    assert np.array_equal(vz.get_entries(), 1.0 / x)
+    vz.init(7.0)
+    assert np.all(vz.get_entries() == 7.0)
+    d = s.create_dof_values()
+    op.get_matrix().extract_diagonal(d)
+    dinv = o.jacobi_setup()
+    assert np.allclose(1.0 / d.get_entries(), dinv, rtol=1e-12)
+
+
+@pytest.mark.parametrize("N,p,func,prm,prec", [((10, 10, 10), 1, FUNC_SHARP_WAVE, WAVE, "jacobi"),
+                                                ((10, 10, 10), 1, FUNC_LINEAR, None, "identity"),
+                                                ((8, 8, 8), 2, FUNC_LINEAR, None, "jacobi"),
+                                                ((6, 6, 6), 2, FUNC_SHARP_WAVE, WAVE, "jacobi"),
+                                                ((4, 4, 4), 3, FUNC_LINEAR, None, "jacobi")])
+@pytest.mark.parametrize("rtol", [1e-6, 1e-12])
+def test_pcg_matches_oracle(fb2, N, p, func, prm, prec, rtol):
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, func, prm, None, 0)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, func, prm, route=1)
+    M = None
+    if prec == "jacobi":
+        M = fb2.JacobiPreconditioner(); M.create(op); M.symbolic_setup(); M.numerical_setup()
+        o.jacobi_setup()
+    ils = fb2.IterativeLinearSolver()
+    ils.set_type_from_string("CG")
+    ils.set_parameters_from_pl({fb2.ILS_RTOL: rtol, fb2.ILS_MAX_NUM_ITERATIONS: 5000, fb2.ILS_TRACK_CONVERGENCE_HISTORY: True})
+    ils.set_operators(op.get_tangent(), M)
+    x = s.create_dof_values()
+    ils.apply(op.get_translation(), x)
+    r = o.cg(prec=1 if M else 0, rtol=rtol, maxit=5000, history=True)
+    assert ils.converged() == r["converged"]
+    assert abs(ils.get_num_iterations() - r["iters"]) <= 1
+    k = min(ils.get_num_iterations(), r["iters"]) // 2
+    assert np.allclose(ils.history[:k], r["history"][:k], rtol=1e-6)
+    xs = x.get_entries()
+    assert np.max(np.abs(xs - r["x"])) <= 100 * rtol * max(1.0, np.max(np.abs(r["x"])))
+    # the reference's own acceptance criterion (par_test_poisson_driver.f90:576-586): error norms < 1e-4 for u = x+y+z
+    if func == FUNC_LINEAR and rtol == 1e-12:
+        h1, l2 = s.error_norms(x, func, prm)
+        assert h1 < 1e-4 and l2 < 1e-4
+        oh1, ol2 = o.errors(r["x"], func, prm)
+        assert oh1 < 1e-4 and ol2 < 1e-4
+
+
+def test_pcg_host_buffers_and_max_iterations(fb2):
+    N, p = (6, 6, 6), 2
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    o.jacobi_setup()
+    M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    ils = fb2.IterativeLinearSolver()
+    ils.set_parameters_from_pl({fb2.ILS_TYPE: "CG", fb2.ILS_RTOL: 1e-10, fb2.ILS_MAX_NUM_ITERATIONS: 2000})
+    ils.set_operators(op.get_tangent(), M)
+    b = op.get_translation().get_entries()
+    x = np.zeros_like(b)
+    ils.apply(b, x)                         # host buffers through fb2_pcg_solve_host
+    r = o.cg(prec=1, rtol=1e-10, maxit=2000)
+    assert ils.converged() and abs(ils.get_num_iterations() - r["iters"]) <= 1
+    assert np.max(np.abs(x - r["x"])) < 1e-8
+    # max-iteration exit leaves did_converge = .false. (cg.f90:214)
+    ils.set_parameters_from_pl({fb2.ILS_MAX_NUM_ITERATIONS: 5})
+    ils.apply(b, x)
+    assert not ils.converged() and ils.get_num_iterations() == 5
+    r5 = o.cg(prec=1, rtol=1e-10, maxit=5)
+    assert np.allclose(x, r5["x"], rtol=1e-9, atol=1e-12)
+    # RES_RHS criterium
+    ils.set_parameters_from_pl({fb2.ILS_MAX_NUM_ITERATIONS: 2000, fb2.ILS_STOPPING_CRITERIUM: fb2.res_rhs})
+    ils.apply(b, x)
+    r2 = o.cg(prec=1, rtol=1e-10, maxit=2000, stop=1)
+    assert abs(ils.get_num_iterations() - r2["iters"]) <= 1
+
+
+def test_tutorial_01_config1_end_to_end(fb2):
+    """config 1: tutorial_01 3-D Q1 10^3 with the sharp-wave data; energy error equals the oracle's."""
+    N, p = (10, 10, 10), 1
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0)
+    assert s.num_free_dofs == 729 and op.get_matrix().nnz == 15625
+    M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    ils = fb2.IterativeLinearSolver()
+    ils.set_parameters_from_pl({fb2.ILS_TYPE: "CG", fb2.ILS_RTOL: 1e-13, fb2.ILS_MAX_NUM_ITERATIONS: 5000})
+    ils.set_operators(op.get_tangent(), M)
+    x = s.create_dof_values()
+    ils.apply(op.get_translation(), x)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=0)
+    o.jacobi_setup()
+    r = o.cg(prec=1, rtol=1e-13, maxit=5000)
+    h1, l2 = s.error_norms(x, FUNC_SHARP_WAVE, WAVE)
+    oh1, ol2 = o.errors(r["x"], FUNC_SHARP_WAVE, WAVE)
+    assert abs(h1 - oh1) <= 1e-9 * oh1 and abs(l2 - ol2) <= 1e-9 * ol2
