@@ -28,6 +28,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <thread>
 #include <vector>
 #ifdef _OPENMP
 #include <omp.h>
@@ -36,6 +37,18 @@
 namespace fo {
 
 typedef long long i64;
+
+// static row/cell range split over std::threads (no OpenMP runtime in this image)
+template <class F>
+static void parallel_for(int n, int nt, F f) {
+  if (nt <= 1 || n < 4096) { f(0, n); return; }
+  std::vector<std::thread> th;
+  for (int t = 0; t < nt; ++t) {
+    int lo = int((long long)n * t / nt), hi = int((long long)n * (t + 1) / nt);
+    th.emplace_back([=]() { f(lo, hi); });
+  }
+  for (auto& t : th) t.join();
+}
 
 // ---------------------------------------------------------------------------
 // polytope_t (hypercube only): n-faces sorted by (dimension, bit code)
@@ -436,6 +449,8 @@ struct Space {
   // par data (filled by par layer)
   std::vector<double> weight;
   double t_integrate = 0, t_pattern = 0;
+  int pattern_built = -1;   // -1 none, 0 full, 1 symmetric storage
+  int nthreads = 1;
 
   bool vef_dirichlet(int v) const {
     int b = m.vef_bid[v];
@@ -697,8 +712,9 @@ struct Space {
         ja.push_back(lc); val.push_back(cv[k]); irp[lr]++;
       }
       for (int i = 0; i < n; ++i) irp[i + 1] += irp[i];
+      pattern_built = -1;
     } else {
-      build_pattern(sym);
+      if (pattern_built != int(sym)) build_pattern(sym);
       std::fill(val.begin(), val.end(), 0.0);
       for (int c = 0; c < m.n_local; ++c) {
         element(c, kind, fn, mat, elmat.data(), elvec.data(), detj.data(), grad.data(), xq.data());
@@ -720,7 +736,7 @@ struct Space {
   }
 
   void build_pattern(bool sym) {
-    sym_storage = sym;
+    sym_storage = sym; pattern_built = int(sym);
     const int nd = fe.ndofs, n = n_free;
     // dof -> cells adjacency
     std::vector<i64> dptr(n + 1, 0);
@@ -752,12 +768,13 @@ struct Space {
   void spmv(const double* x, double* y) const {
     const int n = n_free;
     if (!sym_storage) {
-#pragma omp parallel for schedule(static)
-      for (int i = 0; i < n; ++i) {
-        double s = 0.0;
-        for (i64 k = irp[i]; k < irp[i + 1]; ++k) s += val[k] * x[ja[k] - 1];
-        y[i] = s;
-      }
+      parallel_for(n, nthreads, [&](int lo, int hi) {
+        for (int i = lo; i < hi; ++i) {
+          double s = 0.0;
+          for (i64 k = irp[i]; k < irp[i + 1]; ++k) s += val[k] * x[ja[k] - 1];
+          y[i] = s;
+        }
+      });
     } else {
       std::fill(y, y + n, 0.0);
       for (int i = 0; i < n; ++i) {
@@ -923,11 +940,7 @@ int fo_ref_tables(void* h, double* qw, double* phi, double* dphi) {
   return 0;
 }
 int fo_nq(void* h) { return ((Space*)h)->fe.nq; }
-int fo_num_threads() {
-#ifdef _OPENMP
-  return omp_get_max_threads();
-#else
-  return 1;
-#endif
-}
+int fo_hw_threads() { int n = int(std::thread::hardware_concurrency()); return n > 0 ? n : 1; }
+int fo_set_threads(void* h, int nt) { ((Space*)h)->nthreads = nt > 0 ? nt : 1; return 0; }
+int fo_num_threads(void* h) { return ((Space*)h)->nthreads; }
 }

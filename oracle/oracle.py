@@ -65,6 +65,13 @@ class OracleSpace:
                                              C.c_uint(dir_mask)))
         self.order, self.ncomp = order, ncomp
 
+    def set_threads(self, nt=0):
+        """threads used by the oracle's SpMV (0 = all hardware threads)."""
+        if nt <= 0:
+            nt = self.L.fo_hw_threads()
+        self.L.fo_set_threads(self.h, int(nt))
+        return int(nt)
+
     def close(self):
         if self.h:
             self.L.fo_destroy(self.h)
