@@ -37,6 +37,7 @@ def parse():
     ap.add_argument("--scatter", type=int, default=0)
     ap.add_argument("--cpu-cells", type=int, default=48, help="cells per direction of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--spmv-variant", type=int, default=0, help="0 TMA-streamed tiles, 1 warp-per-row")
     return ap.parse_args()
 
 
@@ -153,6 +154,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     fb.init(local)
+    fb._lib.check(fb._lib.lib().fb2_set_spmv_variant(a.spmv_variant))
     parts = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))

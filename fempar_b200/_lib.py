@@ -47,6 +47,7 @@ _SIGS = {
     "fb2_integrate_assemble": [_VP, _VP, C.c_int, C.c_int, _VP, _VP, C.c_int],
     "fb2_spmv": [_VP, _VP, _VP],
     "fb2_extract_diagonal": [_VP, _VP],
+    "fb2_set_spmv_variant": [C.c_int],
     "fb2_vec_create": [C.POINTER(_VP), _VP],
     "fb2_vec_create_n": [C.POINTER(_VP), C.c_int64],
     "fb2_vec_destroy": [_VP],

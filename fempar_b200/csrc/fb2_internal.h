@@ -97,6 +97,10 @@ struct fb2_matrix_s {
   i64* d_irp = nullptr;   // 0-based offsets, n+1
   int* d_ja = nullptr;    // 1-based columns
   double* d_val = nullptr;
+  // SpMV tile geometry (fb2_spmv.cu)
+  int spmv_R = 0, spmv_cap = 0, spmv_grid = 0;
+  i64 spmv_ntiles = 0;
+  size_t spmv_smem = 0;
 };
 
 struct fb2_vector_s {
@@ -109,6 +113,8 @@ struct fb2_vector_s {
 int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, double* d_result /*device*/);
 double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x 4
 #define FB2_MAX_PARTIALS 4096
+
+int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 
 // comm layer
 struct fb2_import_s;

@@ -131,6 +131,9 @@ __global__ void k_spmv_sym(i64 n, const i64* __restrict__ irp, const int* __rest
   }
 }
 
+static int g_spmv_variant = 0;   // 0: TMA-streamed tiles (fb2_spmv.cu), 1: warp-per-row
+extern "C" int fb2_set_spmv_variant(int v) { g_spmv_variant = v; return 0; }
+
 static int spmv_grid(i64 n, int warps_per_block) {
   i64 b = (n + warps_per_block - 1) / warps_per_block;
   i64 cap = (i64)fb2_num_sms() * (2048 / (warps_per_block * 32));
@@ -148,6 +151,12 @@ static int spmv_local(fb2_matrix_t A, const double* x, double* y, bool fuse_dot,
     k_spmv_sym<<<spmv_grid(A->n, 8), 256, 0, s>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y);
     if (grid_out) *grid_out = 0;
   } else {
+    if (g_spmv_variant == 0) {
+      int g = 0;
+      FB2_TRY(fb2_spmv_stream(A, x, y, fuse_dot, st ? &st->done : nullptr, &g));
+      if (grid_out) *grid_out = g;
+      return 0;
+    }
     int g = spmv_grid(A->n, 8);
     if (fuse_dot) k_spmv<true><<<g, 256, 0, s>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, fb2_scratch_partials(), st);
     else k_spmv<false><<<g, 256, 0, s>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, nullptr, st);

@@ -625,9 +625,10 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
   FB2_TRY(exclusive_scan(cnt, A->d_irp, n + 1));
   FB2_CUDA(cudaMemcpy(&A->nnz, A->d_irp + n, sizeof(i64), cudaMemcpyDeviceToHost));
   cudaFree(cnt);
-  FB2_TRY(fb2_dalloc(&A->d_ja, (size_t)A->nnz));
-  FB2_TRY(fb2_dalloc(&A->d_val, (size_t)A->nnz));
-  FB2_CUDA(cudaMemsetAsync(A->d_val, 0, sizeof(double) * (size_t)A->nnz, st));
+  FB2_TRY(fb2_dalloc(&A->d_ja, (size_t)A->nnz + 16));    // +16: TMA bulk copies read whole 16-byte groups
+  FB2_TRY(fb2_dalloc(&A->d_val, (size_t)A->nnz + 16));
+  FB2_CUDA(cudaMemsetAsync(A->d_ja + A->nnz, 0, 16 * sizeof(int), st));
+  FB2_CUDA(cudaMemsetAsync(A->d_val, 0, sizeof(double) * ((size_t)A->nnz + 16), st));
   int maxrow = (2 * p + 1) * (2 * p + 1) * (2 * p + 1) * ncomp;
   int blocks = fb2_num_sms() * 8, threads = 128;
   if (n > 0) {

@@ -101,6 +101,8 @@ int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind, int func,
                            const double* mat_params, int scatter_variant);
 /* y = A x : csr apply_body (csr_sparse_matrix.f90:626-672); par: + comm() (par_sparse_matrix.f90:739-762) */
 int fb2_spmv(fb2_matrix_t A, fb2_vector_t x, fb2_vector_t y);
+/* SpMV kernel variant: 0 = TMA-streamed row tiles (default), 1 = warp-per-row (kept for ncu comparison) */
+int fb2_set_spmv_variant(int variant);
 int fb2_extract_diagonal(fb2_matrix_t A, fb2_vector_t d);   /* csr_sparse_matrix.f90:4231-4256 */
 
 /* ---- vectors: vector_t TBPs (vector.f90:36-52) on serial_scalar_array.f90:213-419,556-588 ---- */
