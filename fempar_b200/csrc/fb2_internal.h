@@ -98,7 +98,7 @@ struct fb2_matrix_s {
   int* d_ja = nullptr;    // 1-based columns
   double* d_val = nullptr;
   // SpMV tile geometry (fb2_spmv.cu)
-  int spmv_R = 0, spmv_cap = 0, spmv_grid = 0;
+  int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0;
   i64 spmv_ntiles = 0;
   size_t spmv_smem = 0;
 };
