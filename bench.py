@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--cpu-cells", type=int, default=48, help="cells per direction of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--spmv-variant", type=int, default=0, help="0 TMA-streamed tiles, 1 warp-per-row")
+    ap.add_argument("--asm-variant", type=int, default=0, help="0 register-blocked contraction + scatter map, 1 generic kernel")
     return ap.parse_args()
 
 
@@ -155,6 +156,7 @@ def main():
     torch.cuda.set_device(local)
     fb.init(local)
     fb._lib.check(fb._lib.lib().fb2_set_spmv_variant(a.spmv_variant))
+    fb._lib.check(fb._lib.lib().fb2_set_assembly_variant(a.asm_variant))
     parts = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -190,6 +192,10 @@ def main():
     for _ in range(a.warmup):
         step()
     sync_all()
+    try:
+        t_map_ms = op.last_phase_ms("scatter_map")
+    except Exception:
+        t_map_ms = None
     asm_ms, cg_ms, spmv_ms = [], [], []
     with ClockSampler(local) as clk:
         t0 = time.perf_counter()
@@ -250,12 +256,12 @@ def main():
                                    % (a.order, cells, n_free_global, int(nnz_glob), a.cg_iters),
                        "parts": list(parts), "l2": "inputs larger than L2 (no flush needed)", "scatter": a.scatter},
             "assembly_mdof_per_s": asm_mdofs, "assembly_ms": asm_t, "pcg_ms_per_iteration": cg_t / a.cg_iters,
-            "spmv_ms": spmv_t, "setup_ms": {"fe_space": t_space * 1e3, "csr_pattern": t_pattern_ms},
+            "spmv_ms": spmv_t, "setup_ms": {"fe_space": t_space * 1e3, "csr_pattern": t_pattern_ms, "scatter_map": t_map_ms},
             "wall_ms_per_step": wall_t,
-            "roofline": {"bound": "hbm", "kernel": "k_spmv<true> (CSR warp-per-row SpMV + fused <Ap,p>)", "achieved": achieved,
+            "roofline": {"bound": "hbm", "kernel": "k_spmv_stream<true> (TMA-streamed CSR row tiles + fused <Ap,p>)" if a.spmv_variant == 0 else "k_spmv<true> (warp-per-row)", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650"},
-            "roofline_assembly": {"bound": "hbm", "kernel": "k_assemble_generic", "achieved": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9,
+            "roofline_assembly": {"bound": "hbm", "kernel": "k_assemble_fast<2,1,atomic>" if (a.asm_variant == 0 and a.order <= 2) else "k_assemble_generic", "achieved": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9,
                                   "peak": peak, "unit": "GB/s", "frac": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9 / peak},
             "clocks": clk.summary(), "e2e": e2e,
             "gpu_launches": a.steps * (3 + 2 + 9 + 6 * a.cg_iters)}

@@ -1,0 +1,372 @@
+// Fast assembly path for the Laplacian-type operators (Poisson, vector Laplacian) on sm_100a.
+//
+// (1) Scatter map ("cell-local -> CSR-slot map", north_star): slot(c,i,j) = irp[gid(c,i)] + tab[cell_tab[c]][i][j].
+//     An explicit map would cost nd^2 * 4 B per cell (49 GB at Q2 256^3); on a structured part the relative
+//     slots repeat for every cell with the same position class (distance to the ends of the local cell box,
+//     clipped at 2, per direction), so the map is stored as <= 729 class tables of nd^2 uint16 plus explicit
+//     tables for the cells whose class table does not verify (e.g. next to a sub-domain interface after the
+//     interior-then-interface renumbering).  Every cell is verified on the device against ja.
+// (2) Integration: one warp per cell, lane j owns column j of the element matrix,
+//     E[i][j] = sum_q grad_i(q) . (w detJ J^-1 J^-T)(q) grad_j(q): the 3-vector t = D(q) grad_j(q) is formed per lane and
+//     the nn accumulators are updated with the reference gradients of row i read as CONSTANT-BANK operands of
+//     DFMA (no shared-memory traffic in the inner loop); replaces the triple loop of the user plugin
+//     (tutorial_01_..._modules.f90:114-128, par_test_poisson_discrete_integration.f90:117-131).
+// (3) Scatter: RED.ADD.F64 (atomic variant) or plain read-modify-write on one colour class (colored variant)
+//     into val[slot]; strong Dirichlet columns go to the RHS (sbm_fe_cell_iterator.i90:1610-1637).
+#include "fb2_assemble.cuh"
+
+// ------------------------------------------------------------------------------------------
+// scatter map
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int cell_class_key(const CellGeom& g, const int* cl /*local-box coordinates*/) {
+  int key = 0, mul = 1;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    int lo = min(cl[k], 2), hi = min(g.nloc[k] - 1 - cl[k], 2);
+    key += mul * (lo * 3 + hi);
+    mul *= 9;
+  }
+  return key;
+}
+
+__global__ void k_map_keys(CellGeom g, const int* __restrict__ perm, int n_local, int* cell_tab, int* rep /*[729]*/) {
+  int ci = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ci >= n_local) return;
+  int cl[3] = {ci % g.nloc[0], (ci / g.nloc[0]) % g.nloc[1], ci / (g.nloc[0] * g.nloc[1])};
+  int lex = (cl[0] + g.L[0]) + g.ntot[0] * ((cl[1] + g.L[1]) + g.ntot[1] * (cl[2] + g.L[2]));
+  int c = perm ? perm[lex] : lex;
+  int key = cell_class_key(g, cl);
+  cell_tab[c] = key;
+  atomicMin(&rep[key], c);
+}
+__global__ void k_map_remap(int n_local, const int* __restrict__ class_of_key, int* cell_tab) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < n_local) cell_tab[c] = class_of_key[cell_tab[c]];
+}
+
+// one block per table: relative slot of every (i,j) pair of the listed cell
+__global__ void k_map_build(const int* __restrict__ cells, int nd, const int* __restrict__ gids, const i64* __restrict__ irp,
+                            const int* __restrict__ ja, i64 n_free, int sym, unsigned short* tabs /*first table of the list*/) {
+  const int c = cells[blockIdx.x];
+  const int* g = gids + (i64)c * nd;
+  unsigned short* tab = tabs + (size_t)blockIdx.x * nd * nd;
+  for (int e = threadIdx.x; e < nd * nd; e += blockDim.x) {
+    int i = e / nd, j = e - i * nd;
+    int gi = g[i], gj = g[j];
+    unsigned short rel = 0xFFFF;
+    if (gi > 0 && gi <= n_free && gj > 0 && gj <= n_free && !(sym && gi > gj)) {
+      i64 b = irp[gi - 1], end = irp[gi];
+      i64 s = find_slot(ja, b, end, gj);
+      if (s < end && ja[s] == gj && s - b < 0xFFFF) rel = (unsigned short)(s - b);
+    }
+    tab[e] = rel;
+  }
+}
+
+// warp per cell: does the table assigned to the cell reproduce the slots of this cell?
+__global__ void k_map_verify(int n_local, int nd, const int* __restrict__ gids, const i64* __restrict__ irp,
+                             const int* __restrict__ ja, i64 n_free, int sym, const int* __restrict__ cell_tab,
+                             const unsigned short* __restrict__ tabs, int* bad_list, int* n_bad) {
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int c = blockIdx.x * warps + w; c < n_local; c += gridDim.x * warps) {
+    const int* g = gids + (i64)c * nd;
+    const unsigned short* tab = tabs + (size_t)cell_tab[c] * nd * nd;
+    bool bad = false;
+    for (int e = lane; e < nd * nd; e += 32) {
+      int i = e / nd, j = e - i * nd;
+      int gi = g[i], gj = g[j];
+      bool valid = gi > 0 && gi <= n_free && gj > 0 && gj <= n_free && !(sym && gi > gj);
+      unsigned short rel = tab[e];
+      if (valid) {
+        i64 s = irp[gi - 1] + rel;
+        bad |= (rel == 0xFFFF) || s >= irp[gi] || ja[s] != gj;
+      } else bad |= (rel != 0xFFFF);
+    }
+    bad = __any_sync(0xffffffffu, bad);
+    if (bad && lane == 0) bad_list[atomicAdd(n_bad, 1)] = c;
+    __syncwarp();
+  }
+}
+__global__ void k_map_assign(const int* __restrict__ bad_list, int n_bad, int first_tab, int* cell_tab) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n_bad) cell_tab[bad_list[k]] = first_tab + k;
+}
+
+int fb2_build_scatter_map(fb2_matrix_s* A) {
+  if (A->map_state != 0) return 0;
+  fb2_space_s* s = A->s;
+  const int nd = s->rt.ndofs, n_local = s->m.n_local;
+  cudaStream_t st = fb2_stream();
+  if (n_local == 0 || A->n == 0) { A->map_state = -1; return 0; }
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  CellGeom g = make_geom(s);
+  int *d_rep, *d_class_of_key, *d_bad, *d_nbad, *d_reps;
+  FB2_TRY(fb2_dalloc(&A->d_cell_tab, (size_t)n_local));
+  FB2_TRY(fb2_dalloc(&d_rep, 729)); FB2_TRY(fb2_dalloc(&d_class_of_key, 729)); FB2_TRY(fb2_dalloc(&d_reps, 729));
+  FB2_TRY(fb2_dalloc(&d_bad, (size_t)n_local)); FB2_TRY(fb2_dalloc(&d_nbad, 1));
+  FB2_CUDA(cudaMemsetAsync(d_rep, 0x7f, 729 * sizeof(int), st));
+  FB2_CUDA(cudaMemsetAsync(d_nbad, 0, sizeof(int), st));
+  k_map_keys<<<(n_local + 255) / 256, 256, 0, st>>>(g, s->d_perm, n_local, A->d_cell_tab, d_rep);
+  int h_rep[729], h_class[729], h_reps[729], ncls = 0;
+  FB2_CUDA(cudaMemcpyAsync(h_rep, d_rep, sizeof(h_rep), cudaMemcpyDeviceToHost, st));
+  FB2_CUDA(cudaStreamSynchronize(st));
+  for (int k = 0; k < 729; ++k) {
+    h_class[k] = -1;
+    if (h_rep[k] < n_local) { h_class[k] = ncls; h_reps[ncls++] = h_rep[k]; }
+  }
+  FB2_CUDA(cudaMemcpyAsync(d_class_of_key, h_class, sizeof(h_class), cudaMemcpyHostToDevice, st));
+  FB2_CUDA(cudaMemcpyAsync(d_reps, h_reps, sizeof(int) * ncls, cudaMemcpyHostToDevice, st));
+  k_map_remap<<<(n_local + 255) / 256, 256, 0, st>>>(n_local, d_class_of_key, A->d_cell_tab);
+  unsigned short* d_ctabs;
+  const size_t tab_elems = (size_t)nd * nd;
+  FB2_TRY(fb2_dalloc(&d_ctabs, tab_elems * ncls));
+  k_map_build<<<ncls, 256, 0, st>>>(d_reps, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym, d_ctabs);
+  k_map_verify<<<fb2_num_sms() * 8, 256, 0, st>>>(n_local, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym, A->d_cell_tab,
+                                                   d_ctabs, d_bad, d_nbad);
+  int nbad = 0;
+  FB2_CUDA(cudaMemcpyAsync(&nbad, d_nbad, sizeof(int), cudaMemcpyDeviceToHost, st));
+  FB2_CUDA(cudaStreamSynchronize(st));
+  FB2_CUDA(cudaGetLastError());
+  int rc = 0;
+  if ((size_t)nbad * tab_elems * 2 > ((size_t)4 << 30)) {
+    // too irregular for a compressed map: the assembly falls back to searching ja (generic kernel)
+    cudaFree(d_ctabs); cudaFree(A->d_cell_tab); A->d_cell_tab = nullptr;
+    A->map_state = -1;
+  } else {
+    A->n_class_tabs = ncls; A->n_tabs = ncls + nbad;
+    if (nbad == 0) A->d_tabs = d_ctabs;
+    else {
+      rc = fb2_dalloc(&A->d_tabs, tab_elems * A->n_tabs);
+      if (rc == 0) {
+        cudaMemcpyAsync(A->d_tabs, d_ctabs, tab_elems * ncls * 2, cudaMemcpyDeviceToDevice, st);
+        k_map_build<<<nbad, 256, 0, st>>>(d_bad, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym, A->d_tabs + tab_elems * ncls);
+        k_map_assign<<<(nbad + 255) / 256, 256, 0, st>>>(d_bad, nbad, ncls, A->d_cell_tab);
+        cudaStreamSynchronize(st);
+      }
+      cudaFree(d_ctabs);
+    }
+    A->map_state = 1;
+  }
+  cudaEventRecord(e1, st);
+  cudaStreamSynchronize(st);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  fb2_record_phase("scatter_map", ms);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(d_rep); cudaFree(d_class_of_key); cudaFree(d_bad); cudaFree(d_nbad); cudaFree(d_reps);
+  FB2_CUDA(cudaGetLastError());
+  return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// integration + scatter
+// ------------------------------------------------------------------------------------------
+__constant__ double c_G1[8 * 8 * 3];      // reference gradients [q][i][3], Q1
+__constant__ double c_G2[27 * 27 * 3];    // Q2
+template <int P> struct GTab;
+template <> struct GTab<1> { static __device__ __forceinline__ double g(int q, int i, int d) { return c_G1[(q * 8 + i) * 3 + d]; } };
+template <> struct GTab<2> { static __device__ __forceinline__ double g(int q, int i, int d) { return c_G2[(q * 27 + i) * 3 + d]; } };
+
+struct FastArgs {
+  AsmArgs a;
+  const int* cell_tab;
+  const unsigned short* tabs;
+};
+
+template <int P, int NCOMP, bool ATOMIC>
+__global__ void __launch_bounds__(128, 3) k_assemble_fast(FastArgs F, int cells_in_launch) {
+  constexpr int NN = (P + 1) * (P + 1) * (P + 1), NQ = NN, ND = NN * NCOMP;
+  constexpr int CPW = NN <= 16 ? 32 / NN : 1;        // cells per warp
+  constexpr int WARPS = 4;
+  const AsmArgs& A = F.a;
+  constexpr int GROW = (3 * NN + 1) / 2 * 2;          // doubles per q row of s_G, even so that every row is 16-byte aligned
+  __shared__ __align__(16) double s_G[NQ * GROW];    // [q][i][3]: warp-uniform rows, read as LDS.128 broadcasts
+  __shared__ double s_phi[NQ * NN];                  // [q][j]
+  __shared__ double s_D[WARPS * CPW][NQ][6];
+  __shared__ double s_fw[WARPS * CPW][NQ];
+  __shared__ double s_gfix[WARPS * CPW][ND];
+  __shared__ i64 s_base[WARPS * CPW][ND];
+  __shared__ int s_gid[WARPS * CPW][ND];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int sub = lane / NN, j = lane - sub * NN;
+  const bool lane_on = lane < CPW * NN;
+  const int slot = w * CPW + (lane_on ? sub : 0);
+  for (int e = threadIdx.x; e < NQ * NN * 3; e += blockDim.x) {
+    int q = e / (NN * 3), r = e - q * NN * 3, i = r / 3, d = r - i * 3;
+    s_G[q * GROW + i * 3 + d] = A.dphi[e];
+  }
+  for (int e = threadIdx.x; e < NQ * NN; e += blockDim.x) s_phi[e] = A.phi[e];
+  __syncthreads();
+  int cdim[3], coff[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    coff[k] = A.color < 0 ? 0 : (A.color >> k) & 1;
+    cdim[k] = A.color < 0 ? A.g.nloc[k] : (A.g.nloc[k] - coff[k] + 1) / 2;
+  }
+  const bool has_source = A.kind == FB2_KIND_POISSON && A.fn.kind == FB2_FUNC_SHARP_WAVE;
+  const int stride = gridDim.x * WARPS * CPW;
+  for (int ci0 = (blockIdx.x * WARPS + w) * CPW; ci0 < cells_in_launch; ci0 += stride) {
+    const int ci = ci0 + sub;
+    const bool on = lane_on && ci < cells_in_launch;
+    int c = 0;
+    if (on) {
+      int ijk[3], r = ci;
+      ijk[0] = r % cdim[0]; r /= cdim[0];
+      ijk[1] = r % cdim[1]; ijk[2] = r / cdim[1];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) ijk[k] = (A.color < 0 ? ijk[k] : 2 * ijk[k] + coff[k]) + A.g.L[k];
+      const int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
+      c = A.perm ? A.perm[lex] : lex;
+      // --- lane as quadrature point q = j: D(q) = w detJ J^-1 J^-T, source term ---
+      double X[8][3], inv[3][3], det;
+      cell_vertices(A.g, ijk, X);
+      jacobian_at(X, A.gdphi + j * 24, inv, det);
+      const double wd = det * A.qw[j];
+      double* D = s_D[slot][j];
+      D[0] = wd * (inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0]);
+      D[1] = wd * (inv[0][0] * inv[0][1] + inv[1][0] * inv[1][1] + inv[2][0] * inv[2][1]);
+      D[2] = wd * (inv[0][0] * inv[0][2] + inv[1][0] * inv[1][2] + inv[2][0] * inv[2][2]);
+      D[3] = wd * (inv[0][1] * inv[0][1] + inv[1][1] * inv[1][1] + inv[2][1] * inv[2][1]);
+      D[4] = wd * (inv[0][1] * inv[0][2] + inv[1][1] * inv[1][2] + inv[2][1] * inv[2][2]);
+      D[5] = wd * (inv[0][2] * inv[0][2] + inv[1][2] * inv[1][2] + inv[2][2] * inv[2][2]);
+      if (has_source) {
+        double xq[3] = {0, 0, 0};
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+#pragma unroll
+          for (int k = 0; k < 3; ++k) xq[k] += A.gphi[j * 8 + a] * X[a][k];
+        s_fw[slot][j] = wd * func_f(A.fn, xq);
+      }
+      // --- lane as DOF j of every component: ids, Dirichlet values, row starts ---
+#pragma unroll
+      for (int cc = 0; cc < NCOMP; ++cc) {
+        const int l = cc * NN + j;
+        const int g = A.gids[(i64)c * ND + l];
+        s_gid[slot][l] = g;
+        s_gfix[slot][l] = g < 0 ? A.fixed[-g - 1] : 0.0;
+        s_base[slot][l] = (g > 0 && g <= A.n_free) ? A.irp[g - 1] : -1;
+      }
+    }
+    __syncwarp();
+    if (on) {
+      // --- column j of the element matrix ---
+      double acc[NN];
+#pragma unroll
+      for (int i = 0; i < NN; ++i) acc[i] = 0.0;
+      // q is not unrolled (a fully unrolled body, ~120 KB of SASS, thrashed the instruction cache: ncu showed 37 % of the
+      // stall samples as no_instructions); the reference gradients of row i are warp-uniform LDS.128 broadcasts
+      // (constant-bank operands indexed by q compile to slow LDC loads: 3x slower, measured).
+#pragma unroll 1
+      for (int q = 0; q < NQ; ++q) {
+        const double* D = s_D[slot][q];
+        const double g0 = s_G[q * GROW + j * 3], g1 = s_G[q * GROW + j * 3 + 1], g2 = s_G[q * GROW + j * 3 + 2];
+        const double t0 = D[0] * g0 + D[1] * g1 + D[2] * g2;
+        const double t1 = D[1] * g0 + D[3] * g1 + D[4] * g2;
+        const double t2 = D[2] * g0 + D[4] * g1 + D[5] * g2;
+        const unsigned gq_addr = (unsigned)__cvta_generic_to_shared(s_G + q * GROW);
+        double gv[GROW];
+#pragma unroll
+        for (int k = 0; k < GROW / 2; ++k)
+          asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(gv[2 * k]), "=d"(gv[2 * k + 1]) : "r"(gq_addr + 16 * k));
+#pragma unroll
+        for (int i = 0; i < NN; ++i) acc[i] = fma(gv[3 * i], t0, fma(gv[3 * i + 1], t1, fma(gv[3 * i + 2], t2, acc[i])));
+      }
+      // --- element vector of row j: source term and strong Dirichlet columns (E is symmetric: E[j][i] = acc[i]) ---
+      double ev[NCOMP];
+#pragma unroll
+      for (int cc = 0; cc < NCOMP; ++cc) ev[cc] = 0.0;
+      if (has_source) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) sacc += s_fw[slot][q] * s_phi[q * NN + j];
+        ev[0] = sacc;
+      }
+      bool any_dir = false;
+#pragma unroll
+      for (int cc = 0; cc < NCOMP; ++cc) any_dir |= s_gid[slot][cc * NN + j] < 0;
+      if (__any_sync(__activemask(), any_dir)) {
+#pragma unroll
+        for (int cc = 0; cc < NCOMP; ++cc) {
+          double sacc = 0.0;
+#pragma unroll
+          for (int i = 0; i < NN; ++i) sacc += acc[i] * s_gfix[slot][cc * NN + i];
+          ev[cc] -= sacc;
+        }
+      }
+      // --- scatter ---
+      const unsigned short* tab = F.tabs + (size_t)F.cell_tab[c] * (ND * ND);
+#pragma unroll
+      for (int cc = 0; cc < NCOMP; ++cc) {
+#pragma unroll
+        for (int i = 0; i < NN; ++i) {
+          const int li = cc * NN + i;
+          const unsigned short rel = tab[li * ND + cc * NN + j];
+          if (rel != 0xFFFF) {
+            double* dst = A.val + (s_base[slot][li] + rel);
+            if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
+          }
+        }
+        const int g = s_gid[slot][cc * NN + j];
+        if (g > 0 && g <= A.n_free && ev[cc] != 0.0) {
+          if (ATOMIC) atomicAdd(&A.rhs[g - 1], ev[cc]); else A.rhs[g - 1] += ev[cc];
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+
+static int g_const_loaded[3] = {0, 0, 0};
+static int load_const_tables(const fb2_space_s* s) {
+  const int p = s->rt.p;
+  if (g_const_loaded[p]) return 0;
+  const size_t bytes = s->h_dphi.size() * sizeof(double);
+  if (p == 1) FB2_CUDA(cudaMemcpyToSymbol(c_G1, s->h_dphi.data(), bytes));
+  else FB2_CUDA(cudaMemcpyToSymbol(c_G2, s->h_dphi.data(), bytes));
+  g_const_loaded[p] = 1;
+  return 0;
+}
+
+template <int P, int NCOMP>
+static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_variant) {
+  constexpr int NN = (P + 1) * (P + 1) * (P + 1), CPW = NN <= 16 ? 32 / NN : 1, WARPS = 4;
+  FastArgs F = F0;
+  cudaStream_t st = fb2_stream();
+  int bps = 0;
+  FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_assemble_fast<P, NCOMP, true>, WARPS * 32, 0));
+  if (bps < 1) bps = 1;
+  auto grid_for = [&](int ncell) {
+    i64 need = ((i64)ncell + WARPS * CPW - 1) / (WARPS * CPW), cap = (i64)fb2_num_sms() * bps;
+    return (int)(need < cap ? need : cap);
+  };
+  if (scatter_variant == FB2_SCATTER_ATOMIC) {
+    F.a.color = -1;
+    const int ncell = s->m.n_local;
+    k_assemble_fast<P, NCOMP, true><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
+  } else {
+    for (int color = 0; color < 8; ++color) {
+      F.a.color = color;
+      int ncell = 1;
+      for (int k = 0; k < 3; ++k) ncell *= (s->m.nloc[k] - ((color >> k) & 1) + 1) / 2;
+      if (ncell == 0) continue;
+      k_assemble_fast<P, NCOMP, false><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
+    }
+  }
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// returns 0 when the fast path ran, -1 when it does not apply (the caller uses the generic kernel), >0 on error
+int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant) {
+  const fb2_space_s* s = A->s;
+  if (args.kind == FB2_KIND_ELASTICITY || s->rt.p > 2) return -1;
+  FB2_TRY(fb2_build_scatter_map(A));
+  if (A->map_state != 1) return -1;
+  FB2_TRY(load_const_tables(s));
+  FastArgs F;
+  F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs;
+  if (s->rt.p == 1) return s->rt.ncomp == 1 ? launch_fast<1, 1>(F, s, scatter_variant) : launch_fast<1, 3>(F, s, scatter_variant);
+  return s->rt.ncomp == 1 ? launch_fast<2, 1>(F, s, scatter_variant) : launch_fast<2, 3>(F, s, scatter_variant);
+}

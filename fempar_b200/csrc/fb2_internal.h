@@ -97,6 +97,10 @@ struct fb2_matrix_s {
   i64* d_irp = nullptr;   // 0-based offsets, n+1
   int* d_ja = nullptr;    // 1-based columns
   double* d_val = nullptr;
+  // cell-local -> CSR-slot scatter map (fb2_assemble_fast.cu): slot = irp[row] + tabs[cell_tab[c]][i*nd + j]
+  int* d_cell_tab = nullptr;          // [n_local] table id of each local cell
+  unsigned short* d_tabs = nullptr;   // [n_tabs][nd*nd] relative slots, 0xFFFF = entry not stored
+  int n_tabs = 0, n_class_tabs = 0, map_state = 0;   // map_state: 0 not built, 1 built, -1 unavailable (search fallback)
   // SpMV tile geometry (fb2_spmv.cu)
   int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0;
   i64 spmv_ntiles = 0;
@@ -114,6 +118,7 @@ int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, dou
 double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x 4
 #define FB2_MAX_PARTIALS 4096
 
+int fb2_build_scatter_map(fb2_matrix_s* A);
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 
 // comm layer

@@ -656,7 +656,7 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
 }
 extern "C" int fb2_csr_destroy(fb2_matrix_t A) {
   if (!A) return 0;
-  cudaFree(A->d_irp); cudaFree(A->d_ja); cudaFree(A->d_val);
+  cudaFree(A->d_irp); cudaFree(A->d_ja); cudaFree(A->d_val); cudaFree(A->d_cell_tab); cudaFree(A->d_tabs);
   delete A;
   return 0;
 }

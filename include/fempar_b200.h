@@ -63,7 +63,7 @@ int fb2_init(int device);                       /* cudaSetDevice + constant tabl
 const char* fb2_last_error_string(void);
 int fb2_device_synchronize(void);
 int fb2_version(void);
-/* elapsed device time (ms) of the last timed region inside the named phase: "pattern", "integrate", "spmv", "pcg" */
+/* elapsed device time (ms) of the last timed region inside the named phase: "pattern", "scatter_map", "integrate", "spmv", "pcg" */
 int fb2_last_phase_ms(const char* phase, double* ms);
 
 /* ---- distributed context: execution_context_t on NCCL (mpi_context.f90:384-474,522-639) -- */
@@ -99,6 +99,9 @@ int fb2_csr_set_values(fb2_matrix_t A, const double* val_host);
  * func selects source term / boundary function; mat_params = {lambda, mu} for elasticity.           */
 int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind, int func, const double* func_params,
                            const double* mat_params, int scatter_variant);
+/* assembly kernel variant: 0 = register-blocked contraction + precomputed cell-local -> CSR-slot scatter map where it
+ * applies (Poisson / vector Laplacian, Q1-Q2; default), 1 = generic warp-per-cell kernel that searches ja (all kinds/orders) */
+int fb2_set_assembly_variant(int variant);
 /* y = A x : csr apply_body (csr_sparse_matrix.f90:626-672); par: + comm() (par_sparse_matrix.f90:739-762) */
 int fb2_spmv(fb2_matrix_t A, fb2_vector_t x, fb2_vector_t y);
 /* SpMV kernel variant: 0 = TMA-streamed row tiles (default), 1 = warp-per-row (kept for ncu comparison) */

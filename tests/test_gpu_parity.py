@@ -66,10 +66,19 @@ def _assemble(fb2, N, p, ncomp, kind, func, prm, mat, scatter, sym=False):
     return s, op
 
 
-@pytest.mark.parametrize("N,p", [((4, 4, 4), 1), ((10, 10, 10), 1), ((5, 4, 3), 2), ((6, 6, 6), 2), ((3, 3, 2), 3)])
+@pytest.fixture(params=[0, 1], ids=["asm_fast", "asm_generic"])
+def asm_variant(request, fb2):
+    """0 = register-blocked contraction + scatter map (where it applies), 1 = generic kernel searching ja."""
+    fb2._lib.check(fb2._lib.lib().fb2_set_assembly_variant(request.param))
+    yield request.param
+    fb2._lib.check(fb2._lib.lib().fb2_set_assembly_variant(0))
+
+
+@pytest.mark.parametrize("N,p", [((4, 4, 4), 1), ((10, 10, 10), 1), ((1, 1, 1), 1), ((2, 1, 3), 2), ((5, 4, 3), 2), ((6, 6, 6), 2),
+                                 ((9, 8, 7), 2), ((3, 3, 2), 3)])
 @pytest.mark.parametrize("func,prm", [(FUNC_LINEAR, None), (FUNC_SHARP_WAVE, WAVE)])
 @pytest.mark.parametrize("scatter", [0, 1])
-def test_poisson_assembly_matches_oracle(fb2, N, p, func, prm, scatter):
+def test_poisson_assembly_matches_oracle(fb2, asm_variant, N, p, func, prm, scatter):
     s, op = _assemble(fb2, N, p, 1, fb2.poisson, func, prm, None, scatter)
     o = OracleSpace(N, order=p)
     o.assemble(KIND_POISSON, func, prm, route=1)
@@ -94,9 +103,10 @@ def test_poisson_assembly_symmetric_storage(fb2):
 
 
 @pytest.mark.parametrize("kind,okind,mat", [(1, KIND_VECTOR_LAPLACIAN, None), (2, KIND_ELASTICITY, [5.0 / 18.0, 5.0 / 12.0])])
-def test_vector_assembly_matches_oracle(fb2, kind, okind, mat):
+@pytest.mark.parametrize("scatter", [0, 1])
+def test_vector_assembly_matches_oracle(fb2, asm_variant, kind, okind, mat, scatter):
     N, p = (4, 3, 3), 2
-    s, op = _assemble(fb2, N, p, 3, kind, FUNC_LINEAR, None, mat, 0)
+    s, op = _assemble(fb2, N, p, 3, kind, FUNC_LINEAR, None, mat, scatter)
     o = OracleSpace(N, order=p, ncomp=3)
     o.assemble(okind, FUNC_LINEAR, mat=mat, route=1)
     assert _close(op.get_matrix().get_values(), o.val())
