@@ -7,9 +7,9 @@
 //     tables for the cells whose class table does not verify (e.g. next to a sub-domain interface after the
 //     interior-then-interface renumbering).  Every cell is verified on the device against ja.
 // (2) Integration: one warp per cell, lane j owns column j of the element matrix,
-//     E[i][j] = sum_q grad_i(q) . (w detJ J^-1 J^-T)(q) grad_j(q): the 3-vector t = D(q) grad_j(q) is formed per lane and
-//     the nn accumulators are updated with the reference gradients of row i read as CONSTANT-BANK operands of
-//     DFMA (no shared-memory traffic in the inner loop); replaces the triple loop of the user plugin
+//     E[i][j] = sum_q grad_i(q) . (w detJ J^-1 J^-T)(q) grad_j(q), evaluated by SUM FACTORISATION over the three
+//     tensor directions with the 1-D basis tables as constant-bank operands of DFMA (no table traffic in the
+//     inner loop, 2.7x fewer flops than the dense q-loop); replaces the triple loop of the user plugin
 //     (tutorial_01_..._modules.f90:114-128, par_test_poisson_discrete_integration.f90:117-131).
 // (3) Scatter: RED.ADD.F64 (atomic variant) or plain read-modify-write on one colour class (colored variant)
 //     into val[slot]; strong Dirichlet columns go to the RHS (sbm_fe_cell_iterator.i90:1610-1637).
@@ -163,11 +163,10 @@ int fb2_build_scatter_map(fb2_matrix_s* A) {
 // ------------------------------------------------------------------------------------------
 // integration + scatter
 // ------------------------------------------------------------------------------------------
-__constant__ double c_G1[8 * 8 * 3];      // reference gradients [q][i][3], Q1
-__constant__ double c_G2[27 * 27 * 3];    // Q2
-template <int P> struct GTab;
-template <> struct GTab<1> { static __device__ __forceinline__ double g(int q, int i, int d) { return c_G1[(q * 8 + i) * 3 + d]; } };
-template <> struct GTab<2> { static __device__ __forceinline__ double g(int q, int i, int d) { return c_G2[(q * 27 + i) * 3 + d]; } };
+// 1-D Lagrange values B[q][i] and derivatives C[q][i] at the 1-D Gauss points, orders 1..3.  Every index below is
+// a compile-time constant after unrolling, so these become constant-bank / uniform-register operands of DFMA.
+__constant__ double c_B1[3][16];
+__constant__ double c_C1[3][16];
 
 struct FastArgs {
   AsmArgs a;
@@ -175,29 +174,81 @@ struct FastArgs {
   const unsigned short* tabs;
 };
 
+// Column j of the element matrix by sum factorisation.  With q = (q1,q2,q3), i = (i1,i2,i3) and
+// t(q) = w detJ J^-1 J^-T(q) grad_ref phi_j(q):
+//   E[i][j] = sum_q  C[q1][i1] B[q2][i2] B[q3][i3] t0 + B[q1][i1] C[q2][i2] B[q3][i3] t1 + B[q1][i1] B[q2][i2] C[q3][i3] t2
+// contracted direction by direction: 9 (t) + 9 (x) + 9 (y) + 6 (z) FMA per quadrature point for p = 2, i.e. 891 DFMA
+// per column instead of the 2430 of the dense q-loop, and no table traffic in the inner loop.
+template <int P>
+__device__ __forceinline__ void column_sumfact(const double (*__restrict__ D)[6], const double* __restrict__ sB,
+                                               const double* __restrict__ sC, int j, double* __restrict__ acc) {
+  constexpr int N1 = P + 1, NN = N1 * N1 * N1;
+  const int j1 = j % N1, j2 = (j / N1) % N1, j3 = j / (N1 * N1);
+#pragma unroll
+  for (int i = 0; i < NN; ++i) acc[i] = 0.0;
+#pragma unroll
+  for (int q3 = 0; q3 < N1; ++q3) {
+    const double b3 = sB[q3 * N1 + j3], c3 = sC[q3 * N1 + j3];
+    double w01[N1 * N1], w2[N1 * N1];
+#pragma unroll
+    for (int k = 0; k < N1 * N1; ++k) { w01[k] = 0.0; w2[k] = 0.0; }
+#pragma unroll
+    for (int q2 = 0; q2 < N1; ++q2) {
+      const double b2 = sB[q2 * N1 + j2], c2 = sC[q2 * N1 + j2];
+      const double m0 = b2 * b3, m1 = c2 * b3, m2 = b2 * c3;   // grad_ref phi_j = (c1 m0, b1 m1, b1 m2)
+      double a0[N1], a1[N1], a2[N1];
+#pragma unroll
+      for (int k = 0; k < N1; ++k) { a0[k] = 0.0; a1[k] = 0.0; a2[k] = 0.0; }
+#pragma unroll
+      for (int q1 = 0; q1 < N1; ++q1) {
+        const int q = q1 + N1 * (q2 + N1 * q3);
+        const double b1 = sB[q1 * N1 + j1], c1 = sC[q1 * N1 + j1];
+        const double g0 = c1 * m0, g1 = b1 * m1, g2 = b1 * m2;
+        const double* Dq = D[q];
+        const double t0 = Dq[0] * g0 + Dq[1] * g1 + Dq[2] * g2;
+        const double t1 = Dq[1] * g0 + Dq[3] * g1 + Dq[4] * g2;
+        const double t2 = Dq[2] * g0 + Dq[4] * g1 + Dq[5] * g2;
+#pragma unroll
+        for (int i1 = 0; i1 < N1; ++i1) {
+          a0[i1] = fma(c_C1[P - 1][q1 * N1 + i1], t0, a0[i1]);
+          a1[i1] = fma(c_B1[P - 1][q1 * N1 + i1], t1, a1[i1]);
+          a2[i1] = fma(c_B1[P - 1][q1 * N1 + i1], t2, a2[i1]);
+        }
+      }
+#pragma unroll
+      for (int i2 = 0; i2 < N1; ++i2)
+#pragma unroll
+        for (int i1 = 0; i1 < N1; ++i1) {
+          w01[i1 + N1 * i2] = fma(c_B1[P - 1][q2 * N1 + i2], a0[i1], fma(c_C1[P - 1][q2 * N1 + i2], a1[i1], w01[i1 + N1 * i2]));
+          w2[i1 + N1 * i2] = fma(c_B1[P - 1][q2 * N1 + i2], a2[i1], w2[i1 + N1 * i2]);
+        }
+    }
+#pragma unroll
+    for (int i3 = 0; i3 < N1; ++i3)
+#pragma unroll
+      for (int k = 0; k < N1 * N1; ++k)
+        acc[k + N1 * N1 * i3] = fma(c_B1[P - 1][q3 * N1 + i3], w01[k], fma(c_C1[P - 1][q3 * N1 + i3], w2[k], acc[k + N1 * N1 * i3]));
+  }
+}
+
 template <int P, int NCOMP, bool ATOMIC>
-__global__ void __launch_bounds__(128, 3) k_assemble_fast(FastArgs F, int cells_in_launch) {
-  constexpr int NN = (P + 1) * (P + 1) * (P + 1), NQ = NN, ND = NN * NCOMP;
-  constexpr int CPW = NN <= 16 ? 32 / NN : 1;        // cells per warp
+__global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArgs F, int cells_in_launch) {
+  constexpr int N1 = P + 1, NN = N1 * N1 * N1, NQ = NN, ND = NN * NCOMP;
+  constexpr int CPW = NN <= 16 ? 32 / NN : 1;        // cells per warp (Q1: 4)
+  constexpr int CPL = (NN + 31) / 32;                // columns per lane (Q3: 2)
   constexpr int WARPS = 4;
   const AsmArgs& A = F.a;
-  constexpr int GROW = (3 * NN + 1) / 2 * 2;          // doubles per q row of s_G, even so that every row is 16-byte aligned
-  __shared__ __align__(16) double s_G[NQ * GROW];    // [q][i][3]: warp-uniform rows, read as LDS.128 broadcasts
-  __shared__ double s_phi[NQ * NN];                  // [q][j]
+  __shared__ double s_B[N1 * N1], s_C[N1 * N1];      // 1-D tables for the lane-dependent factors
   __shared__ double s_D[WARPS * CPW][NQ][6];
   __shared__ double s_fw[WARPS * CPW][NQ];
   __shared__ double s_gfix[WARPS * CPW][ND];
   __shared__ i64 s_base[WARPS * CPW][ND];
   __shared__ int s_gid[WARPS * CPW][ND];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int sub = lane / NN, j = lane - sub * NN;
-  const bool lane_on = lane < CPW * NN;
+  const int sub = CPW > 1 ? lane / NN : 0, j0 = CPW > 1 ? lane - sub * NN : lane;
+  const bool lane_on = lane < CPW * NN || CPL > 1;
   const int slot = w * CPW + (lane_on ? sub : 0);
-  for (int e = threadIdx.x; e < NQ * NN * 3; e += blockDim.x) {
-    int q = e / (NN * 3), r = e - q * NN * 3, i = r / 3, d = r - i * 3;
-    s_G[q * GROW + i * 3 + d] = A.dphi[e];
-  }
-  for (int e = threadIdx.x; e < NQ * NN; e += blockDim.x) s_phi[e] = A.phi[e];
+  if (threadIdx.x < N1 * N1) { s_B[threadIdx.x] = c_B1[P - 1][threadIdx.x]; s_C[threadIdx.x] = c_C1[P - 1][threadIdx.x]; }
   __syncthreads();
   int cdim[3], coff[3];
 #pragma unroll
@@ -211,6 +262,7 @@ __global__ void __launch_bounds__(128, 3) k_assemble_fast(FastArgs F, int cells_
     const int ci = ci0 + sub;
     const bool on = lane_on && ci < cells_in_launch;
     int c = 0;
+    bool any_dir = false;
     if (on) {
       int ijk[3], r = ci;
       ijk[0] = r % cdim[0]; r /= cdim[0];
@@ -219,98 +271,93 @@ __global__ void __launch_bounds__(128, 3) k_assemble_fast(FastArgs F, int cells_
       for (int k = 0; k < 3; ++k) ijk[k] = (A.color < 0 ? ijk[k] : 2 * ijk[k] + coff[k]) + A.g.L[k];
       const int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
       c = A.perm ? A.perm[lex] : lex;
-      // --- lane as quadrature point q = j: D(q) = w detJ J^-1 J^-T, source term ---
-      double X[8][3], inv[3][3], det;
+      double X[8][3];
       cell_vertices(A.g, ijk, X);
-      jacobian_at(X, A.gdphi + j * 24, inv, det);
-      const double wd = det * A.qw[j];
-      double* D = s_D[slot][j];
-      D[0] = wd * (inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0]);
-      D[1] = wd * (inv[0][0] * inv[0][1] + inv[1][0] * inv[1][1] + inv[2][0] * inv[2][1]);
-      D[2] = wd * (inv[0][0] * inv[0][2] + inv[1][0] * inv[1][2] + inv[2][0] * inv[2][2]);
-      D[3] = wd * (inv[0][1] * inv[0][1] + inv[1][1] * inv[1][1] + inv[2][1] * inv[2][1]);
-      D[4] = wd * (inv[0][1] * inv[0][2] + inv[1][1] * inv[1][2] + inv[2][1] * inv[2][2]);
-      D[5] = wd * (inv[0][2] * inv[0][2] + inv[1][2] * inv[1][2] + inv[2][2] * inv[2][2]);
-      if (has_source) {
-        double xq[3] = {0, 0, 0};
 #pragma unroll
-        for (int a = 0; a < 8; ++a)
+      for (int jj = 0; jj < CPL; ++jj) {
+        const int q = j0 + 32 * jj;
+        if (q < NQ) {
+          // --- lane as quadrature point: D(q) = w detJ J^-1 J^-T (sbm_cell_map.i90:272-296), source term ---
+          double inv[3][3], det;
+          jacobian_at(X, A.gdphi + q * 24, inv, det);
+          const double wd = det * A.qw[q];
+          double* D = s_D[slot][q];
+          D[0] = wd * (inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0]);
+          D[1] = wd * (inv[0][0] * inv[0][1] + inv[1][0] * inv[1][1] + inv[2][0] * inv[2][1]);
+          D[2] = wd * (inv[0][0] * inv[0][2] + inv[1][0] * inv[1][2] + inv[2][0] * inv[2][2]);
+          D[3] = wd * (inv[0][1] * inv[0][1] + inv[1][1] * inv[1][1] + inv[2][1] * inv[2][1]);
+          D[4] = wd * (inv[0][1] * inv[0][2] + inv[1][1] * inv[1][2] + inv[2][1] * inv[2][2]);
+          D[5] = wd * (inv[0][2] * inv[0][2] + inv[1][2] * inv[1][2] + inv[2][2] * inv[2][2]);
+          if (has_source) {
+            double xq[3] = {0, 0, 0};
 #pragma unroll
-          for (int k = 0; k < 3; ++k) xq[k] += A.gphi[j * 8 + a] * X[a][k];
-        s_fw[slot][j] = wd * func_f(A.fn, xq);
-      }
-      // --- lane as DOF j of every component: ids, Dirichlet values, row starts ---
+            for (int a = 0; a < 8; ++a)
 #pragma unroll
-      for (int cc = 0; cc < NCOMP; ++cc) {
-        const int l = cc * NN + j;
-        const int g = A.gids[(i64)c * ND + l];
-        s_gid[slot][l] = g;
-        s_gfix[slot][l] = g < 0 ? A.fixed[-g - 1] : 0.0;
-        s_base[slot][l] = (g > 0 && g <= A.n_free) ? A.irp[g - 1] : -1;
-      }
-    }
-    __syncwarp();
-    if (on) {
-      // --- column j of the element matrix ---
-      double acc[NN];
+              for (int k = 0; k < 3; ++k) xq[k] += A.gphi[q * 8 + a] * X[a][k];
+            s_fw[slot][q] = wd * func_f(A.fn, xq);
+          }
+          // --- lane as DOF of every component: ids, Dirichlet values, row starts ---
 #pragma unroll
-      for (int i = 0; i < NN; ++i) acc[i] = 0.0;
-      // q is not unrolled (a fully unrolled body, ~120 KB of SASS, thrashed the instruction cache: ncu showed 37 % of the
-      // stall samples as no_instructions); the reference gradients of row i are warp-uniform LDS.128 broadcasts
-      // (constant-bank operands indexed by q compile to slow LDC loads: 3x slower, measured).
-#pragma unroll 1
-      for (int q = 0; q < NQ; ++q) {
-        const double* D = s_D[slot][q];
-        const double g0 = s_G[q * GROW + j * 3], g1 = s_G[q * GROW + j * 3 + 1], g2 = s_G[q * GROW + j * 3 + 2];
-        const double t0 = D[0] * g0 + D[1] * g1 + D[2] * g2;
-        const double t1 = D[1] * g0 + D[3] * g1 + D[4] * g2;
-        const double t2 = D[2] * g0 + D[4] * g1 + D[5] * g2;
-        const unsigned gq_addr = (unsigned)__cvta_generic_to_shared(s_G + q * GROW);
-        double gv[GROW];
-#pragma unroll
-        for (int k = 0; k < GROW / 2; ++k)
-          asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(gv[2 * k]), "=d"(gv[2 * k + 1]) : "r"(gq_addr + 16 * k));
-#pragma unroll
-        for (int i = 0; i < NN; ++i) acc[i] = fma(gv[3 * i], t0, fma(gv[3 * i + 1], t1, fma(gv[3 * i + 2], t2, acc[i])));
-      }
-      // --- element vector of row j: source term and strong Dirichlet columns (E is symmetric: E[j][i] = acc[i]) ---
-      double ev[NCOMP];
-#pragma unroll
-      for (int cc = 0; cc < NCOMP; ++cc) ev[cc] = 0.0;
-      if (has_source) {
-        double sacc = 0.0;
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) sacc += s_fw[slot][q] * s_phi[q * NN + j];
-        ev[0] = sacc;
-      }
-      bool any_dir = false;
-#pragma unroll
-      for (int cc = 0; cc < NCOMP; ++cc) any_dir |= s_gid[slot][cc * NN + j] < 0;
-      if (__any_sync(__activemask(), any_dir)) {
-#pragma unroll
-        for (int cc = 0; cc < NCOMP; ++cc) {
-          double sacc = 0.0;
-#pragma unroll
-          for (int i = 0; i < NN; ++i) sacc += acc[i] * s_gfix[slot][cc * NN + i];
-          ev[cc] -= sacc;
-        }
-      }
-      // --- scatter ---
-      const unsigned short* tab = F.tabs + (size_t)F.cell_tab[c] * (ND * ND);
-#pragma unroll
-      for (int cc = 0; cc < NCOMP; ++cc) {
-#pragma unroll
-        for (int i = 0; i < NN; ++i) {
-          const int li = cc * NN + i;
-          const unsigned short rel = tab[li * ND + cc * NN + j];
-          if (rel != 0xFFFF) {
-            double* dst = A.val + (s_base[slot][li] + rel);
-            if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
+          for (int cc = 0; cc < NCOMP; ++cc) {
+            const int l = cc * NN + q;
+            const int g = A.gids[(i64)c * ND + l];
+            s_gid[slot][l] = g;
+            s_gfix[slot][l] = g < 0 ? A.fixed[-g - 1] : 0.0;
+            s_base[slot][l] = (g > 0 && g <= A.n_free) ? A.irp[g - 1] : -1;
+            any_dir |= g < 0;
           }
         }
-        const int g = s_gid[slot][cc * NN + j];
-        if (g > 0 && g <= A.n_free && ev[cc] != 0.0) {
-          if (ATOMIC) atomicAdd(&A.rhs[g - 1], ev[cc]); else A.rhs[g - 1] += ev[cc];
+      }
+    }
+    any_dir = __any_sync(0xffffffffu, any_dir);
+    __syncwarp();
+    if (on) {
+      const unsigned short* tab = F.tabs + (size_t)F.cell_tab[c] * (ND * ND);
+#pragma unroll 1
+      for (int jj = 0; jj < CPL; ++jj) {
+        const int j = j0 + 32 * jj;
+        if (j >= NN) break;
+        double acc[NN];
+        column_sumfact<P>(s_D[slot], s_B, s_C, j, acc);
+        // --- element vector of row j: source term and strong Dirichlet columns (E is symmetric: E[j][i] = acc[i]) ---
+        double ev[NCOMP];
+#pragma unroll
+        for (int cc = 0; cc < NCOMP; ++cc) ev[cc] = 0.0;
+        if (has_source) {
+          const int j1 = j % N1, j2 = (j / N1) % N1, j3 = j / (N1 * N1);
+          double sacc = 0.0;
+#pragma unroll 1
+          for (int q = 0; q < NQ; ++q) {
+            const int q1 = q % N1, q2 = (q / N1) % N1, q3 = q / (N1 * N1);
+            sacc += s_fw[slot][q] * (s_B[q1 * N1 + j1] * s_B[q2 * N1 + j2] * s_B[q3 * N1 + j3]);
+          }
+          ev[0] = sacc;
+        }
+        if (any_dir) {
+#pragma unroll
+          for (int cc = 0; cc < NCOMP; ++cc) {
+            double sacc = 0.0;
+#pragma unroll
+            for (int i = 0; i < NN; ++i) sacc += acc[i] * s_gfix[slot][cc * NN + i];
+            ev[cc] -= sacc;
+          }
+        }
+        // --- scatter through the precomputed map ---
+#pragma unroll
+        for (int cc = 0; cc < NCOMP; ++cc) {
+#pragma unroll
+          for (int i = 0; i < NN; ++i) {
+            const int li = cc * NN + i;
+            const unsigned short rel = tab[li * ND + cc * NN + j];
+            if (rel != 0xFFFF) {
+              double* dst = A.val + (s_base[slot][li] + rel);
+              if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
+            }
+          }
+          const int g = s_gid[slot][cc * NN + j];
+          if (g > 0 && g <= A.n_free && ev[cc] != 0.0) {
+            if (ATOMIC) atomicAdd(&A.rhs[g - 1], ev[cc]); else A.rhs[g - 1] += ev[cc];
+          }
         }
       }
     }
@@ -318,13 +365,14 @@ __global__ void __launch_bounds__(128, 3) k_assemble_fast(FastArgs F, int cells_
   }
 }
 
-static int g_const_loaded[3] = {0, 0, 0};
+static int g_const_loaded[4] = {0, 0, 0, 0};
 static int load_const_tables(const fb2_space_s* s) {
   const int p = s->rt.p;
   if (g_const_loaded[p]) return 0;
-  const size_t bytes = s->h_dphi.size() * sizeof(double);
-  if (p == 1) FB2_CUDA(cudaMemcpyToSymbol(c_G1, s->h_dphi.data(), bytes));
-  else FB2_CUDA(cudaMemcpyToSymbol(c_G2, s->h_dphi.data(), bytes));
+  double b[16] = {0}, c[16] = {0};
+  for (size_t k = 0; k < s->h_b1d.size(); ++k) { b[k] = s->h_b1d[k]; c[k] = s->h_c1d[k]; }
+  FB2_CUDA(cudaMemcpyToSymbol(c_B1, b, sizeof(b), sizeof(b) * (p - 1)));
+  FB2_CUDA(cudaMemcpyToSymbol(c_C1, c, sizeof(c), sizeof(c) * (p - 1)));
   g_const_loaded[p] = 1;
   return 0;
 }
@@ -361,12 +409,13 @@ static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_var
 // returns 0 when the fast path ran, -1 when it does not apply (the caller uses the generic kernel), >0 on error
 int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant) {
   const fb2_space_s* s = A->s;
-  if (args.kind == FB2_KIND_ELASTICITY || s->rt.p > 2) return -1;
+  if (args.kind == FB2_KIND_ELASTICITY || s->rt.p > 3) return -1;
   FB2_TRY(fb2_build_scatter_map(A));
   if (A->map_state != 1) return -1;
   FB2_TRY(load_const_tables(s));
   FastArgs F;
   F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs;
   if (s->rt.p == 1) return s->rt.ncomp == 1 ? launch_fast<1, 1>(F, s, scatter_variant) : launch_fast<1, 3>(F, s, scatter_variant);
-  return s->rt.ncomp == 1 ? launch_fast<2, 1>(F, s, scatter_variant) : launch_fast<2, 3>(F, s, scatter_variant);
+  if (s->rt.p == 2) return s->rt.ncomp == 1 ? launch_fast<2, 1>(F, s, scatter_variant) : launch_fast<2, 3>(F, s, scatter_variant);
+  return s->rt.ncomp == 1 ? launch_fast<3, 1>(F, s, scatter_variant) : launch_fast<3, 3>(F, s, scatter_variant);
 }

@@ -82,6 +82,7 @@ struct fb2_space_s {
   double* d_gphi = nullptr;  // geometry (Q1) basis at q-points [nq][8]
   double* d_gdphi = nullptr; // [nq][8][3]
   std::vector<double> h_qw, h_phi, h_dphi, h_gphi, h_gdphi;
+  std::vector<double> h_b1d, h_c1d;   // 1-D Lagrange values / derivatives at the 1-D Gauss points [q][i]
   i64 n_free = 0, n_dirichlet = 0, n_free_ghost = 0;
   i64 n_interior = 0, n_interface = 0;
   int Mlat[3];               // lattice nodes per direction of the local cell box

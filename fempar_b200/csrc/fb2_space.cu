@@ -168,6 +168,12 @@ static void make_ref_tables(fb2_space_s* s, int p, int ncomp) {
     pts[q * 3 + 0] = x1[q0]; pts[q * 3 + 1] = x1[q1]; pts[q * 3 + 2] = x1[q2];
     s->h_qw[q] = w1[q0] * w1[q1] * w1[q2];
   }
+  s->h_b1d.assign((size_t)nq1 * rt.n1, 0.0); s->h_c1d.assign((size_t)nq1 * rt.n1, 0.0);
+  for (int q = 0; q < nq1; ++q) {
+    double l[8], dl[8];
+    lagrange_eq(p, x1[q], l, dl);
+    for (int i = 0; i < rt.n1; ++i) { s->h_b1d[q * rt.n1 + i] = l[i]; s->h_c1d[q * rt.n1 + i] = dl[i]; }
+  }
   tabulate(p, pts, rt.nq, s->h_phi, s->h_dphi);
   tabulate(1, pts, rt.nq, s->h_gphi, s->h_gdphi);
 }
