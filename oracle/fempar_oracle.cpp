@@ -446,8 +446,12 @@ struct Space {
   std::vector<int> ja;                 // 1-based column ids like the reference
   std::vector<double> val, rhs, fixed;
   std::vector<double> dinv;            // Jacobi inverse diagonal
-  // par data (filled by par layer)
+  // par data (build_par_layer): dof_import_t (LinearAlgebra/Vector/dof_import.f90:49-90); part ids 1-based,
+  // ptrs 0-based offsets (reference ptrs = these + 1), pack/unpack_idx 1-based local dof ids like the reference
   std::vector<double> weight;
+  std::vector<int> list_rcv, rcv_ptrs, unpack_idx, list_snd, snd_ptrs, pack_idx;
+  std::vector<int> perm_old2new;       // 1-based -> 1-based, interior first then interface
+  int n_interior = 0, n_interface = 0;
   double t_integrate = 0, t_pattern = 0;
   int pattern_built = -1;   // -1 none, 0 full, 1 symmetric storage
   int nthreads = 1;
@@ -465,6 +469,8 @@ struct Space {
     gids.assign(size_t(m.n_cells) * fe.ndofs, 0);
     setup_strong_dirichlet();
     list_dofs();
+    n_interior = n_free; n_interface = 0;
+    if (m.par) build_par_layer();
   }
 
   // serial_fe_space_set_up_strong_dirichlet_bcs  Integration/FESpace/sbm_serial_fe_space.i90:525-651
@@ -545,6 +551,119 @@ struct Space {
       }
     }
     n_free_ghost = gcur - cur;
+  }
+
+
+  // par_fe_space_t: interface couplings, owner decision, dof_import and the interior-then-interface renumbering.
+  //   compute_raw_interface_data_by_continuity   Integration/FESpace/sbm_par_fe_space.i90:1877-2033
+  //   raw_interface_data_by_continuity_decide_owner                                      :2737-2851
+  //   generate_non_consecutive_dof_ggid                                                  :1103-1118
+  //   dof_import_create / fill_first_I_then_G_renumbering / renum_dofs  LinearAlgebra/Vector/dof_import.f90:102-213,365-421
+  //   renum_dofs_first_interior_then_interface                          sbm_par_fe_space.i90:449-474
+  //   cells around a vef = cells in increasing local id (sbm_base_static_triangulation.i90:697-741);
+  //   interface vef = touched by local AND ghost cells (:748-784); itfc vefs visited in increasing vef id (sbm_triangulation.i90:201-218)
+  void build_par_layer() {
+    const int nvef = m.nvef, nd = fe.ndofs;
+    const int mypart = m.part_id;
+    int nparts = 1; for (int k = 0; k < m.d; ++k) nparts *= m.P[k];
+    // cells around each vef, increasing cell id
+    std::vector<int> cptr(m.n_vefs + 1, 0);
+    for (int c = 0; c < m.n_cells; ++c) for (int f = 0; f < nvef; ++f) cptr[m.lst_vefs[size_t(c) * nvef + f] + 1]++;
+    for (int v = 0; v < m.n_vefs; ++v) cptr[v + 1] += cptr[v];
+    std::vector<int> ccell(cptr[m.n_vefs]), cface(cptr[m.n_vefs]), pos(cptr.begin(), cptr.end() - 1);
+    for (int c = 0; c < m.n_cells; ++c)
+      for (int f = 0; f < nvef; ++f) { int v = m.lst_vefs[size_t(c) * nvef + f]; ccell[pos[v]] = c; cface[pos[v]] = f; pos[v]++; }
+    struct Col { i64 part, flag, ggid; int dof, maxpart; };
+    std::vector<Col> cols;
+    std::vector<int> local_idof(n_free + 1, 0), lst;
+    std::vector<int> parts_visited;
+    for (int v = 0; v < m.n_vefs; ++v) {
+      bool has_local = false, has_ghost = false;
+      for (int k = cptr[v]; k < cptr[v + 1]; ++k) { if (ccell[k] < m.n_local) has_local = true; else has_ghost = true; }
+      if (!(has_local && has_ghost)) continue;                 // vef%is_at_interface()
+      parts_visited.clear(); lst.clear();
+      int max_part = mypart; i64 max_ggid = 0;
+      for (int k = cptr[v]; k < cptr[v + 1]; ++k) {
+        int c = ccell[k], f = cface[k];
+        int part = m.cells_part[c]; i64 ggid = m.cells_gid[c];
+        for (int l : fe.own[f]) {
+          int g = gids[size_t(c) * nd + l];
+          if (!(g > 0 && g <= n_free)) continue;                // is_free_dof
+          if (ggid >= max_ggid) {
+            max_ggid = ggid;
+            if (local_idof[g] == 0) lst.push_back(g);
+            local_idof[g] = l + 1;
+          }
+          if (part != mypart && std::find(parts_visited.begin(), parts_visited.end(), part) == parts_visited.end()) {
+            parts_visited.push_back(part);
+            max_part = std::max(max_part, part);
+          }
+        }
+      }
+      for (int g : lst)
+        for (int part : parts_visited) {
+          Col cc; cc.part = part; cc.flag = i64(parts_visited.size()) + 1; cc.dof = g; cc.maxpart = max_part;
+          cc.ggid = (max_ggid - 1) + (i64(local_idof[g] - 1) << 44);   // cell_ggid_shift = 44, field_id = 1 (fe_space_parameters.f90:137-139)
+          cols.push_back(cc);
+        }
+    }
+    // sort by (neighbour part, #parts around + 1, non-consecutive global dof id): sort_array_cols_by_row_section, Tools/sort.f90:118-141
+    std::stable_sort(cols.begin(), cols.end(), [](const Col& a, const Col& b) {
+      if (a.part != b.part) return a.part < b.part;
+      if (a.flag != b.flag) return a.flag < b.flag;
+      return a.ggid < b.ggid;
+    });
+    const i64 OWNER = -2, NON_OWNER = -3, UNCOUPLED = -1;
+    size_t col = 0;
+    while (col < cols.size()) {                                  // :2797-2845
+      if (cols[col].flag == 2) {
+        size_t start = col;
+        while (col < cols.size() && cols[col].flag == 2 && cols[col].part == cols[start].part) ++col;
+        size_t size = col - start;
+        bool i_am_max = mypart == cols[start].maxpart;
+        for (size_t j = start; j < start + size / 2; ++j) cols[j].flag = i_am_max ? OWNER : NON_OWNER;
+        for (size_t j = start + size / 2; j < start + size; ++j) cols[j].flag = i_am_max ? NON_OWNER : OWNER;
+      } else {
+        if (mypart == cols[col].maxpart) cols[col].flag = OWNER;
+        else cols[col].flag = (cols[col].part == cols[col].maxpart) ? NON_OWNER : UNCOUPLED;
+        ++col;
+      }
+    }
+    // dof_import_create
+    weight.assign(n_free, 1.0);
+    list_rcv.clear(); list_snd.clear();
+    std::vector<int> rcv_vis(nparts + 1, -1), snd_vis(nparts + 1, -1), rcnt, scnt;
+    for (const Col& c : cols) {
+      if (c.flag == OWNER) { if (rcv_vis[c.part] < 0) { rcv_vis[c.part] = int(list_rcv.size()); list_rcv.push_back(int(c.part)); rcnt.push_back(0); } rcnt[rcv_vis[c.part]]++; }
+      else if (c.flag == NON_OWNER) { if (snd_vis[c.part] < 0) { snd_vis[c.part] = int(list_snd.size()); list_snd.push_back(int(c.part)); scnt.push_back(0); } scnt[snd_vis[c.part]]++; }
+    }
+    rcv_ptrs.assign(list_rcv.size() + 1, 0); snd_ptrs.assign(list_snd.size() + 1, 0);
+    for (size_t i = 0; i < list_rcv.size(); ++i) rcv_ptrs[i + 1] = rcv_ptrs[i] + rcnt[i];
+    for (size_t i = 0; i < list_snd.size(); ++i) snd_ptrs[i + 1] = snd_ptrs[i] + scnt[i];
+    unpack_idx.assign(rcv_ptrs.back(), 0); pack_idx.assign(snd_ptrs.back(), 0);
+    std::vector<int> rp(rcv_ptrs.begin(), rcv_ptrs.end()), sp(snd_ptrs.begin(), snd_ptrs.end());
+    std::vector<char> visited(n_free + 1, 0);
+    n_interface = 0;
+    for (const Col& c : cols) {
+      if (c.flag == OWNER) unpack_idx[rp[rcv_vis[c.part]]++] = c.dof;
+      else if (c.flag == NON_OWNER) { pack_idx[sp[snd_vis[c.part]]++] = c.dof; weight[c.dof - 1] = 0.0; }
+      if (!visited[c.dof]) { visited[c.dof] = 1; ++n_interface; }
+    }
+    n_interior = n_free - n_interface;
+    // fill_first_I_then_G_renumbering
+    perm_old2new.assign(n_free + 1, -1);
+    int cur = n_interior + 1;
+    for (int g : pack_idx) if (perm_old2new[g] == -1) perm_old2new[g] = cur++;
+    for (int g : unpack_idx) if (perm_old2new[g] == -1) perm_old2new[g] = cur++;
+    cur = 1;
+    for (int g = 1; g <= n_free; ++g) if (perm_old2new[g] == -1) perm_old2new[g] = cur++;
+    // renum_dofs_block (only free dofs: sbm_fe_cell_iterator.i90:907-933) and dof_import%renum_dofs
+    for (auto& g : gids) if (g > 0 && g <= n_free) g = perm_old2new[g];
+    for (auto& g : pack_idx) g = perm_old2new[g];
+    for (auto& g : unpack_idx) g = perm_old2new[g];
+    std::vector<double> w2(n_free);
+    for (int g = 1; g <= n_free; ++g) w2[perm_old2new[g] - 1] = weight[g - 1];
+    weight.swap(w2);
   }
 
   // physical coordinates of the FE nodes of a cell through the order-1 geometry map
@@ -939,6 +1058,23 @@ int fo_ref_tables(void* h, double* qw, double* phi, double* dphi) {
   std::copy(s->fe.dphi.begin(), s->fe.dphi.end(), dphi);
   return 0;
 }
+int fo_num_interior(void* h) { return ((Space*)h)->n_interior; }
+int fo_num_interface(void* h) { return ((Space*)h)->n_interface; }
+int fo_imp_sizes(void* h, int* out) {
+  Space* s = (Space*)h;
+  out[0] = int(s->list_rcv.size()); out[1] = int(s->list_snd.size()); out[2] = int(s->unpack_idx.size()); out[3] = int(s->pack_idx.size());
+  return 0;
+}
+const int* fo_imp_ptr(void* h, int which) {
+  Space* s = (Space*)h;
+  switch (which) {
+    case 0: return s->list_rcv.data(); case 1: return s->rcv_ptrs.data(); case 2: return s->unpack_idx.data();
+    case 3: return s->list_snd.data(); case 4: return s->snd_ptrs.data(); case 5: return s->pack_idx.data();
+    case 6: return s->perm_old2new.data();
+  }
+  return nullptr;
+}
+const double* fo_weight(void* h) { return ((Space*)h)->weight.data(); }
 int fo_nq(void* h) { return ((Space*)h)->fe.nq; }
 int fo_hw_threads() { int n = int(std::thread::hardware_concurrency()); return n > 0 ? n : 1; }
 int fo_set_threads(void* h, int nt) { ((Space*)h)->nthreads = nt > 0 ? nt : 1; return 0; }

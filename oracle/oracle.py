@@ -99,6 +99,21 @@ class OracleSpace:
     @property
     def nnz(self): return self.L.fo_nnz(self.h)
 
+    @property
+    def num_interior(self): return self.L.fo_num_interior(self.h)
+    @property
+    def num_interface(self): return self.L.fo_num_interface(self.h)
+
+    def dof_import(self):
+        """dof_import_t of this part: dict with list_rcv, rcv_ptrs (0-based offsets), unpack_idx (1-based), list_snd,
+        snd_ptrs, pack_idx, weight."""
+        sz = (C.c_int * 4)()
+        self.L.fo_imp_sizes(self.h, sz)
+        nr, ns, nu, npk = [int(v) for v in sz]
+        g = lambda w, n: _arr(self.L.fo_imp_ptr(self.h, w), n, np.int32).copy()
+        return dict(list_rcv=g(0, nr), rcv_ptrs=g(1, nr + 1), unpack_idx=g(2, nu), list_snd=g(3, ns), snd_ptrs=g(4, ns + 1),
+                    pack_idx=g(5, npk), weight=_arr(self.L.fo_weight(self.h), self.num_free, np.float64).copy())
+
     def lst_dofs_gids(self):
         return _arr(self.L.fo_lst_dofs_gids(self.h), self.num_cells * self.ndofs_per_cell, np.int32).reshape(
             self.num_cells, self.ndofs_per_cell)
