@@ -38,6 +38,8 @@ _SIGS = {
     "fb2_fe_space_interpolate_dirichlet": [_VP, C.c_int, _VP],
     "fb2_fe_space_get_fixed_values": [_VP, _VP],
     "fb2_fe_space_set_fixed_values": [_VP, _VP],
+    "fb2_dof_import_get_sizes": [_VP, _VP],
+    "fb2_dof_import_get": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP],
     "fb2_csr_create": [C.POINTER(_VP), _VP, C.c_int],
     "fb2_csr_destroy": [_VP],
     "fb2_csr_get_sizes": [_VP, C.POINTER(C.c_int64), C.POINTER(C.c_int64)],

@@ -53,14 +53,6 @@ int fb2_allreduce_sum(double* d_buf, int count) {
 // ------------------------------------------------------------------------------------------
 // dof_import on the device
 // ------------------------------------------------------------------------------------------
-struct fb2_import_s {
-  int num_rcv = 0, num_snd = 0;
-  std::vector<int> list_rcv, rcv_ptrs, list_snd, snd_ptrs;   // part ids 1-based, ptrs 0-based offsets
-  int *d_pack_idx = nullptr, *d_unpack_idx = nullptr;        // 0-based local dof ids
-  double *d_snd_buf = nullptr, *d_rcv_buf = nullptr;
-  double* d_weight = nullptr;
-  i64 n_pack = 0, n_unpack = 0;
-};
 const double* fb2_import_weight(fb2_import_s* imp) { return imp->d_weight; }
 void fb2_import_destroy(fb2_import_s* imp) {
   if (!imp) return;
@@ -113,8 +105,3 @@ int fb2_import_exchange(fb2_import_s* imp, double* d_vec) {
   return 0;
 }
 
-int fb2_build_par_layer(fb2_space_s* s) {
-  (void)s;
-  fb2_set_error("par layer (dof_import) not built yet");
-  return 4;
-}

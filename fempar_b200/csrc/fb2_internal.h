@@ -122,8 +122,16 @@ double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x
 int fb2_build_scatter_map(fb2_matrix_s* A);
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 
-// comm layer
-struct fb2_import_s;
+// comm layer: dof_import_t on the device (dof_import.f90:49-90)
+struct fb2_import_s {
+  int num_rcv = 0, num_snd = 0;
+  std::vector<int> list_rcv, rcv_ptrs, list_snd, snd_ptrs;   // part ids 1-based, ptrs 0-based offsets
+  std::vector<int> h_pack_idx, h_unpack_idx;                 // 1-based local dof ids (host copy for export)
+  int *d_pack_idx = nullptr, *d_unpack_idx = nullptr;        // 0-based local dof ids
+  double *d_snd_buf = nullptr, *d_rcv_buf = nullptr;
+  double* d_weight = nullptr;
+  i64 n_pack = 0, n_unpack = 0;
+};
 int fb2_comm_active();
 int fb2_comm_nranks();
 int fb2_comm_rank();
@@ -131,4 +139,5 @@ int fb2_allreduce_sum(double* d_buf, int count);           // in place, device b
 int fb2_import_exchange(fb2_import_s* imp, double* d_vec); // par_scalar_array%comm()
 const double* fb2_import_weight(fb2_import_s* imp);
 void fb2_import_destroy(fb2_import_s* imp);
-int fb2_build_par_layer(fb2_space_s* s);                   // interface detection + dof_import + I-then-G renumbering
+int fb2_build_par_layer(fb2_space_s* s);                   // fb2_par.cu
+int fb2_build_node_maps(fb2_space_s* s);                   // fb2_space.cu                   // interface detection + dof_import + I-then-G renumbering

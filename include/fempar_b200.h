@@ -87,6 +87,12 @@ int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const double* fu
 int fb2_fe_space_get_fixed_values(fb2_space_t s, double* host_out);
 int fb2_fe_space_set_fixed_values(fb2_space_t s, const double* host_in);
 
+/* dof_import_t of a par space (dof_import.f90:49-90), Fortran conventions (ptrs(1)=1, 1-based local DOF ids in the
+ * interior-then-interface numbering).  sizes = num_rcv, num_snd, size(unpack_idx), size(pack_idx); weight may be NULL. */
+int fb2_dof_import_get_sizes(fb2_space_t s, int32_t sizes[4]);
+int fb2_dof_import_get(fb2_space_t s, int32_t* list_rcv, int32_t* rcv_ptrs, int32_t* unpack_idx, int32_t* list_snd,
+                       int32_t* snd_ptrs, int32_t* pack_idx, double* weight);
+
 /* ---- matrix: csr_sparse_matrix.f90:44-50 ; graph = what coo sort_and_compress would produce ---------- */
 int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_storage);
 int fb2_csr_destroy(fb2_matrix_t A);

@@ -1,0 +1,81 @@
+"""torchrun worker of tests/test_gpu_par.py::test_par_pcg_nccl: one rank = one GPU = one FEMPAR sub-domain.
+Checks the NCCL path (RHS comm, halo exchange in SpMV, weighted dots + all-reduce, Jacobi set-up, PCG) of this rank's part
+against the in-process multi-part oracle."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import fempar_b200 as fb  # noqa: E402
+from oracle.oracle import KIND_POISSON, FUNC_LINEAR, FUNC_SHARP_WAVE  # noqa: E402
+from oracle.par_oracle import ParOracle  # noqa: E402
+
+WAVE = [200.0, 0.7, -0.05, -0.05, -0.05]
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    fb.init(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    fb.comm_init_from_torch(dist)
+    parts = {2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
+    ok = True
+    for N, p, func, prm, prec in [((8, 8, 8), 1, FUNC_LINEAR, None, 1), ((8, 8, 8), 2, FUNC_SHARP_WAVE, WAVE, 1),
+                                  ((8, 8, 8), 2, FUNC_LINEAR, None, 0), ((4, 4, 4), 3, FUNC_LINEAR, None, 1)]:
+        P = ParOracle(N, order=p, parts=parts)
+        P.assemble(KIND_POISSON, func, prm)
+        P.jacobi_setup()
+        ro = P.cg(prec=prec, rtol=1e-12, maxit=5000)
+        s = fb.FeSpace(N, order=p, num_parts_x_dim=parts, part_id=rank + 1)
+        op = fb.FeAffineOperator()
+        op.create(fb.csr_format, [False], [True], [1], s, fb.DiscreteIntegration(fb.poisson, func, prm))
+        op.compute()
+        b = op.get_translation().get_entries()
+        ob = P.b[rank]
+        ok &= bool(np.max(np.abs(b - ob)) <= 1e-12 * max(np.max(np.abs(ob)), 1e-300))          # RHS after comm()
+        ones = s.create_dof_values(); ones.init(1.0); ones.comm()
+        oo = P.comm([np.ones(q.num_free) for q in P.spaces])[rank]
+        ok &= bool(np.array_equal(ones.get_entries(), oo))
+        x = np.random.default_rng(7).standard_normal(s.num_free_dofs)
+        vx, vy = s.create_dof_values(), s.create_dof_values()
+        # a consistent ("fully assembled") input: make interface copies agree through comm of owner values
+        vx.set_entries(x * s.get_dof_import()["weight"]); vx.comm()
+        xs = P.comm([np.random.default_rng(7).standard_normal(q.num_free) * i["weight"] for q, i in zip(P.spaces, P.imp)])
+        op.get_matrix().apply(vx, vy)
+        oy = P.spmv(xs)[rank]
+        ok &= bool(np.max(np.abs(vy.get_entries() - oy)) <= 1e-12 * np.max(np.abs(oy)))
+        ok &= bool(abs(vx.dot(vy) - P.dot(xs, P.spmv(xs))) <= 1e-11 * abs(P.dot(xs, P.spmv(xs))))
+        M = None
+        if prec == 1:
+            M = fb.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+            ok &= bool(np.max(np.abs(M.inverse_diagonal.get_entries() - P.dinv[rank])) <= 1e-12 * np.max(np.abs(P.dinv[rank])))
+        ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG")
+        ils.set_parameters_from_pl({fb.ILS_RTOL: 1e-12, fb.ILS_MAX_NUM_ITERATIONS: 5000})
+        ils.set_operators(op.get_tangent(), M)
+        sol = s.create_dof_values()
+        ils.apply(op.get_translation(), sol)
+        ok &= ils.converged() and abs(ils.get_num_iterations() - ro["iters"]) <= 1
+        ok &= bool(np.max(np.abs(sol.get_entries() - ro["x"][rank])) <= 1e-8)
+        h1, l2 = s.error_norms(sol, func, prm)
+        oh1, ol2 = P.errors(ro["x"], func, prm)
+        ok &= bool(abs(h1 - oh1) <= 1e-8 * max(oh1, 1.0) and abs(l2 - ol2) <= 1e-8 * max(ol2, 1.0))
+        if rank == 0:
+            print("case", N, p, func, prec, "iters", ils.get_num_iterations(), ro["iters"], "ok", ok, flush=True)
+    t = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0 and int(t.item()) == 1:
+        print("PAR_NCCL_OK")
+    fb.comm_finalize()
+    dist.destroy_process_group()
+    sys.exit(0 if int(t.item()) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()
