@@ -27,6 +27,14 @@ def main():
     fb.comm_init_from_torch(dist)
     parts = {2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
     ok = True
+    fails = []
+
+    def chk(name, cond, info=""):
+        nonlocal ok
+        if not cond:
+            ok = False
+            fails.append("rank %d %s %s" % (rank, name, info))
+
     for N, p, func, prm, prec in [((8, 8, 8), 1, FUNC_LINEAR, None, 1), ((8, 8, 8), 2, FUNC_SHARP_WAVE, WAVE, 1),
                                   ((8, 8, 8), 2, FUNC_LINEAR, None, 0), ((4, 4, 4), 3, FUNC_LINEAR, None, 1)]:
         P = ParOracle(N, order=p, parts=parts)
@@ -39,10 +47,10 @@ def main():
         op.compute()
         b = op.get_translation().get_entries()
         ob = P.b[rank]
-        ok &= bool(np.max(np.abs(b - ob)) <= 1e-12 * max(np.max(np.abs(ob)), 1e-300))          # RHS after comm()
+        chk("rhs", np.max(np.abs(b - ob)) <= 1e-12 * max(np.max(np.abs(ob)), 1e-300), np.max(np.abs(b - ob)))   # RHS after comm()
         ones = s.create_dof_values(); ones.init(1.0); ones.comm()
         oo = P.comm([np.ones(q.num_free) for q in P.spaces])[rank]
-        ok &= bool(np.array_equal(ones.get_entries(), oo))
+        chk("comm_ones", np.array_equal(ones.get_entries(), oo))
         x = np.random.default_rng(7).standard_normal(s.num_free_dofs)
         vx, vy = s.create_dof_values(), s.create_dof_values()
         # a consistent ("fully assembled") input: make interface copies agree through comm of owner values
@@ -50,24 +58,27 @@ def main():
         xs = P.comm([np.random.default_rng(7).standard_normal(q.num_free) * i["weight"] for q, i in zip(P.spaces, P.imp)])
         op.get_matrix().apply(vx, vy)
         oy = P.spmv(xs)[rank]
-        ok &= bool(np.max(np.abs(vy.get_entries() - oy)) <= 1e-12 * np.max(np.abs(oy)))
-        ok &= bool(abs(vx.dot(vy) - P.dot(xs, P.spmv(xs))) <= 1e-11 * abs(P.dot(xs, P.spmv(xs))))
+        chk("spmv", np.max(np.abs(vy.get_entries() - oy)) <= 1e-12 * np.max(np.abs(oy)), np.max(np.abs(vy.get_entries() - oy)) / np.max(np.abs(oy)))
+        od = P.dot(xs, P.spmv(xs))
+        chk("dot", abs(vx.dot(vy) - od) <= 1e-11 * abs(od), (vx.dot(vy), od))
         M = None
         if prec == 1:
             M = fb.JacobiPreconditioner(); M.create(op); M.numerical_setup()
-            ok &= bool(np.max(np.abs(M.inverse_diagonal.get_entries() - P.dinv[rank])) <= 1e-12 * np.max(np.abs(P.dinv[rank])))
+            chk("dinv", np.max(np.abs(M.inverse_diagonal.get_entries() - P.dinv[rank])) <= 1e-12 * np.max(np.abs(P.dinv[rank])))
         ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG")
         ils.set_parameters_from_pl({fb.ILS_RTOL: 1e-12, fb.ILS_MAX_NUM_ITERATIONS: 5000})
         ils.set_operators(op.get_tangent(), M)
         sol = s.create_dof_values()
         ils.apply(op.get_translation(), sol)
-        ok &= ils.converged() and abs(ils.get_num_iterations() - ro["iters"]) <= 1
-        ok &= bool(np.max(np.abs(sol.get_entries() - ro["x"][rank])) <= 1e-8)
+        chk("iters", ils.converged() and abs(ils.get_num_iterations() - ro["iters"]) <= 1, (ils.get_num_iterations(), ro["iters"]))
+        chk("solution", np.max(np.abs(sol.get_entries() - ro["x"][rank])) <= 1e-8, np.max(np.abs(sol.get_entries() - ro["x"][rank])))
         h1, l2 = s.error_norms(sol, func, prm)
         oh1, ol2 = P.errors(ro["x"], func, prm)
-        ok &= bool(abs(h1 - oh1) <= 1e-8 * max(oh1, 1.0) and abs(l2 - ol2) <= 1e-8 * max(ol2, 1.0))
+        chk("errors", abs(h1 - oh1) <= 1e-8 * max(oh1, 1.0) and abs(l2 - ol2) <= 1e-8 * max(ol2, 1.0), (h1, oh1, l2, ol2))
         if rank == 0:
             print("case", N, p, func, prec, "iters", ils.get_num_iterations(), ro["iters"], "ok", ok, flush=True)
+    for f in fails:
+        print("FAIL", f, flush=True)
     t = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0 and int(t.item()) == 1:
