@@ -3,7 +3,7 @@
 // (1) Scatter map ("cell-local -> CSR-slot map", north_star): slot(c,i,j) = irp[gid(c,i)] + tab[cell_tab[c]][i][j].
 //     An explicit map would cost nd^2 * 4 B per cell (49 GB at Q2 256^3); on a structured part the relative
 //     slots repeat for every cell with the same position class (distance to the ends of the local cell box,
-//     clipped at 2, per direction), so the map is stored as <= 729 class tables of nd^2 uint16 plus explicit
+//     clipped at 3, per direction), so the map is stored as <= 4096 class tables of nd^2 uint16 plus explicit
 //     tables for the cells whose class table does not verify (e.g. next to a sub-domain interface after the
 //     interior-then-interface renumbering).  Every cell is verified on the device against ja.
 // (2) Integration: one warp per cell, lane j owns column j of the element matrix,
@@ -22,14 +22,16 @@ __device__ __forceinline__ int cell_class_key(const CellGeom& g, const int* cl /
   int key = 0, mul = 1;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    int lo = min(cl[k], 2), hi = min(g.nloc[k] - 1 - cl[k], 2);
-    key += mul * (lo * 3 + hi);
-    mul *= 9;
+    // clip at 3: next to a sub-domain interface the interface cells are numbered last, so the cell that creates the DOFs of
+    // the shared n-faces sits one layer further in than at a Dirichlet boundary (measured: clip 2 left ~all cells irregular)
+    int lo = min(cl[k], 3), hi = min(g.nloc[k] - 1 - cl[k], 3);
+    key += mul * (lo * 4 + hi);
+    mul *= 16;
   }
   return key;
 }
 
-__global__ void k_map_keys(CellGeom g, const int* __restrict__ perm, int n_local, int* cell_tab, int* rep /*[729]*/) {
+__global__ void k_map_keys(CellGeom g, const int* __restrict__ perm, int n_local, int* cell_tab, int* rep /*[4096]*/) {
   int ci = blockIdx.x * blockDim.x + threadIdx.x;
   if (ci >= n_local) return;
   int cl[3] = {ci % g.nloc[0], (ci / g.nloc[0]) % g.nloc[1], ci / (g.nloc[0] * g.nloc[1])};
@@ -104,15 +106,15 @@ int fb2_build_scatter_map(fb2_matrix_s* A) {
   CellGeom g = make_geom(s);
   int *d_rep, *d_class_of_key, *d_bad, *d_nbad, *d_reps;
   FB2_TRY(fb2_dalloc(&A->d_cell_tab, (size_t)n_local));
-  FB2_TRY(fb2_dalloc(&d_rep, 729)); FB2_TRY(fb2_dalloc(&d_class_of_key, 729)); FB2_TRY(fb2_dalloc(&d_reps, 729));
+  FB2_TRY(fb2_dalloc(&d_rep, 4096)); FB2_TRY(fb2_dalloc(&d_class_of_key, 4096)); FB2_TRY(fb2_dalloc(&d_reps, 4096));
   FB2_TRY(fb2_dalloc(&d_bad, (size_t)n_local)); FB2_TRY(fb2_dalloc(&d_nbad, 1));
-  FB2_CUDA(cudaMemsetAsync(d_rep, 0x7f, 729 * sizeof(int), st));
+  FB2_CUDA(cudaMemsetAsync(d_rep, 0x7f, 4096 * sizeof(int), st));
   FB2_CUDA(cudaMemsetAsync(d_nbad, 0, sizeof(int), st));
   k_map_keys<<<(n_local + 255) / 256, 256, 0, st>>>(g, s->d_perm, n_local, A->d_cell_tab, d_rep);
-  int h_rep[729], h_class[729], h_reps[729], ncls = 0;
+  int h_rep[4096], h_class[4096], h_reps[4096], ncls = 0;
   FB2_CUDA(cudaMemcpyAsync(h_rep, d_rep, sizeof(h_rep), cudaMemcpyDeviceToHost, st));
   FB2_CUDA(cudaStreamSynchronize(st));
-  for (int k = 0; k < 729; ++k) {
+  for (int k = 0; k < 4096; ++k) {
     h_class[k] = -1;
     if (h_rep[k] < n_local) { h_class[k] = ncls; h_reps[ncls++] = h_rep[k]; }
   }
@@ -154,6 +156,8 @@ int fb2_build_scatter_map(fb2_matrix_s* A) {
   float ms = 0;
   cudaEventElapsedTime(&ms, e0, e1);
   fb2_record_phase("scatter_map", ms);
+  fb2_record_phase("scatter_map_class_tables", (double)A->n_class_tabs);
+  fb2_record_phase("scatter_map_tables", (double)A->n_tabs);
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   cudaFree(d_rep); cudaFree(d_class_of_key); cudaFree(d_bad); cudaFree(d_nbad); cudaFree(d_reps);
   FB2_CUDA(cudaGetLastError());

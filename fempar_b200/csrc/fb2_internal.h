@@ -105,6 +105,8 @@ struct fb2_matrix_s {
   // SpMV tile geometry (fb2_spmv.cu)
   int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0;
   i64 spmv_ntiles = 0;
+  i64* d_tile_row = nullptr;              // first row of every tile
+  unsigned char* d_tile_nrows = nullptr;  // rows in the tile (<= spmv_R)
   size_t spmv_smem = 0;
 };
 

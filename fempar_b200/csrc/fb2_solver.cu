@@ -169,17 +169,20 @@ static int spmv_local(fb2_matrix_t A, const double* x, double* y, bool fuse_dot,
 extern "C" int fb2_spmv(fb2_matrix_t A, fb2_vector_t x, fb2_vector_t y) {
   FB2_CHECK(A && x && y && x->n == A->n && y->n == A->n, "fb2_spmv: size mismatch");
   cudaStream_t st = fb2_stream();
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEvent_t e0, e1, e2;
+  cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
   cudaEventRecord(e0, st);
   FB2_TRY(spmv_local(A, x->d, y->d, false, nullptr, nullptr));
   cudaEventRecord(e1, st);
   if (A->s->imp && fb2_comm_active()) FB2_TRY(fb2_import_exchange(A->s->imp, y->d));
+  cudaEventRecord(e2, st);
   FB2_CUDA(cudaStreamSynchronize(st));
-  float ms = 0;
+  float ms = 0, ms2 = 0;
   cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventElapsedTime(&ms2, e1, e2);
   fb2_record_phase("spmv", ms);
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  fb2_record_phase("halo", ms2);
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
   return 0;
 }
 
@@ -420,8 +423,8 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
     k_reduce_partials<<<1, 256, 0, s>>>(part, g, 0, 1, &W.st->App);
   } else {
     FB2_TRY(spmv_local(A, W.p, W.Ap, false, A->sym ? nullptr : W.st, &g));
-    if (ev_spmv1) cudaEventRecord(ev_spmv1, s);
     if (par) FB2_TRY(fb2_import_exchange(A->s->imp, W.Ap));                  // par_sparse_matrix.f90:757-758
+    if (ev_spmv1) cudaEventRecord(ev_spmv1, s);                              // par: the timed apply includes the halo exchange
     FB2_TRY(fb2_dot_device(W.Ap, W.p, w, n, &W.st->App));
     if (par) FB2_TRY(fb2_allreduce_sum(&W.st->App, 1));
   }

@@ -623,8 +623,8 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
   const i64 n = A->n;
   i64* cnt;
   FB2_TRY(fb2_dalloc(&cnt, (size_t)n + 1));
-  FB2_TRY(fb2_dalloc(&A->d_irp, (size_t)n + 4));   // +3: the SpMV copies irp slices in 16-byte groups
-  FB2_CUDA(cudaMemsetAsync(A->d_irp, 0, sizeof(i64) * ((size_t)n + 4), st));
+  FB2_TRY(fb2_dalloc(&A->d_irp, (size_t)n + 72));  // padding: the SpMV bulk-copies irp slices of up to 66 entries per tile
+  FB2_CUDA(cudaMemsetAsync(A->d_irp, 0, sizeof(i64) * ((size_t)n + 72), st));
   const int p = s->rt.p, ncomp = s->rt.ncomp;
   k_row_count<<<(unsigned)((n + 1 + 127) / 128), 128, 0, st>>>(p, ncomp, s->Mlat[0], s->Mlat[1], s->Mlat[2], s->lat_size, n,
                                                               A->sym, s->d_dof_node, s->d_node_dof, cnt);
@@ -662,7 +662,7 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
 }
 extern "C" int fb2_csr_destroy(fb2_matrix_t A) {
   if (!A) return 0;
-  cudaFree(A->d_irp); cudaFree(A->d_ja); cudaFree(A->d_val); cudaFree(A->d_cell_tab); cudaFree(A->d_tabs);
+  cudaFree(A->d_irp); cudaFree(A->d_ja); cudaFree(A->d_val); cudaFree(A->d_cell_tab); cudaFree(A->d_tabs); cudaFree(A->d_tile_row); cudaFree(A->d_tile_nrows);
   delete A;
   return 0;
 }

@@ -6,6 +6,7 @@
 // consecutive rows is the contiguous element range [irp[r0], irp[r0+R]) of both.  Algorithmic bytes
 // per row tile: 12 B per non-zero + 24 B per row (irp, y, x).
 #include <stdlib.h>
+#include <cub/cub.cuh>
 #include "fb2_internal.h"
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -52,10 +53,12 @@ template <bool FUSE_DOT>
 __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* __restrict__ irp, const int* __restrict__ ja,
                                                              const double* __restrict__ val, const double* __restrict__ x,
                                                              double* __restrict__ y, double* partials, const int* done_flag,
-                                                             int R, int cap, i64 ntiles, int STAGES) {
+                                                             int R, int cap, i64 ntiles, int STAGES,
+                                                             const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full_bar[SPMV_MAX_STAGES], empty_bar[SPMV_MAX_STAGES];
-  __shared__ i64 s_e0a[SPMV_MAX_STAGES];
+  __shared__ i64 s_e0a[SPMV_MAX_STAGES], s_r0[SPMV_MAX_STAGES];
+  __shared__ int s_nr[SPMV_MAX_STAGES];
   __shared__ double s_red[32];
   if (done_flag && *done_flag) return;
   const int tid = threadIdx.x;
@@ -71,25 +74,27 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
     // ---------------- producer warp ----------------
     if (tid == SPMV_CONSUMERS) {
       i64 t = blockIdx.x;
-      i64 e0 = 0, e1 = 0;
-      if (t < ntiles) { i64 r0 = t * R, r1 = min(r0 + R, n); e0 = irp[r0]; e1 = irp[r1]; }
+      i64 e0 = 0, e1 = 0, r0 = 0;
+      int nr = 0;
+      if (t < ntiles) { r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr]; }
       for (int it = 0; t < ntiles; t += gridDim.x, ++it) {
         const int s = it % STAGES;
-        // prefetch the element range of the next tile before blocking on the empty barrier
-        i64 tn = t + gridDim.x, ne0 = 0, ne1 = 0;
-        if (tn < ntiles) { i64 r0 = tn * R, r1 = min(r0 + R, n); ne0 = irp[r0]; ne1 = irp[r1]; }
+        // prefetch the row / element range of the next tile before blocking on the empty barrier
+        i64 tn = t + gridDim.x, ne0 = 0, ne1 = 0, nr0 = 0;
+        int nnr = 0;
+        if (tn < ntiles) { nr0 = tile_row[tn]; nnr = tile_nrows[tn]; ne0 = irp[nr0]; ne1 = irp[nr0 + nnr]; }
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
         unsigned char* base = smem_raw + s * stage_bytes;
         const i64 e0a = e0 & ~(i64)3;
         const uint32_t cnt4 = (uint32_t)((e1 - e0a + 3) & ~(i64)3);
-        s_e0a[s] = e0a;
+        s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr;
         mbar_expect_tx(&full_bar[s], cnt4 * 12u + (uint32_t)irp_bytes);
-        bulk_g2s(base + (size_t)cap * 12, irp + t * R, (uint32_t)irp_bytes, &full_bar[s]);
+        bulk_g2s(base + (size_t)cap * 12, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
         if (cnt4) {
           bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
           bulk_g2s(base + (size_t)cap * 8, ja + e0a, cnt4 * 4u, &full_bar[s]);
         }
-        e0 = ne0; e1 = ne1;
+        e0 = ne0; e1 = ne1; r0 = nr0; nr = nnr;
       }
     }
     return;
@@ -102,15 +107,15 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
   int it = 0;
   for (i64 t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
     const int s = it % STAGES;
-    const i64 r0 = t * R;
     mbar_wait(&full_bar[s], (it / STAGES) & 1);
+    const i64 r0 = s_r0[s];
     const unsigned char* base = smem_raw + s * stage_bytes;
     const double* sv = (const double*)base;
     const int* sj = (const int*)(base + (size_t)cap * 8);
     const i64* s_irp = (const i64*)(base + (size_t)cap * 12);
     const i64 e0a = s_e0a[s];
     double acc = 0.0;
-    const bool live = r0 + row < n;
+    const bool live = row < s_nr[s];
     if (live) {
       const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
       int k = b + sub;
@@ -144,50 +149,77 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
   }
 }
 
-__global__ void k_tile_max(i64 n, const i64* __restrict__ irp, int R, i64 ntiles, int* out_max) {
+// ---- tile table: fixed tiles of R rows, split in halves (down to 2 rows, so that every tile starts on an even row and its
+// irp slice is 16-byte aligned for the bulk copy) until the aligned element range fits the stage buffer ----
+__device__ __forceinline__ i64 tile_count4(const i64* __restrict__ irp, i64 r0, i64 r1) {
+  return (irp[r1] - (irp[r0] & ~(i64)3) + 3) & ~(i64)3;
+}
+__global__ void k_tile_pieces(i64 n, const i64* __restrict__ irp, int R, int cap, i64 nfixed, int* pieces, int* too_long) {
   i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-  int v = 0;
-  if (t < ntiles) {
-    i64 r0 = t * R, r1 = r0 + R;
-    if (r1 > n) r1 = n;
-    v = (int)(irp[r1] - (irp[r0] & ~(i64)3));
+  if (t > nfixed) return;
+  if (t == nfixed) { pieces[t] = 0; return; }
+  const i64 r0 = t * R, r1 = min(r0 + R, n);
+  int np = 1;
+  for (int rows = R; rows >= 2; rows >>= 1, np <<= 1) {
+    bool fits = true;
+    for (i64 a = r0; a < r1; a += rows) fits &= tile_count4(irp, a, min(a + rows, r1)) <= cap;
+    if (fits) { pieces[t] = (int)((r1 - r0 + rows - 1) / rows); return; }
   }
-  for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_down_sync(0xffffffffu, v, o));
-  if ((threadIdx.x & 31) == 0 && v > 0) atomicMax(out_max, v);
+  pieces[t] = (int)((r1 - r0 + 1) / 2);
+  *too_long = 1;
+}
+__global__ void k_tile_fill(i64 n, const i64* __restrict__ irp, int R, int cap, i64 nfixed, const int* __restrict__ off,
+                            i64* tile_row, unsigned char* tile_nrows) {
+  i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nfixed) return;
+  const i64 r0 = t * R, r1 = min(r0 + R, n);
+  const int np = off[t + 1] - off[t];
+  int rows = R;
+  while ((r1 - r0 + rows - 1) / rows < np) rows >>= 1;
+  int o = off[t];
+  for (i64 a = r0; a < r1; a += rows, ++o) { tile_row[o] = a; tile_nrows[o] = (unsigned char)(min(a + rows, r1) - a); }
 }
 
 // choose the tile geometry once per matrix
 int fb2_spmv_prepare(fb2_matrix_s* A) {
   if (A->spmv_cap > 0 || A->n == 0) return 0;
-  const int p = A->s->rt.p, ncomp = A->s->rt.ncomp;
-  int maxrow = (2 * p + 1) * (2 * p + 1) * (2 * p + 1) * ncomp;
-  // Tile geometry from the B200 sweep (profiles/sweep_spmv_r1.txt): 2 stages of ~25 KB and 4 resident blocks
-  // per SM beat deeper pipelines; take the largest R whose fullest tile stays below ~2.3k non-zeros.
-  int R = 64, STAGES = 2, h = 0;
-  const bool fixedR = getenv("FB2_SPMV_R") != nullptr;
-  if (fixedR) R = atoi(getenv("FB2_SPMV_R"));
+  cudaStream_t st = fb2_stream();
+  // Geometry from the B200 sweep (profiles/sweep_spmv_r1.txt): 2 stages of <= 28 KB keep 4 CTAs resident per SM, which beat
+  // deeper pipelines.  R = the power of two whose average tile fills ~90 % of a stage; tiles that overflow are split.
+  int cap = 2304, STAGES = 2;
+  const double avg_row = (double)A->nnz / (double)A->n;
+  int R = 64;
+  while (R > 8 && R * avg_row > 0.9 * cap) R >>= 1;
+  if (getenv("FB2_SPMV_R")) R = atoi(getenv("FB2_SPMV_R"));
   if (getenv("FB2_SPMV_STAGES")) STAGES = atoi(getenv("FB2_SPMV_STAGES"));
-  FB2_CHECK(R >= 8 && R <= 64 && (R & (R - 1)) == 0 && STAGES >= 2 && STAGES <= SPMV_MAX_STAGES, "bad SpMV tile parameters");
-  (void)maxrow;
-  int* d_max;
-  FB2_TRY(fb2_dalloc(&d_max, 1));
-  i64 ntiles = 0;
-  for (;;) {
-    ntiles = (A->n + R - 1) / R;
-    FB2_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), fb2_stream()));
-    k_tile_max<<<(unsigned)((ntiles + 255) / 256), 256, 0, fb2_stream()>>>(A->n, A->d_irp, R, ntiles, d_max);
-    FB2_CUDA(cudaMemcpyAsync(&h, d_max, sizeof(int), cudaMemcpyDeviceToHost, fb2_stream()));
-    FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
-    if (fixedR || R == 8 || h <= 2304) break;
-    R >>= 1;
+  if (getenv("FB2_SPMV_CAP")) cap = atoi(getenv("FB2_SPMV_CAP"));
+  FB2_CHECK(R >= 8 && R <= 64 && (R & (R - 1)) == 0 && STAGES >= 2 && STAGES <= SPMV_MAX_STAGES && cap % 8 == 0, "bad SpMV tile parameters");
+  const i64 nfixed = (A->n + R - 1) / R;
+  int *pieces, *off, *d_flag, h_flag = 0, total = 0;
+  FB2_TRY(fb2_dalloc(&pieces, (size_t)nfixed + 1)); FB2_TRY(fb2_dalloc(&off, (size_t)nfixed + 1)); FB2_TRY(fb2_dalloc(&d_flag, 1));
+  FB2_CUDA(cudaMemsetAsync(d_flag, 0, sizeof(int), st));
+  k_tile_pieces<<<(unsigned)((nfixed + 256) / 256), 256, 0, st>>>(A->n, A->d_irp, R, cap, nfixed, pieces, d_flag);
+  {
+    void* tmp = nullptr; size_t bytes = 0;
+    FB2_CUDA(cub::DeviceScan::ExclusiveSum(tmp, bytes, pieces, off, nfixed + 1, st));
+    FB2_CUDA(cudaMalloc(&tmp, bytes ? bytes : 1));
+    FB2_CUDA(cub::DeviceScan::ExclusiveSum(tmp, bytes, pieces, off, nfixed + 1, st));
+    FB2_CUDA(cudaStreamSynchronize(st));
+    cudaFree(tmp);
   }
-  cudaFree(d_max);
-  int cap = ((h + 3 + 7) / 8) * 8 + 8;
-  size_t stage = (size_t)cap * 12 + (size_t)(R + 2) * 8;
-  while (STAGES > 2 && stage * STAGES > 200 * 1024) --STAGES;
+  FB2_CUDA(cudaMemcpy(&total, off + nfixed, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(cudaMemcpy(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CHECK(h_flag == 0, "a pair of rows exceeds the SpMV stage buffer: use fb2_set_spmv_variant(1)");
+  FB2_TRY(fb2_dalloc(&A->d_tile_row, (size_t)total)); FB2_TRY(fb2_dalloc(&A->d_tile_nrows, (size_t)total));
+  k_tile_fill<<<(unsigned)((nfixed + 255) / 256), 256, 0, st>>>(A->n, A->d_irp, R, cap, nfixed, off, A->d_tile_row, A->d_tile_nrows);
+  FB2_CUDA(cudaStreamSynchronize(st));
+  cudaFree(pieces); cudaFree(off); cudaFree(d_flag);
+  const i64 ntiles = total;
+  const int capbuf = cap + 8;
+  size_t stage = (size_t)capbuf * 12 + (size_t)(R + 2) * 8;
   size_t smem = stage * STAGES;
   FB2_CHECK(smem <= 200 * 1024, "SpMV tile does not fit in shared memory");
-  A->spmv_R = R; A->spmv_cap = cap; A->spmv_ntiles = ntiles; A->spmv_smem = smem; A->spmv_stages = STAGES;
+  A->spmv_R = R; A->spmv_cap = capbuf; A->spmv_ntiles = ntiles; A->spmv_smem = smem; A->spmv_stages = STAGES;
   FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int bps = 0;
@@ -197,6 +229,7 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   if (grid > ntiles) grid = ntiles;
   if (grid > FB2_MAX_PARTIALS) grid = FB2_MAX_PARTIALS;
   A->spmv_grid = (int)grid;
+  fb2_record_phase("spmv_R", R); fb2_record_phase("spmv_tiles", (double)ntiles); fb2_record_phase("spmv_ctas_per_sm", bps);
   return 0;
 }
 
@@ -207,10 +240,10 @@ int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, 
   if (fuse_dot)
     k_spmv_stream<true><<<A->spmv_grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y,
                                                                           fb2_scratch_partials(), done_flag, A->spmv_R,
-                                                                          A->spmv_cap, A->spmv_ntiles, A->spmv_stages);
+                                                                          A->spmv_cap, A->spmv_ntiles, A->spmv_stages, A->d_tile_row, A->d_tile_nrows);
   else
     k_spmv_stream<false><<<A->spmv_grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, nullptr,
-                                                                           done_flag, A->spmv_R, A->spmv_cap, A->spmv_ntiles, A->spmv_stages);
+                                                                           done_flag, A->spmv_R, A->spmv_cap, A->spmv_ntiles, A->spmv_stages, A->d_tile_row, A->d_tile_nrows);
   FB2_CUDA(cudaGetLastError());
   if (grid_out) *grid_out = A->spmv_grid;
   return 0;
