@@ -33,7 +33,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", type=int, default=0, help="cells per direction (0 = 256 if it fits, else largest that fits)")
     ap.add_argument("--order", type=int, default=2)
-    ap.add_argument("--cg-iters", type=int, default=10)
+    ap.add_argument("--cg-iters", type=int, default=25)
     ap.add_argument("--scatter", type=int, default=0)
     ap.add_argument("--cpu-cells", type=int, default=48, help="cells per direction of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")

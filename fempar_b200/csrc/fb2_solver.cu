@@ -444,10 +444,10 @@ static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const d
   CgWork& W = g_work;
   const i64 n = A->n;
   // x <- 0 ; r = A x ; r = b - r   (cg.f90:142,158-162)
+  // The initial solution is zero (base_iterative_linear_solver.f90:281-282), so r = b - A*0 = b bit for bit: the
+  // reference's initial SpMV and its halo exchange are skipped.
   k_init<<<vec_grid(n), 256, 0, s>>>(x, 0.0, n);
-  FB2_TRY(spmv_local(A, x, W.r, false, nullptr, nullptr));
-  if (par) FB2_TRY(fb2_import_exchange(A->s->imp, W.r));
-  k_axpby<<<vec_grid(n), 256, 0, s>>>(W.r, 1.0, b, -1.0, n);
+  FB2_CUDA(cudaMemcpyAsync(W.r, b, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
   // z = M^-1 r ; p = z ; r_z = <r,z>
   if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, dinv, W.r, n);
   else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
