@@ -327,9 +327,9 @@ extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const do
   FB2_CUDA(cudaStreamSynchronize(st));
   if (fb2_comm_active()) {
     // local cells partition the mesh: plain sum over parts
-    FB2_CUDA(cudaMemcpy(d_out, h, 2 * sizeof(double), cudaMemcpyHostToDevice));
     FB2_TRY(fb2_allreduce_sum(d_out, 2));
-    FB2_CUDA(cudaMemcpy(h, d_out, 2 * sizeof(double), cudaMemcpyDeviceToHost));
+    FB2_CUDA(cudaMemcpyAsync(h, d_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    FB2_CUDA(cudaStreamSynchronize(st));
   }
   *h1_seminorm = sqrt(h[0]);
   *l2_norm = sqrt(h[1]);

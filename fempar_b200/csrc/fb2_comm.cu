@@ -57,7 +57,7 @@ const double* fb2_import_weight(fb2_import_s* imp) { return imp->d_weight; }
 void fb2_import_destroy(fb2_import_s* imp) {
   if (!imp) return;
   cudaFree(imp->d_pack_idx); cudaFree(imp->d_unpack_idx); cudaFree(imp->d_snd_buf); cudaFree(imp->d_rcv_buf);
-  cudaFree(imp->d_weight);
+  cudaFree(imp->d_weight); cudaFree(imp->d_add_dst); cudaFree(imp->d_add_ptr); cudaFree(imp->d_add_pos);
   delete imp;
 }
 
@@ -66,9 +66,18 @@ __global__ void k_pack(const double* __restrict__ x, const int* __restrict__ idx
   int i = lo + blockIdx.x * blockDim.x + threadIdx.x;
   if (i < hi) buf[i] = x[idx[i]];
 }
-__global__ void k_unpack(double* __restrict__ x, const int* __restrict__ idx, int lo, int hi, const double* buf, int add) {
+__global__ void k_unpack(double* __restrict__ x, const int* __restrict__ idx, int lo, int hi, const double* buf) {
   int i = lo + blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < hi) { if (add) x[idx[i]] += buf[i]; else x[idx[i]] = buf[i]; }
+  if (i < hi) x[idx[i]] = buf[i];
+}
+// x[dst] += buf[pos_0] + buf[pos_1] + ... added one after the other in neighbour-list order (one thread per destination DOF)
+__global__ void k_unpack_add(double* __restrict__ x, int ndst, const int* __restrict__ dst, const int* __restrict__ ptr,
+                             const int* __restrict__ pos, const double* __restrict__ buf) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ndst) return;
+  double v = x[dst[i]];
+  for (int k = ptr[i]; k < ptr[i + 1]; ++k) v += buf[pos[k]];
+  x[dst[i]] = v;
 }
 
 // one neighbours exchange.  forward: pack_idx -> snd neighbours, unpack into unpack_idx (add or overwrite);
@@ -89,8 +98,11 @@ static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add) 
   for (size_t i = 0; i < sl.size(); ++i)
     if (sp[i + 1] > sp[i]) FB2_NCCL(ncclSend(imp->d_snd_buf + sp[i], sp[i + 1] - sp[i], ncclDouble, sl[i] - 1, g_comm, s));
   FB2_NCCL(ncclGroupEnd());
-  // unpack neighbour by neighbour IN LIST ORDER so that additions happen in the reference's order
-  if (nr > 0) k_unpack<<<(nr + 255) / 256, 256, 0, s>>>(x, ridx, 0, nr, imp->d_rcv_buf, add ? 1 : 0);
+  if (add) {
+    // stage 1 always unpacks into unpack_idx; additions in neighbour-list order (the reference's order)
+    if (imp->n_add_dst > 0)
+      k_unpack_add<<<(imp->n_add_dst + 255) / 256, 256, 0, s>>>(x, imp->n_add_dst, imp->d_add_dst, imp->d_add_ptr, imp->d_add_pos, imp->d_rcv_buf);
+  } else if (nr > 0) k_unpack<<<(nr + 255) / 256, 256, 0, s>>>(x, ridx, 0, nr, imp->d_rcv_buf);   // each non-owned DOF has one owner
   FB2_CUDA(cudaGetLastError());
   return 0;
 }

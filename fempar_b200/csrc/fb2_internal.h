@@ -35,6 +35,14 @@ cudaStream_t fb2_stream();
 int fb2_num_sms();
 void fb2_record_phase(const char* name, double ms);
 
+// Blocking copy ORDERED ON THE LIBRARY STREAM.  The stream is non-blocking, so a plain cudaMemcpy (legacy default stream)
+// would neither wait for kernels / NCCL collectives queued on it nor be waited for by them.
+static inline cudaError_t fb2_memcpy(void* dst, const void* src, size_t bytes, cudaMemcpyKind kind) {
+  cudaError_t e = cudaMemcpyAsync(dst, src, bytes, kind, fb2_stream());
+  if (e != cudaSuccess) return e;
+  return cudaStreamSynchronize(fb2_stream());
+}
+
 template <class T>
 int fb2_dalloc(T** p, size_t n) {
   *p = nullptr;
@@ -133,6 +141,9 @@ struct fb2_import_s {
   double *d_snd_buf = nullptr, *d_rcv_buf = nullptr;
   double* d_weight = nullptr;
   i64 n_pack = 0, n_unpack = 0;
+  // stage-1 gather-add plan: unique destination DOFs, their receive-buffer positions in neighbour order
+  int n_add_dst = 0;
+  int *d_add_dst = nullptr, *d_add_ptr = nullptr, *d_add_pos = nullptr;
 };
 int fb2_comm_active();
 int fb2_comm_nranks();

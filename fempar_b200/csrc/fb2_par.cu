@@ -11,6 +11,7 @@
 // (neighbour part, #parts around + 1, non-consecutive global DOF id) and one thread per coupling decides ownership.
 #include <cub/cub.cuh>
 #include <limits.h>
+#include <algorithm>
 #include "fb2_internal.h"
 
 struct ParGeom {
@@ -222,7 +223,7 @@ int fb2_build_par_layer(fb2_space_s* s) {
   k_par_count<<<GRID(n + 1)>>>(G, n, s->d_dof_node, cnt);
   FB2_TRY(scan_excl(cnt, off, n + 1));
   int ncol = 0;
-  FB2_CUDA(cudaMemcpy(&ncol, off + n, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&ncol, off + n, sizeof(int), cudaMemcpyDeviceToHost));
   std::vector<int> h_part(ncol), h_owner(ncol), h_dof(ncol);
   if (ncol > 0) {
     unsigned *major, *major_s; unsigned long long *ggid, *ggid_s; int *dof, *maxpart, *idx0, *idx1, *idx2, *owner, *dof_s, *maxpart_s;
@@ -240,9 +241,9 @@ int fb2_build_par_layer(fb2_space_s* s) {
     k_par_owner<<<GRID(ncol)>>>(ncol, s->part_id, major, maxpart_s, owner);
     FB2_CUDA(cudaGetLastError());
     std::vector<unsigned> h_major(ncol);
-    FB2_CUDA(cudaMemcpy(h_major.data(), major, sizeof(unsigned) * ncol, cudaMemcpyDeviceToHost));
-    FB2_CUDA(cudaMemcpy(h_owner.data(), owner, sizeof(int) * ncol, cudaMemcpyDeviceToHost));
-    FB2_CUDA(cudaMemcpy(h_dof.data(), dof_s, sizeof(int) * ncol, cudaMemcpyDeviceToHost));
+    FB2_CUDA(fb2_memcpy(h_major.data(), major, sizeof(unsigned) * ncol, cudaMemcpyDeviceToHost));
+    FB2_CUDA(fb2_memcpy(h_owner.data(), owner, sizeof(int) * ncol, cudaMemcpyDeviceToHost));
+    FB2_CUDA(fb2_memcpy(h_dof.data(), dof_s, sizeof(int) * ncol, cudaMemcpyDeviceToHost));
     for (int c = 0; c < ncol; ++c) h_part[c] = (int)(h_major[c] >> 4);
     cudaFree(major); cudaFree(major_s); cudaFree(ggid); cudaFree(ggid_s); cudaFree(dof); cudaFree(maxpart); cudaFree(idx0); cudaFree(idx1);
     cudaFree(idx2); cudaFree(owner); cudaFree(dof_s); cudaFree(maxpart_s);
@@ -273,13 +274,13 @@ int fb2_build_par_layer(fb2_space_s* s) {
   FB2_TRY(fb2_dalloc(&seq, (size_t)nseq + 1)); FB2_TRY(fb2_dalloc(&first, (size_t)n)); FB2_TRY(fb2_dalloc(&perm, (size_t)n));
   const i64 nmax = n > nseq ? n : nseq;
   FB2_TRY(fb2_dalloc(&flag, (size_t)nmax + 1)); FB2_TRY(fb2_dalloc(&rank, (size_t)nmax + 1));
-  if (nseq) FB2_CUDA(cudaMemcpy(seq, h_seq.data(), sizeof(int) * nseq, cudaMemcpyHostToDevice));
+  if (nseq) FB2_CUDA(fb2_memcpy(seq, h_seq.data(), sizeof(int) * nseq, cudaMemcpyHostToDevice));
   k_fill_int<<<GRID(n)>>>(n, first, INT_MAX);
   if (nseq) k_first_pos<<<GRID(nseq)>>>(nseq, seq, first);
   k_flag_first<<<GRID(nseq + 1)>>>(nseq, seq, first, flag);
   FB2_TRY(scan_excl(flag, rank, (i64)nseq + 1));
   int n_itf = 0;
-  FB2_CUDA(cudaMemcpy(&n_itf, rank + nseq, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&n_itf, rank + nseq, sizeof(int), cudaMemcpyDeviceToHost));
   s->n_interface = n_itf; s->n_interior = n - n_itf;
   if (nseq) k_perm_interface<<<GRID(nseq)>>>(nseq, seq, first, rank, (int)s->n_interior, perm);
   k_flag_interior<<<GRID(n + 1)>>>(n, first, flag);
@@ -294,8 +295,28 @@ int fb2_build_par_layer(fb2_space_s* s) {
   if (imp->n_pack) k_apply_perm_idx<<<GRID(imp->n_pack)>>>((int)imp->n_pack, perm, seq, imp->d_pack_idx, imp->d_weight);
   if (imp->n_unpack) k_apply_perm_idx<<<GRID(imp->n_unpack)>>>((int)imp->n_unpack, perm, seq + imp->n_pack, imp->d_unpack_idx, nullptr);
   FB2_CUDA(cudaGetLastError());
-  if (imp->n_pack) FB2_CUDA(cudaMemcpy(imp->h_pack_idx.data(), imp->d_pack_idx, sizeof(int) * imp->n_pack, cudaMemcpyDeviceToHost));
-  if (imp->n_unpack) FB2_CUDA(cudaMemcpy(imp->h_unpack_idx.data(), imp->d_unpack_idx, sizeof(int) * imp->n_unpack, cudaMemcpyDeviceToHost));
+  if (imp->n_pack) FB2_CUDA(fb2_memcpy(imp->h_pack_idx.data(), imp->d_pack_idx, sizeof(int) * imp->n_pack, cudaMemcpyDeviceToHost));
+  if (imp->n_unpack) FB2_CUDA(fb2_memcpy(imp->h_unpack_idx.data(), imp->d_unpack_idx, sizeof(int) * imp->n_unpack, cudaMemcpyDeviceToHost));
+  // Gather-add plan of stage 1 of comm(): a DOF shared by more than two parts is received from several neighbours, so
+  // unpack_idx holds it several times.  Group the receive-buffer positions by destination DOF (positions ascending =
+  // neighbour list order = the order mpi_context.f90:610-632 adds them in) -> one thread per DOF, no atomics, deterministic.
+  {
+    const int nu = (int)imp->n_unpack;
+    std::vector<int> pos(nu);
+    for (int i = 0; i < nu; ++i) pos[i] = i;
+    std::stable_sort(pos.begin(), pos.end(), [&](int a, int b) { return imp->h_unpack_idx[a] < imp->h_unpack_idx[b]; });
+    std::vector<int> dst, ptr;
+    for (int i = 0; i < nu; ++i)
+      if (i == 0 || imp->h_unpack_idx[pos[i]] != imp->h_unpack_idx[pos[i - 1]]) { dst.push_back(imp->h_unpack_idx[pos[i]]); ptr.push_back(i); }
+    ptr.push_back(nu);
+    imp->n_add_dst = (int)dst.size();
+    FB2_TRY(fb2_dalloc(&imp->d_add_dst, dst.size())); FB2_TRY(fb2_dalloc(&imp->d_add_ptr, ptr.size())); FB2_TRY(fb2_dalloc(&imp->d_add_pos, (size_t)nu));
+    if (nu) {
+      FB2_CUDA(fb2_memcpy(imp->d_add_dst, dst.data(), sizeof(int) * dst.size(), cudaMemcpyHostToDevice));
+      FB2_CUDA(fb2_memcpy(imp->d_add_pos, pos.data(), sizeof(int) * (size_t)nu, cudaMemcpyHostToDevice));
+    }
+    FB2_CUDA(fb2_memcpy(imp->d_add_ptr, ptr.data(), sizeof(int) * ptr.size(), cudaMemcpyHostToDevice));
+  }
   for (auto& v : imp->h_pack_idx) v += 1;
   for (auto& v : imp->h_unpack_idx) v += 1;
   const i64 nbuf = imp->n_pack > imp->n_unpack ? imp->n_pack : imp->n_unpack;
@@ -321,6 +342,6 @@ extern "C" int fb2_dof_import_get(fb2_space_t s, int32_t* list_rcv, int32_t* rcv
   for (int i = 0; i < imp->num_snd; ++i) list_snd[i] = imp->list_snd[i];
   for (int i = 0; i <= imp->num_snd; ++i) snd_ptrs[i] = imp->snd_ptrs[i] + 1;
   for (i64 i = 0; i < imp->n_pack; ++i) pack_idx[i] = imp->h_pack_idx[i];
-  if (weight) FB2_CUDA(cudaMemcpy(weight, imp->d_weight, sizeof(double) * (size_t)s->n_free, cudaMemcpyDeviceToHost));
+  if (weight) FB2_CUDA(fb2_memcpy(weight, imp->d_weight, sizeof(double) * (size_t)s->n_free, cudaMemcpyDeviceToHost));
   return 0;
 }

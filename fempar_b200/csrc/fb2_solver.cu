@@ -71,8 +71,8 @@ int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, dou
 // SpMV: warp per row, 4 independent 32-wide passes in flight per warp, coalesced val/ja streams
 // ------------------------------------------------------------------------------------------
 struct CgState {
-  double rz, App, rr, rz_new, tol, alpha, beta, err;
-  int iter, converged, done, maxit;
+  double rz, App, rr, rz_new, pp, tol, tol_extra, rtol, atol, alpha, beta, err, err_extra;   // rr, rz_new, pp adjacent (one reduction)
+  int iter, converged, done, maxit, crit;
 };
 
 template <bool FUSE_DOT>
@@ -217,7 +217,7 @@ extern "C" int fb2_vec_create_n(fb2_vector_t* out, int64_t n) {
   fb2_vector_s* v = new fb2_vector_s();
   v->n = n;
   FB2_TRY(fb2_dalloc(&v->d, (size_t)n));
-  FB2_CUDA(cudaMemset(v->d, 0, sizeof(double) * (size_t)(n ? n : 1)));
+  FB2_CUDA(cudaMemsetAsync(v->d, 0, sizeof(double) * (size_t)(n ? n : 1), fb2_stream()));
   *out = v;
   return 0;
 }
@@ -342,27 +342,47 @@ __global__ void __launch_bounds__(256) k_cg_update_xr(i64 n, CgState* st, const 
   if (st->done) return;
   const double App = st->App;
   const double alpha = (App != 0.0) ? st->rz / App : 0.0;   // cg.f90:195-199
-  double a_rr = 0.0, a_rz = 0.0;
+  const bool need_pp = st->crit >= FB2_STOP_DELTA_RHS;
+  double a_rr = 0.0, a_rz = 0.0, a_pp = 0.0;
   for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
-    x[i] += alpha * p[i];
+    const double pi = p[i];
+    x[i] += alpha * pi;
     double ri = r[i] - alpha * Ap[i];
     r[i] = ri;
     double wi = w ? w[i] : 1.0;
     a_rr += wi * ri * ri;
     a_rz += wi * ri * (dinv ? dinv[i] * ri : ri);
+    a_pp += wi * pi * pi;
   }
   double s1 = block_sum(a_rr, s_red);
   double s2 = block_sum(a_rz, s_red);
-  if (threadIdx.x == 0) { partials[blockIdx.x] = s1; partials[stride + blockIdx.x] = s2; }
+  double s3 = need_pp ? block_sum(a_pp, s_red) : 0.0;
+  if (threadIdx.x == 0) { partials[blockIdx.x] = s1; partials[stride + blockIdx.x] = s2; partials[2 * stride + blockIdx.x] = s3; }
 }
-// convergence bookkeeping: cg.f90:208-226 and update_convergence_data_and_evaluate_stopping_criteria :331-407
+// convergence bookkeeping: cg.f90:208-226 and update_convergence_data_and_evaluate_stopping_criteria :331-407 (all ten criteria)
 __global__ void k_cg_scalars(CgState* st, double* hist) {
   if (st->done) return;
   st->iter += 1;
-  double e = sqrt(st->rr);
+  const int crit = st->crit;
+  const double alpha = (st->App != 0.0) ? st->rz / st->App : 0.0;
+  st->alpha = alpha;
+  double e;
+  if (crit == FB2_STOP_RES_RES || crit == FB2_STOP_RES_RHS) e = sqrt(st->rr);                 // || r(i) ||
+  else if (crit == FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN || crit == FB2_STOP_RES_NRMGIVEN_RES_NRMGIVEN)
+    e = sqrt(st->rz);   // r_nrm_M as the reference passes it: still sqrt(<r,z>) of the PREVIOUS residual (cg.f90:208 vs :228-231)
+  else {
+    e = alpha * sqrt(st->pp);                                                                 // || dx(i) || = alpha ||p||
+    if (st->iter == 1 && (crit == FB2_STOP_DELTA_DELTA || crit == FB2_STOP_DELTA_DELTA_AND_RES_RES ||
+                          crit == FB2_STOP_DELTA_DELTA_AND_RES_RHS))
+      st->tol = st->rtol * e + st->atol;                                                      // cg.f90:349-357
+  }
   st->err = e;
   if (hist) hist[st->iter - 1] = e;
   bool conv = e <= st->tol;
+  if (conv && crit >= FB2_STOP_DELTA_RHS_AND_RES_RES) {                                       // 2nd criterion, cg.f90:391-403
+    st->err_extra = sqrt(st->rr);
+    conv = st->err_extra <= st->tol_extra;
+  }
   st->converged = conv ? 1 : 0;
   if (conv || st->iter >= st->maxit) { st->done = 1; return; }
   st->beta = st->rz_new / st->rz;
@@ -376,9 +396,10 @@ __global__ void __launch_bounds__(256) k_cg_update_p(i64 n, const CgState* st, c
   for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x)
     p[i] = (dinv ? dinv[i] * r[i] : r[i]) + beta * p[i];
 }
-__global__ void k_cg_init_state(CgState* st, double rz, double tol, int maxit) {
-  st->rz = rz; st->App = 0; st->rr = 0; st->rz_new = 0; st->tol = tol; st->alpha = 0; st->beta = 0; st->err = 0;
-  st->iter = 0; st->converged = 0; st->done = 0; st->maxit = maxit;
+__global__ void k_cg_init_state(CgState* st, double rz, double tol, double tol_extra, double rtol, double atol, int maxit, int crit) {
+  st->rz = rz; st->App = 0; st->rr = 0; st->rz_new = 0; st->pp = 0; st->tol = tol; st->tol_extra = tol_extra; st->rtol = rtol;
+  st->atol = atol; st->alpha = 0; st->beta = 0; st->err = 0; st->err_extra = 0;
+  st->iter = 0; st->converged = 0; st->done = 0; st->maxit = maxit; st->crit = crit;
 }
 
 struct CgWork {
@@ -430,8 +451,8 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
   }
   int g2 = reduce_grid(n);
   k_cg_update_xr<<<g2, 256, 0, s>>>(n, W.st, W.p, W.Ap, dinv, w, x, W.r, part, FB2_MAX_PARTIALS);
-  k_reduce_partials<<<1, 256, 0, s>>>(part, g2, FB2_MAX_PARTIALS, 2, &W.st->rr);   // rr, rz_new are adjacent
-  if (par) FB2_TRY(fb2_allreduce_sum(&W.st->rr, 2));
+  k_reduce_partials<<<1, 256, 0, s>>>(part, g2, FB2_MAX_PARTIALS, 3, &W.st->rr);   // rr, rz_new, pp are adjacent
+  if (par) FB2_TRY(fb2_allreduce_sum(&W.st->rr, 3));
   k_cg_scalars<<<1, 1, 0, s>>>(W.st, hist);
   k_cg_update_p<<<vec_grid(n), 256, 0, s>>>(n, W.st, W.r, dinv, W.p);
   FB2_CUDA(cudaGetLastError());
@@ -452,14 +473,31 @@ static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const d
   if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, dinv, W.r, n);
   else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
   double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 3;
-  FB2_TRY(fb2_dot_device(W.r, W.p, w, n, d_tmp));
-  FB2_TRY(fb2_dot_device(stop == FB2_STOP_RES_RHS ? b : W.r, stop == FB2_STOP_RES_RHS ? b : W.r, w, n, d_tmp + 1));
-  if (par) FB2_TRY(fb2_allreduce_sum(d_tmp, 2));
-  double h[2];
-  FB2_CUDA(cudaMemcpyAsync(h, d_tmp, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  FB2_TRY(fb2_dot_device(W.r, W.p, w, n, d_tmp));          // r_z
+  FB2_TRY(fb2_dot_device(W.r, W.r, w, n, d_tmp + 1));      // ||r(0)||^2
+  FB2_TRY(fb2_dot_device(b, b, w, n, d_tmp + 2));          // ||b||^2
+  if (stop == FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN) {        // |b|_inv(M): r = inv(M) b ; b.r   (cg.f90:144-154), Ap is free here
+    if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.Ap, dinv, b, n);
+    FB2_TRY(fb2_dot_device(b, dinv ? W.Ap : b, w, n, d_tmp + 3));
+  } else FB2_CUDA(cudaMemsetAsync(d_tmp + 3, 0, sizeof(double), s));
+  if (par) FB2_TRY(fb2_allreduce_sum(d_tmp, 4));
+  double h[4];
+  FB2_CUDA(cudaMemcpyAsync(h, d_tmp, 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
   FB2_CUDA(cudaStreamSynchronize(s));
-  double tol = rtol * sqrt(h[1]) + atol;   // init_convergence_data, cg.f90:279-321
-  k_cg_init_state<<<1, 1, 0, s>>>(W.st, h[0], tol, maxit);
+  // init_convergence_data, cg.f90:279-321
+  const double nr0 = sqrt(h[1]), nb = sqrt(h[2]);
+  double tol = 0.0, tol_extra = 0.0;
+  switch (stop) {
+    case FB2_STOP_DELTA_RHS: case FB2_STOP_RES_RHS: tol = rtol * nb + atol; break;
+    case FB2_STOP_DELTA_RHS_AND_RES_RHS: case FB2_STOP_DELTA_DELTA_AND_RES_RHS: tol = tol_extra = rtol * nb + atol; break;
+    case FB2_STOP_RES_RES: tol = rtol * nr0 + atol; break;
+    case FB2_STOP_DELTA_DELTA_AND_RES_RES: tol = tol_extra = rtol * nr0 + atol; break;
+    case FB2_STOP_DELTA_RHS_AND_RES_RES: tol = rtol * nb + atol; tol_extra = rtol * nr0 + atol; break;
+    case FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN: tol = rtol * sqrt(h[3]) + atol; break;
+    case FB2_STOP_RES_NRMGIVEN_RES_NRMGIVEN: tol = rtol * sqrt(h[0]) + atol; break;
+    default: break;   // delta_delta: set at the first iteration
+  }
+  k_cg_init_state<<<1, 1, 0, s>>>(W.st, h[0], tol, tol_extra, rtol, atol, maxit, stop);
   FB2_CUDA(cudaGetLastError());
   return 0;
 }
@@ -468,8 +506,8 @@ extern "C" int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, 
                              int* num_iterations, int* did_converge, double* error_estimate, double* history) {
   FB2_CHECK(A && b && x && prm, "null argument");
   FB2_CHECK(b->n == A->n && x->n == A->n && (!dinv || dinv->n == A->n), "size mismatch");
-  FB2_CHECK(prm->stopping_criterium == FB2_STOP_RES_RES || prm->stopping_criterium == FB2_STOP_RES_RHS,
-            "stopping criterium not supported by the device CG");
+  FB2_CHECK(prm->stopping_criterium >= FB2_STOP_RES_RES && prm->stopping_criterium <= FB2_STOP_DELTA_DELTA_AND_RES_RHS,
+            "unknown stopping criterium (cg_supports_stopping_criteria, cg.f90:240-255)");
   const int maxit = prm->max_num_iterations;
   const bool par = A->s->imp && fb2_comm_active();
   const double* w = par ? fb2_import_weight(A->s->imp) : nullptr;
@@ -503,7 +541,7 @@ extern "C" int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, 
   *num_iterations = h.iter;
   *did_converge = h.converged;
   *error_estimate = h.err;
-  if (track && h.iter > 0) FB2_CUDA(cudaMemcpy(history, g_work.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
+  if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, g_work.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
   return 0;
 }
 

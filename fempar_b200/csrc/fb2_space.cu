@@ -453,9 +453,9 @@ extern "C" int fb2_fe_space_create(fb2_space_t* out, const int num_cells[3], con
   FB2_TRY(exclusive_scan(cnt_free, base_free, (i64)nc + 1));
   FB2_TRY(exclusive_scan(cnt_dir, base_dir, (i64)nc + 1));
   int h_tot[3];
-  FB2_CUDA(cudaMemcpy(&h_tot[0], base_free + m.n_local, sizeof(int), cudaMemcpyDeviceToHost));
-  FB2_CUDA(cudaMemcpy(&h_tot[1], base_free + nc, sizeof(int), cudaMemcpyDeviceToHost));
-  FB2_CUDA(cudaMemcpy(&h_tot[2], base_dir + nc, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&h_tot[0], base_free + m.n_local, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&h_tot[1], base_free + nc, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&h_tot[2], base_dir + nc, sizeof(int), cudaMemcpyDeviceToHost));
   s->n_free = h_tot[0]; s->n_free_ghost = h_tot[1] - h_tot[0]; s->n_dirichlet = h_tot[2];
   s->n_interior = s->n_free; s->n_interface = 0;
   i64 total = (i64)nc * s->rt.ndofs;
@@ -468,13 +468,13 @@ extern "C" int fb2_fe_space_create(fb2_space_t* out, const int num_cells[3], con
   // 3. reference tables to the device
   auto up = [&](double** d, const std::vector<double>& h) -> int {
     FB2_TRY(fb2_dalloc(d, h.size()));
-    FB2_CUDA(cudaMemcpy(*d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+    FB2_CUDA(fb2_memcpy(*d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
     return 0;
   };
   FB2_TRY(up(&s->d_qw, s->h_qw)); FB2_TRY(up(&s->d_phi, s->h_phi)); FB2_TRY(up(&s->d_dphi, s->h_dphi));
   FB2_TRY(up(&s->d_gphi, s->h_gphi)); FB2_TRY(up(&s->d_gdphi, s->h_gdphi));
   FB2_TRY(fb2_dalloc(&s->d_fixed, (size_t)s->n_dirichlet));
-  FB2_CUDA(cudaMemset(s->d_fixed, 0, sizeof(double) * (s->n_dirichlet ? s->n_dirichlet : 1)));
+  FB2_CUDA(cudaMemsetAsync(s->d_fixed, 0, sizeof(double) * (s->n_dirichlet ? s->n_dirichlet : 1), fb2_stream()));
   // 4. par layer: interface DOFs, dof_import, interior-then-interface renumbering
   if (m.par) FB2_TRY(fb2_build_par_layer(s));
   // 5. lattice maps for the graph builder
@@ -498,14 +498,14 @@ extern "C" int fb2_fe_space_get_sizes(fb2_space_t s, int64_t sizes[8]) {
   return 0;
 }
 extern "C" int fb2_fe_space_get_lst_dofs_gids(fb2_space_t s, int32_t* host_out) {
-  FB2_CUDA(cudaMemcpy(host_out, s->d_gids, sizeof(int) * (size_t)s->m.n_cells * s->rt.ndofs, cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(host_out, s->d_gids, sizeof(int) * (size_t)s->m.n_cells * s->rt.ndofs, cudaMemcpyDeviceToHost));
   return 0;
 }
 extern "C" int fb2_fe_space_get_cells_gids(fb2_space_t s, int64_t* gid_out, int32_t* part_out) {
   // uniform_hex_mesh_generator.f90:468-489 (closed form; tiny, evaluated on the host from the device permutation)
   const MeshDesc& m = s->m;
   std::vector<int> perm(m.n_cells);
-  if (s->d_perm) FB2_CUDA(cudaMemcpy(perm.data(), s->d_perm, sizeof(int) * m.n_cells, cudaMemcpyDeviceToHost));
+  if (s->d_perm) FB2_CUDA(fb2_memcpy(perm.data(), s->d_perm, sizeof(int) * m.n_cells, cudaMemcpyDeviceToHost));
   else for (int i = 0; i < m.n_cells; ++i) perm[i] = i;
   for (int lex = 0; lex < m.n_cells; ++lex) {
     int ijk[3] = {lex % m.ntot[0], (lex / m.ntot[0]) % m.ntot[1], lex / (m.ntot[0] * m.ntot[1])};
@@ -522,11 +522,11 @@ extern "C" int fb2_fe_space_get_cells_gids(fb2_space_t s, int64_t* gid_out, int3
   return 0;
 }
 extern "C" int fb2_fe_space_get_fixed_values(fb2_space_t s, double* host_out) {
-  FB2_CUDA(cudaMemcpy(host_out, s->d_fixed, sizeof(double) * (size_t)s->n_dirichlet, cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(host_out, s->d_fixed, sizeof(double) * (size_t)s->n_dirichlet, cudaMemcpyDeviceToHost));
   return 0;
 }
 extern "C" int fb2_fe_space_set_fixed_values(fb2_space_t s, const double* host_in) {
-  FB2_CUDA(cudaMemcpy(s->d_fixed, host_in, sizeof(double) * (size_t)s->n_dirichlet, cudaMemcpyHostToDevice));
+  FB2_CUDA(fb2_memcpy(s->d_fixed, host_in, sizeof(double) * (size_t)s->n_dirichlet, cudaMemcpyHostToDevice));
   return 0;
 }
 
@@ -630,7 +630,7 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
                                                               A->sym, s->d_dof_node, s->d_node_dof, cnt);
   FB2_CUDA(cudaGetLastError());
   FB2_TRY(exclusive_scan(cnt, A->d_irp, n + 1));
-  FB2_CUDA(cudaMemcpy(&A->nnz, A->d_irp + n, sizeof(i64), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&A->nnz, A->d_irp + n, sizeof(i64), cudaMemcpyDeviceToHost));
   cudaFree(cnt);
   FB2_TRY(fb2_dalloc(&A->d_ja, (size_t)A->nnz + 16));    // +16: TMA bulk copies read whole 16-byte groups
   FB2_TRY(fb2_dalloc(&A->d_val, (size_t)A->nnz + 16));
@@ -672,18 +672,18 @@ extern "C" int fb2_csr_get_sizes(fb2_matrix_t A, int64_t* num_rows, int64_t* nnz
 }
 extern "C" int fb2_csr_get_pattern(fb2_matrix_t A, int64_t* irp_host, int32_t* ja_host) {
   if (irp_host) {
-    FB2_CUDA(cudaMemcpy(irp_host, A->d_irp, sizeof(i64) * (size_t)(A->n + 1), cudaMemcpyDeviceToHost));
+    FB2_CUDA(fb2_memcpy(irp_host, A->d_irp, sizeof(i64) * (size_t)(A->n + 1), cudaMemcpyDeviceToHost));
     for (i64 i = 0; i <= A->n; ++i) irp_host[i] += 1;  // Fortran irp(1) = 1
   }
-  if (ja_host) FB2_CUDA(cudaMemcpy(ja_host, A->d_ja, sizeof(int) * (size_t)A->nnz, cudaMemcpyDeviceToHost));
+  if (ja_host) FB2_CUDA(fb2_memcpy(ja_host, A->d_ja, sizeof(int) * (size_t)A->nnz, cudaMemcpyDeviceToHost));
   return 0;
 }
 extern "C" int fb2_csr_get_values(fb2_matrix_t A, double* val_host) {
   FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
-  FB2_CUDA(cudaMemcpy(val_host, A->d_val, sizeof(double) * (size_t)A->nnz, cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(val_host, A->d_val, sizeof(double) * (size_t)A->nnz, cudaMemcpyDeviceToHost));
   return 0;
 }
 extern "C" int fb2_csr_set_values(fb2_matrix_t A, const double* val_host) {
-  FB2_CUDA(cudaMemcpy(A->d_val, val_host, sizeof(double) * (size_t)A->nnz, cudaMemcpyHostToDevice));
+  FB2_CUDA(fb2_memcpy(A->d_val, val_host, sizeof(double) * (size_t)A->nnz, cudaMemcpyHostToDevice));
   return 0;
 }

@@ -207,8 +207,8 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
     FB2_CUDA(cudaStreamSynchronize(st));
     cudaFree(tmp);
   }
-  FB2_CUDA(cudaMemcpy(&total, off + nfixed, sizeof(int), cudaMemcpyDeviceToHost));
-  FB2_CUDA(cudaMemcpy(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&total, off + nfixed, sizeof(int), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost));
   FB2_CHECK(h_flag == 0, "a pair of rows exceeds the SpMV stage buffer: use fb2_set_spmv_variant(1)");
   FB2_TRY(fb2_dalloc(&A->d_tile_row, (size_t)total)); FB2_TRY(fb2_dalloc(&A->d_tile_nrows, (size_t)total));
   k_tile_fill<<<(unsigned)((nfixed + 255) / 256), 256, 0, st>>>(A->n, A->d_irp, R, cap, nfixed, off, A->d_tile_row, A->d_tile_nrows);

@@ -45,8 +45,20 @@ enum {
 };
 /* scatter variants of the assembly (north_star: atomic vs conflict-free, chosen by ncu) */
 enum { FB2_SCATTER_ATOMIC = 0, FB2_SCATTER_COLORED = 1 };
-/* iterative_solver_parameters.f90:76-83 stopping criteria supported by the CG path */
-enum { FB2_STOP_RES_RES = 0, FB2_STOP_RES_RHS = 1 };
+/* iterative_solver_parameters.f90:37-46 stopping criteria; the CG path supports all ten (cg.f90:240-255).
+ * Order: residual-based, preconditioned-norm-based, increment-based, then the AND combinations. */
+enum {
+  FB2_STOP_RES_RES = 0,                    /* ||r(i)||  <= rtol*||r(0)|| + atol (CG default) */
+  FB2_STOP_RES_RHS = 1,                    /* ||r(i)||  <= rtol*||b|| + atol */
+  FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN = 2,  /* ||r(i)||g <= rtol*||b||g + atol, g = inv(M)-norm */
+  FB2_STOP_RES_NRMGIVEN_RES_NRMGIVEN = 3,  /* ||r(i)||g <= rtol*||r(0)||g + atol */
+  FB2_STOP_DELTA_RHS = 4,                  /* ||dx(i)|| <= rtol*||b|| + atol */
+  FB2_STOP_DELTA_DELTA = 5,                /* ||dx(i)|| <= rtol*||dx(1)|| + atol */
+  FB2_STOP_DELTA_RHS_AND_RES_RES = 6,
+  FB2_STOP_DELTA_RHS_AND_RES_RHS = 7,
+  FB2_STOP_DELTA_DELTA_AND_RES_RES = 8,
+  FB2_STOP_DELTA_DELTA_AND_RES_RHS = 9
+};
 
 /* ILS_* parameter-list keys (iterative_solver_parameters.f90:167-183) */
 typedef struct {

@@ -923,8 +923,10 @@ struct Space {
 
   static double dot(const double* a, const double* b, int n) { double s = 0; for (int i = 0; i < n; ++i) s += a[i] * b[i]; return s; }
 
-  // cg_solve_body  LinearAlgebra/IterativeLinearSolver/cg.f90:101-238; stopping criteria :279-407
-  //  stop: 0 = res_res (default for CG), 1 = res_rhs
+  // cg_solve_body  LinearAlgebra/IterativeLinearSolver/cg.f90:101-238; init_convergence_data :279-321;
+  // update_convergence_data_and_evaluate_stopping_criteria :323-407.  stop (iterative_solver_parameters.f90:37-46):
+  //  0 res_res (CG default)  1 res_rhs  2 res_nrmgiven_rhs_nrmgiven  3 res_nrmgiven_res_nrmgiven  4 delta_rhs  5 delta_delta
+  //  6 delta_rhs_and_res_res  7 delta_rhs_and_res_rhs  8 delta_delta_and_res_res  9 delta_delta_and_res_rhs
   int cg(int prec /*0 identity, 1 jacobi*/, double rtol, double atol, int maxit, int stop, const double* b, double* x,
          int* iters, int* converged, double* err, double* hist, double* t_spmv_acc) {
     const int n = n_free;
@@ -933,13 +935,28 @@ struct Space {
       if (prec == 1) for (int i = 0; i < n; ++i) out[i] = dinv[i] * in[i];
       else std::copy(in, in + n, out);
     };
+    auto nrm2 = [&](const double* v) { return std::sqrt(dot(v, v, n)); };
     std::fill(x, x + n, 0.0);                       // x <- initial_solution (zero)
+    double b_nrm_M = 0.0;                           // |b|_inv(M), cg.f90:144-154
+    if (stop == 2) { applyM(b, r.data()); b_nrm_M = std::sqrt(dot(b, r.data(), n)); }
     spmv(x, r.data());                              // r = A x
     for (int i = 0; i < n; ++i) r[i] = b[i] - r[i]; // r = b - r
     applyM(r.data(), z.data());
     double r_z = dot(r.data(), z.data(), n);
+    double r_nrm_M = std::sqrt(r_z);
     p = z;
-    double tol = (stop == 1 ? rtol * std::sqrt(dot(b, b, n)) : rtol * std::sqrt(dot(r.data(), r.data(), n))) + atol;
+    // init_convergence_data
+    double tol = 0.0, tol_extra = 0.0;
+    switch (stop) {
+      case 4: case 1: tol = rtol * nrm2(b) + atol; break;
+      case 7: case 9: tol = tol_extra = rtol * nrm2(b) + atol; break;
+      case 0: tol = rtol * nrm2(r.data()) + atol; break;
+      case 8: tol = tol_extra = rtol * nrm2(r.data()) + atol; break;
+      case 6: tol = rtol * nrm2(b) + atol; tol_extra = rtol * nrm2(r.data()) + atol; break;
+      case 2: tol = rtol * b_nrm_M + atol; break;
+      case 3: tol = rtol * r_nrm_M + atol; break;
+      default: break;
+    }
     int it = 0; bool conv = false; double e = 0;
     for (;;) {
       ++it;
@@ -948,14 +965,24 @@ struct Space {
       double alpha = (App != 0.0) ? r_z / App : 0.0;
       for (int i = 0; i < n; ++i) x[i] += alpha * p[i];
       for (int i = 0; i < n; ++i) r[i] -= alpha * Ap[i];
-      e = std::sqrt(dot(r.data(), r.data(), n));
+      // update_convergence_data_and_evaluate_stopping_criteria(r, r_nrm_M, alpha, p)
+      const bool delta = stop >= 4;
+      if (it == 1 && delta) {
+        e = alpha * nrm2(p.data());
+        if (stop == 5 || stop == 8 || stop == 9) tol = rtol * e + atol;
+      }
+      if (stop == 0 || stop == 1) e = nrm2(r.data());
+      else if (delta) { if (it != 1) e = alpha * nrm2(p.data()); }
+      else e = r_nrm_M;                              // NOTE: still the M-norm of the previous residual (updated below, :228-231)
       if (hist) hist[it - 1] = e;
       conv = e <= tol;
+      if (stop >= 6 && conv) conv = nrm2(r.data()) <= tol_extra;
       if (conv || it >= maxit) break;
       applyM(r.data(), z.data());
       double beta = 1.0 / r_z;
       r_z = dot(r.data(), z.data(), n);
       beta *= r_z;
+      r_nrm_M = std::sqrt(r_z);
       for (int i = 0; i < n; ++i) p[i] = z[i] + beta * p[i];
     }
     *iters = it; *converged = conv ? 1 : 0; *err = e;

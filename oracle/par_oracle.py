@@ -68,15 +68,33 @@ class ParOracle:
         self.dinv = [1.0 / v for v in self.comm(d)]
         return self.dinv
 
-    def cg(self, prec=1, rtol=1e-6, atol=0.0, maxit=1000):
+    def cg(self, prec=1, rtol=1e-6, atol=0.0, maxit=1000, stop=0):
+        """cg.f90:101-238 on par_scalar_array_t; `stop` numbering as in fempar_oracle.cpp (cg.f90:279-407)."""
         b = self.b
         M = (lambda r: [d * v for d, v in zip(self.dinv, r)]) if prec == 1 else (lambda r: [v.copy() for v in r])
+        nrm2 = lambda v: np.sqrt(self.dot(v, v))
         x = [np.zeros_like(v) for v in b]
+        b_nrm_M = np.sqrt(self.dot(b, M(b))) if stop == 2 else 0.0
         r = [bv - av for bv, av in zip(b, self.spmv(x))]
         z = M(r)
         r_z = self.dot(r, z)
+        r_nrm_M = np.sqrt(r_z)
         p = [v.copy() for v in z]
-        tol = rtol * np.sqrt(self.dot(r, r)) + atol
+        tol = tol_extra = 0.0
+        if stop in (4, 1):
+            tol = rtol * nrm2(b) + atol
+        elif stop in (7, 9):
+            tol = tol_extra = rtol * nrm2(b) + atol
+        elif stop == 0:
+            tol = rtol * nrm2(r) + atol
+        elif stop == 8:
+            tol = tol_extra = rtol * nrm2(r) + atol
+        elif stop == 6:
+            tol, tol_extra = rtol * nrm2(b) + atol, rtol * nrm2(r) + atol
+        elif stop == 2:
+            tol = rtol * b_nrm_M + atol
+        elif stop == 3:
+            tol = rtol * r_nrm_M + atol
         it, conv, e, hist = 0, False, 0.0, []
         while True:
             it += 1
@@ -86,15 +104,29 @@ class ParOracle:
             for xv, rv, pv, av in zip(x, r, p, Ap):
                 xv += alpha * pv
                 rv -= alpha * av
-            e = np.sqrt(self.dot(r, r))
+            delta = stop >= 4
+            if it == 1 and delta:
+                e = alpha * nrm2(p)
+                if stop in (5, 8, 9):
+                    tol = rtol * e + atol
+            if stop in (0, 1):
+                e = nrm2(r)
+            elif delta:
+                if it != 1:
+                    e = alpha * nrm2(p)
+            else:
+                e = r_nrm_M
             hist.append(e)
             conv = e <= tol
+            if stop >= 6 and conv:
+                conv = nrm2(r) <= tol_extra
             if conv or it >= maxit:
                 break
             z = M(r)
             beta = 1.0 / r_z
             r_z = self.dot(r, z)
             beta *= r_z
+            r_nrm_M = np.sqrt(r_z)
             p = [zv + beta * pv for zv, pv in zip(z, p)]
         return dict(x=x, iters=it, converged=bool(conv), err=float(e), history=np.array(hist))
 

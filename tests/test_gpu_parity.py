@@ -230,3 +230,34 @@ def test_tutorial_01_config1_end_to_end(fb2):
     h1, l2 = s.error_norms(x, FUNC_SHARP_WAVE, WAVE)
     oh1, ol2 = o.errors(r["x"], FUNC_SHARP_WAVE, WAVE)
     assert abs(h1 - oh1) <= 1e-9 * oh1 and abs(l2 - ol2) <= 1e-9 * ol2
+
+
+STOPS = ["RES_RES", "RES_RHS", "RES_NRMGIVEN_RHS_NRMGIVEN", "RES_NRMGIVEN_RES_NRMGIVEN", "DELTA_RHS", "DELTA_DELTA",
+         "DELTA_RHS_AND_RES_RES", "DELTA_RHS_AND_RES_RHS", "DELTA_DELTA_AND_RES_RES", "DELTA_DELTA_AND_RES_RHS"]
+
+
+@pytest.mark.parametrize("stop", range(10), ids=STOPS)
+@pytest.mark.parametrize("prec", ["jacobi", "identity"])
+def test_pcg_all_ten_stopping_criteria(fb2, stop, prec):
+    """cg_supports_stopping_criteria (cg.f90:240-255): every criterion stops at the oracle's iteration (+-1) with the
+    oracle's error estimate; init_convergence_data / update_convergence_data (cg.f90:279-407)."""
+    N, p = (6, 6, 6), 2
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    M = None
+    if prec == "jacobi":
+        M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+        o.jacobi_setup()
+    ils = fb2.IterativeLinearSolver()
+    ils.set_parameters_from_pl({fb2.ILS_TYPE: "CG", fb2.ILS_RTOL: 1e-8, fb2.ILS_MAX_NUM_ITERATIONS: 2000,
+                                fb2.ILS_STOPPING_CRITERIUM: STOPS[stop], fb2.ILS_TRACK_CONVERGENCE_HISTORY: True})
+    ils.set_operators(op.get_tangent(), M)
+    x = s.create_dof_values()
+    ils.apply(op.get_translation(), x)
+    r = o.cg(prec=1 if M else 0, rtol=1e-8, maxit=2000, stop=stop, history=True)
+    assert ils.converged() and r["converged"]
+    assert abs(ils.get_num_iterations() - r["iters"]) <= 1
+    k = min(ils.get_num_iterations(), r["iters"]) // 2
+    assert np.allclose(ils.history[:k], r["history"][:k], rtol=1e-6)
+    assert np.max(np.abs(x.get_entries() - r["x"])) <= 1e-6 * np.max(np.abs(r["x"]))

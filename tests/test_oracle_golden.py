@@ -82,3 +82,17 @@ def test_vector_laplacian_keeps_explicit_zeros():
     s.assemble(KIND_VECTOR_LAPLACIAN, FUNC_LINEAR, route=0)
     assert s.num_free == 3 * 8 and s.nnz == 24 * 24
     assert np.count_nonzero(s.val() == 0.0) >= 24 * 16
+
+
+def test_oracle_cg_stopping_criteria_are_consistent():
+    """The ten criteria of cg.f90:279-407 on one system: every run converges, the residual-type ones coincide where their
+    right-hand sides coincide (x0 = 0 => r(0) = b), and the AND-combinations never stop before their first criterion."""
+    from oracle.oracle import OracleSpace, KIND_POISSON, FUNC_SHARP_WAVE
+    s = OracleSpace([5, 5, 5], order=2)
+    s.assemble(KIND_POISSON, FUNC_SHARP_WAVE, [200.0, 0.7, -0.05, -0.05, -0.05], route=1)
+    s.jacobi_setup()
+    it = [s.cg(prec=1, rtol=1e-8, maxit=2000, stop=k) for k in range(10)]
+    assert all(r["converged"] for r in it)
+    n = [r["iters"] for r in it]
+    assert n[0] == n[1] and n[2] == n[3] and n[6] == n[7] and n[8] == n[9]
+    assert n[6] >= n[4] and n[8] >= n[5]
