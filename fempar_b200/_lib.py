@@ -36,6 +36,7 @@ _SIGS = {
     "fb2_fe_space_get_lst_dofs_gids": [_VP, _VP],
     "fb2_fe_space_get_cells_gids": [_VP, _VP, _VP],
     "fb2_fe_space_interpolate_dirichlet": [_VP, C.c_int, _VP],
+    "fb2_fe_space_interpolate": [_VP, C.c_int, _VP, _VP],
     "fb2_fe_space_get_fixed_values": [_VP, _VP],
     "fb2_fe_space_set_fixed_values": [_VP, _VP],
     "fb2_dof_import_get_sizes": [_VP, _VP],

@@ -257,6 +257,38 @@ extern "C" int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const
   return 0;
 }
 
+// nodal interpolation of an analytic scalar function into the FREE DOF values of an fe_function
+// (serial_fe_space_interpolate_scalar_function, sbm_serial_fe_space.i90:734-819); every component gets u
+__global__ void k_interp_free(CellGeom g, int p, int nn, int nd, int n_local, const int* __restrict__ lex_of,
+                              const int* __restrict__ gids, i64 n_free, FuncPrm fn, double* x_out) {
+  i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (i64)n_local * nd) return;
+  int c = (int)(tid / nd), l = (int)(tid % nd);
+  int gid = gids[tid];
+  if (gid <= 0 || gid > n_free) return;
+  int lex = lex_of ? lex_of[c] : c;
+  int ijk[3] = {lex % g.ntot[0], (lex / g.ntot[0]) % g.ntot[1], lex / (g.ntot[0] * g.ntot[1])};
+  int node = l % nn, n1 = p + 1;
+  int in[3] = {node % n1, (node / n1) % n1, node / (n1 * n1)};
+  double x[3];
+  for (int k = 0; k < 3; ++k) {
+    double x0 = (double)(g.first[k] + ijk[k]) / (double)g.N[k], x1 = (double)(g.first[k] + ijk[k] + 1) / (double)g.N[k];
+    double sfrac = (double)in[k] / (double)p;
+    x[k] = (1.0 - sfrac) * x0 + sfrac * x1;
+  }
+  x_out[gid - 1] = func_u(fn, x);   // every cell sharing the node writes the same value
+}
+extern "C" int fb2_fe_space_interpolate(fb2_space_t s, int func, const double* func_params, fb2_vector_t x) {
+  FB2_CHECK(s && x && x->n == s->n_free, "fb2_fe_space_interpolate: size mismatch");
+  i64 total = (i64)s->m.n_local * s->rt.ndofs;
+  if (total > 0)
+    k_interp_free<<<(unsigned)((total + 255) / 256), 256, 0, fb2_stream()>>>(make_geom(s), s->rt.p, s->rt.nnode, s->rt.ndofs,
+                                                                            s->m.n_local, s->d_lex_of, s->d_gids, s->n_free,
+                                                                            make_func(func, func_params), x->d);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // ------------------------------------------------------------------------------------------
 // error norms (tutorial_01_..._modules.f90:611-661; ErrorNorms/): warp per cell, lanes over q
 // ------------------------------------------------------------------------------------------

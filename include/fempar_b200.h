@@ -96,6 +96,9 @@ int fb2_fe_space_get_lst_dofs_gids(fb2_space_t s, int32_t* host_out);
 int fb2_fe_space_get_cells_gids(fb2_space_t s, int64_t* host_out, int32_t* host_mypart_out);
 /* fixed_dof_values(1..num_dirichlet) = g(x_node): interpolate_dirichlet_values, sbm_serial_fe_space.i90:997-1176 */
 int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const double* func_params);
+/* free DOF values of an fe_function by nodal interpolation of the analytic function:
+ * serial_fe_space_interpolate_scalar_function, sbm_serial_fe_space.i90:734-819 (x has num_free_dofs entries) */
+int fb2_fe_space_interpolate(fb2_space_t s, int func, const double* func_params, fb2_vector_t x);
 int fb2_fe_space_get_fixed_values(fb2_space_t s, double* host_out);
 int fb2_fe_space_set_fixed_values(fb2_space_t s, const double* host_in);
 
