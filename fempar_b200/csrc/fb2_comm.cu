@@ -82,8 +82,7 @@ __global__ void k_unpack_add(double* __restrict__ x, int ndst, const int* __rest
 
 // one neighbours exchange.  forward: pack_idx -> snd neighbours, unpack into unpack_idx (add or overwrite);
 // reverse: roles of the two lists swapped (stage 2 of comm()).
-static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add) {
-  cudaStream_t s = fb2_stream();
+static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add, cudaStream_t s) {
   const std::vector<int>& sl = reverse ? imp->list_rcv : imp->list_snd;
   const std::vector<int>& sp = reverse ? imp->rcv_ptrs : imp->snd_ptrs;
   const std::vector<int>& rl = reverse ? imp->list_snd : imp->list_rcv;
@@ -110,10 +109,11 @@ static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add) 
 // par_scalar_array_comm (par_scalar_array.f90:498-533):
 //  stage 1: non-owners send their partial sums, the owner receives and adds   (rcv side = owner)
 //  stage 2: the owner sends the total, non-owners receive and overwrite
-int fb2_import_exchange(fb2_import_s* imp, double* d_vec) {
+int fb2_import_exchange_on(fb2_import_s* imp, double* d_vec, cudaStream_t stream) {
   if (!g_comm || !imp) return 0;
-  FB2_TRY(exchange_stage(imp, d_vec, false, true));
-  FB2_TRY(exchange_stage(imp, d_vec, true, false));
+  FB2_TRY(exchange_stage(imp, d_vec, false, true, stream));
+  FB2_TRY(exchange_stage(imp, d_vec, true, false, stream));
   return 0;
 }
+int fb2_import_exchange(fb2_import_s* imp, double* d_vec) { return fb2_import_exchange_on(imp, d_vec, fb2_stream()); }
 

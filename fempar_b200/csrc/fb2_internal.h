@@ -32,6 +32,7 @@ void fb2_set_error(const char* fmt, ...);
   } while (0)
 
 cudaStream_t fb2_stream();
+cudaStream_t fb2_comm_stream();   // high-priority stream of the overlapped halo exchange
 int fb2_num_sms();
 void fb2_record_phase(const char* name, double ms);
 
@@ -116,6 +117,7 @@ struct fb2_matrix_s {
   i64* d_tile_row = nullptr;              // first row of every tile
   unsigned char* d_tile_nrows = nullptr;  // rows in the tile (<= spmv_R)
   size_t spmv_smem = 0;
+  i64 spmv_t_itf = -1, spmv_row_itf = -1;   // interface split of the tile table (par overlap)
 };
 
 struct fb2_vector_s {
@@ -127,10 +129,17 @@ struct fb2_vector_s {
 // reductions
 int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, double* d_result /*device*/);
 double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x 4
-#define FB2_MAX_PARTIALS 4096
+#define FB2_MAX_PARTIALS 65536
 
 int fb2_build_scatter_map(fb2_matrix_s* A);
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
+int fb2_spmv_prepare(fb2_matrix_s* A);
+// tiles [t0, t1) only; chunk = 0: persistent CTAs striding over the range, chunk > 0: one CTA per `chunk` consecutive tiles
+// (short-lived CTAs, so that a higher-priority stream gets SM resources while the launch is running)
+int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, i64 t0, i64 t1,
+                          int chunk, double* partials, int* grid_out);
+// first tile holding an interface row (rows >= n_interior) and its first row
+int fb2_spmv_interface_split(fb2_matrix_s* A, i64 n_interior, i64* t_itf, i64* row_itf);
 
 // comm layer: dof_import_t on the device (dof_import.f90:49-90)
 struct fb2_import_s {
@@ -150,6 +159,7 @@ int fb2_comm_nranks();
 int fb2_comm_rank();
 int fb2_allreduce_sum(double* d_buf, int count);           // in place, device buffer
 int fb2_import_exchange(fb2_import_s* imp, double* d_vec); // par_scalar_array%comm()
+int fb2_import_exchange_on(fb2_import_s* imp, double* d_vec, cudaStream_t stream);
 const double* fb2_import_weight(fb2_import_s* imp);
 void fb2_import_destroy(fb2_import_s* imp);
 int fb2_build_par_layer(fb2_space_s* s);                   // fb2_par.cu

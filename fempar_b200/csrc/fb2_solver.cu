@@ -3,6 +3,7 @@
 // (dot/axpby/nrm2/copy/scal/entrywise_*), par_scalar_array.f90:303-350 (weighted dot + all-reduce),
 // jacobi_preconditioner.f90:356-412, cg.f90:101-238,279-407.
 #include <math.h>
+#include <stdlib.h>
 #include "fb2_internal.h"
 
 // ------------------------------------------------------------------------------------------
@@ -132,6 +133,10 @@ __global__ void k_spmv_sym(i64 n, const i64* __restrict__ irp, const int* __rest
 }
 
 static int g_spmv_variant = 0;   // 0: TMA-streamed tiles (fb2_spmv.cu), 1: warp-per-row
+// par apply: overlap the halo exchange with the interior rows (FB2_PAR_OVERLAP=0 restores the sequential order);
+// interior tiles per short-lived CTA (FB2_PAR_CHUNK)
+static int g_par_overlap = getenv("FB2_PAR_OVERLAP") ? atoi(getenv("FB2_PAR_OVERLAP")) : 1;
+static int g_par_chunk = getenv("FB2_PAR_CHUNK") ? atoi(getenv("FB2_PAR_CHUNK")) : 64;
 extern "C" int fb2_set_spmv_variant(int v) { g_spmv_variant = v; return 0; }
 
 static int spmv_grid(i64 n, int warps_per_block) {
@@ -442,6 +447,33 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
     FB2_TRY(spmv_local(A, W.p, W.Ap, true, W.st, &g));                       // Ap = A p, partial <Ap,p> fused
     if (ev_spmv1) cudaEventRecord(ev_spmv1, s);
     k_reduce_partials<<<1, 256, 0, s>>>(part, g, 0, 1, &W.st->App);
+  } else if (par && !A->sym && g_spmv_variant == 0 && g_par_overlap) {
+    // Overlapped par apply (par_sparse_matrix.f90:739-762): interface rows are numbered last, so
+    //   (1) the tiles holding interface rows run first,
+    //   (2) their halo exchange (pack / NCCL send-recv / gather-add / owner broadcast) runs on the high-priority comm stream
+    //   (3) while the interior tiles run as short-lived CTAs on the compute stream with <Ap,p> fused (weights are 1 there),
+    //   (4) then the weighted <Ap,p> of the interface rows is added and the partials are summed in a fixed order.
+    i64 t_itf = 0, row_itf = 0;
+    FB2_TRY(fb2_spmv_interface_split(A, A->s->n_interior, &t_itf, &row_itf));
+    static cudaEvent_t ev_itf = nullptr, ev_halo = nullptr;
+    if (!ev_itf) { cudaEventCreateWithFlags(&ev_itf, cudaEventDisableTiming); cudaEventCreateWithFlags(&ev_halo, cudaEventDisableTiming); }
+    cudaStream_t cs = fb2_comm_stream();
+    FB2_TRY(fb2_spmv_stream_range(A, W.p, W.Ap, false, &W.st->done, t_itf, A->spmv_ntiles, 0, nullptr, nullptr));
+    FB2_CUDA(cudaEventRecord(ev_itf, s));
+    FB2_CUDA(cudaStreamWaitEvent(cs, ev_itf, 0));
+    FB2_TRY(fb2_import_exchange_on(A->s->imp, W.Ap, cs));
+    FB2_CUDA(cudaEventRecord(ev_halo, cs));
+    FB2_TRY(fb2_spmv_stream_range(A, W.p, W.Ap, true, &W.st->done, 0, t_itf, g_par_chunk, part, &g));
+    FB2_CUDA(cudaStreamWaitEvent(s, ev_halo, 0));
+    if (ev_spmv1) cudaEventRecord(ev_spmv1, s);
+    int gd = 0;
+    if (row_itf < n) {
+      gd = reduce_grid(n - row_itf);
+      if (gd > 64) gd = 64;
+      k_dot<<<gd, 256, 0, s>>>(W.Ap + row_itf, W.p + row_itf, w + row_itf, n - row_itf, part + g);
+    }
+    k_reduce_partials<<<1, 1024, 0, s>>>(part, g + gd, 0, 1, &W.st->App);
+    FB2_TRY(fb2_allreduce_sum(&W.st->App, 1));
   } else {
     FB2_TRY(spmv_local(A, W.p, W.Ap, false, A->sym ? nullptr : W.st, &g));
     if (par) FB2_TRY(fb2_import_exchange(A->s->imp, W.Ap));                  // par_sparse_matrix.f90:757-758

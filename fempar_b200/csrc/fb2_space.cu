@@ -30,6 +30,8 @@ void fb2_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 cudaStream_t fb2_stream() { return g_stream; }
+static cudaStream_t g_comm_stream = nullptr;
+cudaStream_t fb2_comm_stream() { return g_comm_stream; }
 int fb2_num_sms() { return g_nsm; }
 double* fb2_scratch_partials() { return g_partials; }
 void fb2_record_phase(const char* name, double ms) { g_phase_ms[name] = ms; }
@@ -50,7 +52,12 @@ extern "C" int fb2_init(int device) {
   FB2_CUDA(cudaGetDeviceProperties(&prop, device));
   g_nsm = prop.multiProcessorCount;
   if (!g_inited) {
-    FB2_CUDA(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+    // compute stream at the lowest priority, halo-exchange stream at the highest: CTAs of the pack/NCCL/unpack kernels are
+    // scheduled ahead of pending SpMV CTAs, so the exchange overlaps the interior rows (fb2_solver.cu)
+    int prio_lo = 0, prio_hi = 0;
+    FB2_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    FB2_CUDA(cudaStreamCreateWithPriority(&g_stream, cudaStreamNonBlocking, prio_lo));
+    FB2_CUDA(cudaStreamCreateWithPriority(&g_comm_stream, cudaStreamNonBlocking, prio_hi));
     FB2_CUDA(cudaMalloc((void**)&g_partials, sizeof(double) * FB2_MAX_PARTIALS * 4));
     g_inited = 1;
   }

@@ -54,7 +54,8 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
                                                              const double* __restrict__ val, const double* __restrict__ x,
                                                              double* __restrict__ y, double* partials, const int* done_flag,
                                                              int R, int cap, i64 ntiles, int STAGES,
-                                                             const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows) {
+                                                             const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
+                                                             int chunk) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full_bar[SPMV_MAX_STAGES], empty_bar[SPMV_MAX_STAGES];
   __shared__ i64 s_e0a[SPMV_MAX_STAGES], s_r0[SPMV_MAX_STAGES];
@@ -64,6 +65,10 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
   const int tid = threadIdx.x;
   const size_t irp_bytes = (size_t)(R + 2) * 8;
   const size_t stage_bytes = (size_t)cap * 12 + irp_bytes;
+  // tiles of this CTA: persistent (chunk == 0): blockIdx.x, blockIdx.x + gridDim.x, ... ; chunked: `chunk` consecutive tiles
+  const i64 t_first = chunk ? (i64)blockIdx.x * chunk : (i64)blockIdx.x;
+  const i64 t_step = chunk ? 1 : (i64)gridDim.x;
+  const i64 t_end = chunk ? min(t_first + chunk, ntiles) : ntiles;
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], SPMV_CONSUMERS / 32); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -73,16 +78,16 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
   if (tid >= SPMV_CONSUMERS) {
     // ---------------- producer warp ----------------
     if (tid == SPMV_CONSUMERS) {
-      i64 t = blockIdx.x;
+      i64 t = t_first;
       i64 e0 = 0, e1 = 0, r0 = 0;
       int nr = 0;
-      if (t < ntiles) { r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr]; }
-      for (int it = 0; t < ntiles; t += gridDim.x, ++it) {
+      if (t < t_end) { r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr]; }
+      for (int it = 0; t < t_end; t += t_step, ++it) {
         const int s = it % STAGES;
         // prefetch the row / element range of the next tile before blocking on the empty barrier
-        i64 tn = t + gridDim.x, ne0 = 0, ne1 = 0, nr0 = 0;
+        i64 tn = t + t_step, ne0 = 0, ne1 = 0, nr0 = 0;
         int nnr = 0;
-        if (tn < ntiles) { nr0 = tile_row[tn]; nnr = tile_nrows[tn]; ne0 = irp[nr0]; ne1 = irp[nr0 + nnr]; }
+        if (tn < t_end) { nr0 = tile_row[tn]; nnr = tile_nrows[tn]; ne0 = irp[nr0]; ne1 = irp[nr0 + nnr]; }
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
         unsigned char* base = smem_raw + s * stage_bytes;
         const i64 e0a = e0 & ~(i64)3;
@@ -105,7 +110,7 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
   const int lane = tid & 31, w = tid >> 5;
   double dacc = 0.0;
   int it = 0;
-  for (i64 t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+  for (i64 t = t_first; t < t_end; t += t_step, ++it) {
     const int s = it % STAGES;
     mbar_wait(&full_bar[s], (it / STAGES) & 1);
     const i64 r0 = s_r0[s];
@@ -233,18 +238,50 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   return 0;
 }
 
+int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, i64 t0, i64 t1,
+                          int chunk, double* partials, int* grid_out) {
+  FB2_TRY(fb2_spmv_prepare(A));
+  const i64 nt = t1 - t0;
+  if (A->n == 0 || nt <= 0) { if (grid_out) *grid_out = 0; return 0; }
+  cudaStream_t st = fb2_stream();
+  if (chunk && (nt + chunk - 1) / chunk > FB2_MAX_PARTIALS / 2) chunk = (int)((nt + FB2_MAX_PARTIALS / 2 - 1) / (FB2_MAX_PARTIALS / 2));
+  i64 grid = chunk ? (nt + chunk - 1) / chunk : (nt < A->spmv_grid ? nt : (i64)A->spmv_grid);
+  if (fuse_dot)
+    k_spmv_stream<true><<<(unsigned)grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, partials, done_flag,
+                                                                             A->spmv_R, A->spmv_cap, nt, A->spmv_stages,
+                                                                             A->d_tile_row + t0, A->d_tile_nrows + t0, chunk);
+  else
+    k_spmv_stream<false><<<(unsigned)grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, nullptr, done_flag,
+                                                                              A->spmv_R, A->spmv_cap, nt, A->spmv_stages,
+                                                                              A->d_tile_row + t0, A->d_tile_nrows + t0, chunk);
+  FB2_CUDA(cudaGetLastError());
+  if (grid_out) *grid_out = (int)grid;
+  return 0;
+}
+
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out) {
   FB2_TRY(fb2_spmv_prepare(A));
-  if (A->n == 0) { if (grid_out) *grid_out = 0; return 0; }
-  cudaStream_t st = fb2_stream();
-  if (fuse_dot)
-    k_spmv_stream<true><<<A->spmv_grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y,
-                                                                          fb2_scratch_partials(), done_flag, A->spmv_R,
-                                                                          A->spmv_cap, A->spmv_ntiles, A->spmv_stages, A->d_tile_row, A->d_tile_nrows);
-  else
-    k_spmv_stream<false><<<A->spmv_grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, nullptr,
-                                                                           done_flag, A->spmv_R, A->spmv_cap, A->spmv_ntiles, A->spmv_stages, A->d_tile_row, A->d_tile_nrows);
-  FB2_CUDA(cudaGetLastError());
-  if (grid_out) *grid_out = A->spmv_grid;
+  // short-lived CTAs over 32 consecutive tiles beat persistent striding CTAs (dynamic balance, contiguous streams per CTA):
+  // profiles/r1_spmv_chunk_sweep.txt
+  static int chunk = getenv("FB2_SPMV_CHUNK") ? atoi(getenv("FB2_SPMV_CHUNK")) : 32;
+  return fb2_spmv_stream_range(A, x, y, fuse_dot, done_flag, 0, A->spmv_ntiles, chunk, fb2_scratch_partials(), grid_out);
+}
+
+// par overlap: the tile table is in row order and interface rows are numbered last (dof_import.f90:391-421), so the tiles
+// from the one holding row n_interior onwards are the "interface" launch
+int fb2_spmv_interface_split(fb2_matrix_s* A, i64 n_interior, i64* t_itf, i64* row_itf) {
+  FB2_TRY(fb2_spmv_prepare(A));
+  if (A->spmv_t_itf < 0) {
+    std::vector<i64> rows((size_t)A->spmv_ntiles);
+    if (A->spmv_ntiles) FB2_CUDA(fb2_memcpy(rows.data(), A->d_tile_row, sizeof(i64) * rows.size(), cudaMemcpyDeviceToHost));
+    // last tile whose first row is <= n_interior (it holds row n_interior unless n_interior == n)
+    i64 lo = 0, hi = A->spmv_ntiles;
+    while (lo < hi) { i64 mid = (lo + hi) >> 1; if (rows[mid] <= n_interior) lo = mid + 1; else hi = mid; }
+    i64 t = lo > 0 ? lo - 1 : 0;
+    if (n_interior >= A->n) t = A->spmv_ntiles;
+    A->spmv_t_itf = t;
+    A->spmv_row_itf = t < A->spmv_ntiles ? rows[t] : A->n;
+  }
+  *t_itf = A->spmv_t_itf; *row_itf = A->spmv_row_itf;
   return 0;
 }
