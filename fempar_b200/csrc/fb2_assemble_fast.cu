@@ -118,6 +118,7 @@ int fb2_build_scatter_map(fb2_matrix_s* A) {
     h_class[k] = -1;
     if (h_rep[k] < n_local) { h_class[k] = ncls; h_reps[ncls++] = h_rep[k]; }
   }
+  A->common_tab = h_class[(3 * 4 + 3) * (1 + 16 + 256)];   // lo = hi = 3 (clipped) in x, y, z: the interior class
   FB2_CUDA(cudaMemcpyAsync(d_class_of_key, h_class, sizeof(h_class), cudaMemcpyHostToDevice, st));
   FB2_CUDA(cudaMemcpyAsync(d_reps, h_reps, sizeof(int) * ncls, cudaMemcpyHostToDevice, st));
   k_map_remap<<<(n_local + 255) / 256, 256, 0, st>>>(n_local, d_class_of_key, A->d_cell_tab);
@@ -176,6 +177,7 @@ struct FastArgs {
   AsmArgs a;
   const int* cell_tab;
   const unsigned short* tabs;
+  int common_tab;   // table id of the interior position class (-1: none); cached in shared memory by the kernel
 };
 
 // Column j of the element matrix by sum factorisation.  With q = (q1,q2,q3), i = (i1,i2,i3) and
@@ -235,24 +237,39 @@ __device__ __forceinline__ void column_sumfact(const double (*__restrict__ D)[6]
   }
 }
 
+// Per-cell input data (cell id through perm, DOF ids, row starts, Dirichlet values, table id) is software-pipelined three
+// cells ahead in registers: the ncu source view of the previous version showed 32 % of the stall samples as long-scoreboard
+// waits on exactly these dependent loads (perm -> gids -> irp / fixed) and on the per-entry scatter-table loads; the table of
+// the most frequent position class (interior cells) is now kept in shared memory, as are the geometry-basis gradients.
 template <int P, int NCOMP, bool ATOMIC>
 __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArgs F, int cells_in_launch) {
   constexpr int N1 = P + 1, NN = N1 * N1 * N1, NQ = NN, ND = NN * NCOMP;
   constexpr int CPW = NN <= 16 ? 32 / NN : 1;        // cells per warp (Q1: 4)
   constexpr int CPL = (NN + 31) / 32;                // columns per lane (Q3: 2)
+  constexpr int G = CPL * NCOMP;                     // DOFs handled by one lane in its "lane as DOF" role
   constexpr int WARPS = 4;
+  constexpr bool TABCACHE = ND * ND * 2 <= 16384;    // scalar Q1-Q3 and vector Q1/Q2
   const AsmArgs& A = F.a;
   __shared__ double s_B[N1 * N1], s_C[N1 * N1];      // 1-D tables for the lane-dependent factors
+  __shared__ double s_gd[NQ * 24], s_qw[NQ];         // trilinear geometry gradients at the quadrature points, weights
   __shared__ double s_D[WARPS * CPW][NQ][6];
   __shared__ double s_fw[WARPS * CPW][NQ];
   __shared__ double s_gfix[WARPS * CPW][ND];
   __shared__ i64 s_base[WARPS * CPW][ND];
   __shared__ int s_gid[WARPS * CPW][ND];
+  __shared__ unsigned short s_tabc[TABCACHE ? ND * ND : 2];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sub = CPW > 1 ? lane / NN : 0, j0 = CPW > 1 ? lane - sub * NN : lane;
   const bool lane_on = lane < CPW * NN || CPL > 1;
   const int slot = w * CPW + (lane_on ? sub : 0);
   if (threadIdx.x < N1 * N1) { s_B[threadIdx.x] = c_B1[P - 1][threadIdx.x]; s_C[threadIdx.x] = c_C1[P - 1][threadIdx.x]; }
+  for (int e = threadIdx.x; e < NQ * 24; e += blockDim.x) s_gd[e] = A.gdphi[e];
+  for (int e = threadIdx.x; e < NQ; e += blockDim.x) s_qw[e] = A.qw[e];
+  const bool have_cache = TABCACHE && F.common_tab >= 0;
+  if (have_cache) {
+    const unsigned short* src = F.tabs + (size_t)F.common_tab * (ND * ND);
+    for (int e = threadIdx.x; e < ND * ND; e += blockDim.x) s_tabc[e] = src[e];
+  }
   __syncthreads();
   int cdim[3], coff[3];
 #pragma unroll
@@ -262,19 +279,78 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
   }
   const bool has_source = A.kind == FB2_KIND_POISSON && A.fn.kind == FB2_FUNC_SHARP_WAVE;
   const int stride = gridDim.x * WARPS * CPW;
+  // total-box position and lexicographic index of the ci-th cell of this launch
+  auto cell_pos = [&](int ci, int* ijk) {
+    int r = ci;
+    ijk[0] = r % cdim[0]; r /= cdim[0];
+    ijk[1] = r % cdim[1]; ijk[2] = r / cdim[1];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) ijk[k] = (A.color < 0 ? ijk[k] : 2 * ijk[k] + coff[k]) + A.g.L[k];
+    return ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
+  };
+  auto cell_id = [&](int ci) {            // stage A: local cell id (one dependent load through perm in the par numbering)
+    if (!lane_on || ci >= cells_in_launch) return -1;
+    int ijk[3];
+    const int lex = cell_pos(ci, ijk);
+    return A.perm ? A.perm[lex] : lex;
+  };
+  auto load_gids = [&](int c, int* gid, int& tabid) {   // stage B
+#pragma unroll
+    for (int jj = 0; jj < CPL; ++jj)
+#pragma unroll
+      for (int cc = 0; cc < NCOMP; ++cc) {
+        const int q = j0 + 32 * jj;
+        gid[jj * NCOMP + cc] = (c >= 0 && q < NQ) ? A.gids[(i64)c * ND + cc * NN + q] : 0;
+      }
+    tabid = c >= 0 ? F.cell_tab[c] : 0;
+  };
+  auto load_rows = [&](const int* gid, i64* base, double* fix) {   // stage C
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      base[g] = (gid[g] > 0 && gid[g] <= A.n_free) ? A.irp[gid[g] - 1] : -1;
+      fix[g] = gid[g] < 0 ? A.fixed[-gid[g] - 1] : 0.0;
+    }
+  };
+  // ---- pipeline prologue ----
+  const int ci_first = (blockIdx.x * WARPS + w) * CPW + sub;
+  int gidC[G], gidN[G], tabC = 0, tabN = 0, cNN;
+  i64 baseC[G];
+  double fixC[G];
+  {
+    const int c0 = cell_id(ci_first), c1 = cell_id(ci_first + stride);
+    cNN = cell_id(ci_first + 2 * stride);
+    load_gids(c0, gidC, tabC);
+    load_gids(c1, gidN, tabN);
+    load_rows(gidC, baseC, fixC);
+  }
   for (int ci0 = (blockIdx.x * WARPS + w) * CPW; ci0 < cells_in_launch; ci0 += stride) {
     const int ci = ci0 + sub;
     const bool on = lane_on && ci < cells_in_launch;
-    int c = 0;
+    const int tab_cur = tabC;
     bool any_dir = false;
-    if (on) {
-      int ijk[3], r = ci;
-      ijk[0] = r % cdim[0]; r /= cdim[0];
-      ijk[1] = r % cdim[1]; ijk[2] = r / cdim[1];
+    // ---- hand the current cell's DOF data to the warp, then advance the pipeline by one cell ----
 #pragma unroll
-      for (int k = 0; k < 3; ++k) ijk[k] = (A.color < 0 ? ijk[k] : 2 * ijk[k] + coff[k]) + A.g.L[k];
-      const int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
-      c = A.perm ? A.perm[lex] : lex;
+    for (int jj = 0; jj < CPL; ++jj)
+#pragma unroll
+      for (int cc = 0; cc < NCOMP; ++cc) {
+        const int q = j0 + 32 * jj, g = jj * NCOMP + cc;
+        if (on && q < NQ) {
+          const int l = cc * NN + q;
+          s_gid[slot][l] = gidC[g];
+          s_gfix[slot][l] = fixC[g];
+          s_base[slot][l] = baseC[g];
+          any_dir |= gidC[g] < 0;
+        }
+      }
+    load_rows(gidN, baseC, fixC);                       // rows / Dirichlet values of cell k+1
+#pragma unroll
+    for (int g = 0; g < G; ++g) gidC[g] = gidN[g];
+    tabC = tabN;
+    load_gids(cNN, gidN, tabN);                         // DOF ids and table id of cell k+2
+    cNN = cell_id(ci + 3 * stride);                     // cell id of cell k+3
+    if (on) {
+      int ijk[3];
+      cell_pos(ci, ijk);
       double X[8][3];
       cell_vertices(A.g, ijk, X);
 #pragma unroll
@@ -283,8 +359,8 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
         if (q < NQ) {
           // --- lane as quadrature point: D(q) = w detJ J^-1 J^-T (sbm_cell_map.i90:272-296), source term ---
           double inv[3][3], det;
-          jacobian_at(X, A.gdphi + q * 24, inv, det);
-          const double wd = det * A.qw[q];
+          jacobian_at(X, s_gd + q * 24, inv, det);
+          const double wd = det * s_qw[q];
           double* D = s_D[slot][q];
           D[0] = wd * (inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0]);
           D[1] = wd * (inv[0][0] * inv[0][1] + inv[1][0] * inv[1][1] + inv[2][0] * inv[2][1]);
@@ -300,23 +376,14 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
               for (int k = 0; k < 3; ++k) xq[k] += A.gphi[q * 8 + a] * X[a][k];
             s_fw[slot][q] = wd * func_f(A.fn, xq);
           }
-          // --- lane as DOF of every component: ids, Dirichlet values, row starts ---
-#pragma unroll
-          for (int cc = 0; cc < NCOMP; ++cc) {
-            const int l = cc * NN + q;
-            const int g = A.gids[(i64)c * ND + l];
-            s_gid[slot][l] = g;
-            s_gfix[slot][l] = g < 0 ? A.fixed[-g - 1] : 0.0;
-            s_base[slot][l] = (g > 0 && g <= A.n_free) ? A.irp[g - 1] : -1;
-            any_dir |= g < 0;
-          }
         }
       }
     }
     any_dir = __any_sync(0xffffffffu, any_dir);
     __syncwarp();
     if (on) {
-      const unsigned short* tab = F.tabs + (size_t)F.cell_tab[c] * (ND * ND);
+      const unsigned short* tab = (have_cache && tab_cur == F.common_tab) ? (const unsigned short*)s_tabc
+                                                                          : F.tabs + (size_t)tab_cur * (ND * ND);
 #pragma unroll 1
       for (int jj = 0; jj < CPL; ++jj) {
         const int j = j0 + 32 * jj;
@@ -418,7 +485,7 @@ int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant)
   if (A->map_state != 1) return -1;
   FB2_TRY(load_const_tables(s));
   FastArgs F;
-  F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs;
+  F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs; F.common_tab = A->common_tab;
   if (s->rt.p == 1) return s->rt.ncomp == 1 ? launch_fast<1, 1>(F, s, scatter_variant) : launch_fast<1, 3>(F, s, scatter_variant);
   if (s->rt.p == 2) return s->rt.ncomp == 1 ? launch_fast<2, 1>(F, s, scatter_variant) : launch_fast<2, 3>(F, s, scatter_variant);
   return s->rt.ncomp == 1 ? launch_fast<3, 1>(F, s, scatter_variant) : launch_fast<3, 3>(F, s, scatter_variant);

@@ -110,6 +110,7 @@ struct fb2_matrix_s {
   // cell-local -> CSR-slot scatter map (fb2_assemble_fast.cu): slot = irp[row] + tabs[cell_tab[c]][i*nd + j]
   int* d_cell_tab = nullptr;          // [n_local] table id of each local cell
   unsigned short* d_tabs = nullptr;   // [n_tabs][nd*nd] relative slots, 0xFFFF = entry not stored
+  int common_tab = -1;                // table id of the interior position class
   int n_tabs = 0, n_class_tabs = 0, map_state = 0;   // map_state: 0 not built, 1 built, -1 unavailable (search fallback)
   // SpMV tile geometry (fb2_spmv.cu)
   int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0;
