@@ -61,6 +61,30 @@ void fb2_import_destroy(fb2_import_s* imp) {
   delete imp;
 }
 
+// Gather-add plan of stage 1 of comm(): a DOF shared by more than two parts is received from several neighbours, so
+// unpack_idx holds it several times.  Group the receive-buffer positions by destination DOF (positions ascending =
+// neighbour list order = the order mpi_context.f90:610-632 adds them in) -> one thread per DOF, no atomics, deterministic.
+// imp->h_unpack_idx must hold 0-based ids.
+int fb2_import_build_add_plan(fb2_import_s* imp) {
+  const int nu = (int)imp->n_unpack;
+  std::vector<int> pos(nu);
+  for (int i = 0; i < nu; ++i) pos[i] = i;
+  std::stable_sort(pos.begin(), pos.end(), [&](int a, int b) { return imp->h_unpack_idx[a] < imp->h_unpack_idx[b]; });
+  std::vector<int> dst, ptr;
+  for (int i = 0; i < nu; ++i)
+    if (i == 0 || imp->h_unpack_idx[pos[i]] != imp->h_unpack_idx[pos[i - 1]]) { dst.push_back(imp->h_unpack_idx[pos[i]]); ptr.push_back(i); }
+  ptr.push_back(nu);
+  imp->n_add_dst = (int)dst.size();
+  cudaFree(imp->d_add_dst); cudaFree(imp->d_add_ptr); cudaFree(imp->d_add_pos);
+  FB2_TRY(fb2_dalloc(&imp->d_add_dst, dst.size())); FB2_TRY(fb2_dalloc(&imp->d_add_ptr, ptr.size())); FB2_TRY(fb2_dalloc(&imp->d_add_pos, (size_t)nu));
+  if (nu) {
+    FB2_CUDA(fb2_memcpy(imp->d_add_dst, dst.data(), sizeof(int) * dst.size(), cudaMemcpyHostToDevice));
+    FB2_CUDA(fb2_memcpy(imp->d_add_pos, pos.data(), sizeof(int) * (size_t)nu, cudaMemcpyHostToDevice));
+  }
+  FB2_CUDA(fb2_memcpy(imp->d_add_ptr, ptr.data(), sizeof(int) * ptr.size(), cudaMemcpyHostToDevice));
+  return 0;
+}
+
 // pack_rp / unpack_rp of mpi_context.f90:522-639
 __global__ void k_pack(const double* __restrict__ x, const int* __restrict__ idx, int lo, int hi, double* buf) {
   int i = lo + blockIdx.x * blockDim.x + threadIdx.x;

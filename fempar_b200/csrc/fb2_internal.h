@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 #include <string>
 #include <vector>
 #include "../../include/fempar_b200.h"
@@ -118,6 +119,7 @@ struct fb2_matrix_s {
   i64* d_tile_row = nullptr;              // first row of every tile
   unsigned char* d_tile_nrows = nullptr;  // rows in the tile (<= spmv_R)
   size_t spmv_smem = 0;
+  int owns_space = 0;                       // matrix created from host arrays without a space: it owns a bare one
   i64 spmv_t_itf = -1, spmv_row_itf = -1;   // interface split of the tile table (par overlap)
 };
 
@@ -163,5 +165,6 @@ int fb2_import_exchange(fb2_import_s* imp, double* d_vec); // par_scalar_array%c
 int fb2_import_exchange_on(fb2_import_s* imp, double* d_vec, cudaStream_t stream);
 const double* fb2_import_weight(fb2_import_s* imp);
 void fb2_import_destroy(fb2_import_s* imp);
+int fb2_import_build_add_plan(fb2_import_s* imp);   // from imp->h_unpack_idx (0-based)
 int fb2_build_par_layer(fb2_space_s* s);                   // fb2_par.cu
 int fb2_build_node_maps(fb2_space_s* s);                   // fb2_space.cu                   // interface detection + dof_import + I-then-G renumbering

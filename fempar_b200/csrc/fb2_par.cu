@@ -297,26 +297,7 @@ int fb2_build_par_layer(fb2_space_s* s) {
   FB2_CUDA(cudaGetLastError());
   if (imp->n_pack) FB2_CUDA(fb2_memcpy(imp->h_pack_idx.data(), imp->d_pack_idx, sizeof(int) * imp->n_pack, cudaMemcpyDeviceToHost));
   if (imp->n_unpack) FB2_CUDA(fb2_memcpy(imp->h_unpack_idx.data(), imp->d_unpack_idx, sizeof(int) * imp->n_unpack, cudaMemcpyDeviceToHost));
-  // Gather-add plan of stage 1 of comm(): a DOF shared by more than two parts is received from several neighbours, so
-  // unpack_idx holds it several times.  Group the receive-buffer positions by destination DOF (positions ascending =
-  // neighbour list order = the order mpi_context.f90:610-632 adds them in) -> one thread per DOF, no atomics, deterministic.
-  {
-    const int nu = (int)imp->n_unpack;
-    std::vector<int> pos(nu);
-    for (int i = 0; i < nu; ++i) pos[i] = i;
-    std::stable_sort(pos.begin(), pos.end(), [&](int a, int b) { return imp->h_unpack_idx[a] < imp->h_unpack_idx[b]; });
-    std::vector<int> dst, ptr;
-    for (int i = 0; i < nu; ++i)
-      if (i == 0 || imp->h_unpack_idx[pos[i]] != imp->h_unpack_idx[pos[i - 1]]) { dst.push_back(imp->h_unpack_idx[pos[i]]); ptr.push_back(i); }
-    ptr.push_back(nu);
-    imp->n_add_dst = (int)dst.size();
-    FB2_TRY(fb2_dalloc(&imp->d_add_dst, dst.size())); FB2_TRY(fb2_dalloc(&imp->d_add_ptr, ptr.size())); FB2_TRY(fb2_dalloc(&imp->d_add_pos, (size_t)nu));
-    if (nu) {
-      FB2_CUDA(fb2_memcpy(imp->d_add_dst, dst.data(), sizeof(int) * dst.size(), cudaMemcpyHostToDevice));
-      FB2_CUDA(fb2_memcpy(imp->d_add_pos, pos.data(), sizeof(int) * (size_t)nu, cudaMemcpyHostToDevice));
-    }
-    FB2_CUDA(fb2_memcpy(imp->d_add_ptr, ptr.data(), sizeof(int) * ptr.size(), cudaMemcpyHostToDevice));
-  }
+  FB2_TRY(fb2_import_build_add_plan(imp));   // h_unpack_idx is still 0-based here
   for (auto& v : imp->h_pack_idx) v += 1;
   for (auto& v : imp->h_unpack_idx) v += 1;
   const i64 nbuf = imp->n_pack > imp->n_unpack ? imp->n_pack : imp->n_unpack;

@@ -131,7 +131,16 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
         acc += sv[k + 2 * TPR] * x2;
         acc += sv[k + 3 * TPR] * x3;
       }
-      for (; k < e; k += TPR) acc += sv[k] * x[sj[k] - 1];
+      if (k < e) {
+        // tail of up to 3 entries per lane as ONE masked batch, so that its gathers are in flight together
+        const int k1 = k + TPR, k2 = k + 2 * TPR;
+        const bool p1 = k1 < e, p2 = k2 < e;
+        const int c0 = sj[k], c1 = p1 ? sj[k1] : c0, c2 = p2 ? sj[k2] : c0;
+        const double x0 = x[c0 - 1], x1 = x[c1 - 1], x2 = x[c2 - 1];
+        acc += sv[k] * x0;
+        if (p1) acc += sv[k1] * x1;
+        if (p2) acc += sv[k2] * x2;
+      }
     }
     for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
     if (sub == 0 && live) {

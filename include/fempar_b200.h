@@ -108,6 +108,27 @@ int fb2_dof_import_get_sizes(fb2_space_t s, int32_t sizes[4]);
 int fb2_dof_import_get(fb2_space_t s, int32_t* list_rcv, int32_t* rcv_ptrs, int32_t* unpack_idx, int32_t* list_snd,
                        int32_t* snd_ptrs, int32_t* pack_idx, double* weight);
 
+/* ---- host-built FEMPAR objects handed to the device path (matrix-format, assembler and comm seams) ------ */
+/* a space that is only a number of local DOFs (unstructured meshes, other reference FEs: the reference numbers the DOFs) */
+int fb2_fe_space_create_bare(fb2_space_t* out, int64_t num_dofs);
+/* attach the dof_import_t the reference computed (dof_import.f90:49-90; Fortran conventions: part ids, ptrs and local
+ * DOF ids 1-based; weight may be NULL = 0 on every packed, i.e. non-owned, DOF) */
+int fb2_dof_import_set(fb2_space_t s, int32_t num_rcv, const int32_t* list_rcv, const int32_t* rcv_ptrs,
+                       const int32_t* unpack_idx, int32_t num_snd, const int32_t* list_snd, const int32_t* snd_ptrs,
+                       const int32_t* pack_idx, const double* weight);
+/* base_sparse_matrix_t%move_from_coo_body / convert target (sparse_matrix.f90:783-833): the reference's csr_sparse_matrix_t
+ * arrays irp(1)=1 (int32), ja, val copied to the device.  space NULL = serial; val NULL = zero values (graph only). */
+int fb2_csr_create_from_host(fb2_matrix_t* out, fb2_space_t space, int64_t num_rows, const int32_t* irp, const int32_t* ja,
+                             const double* val, int symmetric_storage);
+int fb2_csr_initialize_values(fb2_matrix_t A, double alpha);   /* csr initialize_values */
+/* sparse_assembler_t%assembly_matrix / assembly_array for a batch of cells (sparse_assembler.f90:58-126,154-206):
+ * fe_dofs[num_cells][nd] signed 1-based ids, elmat[num_cells][nd*nd] column-major (elmat(idof,jdof), test = row), elvec
+ * [num_cells][nd]; entries with ids < 1 or > num_rows are skipped (base_sparse_matrix.f90:3469-3513).  elmat / elvec / rhs
+ * may be NULL.  With fixed_dof_values != NULL the strong-Dirichlet elimination of fe_cell_iterator%assembly
+ * (sbm_fe_cell_iterator.i90:1610-1637) is applied to negative column ids first. */
+int fb2_assemble_batch(fb2_matrix_t A, fb2_vector_t rhs, int32_t num_cells, int32_t num_dofs_per_cell, const int32_t* fe_dofs,
+                       const double* elmat, const double* elvec, const double* fixed_dof_values, int64_t num_fixed);
+
 /* ---- matrix: csr_sparse_matrix.f90:44-50 ; graph = what coo sort_and_compress would produce ---------- */
 int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_storage);
 int fb2_csr_destroy(fb2_matrix_t A);

@@ -77,6 +77,29 @@ def main():
         chk("errors", abs(h1 - oh1) <= 1e-8 * max(oh1, 1.0) and abs(l2 - ol2) <= 1e-8 * max(ol2, 1.0), (h1, oh1, l2, ol2))
         if rank == 0:
             print("case", N, p, func, prec, "iters", ils.get_num_iterations(), ro["iters"], "ok", ok, flush=True)
+    # --- host-built objects (SURVEY 8b comm / matrix-format seams): the oracle's dof_import_t and local CSR matrix are
+    #     handed over through fb2_dof_import_set / fb2_csr_create_from_host; the par PCG must give the same answer ---
+    N, p = (8, 8, 8), 2
+    P = ParOracle(N, order=p, parts=parts)
+    P.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE)
+    P.jacobi_setup()
+    ro = P.cg(prec=1, rtol=1e-12, maxit=5000)
+    q, im = P.spaces[rank], P.imp[rank]
+    bs = fb.BareFeSpace(q.num_free)
+    bs.set_dof_import(im["list_rcv"], im["rcv_ptrs"] + 1, im["unpack_idx"], im["list_snd"], im["snd_ptrs"] + 1, im["pack_idx"])
+    Ah = fb.SparseMatrix(space=bs, host_csr=(q.irp() + 1, q.ja(), q.val()))
+    Mh = fb.JacobiPreconditioner(); Mh.create(Ah); Mh.numerical_setup()
+    chk("host_dinv", np.max(np.abs(Mh.inverse_diagonal.get_entries() - P.dinv[rank])) <= 1e-12 * np.max(np.abs(P.dinv[rank])))
+    bh = bs.create_dof_values(); bh.set_entries(P.b[rank])
+    xh = bs.create_dof_values()
+    ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG")
+    ils.set_parameters_from_pl({fb.ILS_RTOL: 1e-12, fb.ILS_MAX_NUM_ITERATIONS: 5000})
+    ils.set_operators(Ah, Mh)
+    ils.apply(bh, xh)
+    chk("host_iters", ils.converged() and abs(ils.get_num_iterations() - ro["iters"]) <= 1, (ils.get_num_iterations(), ro["iters"]))
+    chk("host_solution", np.max(np.abs(xh.get_entries() - ro["x"][rank])) <= 1e-8)
+    if rank == 0:
+        print("host-built import + CSR: iters", ils.get_num_iterations(), ro["iters"], "ok", ok, flush=True)
     for f in fails:
         print("FAIL", f, flush=True)
     t = torch.tensor([1 if ok else 0], device="cuda")
