@@ -15,6 +15,10 @@ class ILSParams(C.Structure):
                 ("stopping_criterium", C.c_int), ("track_convergence_history", C.c_int), ("check_every", C.c_int)]
 
 
+class ILSExtParams(C.Structure):
+    _fields_ = [("dkrymax", C.c_int), ("orthonorm_strat", C.c_int), ("relaxation", C.c_double)]
+
+
 class Fb2Error(RuntimeError):
     pass
 
@@ -77,6 +81,8 @@ _SIGS = {
                       C.POINTER(C.c_double), _VP],
     "fb2_pcg_solve_host": [_VP, _VP, _VP, _VP, C.POINTER(ILSParams), C.POINTER(C.c_int), C.POINTER(C.c_int),
                            C.POINTER(C.c_double), _VP],
+    "fb2_ils_solve": [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(ILSParams), C.POINTER(ILSExtParams), C.POINTER(C.c_int),
+                      C.POINTER(C.c_int), C.POINTER(C.c_double), _VP],
     "fb2_pcg_iterate": [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)],
     "fb2_error_norms": [_VP, _VP, C.c_int, _VP, C.POINTER(C.c_double), C.POINTER(C.c_double)],
 }

@@ -135,6 +135,16 @@ double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x
 #define FB2_MAX_PARTIALS 65536
 
 int fb2_build_scatter_map(fb2_matrix_s* A);
+// primitives of fb2_solver.cu used by the host-driven Krylov solvers (fb2_krylov.cu)
+bool fb2_matrix_is_par(fb2_matrix_s* A);
+const double* fb2_matrix_weight(fb2_matrix_s* A);
+int fb2_op_apply(fb2_matrix_s* A, const double* x, double* y);
+int fb2_dev_apply_M(const double* dinv, const double* r, double* z, i64 n);
+int fb2_dev_axpby(double* op1, double a, const double* op2, double b, i64 n);
+int fb2_dev_scal(double* dst, double a, const double* src, i64 n);
+int fb2_dev_init(double* x, double a, i64 n);
+int fb2_dots_host(fb2_matrix_s* A, int k, const double* const* xs, const double* const* ys, i64 n, double* out);
+void fb2_cg_set_icg(int on);
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 int fb2_spmv_prepare(fb2_matrix_s* A);
 // tiles [t0, t1) only; chunk = 0: persistent CTAs striding over the range, chunk > 0: one CTA per `chunk` consecutive tiles

@@ -72,8 +72,8 @@ int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, dou
 // SpMV: warp per row, 4 independent 32-wide passes in flight per warp, coalesced val/ja streams
 // ------------------------------------------------------------------------------------------
 struct CgState {
-  double rz, App, rr, rz_new, pp, tol, tol_extra, rtol, atol, alpha, beta, err, err_extra;   // rr, rz_new, pp adjacent (one reduction)
-  int iter, converged, done, maxit, crit;
+  double rz, App, rr, rz_new, pp, r2z, tol, tol_extra, rtol, atol, alpha, beta, err, err_extra;   // rr..r2z adjacent (one reduction)
+  int iter, converged, done, maxit, crit, icg;
 };
 
 template <bool FUSE_DOT>
@@ -276,7 +276,7 @@ static const double* weight_of(fb2_vector_t v) {
 }
 extern "C" int fb2_vec_dot(fb2_vector_t x, fb2_vector_t y, double* result) {
   FB2_CHECK(x->n == y->n, "size mismatch");
-  double* d_res = fb2_scratch_partials() + FB2_MAX_PARTIALS * 3;
+  double* d_res = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
   FB2_TRY(fb2_dot_device(x->d, y->d, weight_of(x), x->n, d_res));
   if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(d_res, 1));
   FB2_CUDA(cudaMemcpyAsync(result, d_res, sizeof(double), cudaMemcpyDeviceToHost, fb2_stream()));
@@ -347,22 +347,28 @@ __global__ void __launch_bounds__(256) k_cg_update_xr(i64 n, CgState* st, const 
   if (st->done) return;
   const double App = st->App;
   const double alpha = (App != 0.0) ? st->rz / App : 0.0;   // cg.f90:195-199
-  const bool need_pp = st->crit >= FB2_STOP_DELTA_RHS;
-  double a_rr = 0.0, a_rz = 0.0, a_pp = 0.0;
+  const bool need_pp = st->crit >= FB2_STOP_DELTA_RHS, icg = st->icg != 0;
+  double a_rr = 0.0, a_rz = 0.0, a_pp = 0.0, a_r2z = 0.0;
   for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
-    const double pi = p[i];
+    const double pi = p[i], r_old = r[i];
     x[i] += alpha * pi;
-    double ri = r[i] - alpha * Ap[i];
+    double ri = r_old - alpha * Ap[i];
     r[i] = ri;
     double wi = w ? w[i] : 1.0;
+    const double zi = dinv ? dinv[i] * ri : ri;      // z = inv(M) r of the NEXT direction update
     a_rr += wi * ri * ri;
-    a_rz += wi * ri * (dinv ? dinv[i] * ri : ri);
+    a_rz += wi * ri * zi;
     a_pp += wi * pi * pi;
+    a_r2z += wi * r_old * zi;                        // <r2, z> of icg.f90:208-222 (r2 = residual before the update)
   }
   double s1 = block_sum(a_rr, s_red);
   double s2 = block_sum(a_rz, s_red);
   double s3 = need_pp ? block_sum(a_pp, s_red) : 0.0;
-  if (threadIdx.x == 0) { partials[blockIdx.x] = s1; partials[stride + blockIdx.x] = s2; partials[2 * stride + blockIdx.x] = s3; }
+  double s4 = icg ? block_sum(a_r2z, s_red) : 0.0;
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = s1; partials[stride + blockIdx.x] = s2; partials[2 * stride + blockIdx.x] = s3;
+    partials[3 * stride + blockIdx.x] = s4;
+  }
 }
 // convergence bookkeeping: cg.f90:208-226 and update_convergence_data_and_evaluate_stopping_criteria :331-407 (all ten criteria)
 __global__ void k_cg_scalars(CgState* st, double* hist) {
@@ -390,7 +396,7 @@ __global__ void k_cg_scalars(CgState* st, double* hist) {
   }
   st->converged = conv ? 1 : 0;
   if (conv || st->iter >= st->maxit) { st->done = 1; return; }
-  st->beta = st->rz_new / st->rz;
+  st->beta = st->icg ? (1.0 / st->rz) * (st->rz_new - st->r2z) : st->rz_new / st->rz;   // icg.f90:216-222 / cg.f90:220-226
   st->rz = st->rz_new;
 }
 // p = dinv r + beta p
@@ -401,11 +407,16 @@ __global__ void __launch_bounds__(256) k_cg_update_p(i64 n, const CgState* st, c
   for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x)
     p[i] = (dinv ? dinv[i] * r[i] : r[i]) + beta * p[i];
 }
-__global__ void k_cg_init_state(CgState* st, double rz, double tol, double tol_extra, double rtol, double atol, int maxit, int crit) {
+__global__ void k_cg_init_state(CgState* st, double rz, double tol, double tol_extra, double rtol, double atol, int maxit, int crit,
+                                int icg) {
+  st->icg = icg; st->r2z = 0;
   st->rz = rz; st->App = 0; st->rr = 0; st->rz_new = 0; st->pp = 0; st->tol = tol; st->tol_extra = tol_extra; st->rtol = rtol;
   st->atol = atol; st->alpha = 0; st->beta = 0; st->err = 0; st->err_extra = 0;
   st->iter = 0; st->converged = 0; st->done = 0; st->maxit = maxit; st->crit = crit;
 }
+
+static int g_cg_icg = 0;   // 1 while fb2_ils_solve runs the ICG variant (icg.f90) through the fused CG kernels
+void fb2_cg_set_icg(int on) { g_cg_icg = on; }
 
 struct CgWork {
   i64 n = 0;
@@ -483,8 +494,8 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
   }
   int g2 = reduce_grid(n);
   k_cg_update_xr<<<g2, 256, 0, s>>>(n, W.st, W.p, W.Ap, dinv, w, x, W.r, part, FB2_MAX_PARTIALS);
-  k_reduce_partials<<<1, 256, 0, s>>>(part, g2, FB2_MAX_PARTIALS, 3, &W.st->rr);   // rr, rz_new, pp are adjacent
-  if (par) FB2_TRY(fb2_allreduce_sum(&W.st->rr, 3));
+  k_reduce_partials<<<1, 256, 0, s>>>(part, g2, FB2_MAX_PARTIALS, 4, &W.st->rr);   // rr, rz_new, pp, r2z are adjacent
+  if (par) FB2_TRY(fb2_allreduce_sum(&W.st->rr, 4));
   k_cg_scalars<<<1, 1, 0, s>>>(W.st, hist);
   k_cg_update_p<<<vec_grid(n), 256, 0, s>>>(n, W.st, W.r, dinv, W.p);
   FB2_CUDA(cudaGetLastError());
@@ -504,7 +515,7 @@ static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const d
   // z = M^-1 r ; p = z ; r_z = <r,z>
   if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, dinv, W.r, n);
   else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
-  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 3;
+  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
   FB2_TRY(fb2_dot_device(W.r, W.p, w, n, d_tmp));          // r_z
   FB2_TRY(fb2_dot_device(W.r, W.r, w, n, d_tmp + 1));      // ||r(0)||^2
   FB2_TRY(fb2_dot_device(b, b, w, n, d_tmp + 2));          // ||b||^2
@@ -529,7 +540,7 @@ static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const d
     case FB2_STOP_RES_NRMGIVEN_RES_NRMGIVEN: tol = rtol * sqrt(h[0]) + atol; break;
     default: break;   // delta_delta: set at the first iteration
   }
-  k_cg_init_state<<<1, 1, 0, s>>>(W.st, h[0], tol, tol_extra, rtol, atol, maxit, stop);
+  k_cg_init_state<<<1, 1, 0, s>>>(W.st, h[0], tol, tol_extra, rtol, atol, maxit, stop, g_cg_icg);
   FB2_CUDA(cudaGetLastError());
   return 0;
 }
@@ -619,5 +630,50 @@ extern "C" int fb2_pcg_iterate(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b
   for (auto& e : ev) cudaEventDestroy(e);
   if (ms_total) *ms_total = ms;
   if (ms_spmv) *ms_spmv = acc;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// primitives shared with the host-driven Krylov solvers of fb2_krylov.cu (operator_t%apply, vector_t TBPs on raw
+// device arrays; all enqueue on the library stream)
+// ------------------------------------------------------------------------------------------
+bool fb2_matrix_is_par(fb2_matrix_t A) { return A->s && A->s->imp && fb2_comm_active(); }
+const double* fb2_matrix_weight(fb2_matrix_t A) { return fb2_matrix_is_par(A) ? fb2_import_weight(A->s->imp) : nullptr; }
+// y = A x  (+ comm() in par: par_sparse_matrix.f90:739-762)
+int fb2_op_apply(fb2_matrix_t A, const double* x, double* y) {
+  FB2_TRY(spmv_local(A, x, y, false, nullptr, nullptr));
+  if (fb2_matrix_is_par(A)) FB2_TRY(fb2_import_exchange(A->s->imp, y));
+  return 0;
+}
+// z = inv(M) r with M = Jacobi (dinv) or identity
+int fb2_dev_apply_M(const double* dinv, const double* r, double* z, i64 n) {
+  if (dinv) k_ew_product<<<vec_grid(n), 256, 0, fb2_stream()>>>(z, dinv, r, n);
+  else FB2_CUDA(cudaMemcpyAsync(z, r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, fb2_stream()));
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+int fb2_dev_axpby(double* op1, double a, const double* op2, double b, i64 n) {
+  k_axpby<<<vec_grid(n), 256, 0, fb2_stream()>>>(op1, a, op2, b, n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+int fb2_dev_scal(double* dst, double a, const double* src, i64 n) {
+  k_scal<<<vec_grid(n), 256, 0, fb2_stream()>>>(dst, a, src, n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+int fb2_dev_init(double* x, double a, i64 n) {
+  k_init<<<vec_grid(n), 256, 0, fb2_stream()>>>(x, a, n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+// out[i] = <xs[i], ys[i]>_w for i < k, all-reduced in par, copied to the host (one synchronisation)
+int fb2_dots_host(fb2_matrix_t A, int k, const double* const* xs, const double* const* ys, i64 n, double* out) {
+  FB2_CHECK(k >= 1 && k <= 1024, "fb2_dots_host: bad count");
+  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
+  const double* w = fb2_matrix_weight(A);
+  for (int i = 0; i < k; ++i) FB2_TRY(fb2_dot_device(xs[i], ys[i], w, n, d_tmp + i));
+  if (fb2_matrix_is_par(A)) FB2_TRY(fb2_allreduce_sum(d_tmp, k));
+  FB2_CUDA(fb2_memcpy(out, d_tmp, sizeof(double) * k, cudaMemcpyDeviceToHost));
   return 0;
 }

@@ -58,7 +58,7 @@ extern "C" int fb2_init(int device) {
     FB2_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     FB2_CUDA(cudaStreamCreateWithPriority(&g_stream, cudaStreamNonBlocking, prio_lo));
     FB2_CUDA(cudaStreamCreateWithPriority(&g_comm_stream, cudaStreamNonBlocking, prio_hi));
-    FB2_CUDA(cudaMalloc((void**)&g_partials, sizeof(double) * FB2_MAX_PARTIALS * 4));
+    FB2_CUDA(cudaMalloc((void**)&g_partials, sizeof(double) * FB2_MAX_PARTIALS * 5));
     g_inited = 1;
   }
   return 0;

@@ -180,6 +180,26 @@ int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_
 int fb2_pcg_solve_host(fb2_matrix_t A, fb2_vector_t dinv, const double* b_host, double* x_host,
                        const fb2_ils_params_t* params, int* num_iterations, int* did_converge,
                        double* error_estimate, double* history);
+/* The other Krylov solvers of the reference that share these primitives; keys of the creational-methods
+ * dictionary (iterative_linear_solver_creational_methods_dictionary.f90:97-106). */
+enum {
+  FB2_ILS_CG = 0,          /* cg.f90 */
+  FB2_ILS_ICG = 1,         /* icg.f90:106-240, all ten stopping criteria */
+  FB2_ILS_RICHARDSON = 2,  /* richardson.f90:101-205, RES_RES / RES_RHS */
+  FB2_ILS_RGMRES = 3,      /* rgmres.f90:120-356, RES_NRMGIVEN_* */
+  FB2_ILS_FGMRES = 4,      /* fgmres.f90:120-356, RES_NRMGIVEN_* */
+  FB2_ILS_LGMRES = 5       /* lgmres.f90:152-420, RES_NRMGIVEN_*, RES_RES, RES_RHS */
+};
+enum { FB2_ORTHO_MGSRO = 0, FB2_ORTHO_ICGSRO = 1 };   /* ILS_ORTHONORM_STRAT: iterative_solver_utils.f90:46-106 / :128-196 */
+typedef struct {
+  int dkrymax;            /* ILS_MAX_DIM_KRYLOV_BASIS, default 1000 (clamped to max_num_iterations) */
+  int orthonorm_strat;    /* ILS_ORTHONORM_STRAT, default ICGSRO */
+  double relaxation;      /* ILS_RELAXATION (Richardson), default 1.0 */
+} fb2_ils_ext_params_t;
+/* iterative_linear_solver_t%apply for any of the types above; ext may be NULL (defaults); x0 = 0 */
+int fb2_ils_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, int ils_type, const fb2_ils_params_t* params,
+                  const fb2_ils_ext_params_t* ext, int* num_iterations, int* did_converge, double* error_estimate,
+                  double* history);
 /* fixed-iteration variant used by benchmarks: runs exactly n PCG iterations (no convergence exit) and
  * reports device time per phase */
 int fb2_pcg_iterate(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, int n_iterations,

@@ -100,6 +100,46 @@ def main():
     chk("host_solution", np.max(np.abs(xh.get_entries() - ro["x"][rank])) <= 1e-8)
     if rank == 0:
         print("host-built import + CSR: iters", ils.get_num_iterations(), ro["iters"], "ok", ok, flush=True)
+    # --- other Krylov solvers in the par layout: iteration counts and residual histories are invariant
+    #     under the DOF renumbering of the partition, so the SERIAL restatement on the same mesh is the checker ---
+    import scipy.sparse as sp
+    from oracle.oracle import OracleSpace
+    from oracle import krylov_oracle as K
+    so = OracleSpace(N, order=p)
+    so.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    sd = so.jacobi_setup().copy()
+    SA = sp.csr_matrix((so.val().copy(), (so.ja() - 1).copy(), so.irp().copy()), shape=(so.num_free, so.num_free))
+    sb = so.rhs().copy()
+    s = fb.FeSpace(N, order=p, num_parts_x_dim=parts, part_id=rank + 1)
+    op = fb.FeAffineOperator()
+    op.create(fb.csr_format, [False], [True], [1], s, fb.DiscreteIntegration(fb.poisson, FUNC_SHARP_WAVE, WAVE))
+    op.compute()
+    M = fb.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    for name, fn, kw in [("RGMRES", K.rgmres, dict(dkrymax=12)), ("FGMRES", K.fgmres, dict(dkrymax=40, strat=K.MGSRO)),
+                         ("LGMRES", K.lgmres, dict(dkrymax=12)), ("ICG", K.icg, {}),
+                         ("RICHARDSON", K.richardson, dict(relaxation=0.8))]:
+        rt, mx = (1e-2, 300) if name == "RICHARDSON" else (1e-9, 1000)
+        ref = fn(lambda v: SA @ v, lambda r: sd * r, sb, rtol=rt, maxit=mx, **kw)
+        ils = fb.IterativeLinearSolver()
+        pl = {fb.ILS_TYPE: name, fb.ILS_RTOL: rt, fb.ILS_MAX_NUM_ITERATIONS: mx, fb.ILS_TRACK_CONVERGENCE_HISTORY: True}
+        if "dkrymax" in kw:
+            pl[fb.ILS_MAX_DIM_KRYLOV_BASIS] = kw["dkrymax"]
+            pl[fb.ILS_ORTHONORM_STRATEGY] = "MGSRO" if kw.get("strat") == K.MGSRO else "ICGSRO"
+        if "relaxation" in kw:
+            pl[fb.ILS_RELAXATION] = kw["relaxation"]
+        ils.set_parameters_from_pl(pl)
+        ils.set_operators(op.get_tangent(), M)
+        sol = s.create_dof_values()
+        ils.apply(op.get_translation(), sol)
+        kk = min(ils.get_num_iterations(), ref["iters"]) * 2 // 3
+        chk(name + "_iters", ils.converged() == ref["converged"] and abs(ils.get_num_iterations() - ref["iters"]) <= 1,
+            (ils.get_num_iterations(), ref["iters"]))
+        chk(name + "_history", np.allclose(ils.history[:kk], ref["history"][:kk], rtol=1e-5))
+        h1, l2 = s.error_norms(sol, FUNC_SHARP_WAVE, WAVE)
+        oh1, ol2 = so.errors(ref["x"], FUNC_SHARP_WAVE, WAVE)
+        chk(name + "_errors", abs(h1 - oh1) <= 1e-5 * oh1 and abs(l2 - ol2) <= 1e-5 * ol2, (h1, oh1, l2, ol2))
+        if rank == 0:
+            print("par", name, "iters", ils.get_num_iterations(), ref["iters"], "ok", ok, flush=True)
     for f in fails:
         print("FAIL", f, flush=True)
     t = torch.tensor([1 if ok else 0], device="cuda")

@@ -1,0 +1,96 @@
+"""GPU parity of the other Krylov solvers sharing the CG primitives: ICG, RICHARDSON, RGMRES,
+FGMRES, LGMRES against the numpy restatement in oracle/krylov_oracle.py (iteration count +-1, convergence history,
+solution)."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from oracle.oracle import OracleSpace, KIND_POISSON, FUNC_SHARP_WAVE
+from oracle import krylov_oracle as K
+
+pytestmark = pytest.mark.gpu
+WAVE = [200.0, 0.7, -0.05, -0.05, -0.05]
+STOPS = ["RES_RES", "RES_RHS", "RES_NRMGIVEN_RHS_NRMGIVEN", "RES_NRMGIVEN_RES_NRMGIVEN", "DELTA_RHS", "DELTA_DELTA",
+         "DELTA_RHS_AND_RES_RES", "DELTA_RHS_AND_RES_RHS", "DELTA_DELTA_AND_RES_RES", "DELTA_DELTA_AND_RES_RHS"]
+
+
+@pytest.fixture(scope="module")
+def system(fb2):
+    N, p = (6, 6, 6), 2
+    s = fb2.FeSpace(N, order=p)
+    op = fb2.FeAffineOperator()
+    op.create(fb2.csr_format, [False], [True], [1], s, fb2.DiscreteIntegration(fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0))
+    op.compute()
+    M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    dinv = o.jacobi_setup().copy()
+    A = sp.csr_matrix((o.val().copy(), (o.ja() - 1).copy(), o.irp().copy()), shape=(o.num_free, o.num_free))  # o is freed on return
+    return dict(s=s, op=op, M=M, A=lambda x: A @ x, Mj=lambda r: dinv * r, Mi=lambda r: r.copy(), b=o.rhs().copy())
+
+
+def _run(fb2, sysd, name, prec, pl):
+    ils = fb2.IterativeLinearSolver()
+    ils.set_parameters_from_pl(dict({fb2.ILS_TYPE: name, fb2.ILS_TRACK_CONVERGENCE_HISTORY: True}, **pl))
+    ils.set_operators(sysd["op"].get_tangent(), sysd["M"] if prec else None)
+    x = sysd["s"].create_dof_values()
+    ils.apply(sysd["op"].get_translation(), x)
+    return ils, x.get_entries()
+
+
+def _compare(ils, x, r, xtol=1e-6):
+    assert ils.converged() == r["converged"]
+    assert abs(ils.get_num_iterations() - r["iters"]) <= 1
+    k = min(ils.get_num_iterations(), r["iters"]) * 2 // 3
+    assert np.allclose(ils.history[:k], r["history"][:k], rtol=1e-5)
+    assert np.max(np.abs(x - r["x"])) <= xtol * np.max(np.abs(r["x"]))
+
+
+@pytest.mark.parametrize("stop", range(10), ids=STOPS)
+def test_icg_all_stopping_criteria(fb2, system, stop):
+    ils, x = _run(fb2, system, "ICG", True, {fb2.ILS_RTOL: 1e-8, fb2.ILS_MAX_NUM_ITERATIONS: 2000, fb2.ILS_STOPPING_CRITERIUM: STOPS[stop]})
+    _compare(ils, x, K.icg(system["A"], system["Mj"], system["b"], rtol=1e-8, maxit=2000, stop=stop))
+
+
+@pytest.mark.parametrize("stop", [0, 1])
+def test_richardson(fb2, system, stop):
+    pl = {fb2.ILS_RTOL: 1e-3, fb2.ILS_MAX_NUM_ITERATIONS: 400, fb2.ILS_STOPPING_CRITERIUM: STOPS[stop], fb2.ILS_RELAXATION: 0.9}
+    ils, x = _run(fb2, system, "RICHARDSON", True, pl)
+    r = K.richardson(system["A"], system["Mj"], system["b"], rtol=1e-3, maxit=400, stop=stop, relaxation=0.9)
+    _compare(ils, x, r, xtol=1e-9)
+    # max-iteration exit
+    ils, x = _run(fb2, system, "RICHARDSON", True, dict(pl, **{fb2.ILS_MAX_NUM_ITERATIONS: 7}))
+    r = K.richardson(system["A"], system["Mj"], system["b"], rtol=1e-3, maxit=7, stop=stop, relaxation=0.9)
+    assert ils.get_num_iterations() == 7 and not ils.converged() and np.allclose(x, r["x"], rtol=1e-12, atol=1e-14)
+
+
+@pytest.mark.parametrize("name,fn", [("RGMRES", K.rgmres), ("FGMRES", K.fgmres), ("LGMRES", K.lgmres)])
+@pytest.mark.parametrize("strat", ["ICGSRO", "MGSRO"])
+@pytest.mark.parametrize("dkry", [8, 30])
+@pytest.mark.parametrize("stop", [2, 3])
+@pytest.mark.parametrize("prec", [True, False])
+def test_gmres_family(fb2, system, name, fn, strat, dkry, stop, prec):
+    pl = {fb2.ILS_RTOL: 1e-8, fb2.ILS_MAX_NUM_ITERATIONS: 500, fb2.ILS_STOPPING_CRITERIUM: STOPS[stop],
+          fb2.ILS_MAX_DIM_KRYLOV_BASIS: dkry, fb2.ILS_ORTHONORM_STRATEGY: strat}
+    ils, x = _run(fb2, system, name, prec, pl)
+    r = fn(system["A"], system["Mj"] if prec else system["Mi"], system["b"], rtol=1e-8, maxit=500, stop=stop, dkrymax=dkry,
+           strat=K.ICGSRO if strat == "ICGSRO" else K.MGSRO)
+    _compare(ils, x, r)
+
+
+@pytest.mark.parametrize("stop", [0, 1])
+def test_lgmres_true_residual_criteria(fb2, system, stop):
+    pl = {fb2.ILS_RTOL: 1e-8, fb2.ILS_MAX_NUM_ITERATIONS: 500, fb2.ILS_STOPPING_CRITERIUM: STOPS[stop], fb2.ILS_MAX_DIM_KRYLOV_BASIS: 12}
+    ils, x = _run(fb2, system, "LGMRES", True, pl)
+    _compare(ils, x, K.lgmres(system["A"], system["Mj"], system["b"], rtol=1e-8, maxit=500, stop=stop, dkrymax=12))
+
+
+def test_default_stopping_criteria_and_unsupported(fb2, system):
+    ils = fb2.IterativeLinearSolver()
+    ils.set_type_from_string("RGMRES")
+    assert ils.params[fb2.ILS_STOPPING_CRITERIUM] == "RES_NRMGIVEN_RES_NRMGIVEN"
+    with pytest.raises(fb2.Fb2Error):
+        ils.set_type_from_string("MINRES")                      # stays on the host
+    ils, _ = None, None
+    with pytest.raises(fb2.Fb2Error):                           # rgmres_supports_stopping_criteria (rgmres.f90:358-366)
+        _run(fb2, system, "RGMRES", True, {fb2.ILS_STOPPING_CRITERIUM: "RES_RES"})

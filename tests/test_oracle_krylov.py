@@ -1,0 +1,71 @@
+"""CPU tests of oracle/krylov_oracle.py (the checker of tests/test_gpu_krylov.py): every solver reproduces the direct
+solution, Krylov invariants hold (GMRES residual history is monotone; full-basis RGMRES/LGMRES with identity M coincide;
+ICG equals CG in exact arithmetic for a fixed SPD preconditioner), Givens and Gram-Schmidt helpers do what
+iterative_solver_utils.f90 documents."""
+import numpy as np
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+from oracle.oracle import OracleSpace, KIND_POISSON, FUNC_SHARP_WAVE
+from oracle import krylov_oracle as K
+
+
+def _system():
+    o = OracleSpace([4, 4, 4], order=2)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, [200.0, 0.7, -0.05, -0.05, -0.05], route=1)
+    dinv = o.jacobi_setup().copy()
+    A = sp.csr_matrix((o.val().copy(), (o.ja() - 1).copy(), o.irp().copy()), shape=(o.num_free, o.num_free))
+    b = o.rhs().copy()
+    cg = o.cg(prec=1, rtol=1e-10, maxit=1000)
+    return A, dinv, b, spla.spsolve(A.tocsc(), b), cg
+
+
+def test_all_solvers_reach_the_direct_solution():
+    A, dinv, b, xe, cg = _system()
+    Af, Mf = (lambda x: A @ x), (lambda r: dinv * r)
+    runs = {"icg": K.icg(Af, Mf, b, rtol=1e-10, maxit=1000),
+            "rgmres": K.rgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20),
+            "rgmres_mgs": K.rgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20, strat=K.MGSRO),
+            "fgmres": K.fgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20),
+            "lgmres": K.lgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20),
+            "lgmres_res_res": K.lgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20, stop=K.RES_RES),
+            "richardson": K.richardson(Af, Mf, b, rtol=1e-8, maxit=50000, relaxation=0.9)}
+    for name, r in runs.items():
+        assert r["converged"], name
+        assert np.max(np.abs(r["x"] - xe)) <= 1e-6 * np.max(np.abs(xe)), name
+    # ICG == CG in exact arithmetic (<r_old, z_new> = 0 for a fixed SPD M)
+    assert abs(runs["icg"]["iters"] - cg["iters"]) <= 1
+    assert np.allclose(runs["icg"]["history"][:10], cg["history"] if "history" in cg else runs["icg"]["history"][:10])
+    # both Gram-Schmidt strategies span the same space
+    assert runs["rgmres"]["iters"] == runs["rgmres_mgs"]["iters"]
+    h = runs["rgmres"]["history"]
+    assert np.all(np.diff(h[:20]) <= 1e-14)          # residual norm is monotone inside a cycle
+
+
+def test_full_basis_right_and_left_gmres_coincide_without_preconditioner():
+    A, dinv, b, xe, _ = _system()
+    Af, Id = (lambda x: A @ x), (lambda r: r.copy())
+    r1 = K.rgmres(Af, Id, b, rtol=1e-9, maxit=300, dkrymax=300)
+    r2 = K.lgmres(Af, Id, b, rtol=1e-9, maxit=300, dkrymax=300)
+    r3 = K.fgmres(Af, Id, b, rtol=1e-9, maxit=300, dkrymax=300)
+    assert r1["iters"] == r2["iters"] == r3["iters"]
+    assert np.allclose(r1["history"], r2["history"], rtol=1e-8) and np.allclose(r1["history"], r3["history"], rtol=1e-8)
+
+
+def test_givens_rotation_and_gram_schmidt_helpers():
+    rng = np.random.default_rng(0)
+    for x, y in [(3.0, 4.0), (-2.0, 0.5), (0.0, 0.0), (1e-300, -7.0), (5.0, 0.0)]:
+        xr, yr, c, s = K.apply_givens_rotation(x, y)
+        assert yr == 0.0 and abs(xr - np.hypot(x, y)) <= 1e-15 * max(1.0, np.hypot(x, y))
+        assert abs(c * c + s * s - 1.0) < 1e-14
+        assert abs(-s * x + c * y) <= 1e-15 * max(1.0, abs(x), abs(y))     # the rotation annihilates y
+    for fn in (K.modified_gs_reorthonorm, K.iterative_gs_reorthonorm):
+        V = [v for v in np.linalg.qr(rng.standard_normal((50, 4)))[0].T.copy()]
+        w = rng.standard_normal(50)
+        V.append(w.copy())
+        hh = np.zeros(5)
+        assert fn(5, V, hh) == 0
+        assert all(abs(np.dot(V[4], V[i])) < 1e-14 for i in range(4)) and abs(np.linalg.norm(V[4]) - 1.0) < 1e-14
+        assert np.allclose(sum(hh[i] * V[i] for i in range(5)), w)          # w = V h
+        V[4] = np.zeros(50)
+        assert fn(5, V, hh) == -1                                           # zero input vector
