@@ -248,6 +248,15 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    # DRAM bytes per SpMV launch from the committed ncu capture of this workload (profiles/r1_spmv_traffic.json), else null
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_spmv_traffic.json")))
+        key = "Q%d_%d_parts%d" % (a.order, cells, world)
+        if key in tr:
+            traffic = tr[key]["dram_bytes_per_launch"]
+    except Exception:
+        pass
     per_gpu_bytes = spmv_bytes(n_loc, nnz_loc)
     achieved = per_gpu_bytes / (np.mean(spmv_ms) / a.cg_iters * 1e-3) / 1e9
     asm_bytes = nnz_loc * 8 + n_loc * 8
@@ -261,13 +270,17 @@ def main():
             "assembly_mdof_per_s": asm_mdofs, "assembly_ms": asm_t, "pcg_ms_per_iteration": cg_t / a.cg_iters,
             "spmv_ms": spmv_t, "setup_ms": {"fe_space": t_space * 1e3, "csr_pattern": t_pattern_ms, "scatter_map": t_map_ms},
             "wall_ms_per_step": wall_t,
-            "roofline": {"bound": "hbm", "kernel": "k_spmv_stream<true> (TMA-streamed CSR row tiles + fused <Ap,p>)" if a.spmv_variant == 0 else "k_spmv<true> (warp-per-row)", "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": "k_spmv_stream<true> (TMA-streamed CSR row tiles, short-lived CTAs over 32 tiles, fused <Ap,p>)" if a.spmv_variant == 0 else "k_spmv<true> (warp-per-row)", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": per_gpu_bytes,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650"},
             "roofline_assembly": {"bound": "hbm", "kernel": "k_assemble_fast<2,1,atomic>" if (a.asm_variant == 0 and a.order <= 2) else "k_assemble_generic", "achieved": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9,
                                   "peak": peak, "unit": "GB/s", "frac": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9 / peak},
             "clocks": clk.summary(), "e2e": e2e,
-            "gpu_launches": a.steps * (3 + 2 + 9 + 6 * a.cg_iters)}
+            # kernels of libfempar_b200.so per step: Dirichlet interpolation + memsets/assembly (3), Jacobi set-up (2), PCG set-up
+            # (9), then per PCG iteration: serial 6 (SpMV, 2 partial reductions, x/r update, scalars, p update); par 14 (two
+            # SpMV launches, 4 pack/unpack kernels, interface dot, reductions, updates; NCCL's own kernels not counted)
+            "gpu_launches": a.steps * (3 + 2 + 9 + (6 if world == 1 else 14) * a.cg_iters)}
     if not a.no_cpu_baseline:
         r = cpu_reference_run(a.cpu_cells, a.order, a.cg_iters, 1, 0)
         line["cpu_baseline"] = {"value": r["spmv_gbs"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],

@@ -457,7 +457,7 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
   if (!par && !A->sym) {
     FB2_TRY(spmv_local(A, W.p, W.Ap, true, W.st, &g));                       // Ap = A p, partial <Ap,p> fused
     if (ev_spmv1) cudaEventRecord(ev_spmv1, s);
-    k_reduce_partials<<<1, 256, 0, s>>>(part, g, 0, 1, &W.st->App);
+    k_reduce_partials<<<1, 1024, 0, s>>>(part, g, 0, 1, &W.st->App);
   } else if (par && !A->sym && g_spmv_variant == 0 && g_par_overlap) {
     // Overlapped par apply (par_sparse_matrix.f90:739-762): interface rows are numbered last, so
     //   (1) the tiles holding interface rows run first,
