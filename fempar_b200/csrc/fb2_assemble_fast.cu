@@ -13,6 +13,7 @@
 //     (tutorial_01_..._modules.f90:114-128, par_test_poisson_discrete_integration.f90:117-131).
 // (3) Scatter: RED.ADD.F64 (atomic variant) or plain read-modify-write on one colour class (colored variant)
 //     into val[slot]; strong Dirichlet columns go to the RHS (sbm_fe_cell_iterator.i90:1610-1637).
+#include <stdlib.h>
 #include "fb2_assemble.cuh"
 
 // ------------------------------------------------------------------------------------------
@@ -257,7 +258,10 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
   __shared__ double s_gfix[WARPS * CPW][ND];
   __shared__ i64 s_base[WARPS * CPW][ND];
   __shared__ int s_gid[WARPS * CPW][ND];
+  constexpr bool TABSTAGE = ND * ND * 2 <= 2048;     // per-cell staging of non-interior tables: Q1, Q2 scalar, vector Q1
   __shared__ unsigned short s_tabc[TABCACHE ? ND * ND : 2];
+  __shared__ unsigned short s_tabw[TABSTAGE ? WARPS * CPW : 1][TABSTAGE ? ND * ND : 2];
+  int staged = -1;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sub = CPW > 1 ? lane / NN : 0, j0 = CPW > 1 ? lane - sub * NN : lane;
   const bool lane_on = lane < CPW * NN || CPL > 1;
@@ -279,6 +283,9 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
   }
   const bool has_source = A.kind == FB2_KIND_POISSON && A.fn.kind == FB2_FUNC_SHARP_WAVE;
   const int stride = gridDim.x * WARPS * CPW;
+  double dN[3], rN[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { dN[k] = (double)A.g.N[k]; rN[k] = 1.0 / dN[k]; }
   // total-box position and lexicographic index of the ci-th cell of this launch
   auto cell_pos = [&](int ci, int* ijk) {
     int r = ci;
@@ -351,8 +358,26 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
     if (on) {
       int ijk[3];
       cell_pos(ci, ijk);
+      // vertex coordinates (first + ijk + {0,1}) / N (uniform_hex_mesh_generator.f90:608-635): the quotient is formed with the
+      // precomputed reciprocal and one residual correction (q0 = a*y; r = fma(-q0, N, a); q = fma(r, y, q0)), which gives the
+      // correctly rounded a/N in 3 DFMA-class operations instead of the ~25-instruction IEEE division sequence per coordinate
       double X[8][3];
-      cell_vertices(A.g, ijk, X);
+      if constexpr (P >= 3) cell_vertices(A.g, ijk, X);   // Q3 is at the 255-register limit: the two extra invariants spill
+      else {
+        double lohi[3][2];
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            const double a = (double)(A.g.first[k] + ijk[k] + b);
+            const double q0 = a * rN[k];
+            lohi[k][b] = fma(fma(-q0, dN[k], a), rN[k], q0);
+          }
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+#pragma unroll
+          for (int k = 0; k < 3; ++k) X[a][k] = lohi[k][(a >> k) & 1];
+      }
 #pragma unroll
       for (int jj = 0; jj < CPL; ++jj) {
         const int q = j0 + 32 * jj;
@@ -379,11 +404,22 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
         }
       }
     }
+    const bool use_common = have_cache && tab_cur == F.common_tab;
+    if constexpr (TABSTAGE) {
+      if (on && !use_common && staged != tab_cur) {      // the lanes of this cell stage its (boundary-class or explicit) table
+        const unsigned short* src = F.tabs + (size_t)tab_cur * (ND * ND);
+        constexpr int NL = CPW > 1 ? NN : (NN < 32 ? NN : 32);
+        for (int e = j0; e < ND * ND; e += NL) s_tabw[slot][e] = src[e];
+        staged = tab_cur;
+      }
+    }
     any_dir = __any_sync(0xffffffffu, any_dir);
     __syncwarp();
     if (on) {
-      const unsigned short* tab = (have_cache && tab_cur == F.common_tab) ? (const unsigned short*)s_tabc
-                                                                          : F.tabs + (size_t)tab_cur * (ND * ND);
+      // scatter table in shared memory: the block-wide copy of the interior position class or this cell's staged copy
+      const unsigned short* tab;
+      if constexpr (TABSTAGE) tab = use_common ? (const unsigned short*)s_tabc : (const unsigned short*)s_tabw[slot];
+      else tab = use_common ? (const unsigned short*)s_tabc : F.tabs + (size_t)tab_cur * (ND * ND);
 #pragma unroll 1
       for (int jj = 0; jj < CPL; ++jj) {
         const int j = j0 + 32 * jj;
