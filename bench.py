@@ -147,6 +147,11 @@ def main():
     a = parse()
     if a.impl == "reference":
         return run_reference(a)
+    # Everything native libraries write to stdout during the run (e.g. "NCCL version ..." when NCCL_DEBUG=VERSION) goes to
+    # stderr: stdout carries exactly ONE JSON line, printed by rank 0 at the end.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     import fempar_b200 as fb
@@ -285,7 +290,10 @@ def main():
         r = cpu_reference_run(a.cpu_cells, a.order, a.cg_iters, 1, 0)
         line["cpu_baseline"] = {"value": r["spmv_gbs"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
                                 "assembly_mdof_per_s": r["asm_mdofs"]}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
+    os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()
 
