@@ -186,8 +186,9 @@ struct FastArgs {
 //   E[i][j] = sum_q  C[q1][i1] B[q2][i2] B[q3][i3] t0 + B[q1][i1] C[q2][i2] B[q3][i3] t1 + B[q1][i1] B[q2][i2] C[q3][i3] t2
 // contracted direction by direction: 9 (t) + 9 (x) + 9 (y) + 6 (z) FMA per quadrature point for p = 2, i.e. 891 DFMA
 // per column instead of the 2430 of the dense q-loop, and no table traffic in the inner loop.
-template <int P>
-__device__ __forceinline__ void column_sumfact(const double (*__restrict__ D)[6], const double* __restrict__ sB,
+// tfun(q, g0, g1, g2, t0, t1, t2) maps the reference gradient of phi_j at quadrature point q to the flux t(q)
+template <int P, class TFun>
+__device__ __forceinline__ void column_sumfact(TFun tfun, const double* __restrict__ sB,
                                                const double* __restrict__ sC, int j, double* __restrict__ acc) {
   constexpr int N1 = P + 1, NN = N1 * N1 * N1;
   const int j1 = j % N1, j2 = (j / N1) % N1, j3 = j / (N1 * N1);
@@ -211,10 +212,8 @@ __device__ __forceinline__ void column_sumfact(const double (*__restrict__ D)[6]
         const int q = q1 + N1 * (q2 + N1 * q3);
         const double b1 = sB[q1 * N1 + j1], c1 = sC[q1 * N1 + j1];
         const double g0 = c1 * m0, g1 = b1 * m1, g2 = b1 * m2;
-        const double* Dq = D[q];
-        const double t0 = Dq[0] * g0 + Dq[1] * g1 + Dq[2] * g2;
-        const double t1 = Dq[1] * g0 + Dq[3] * g1 + Dq[4] * g2;
-        const double t2 = Dq[2] * g0 + Dq[4] * g1 + Dq[5] * g2;
+        double t0, t1, t2;
+        tfun(q, g0, g1, g2, t0, t1, t2);
 #pragma unroll
         for (int i1 = 0; i1 < N1; ++i1) {
           a0[i1] = fma(c_C1[P - 1][q1 * N1 + i1], t0, a0[i1]);
@@ -242,8 +241,15 @@ __device__ __forceinline__ void column_sumfact(const double (*__restrict__ D)[6]
 // cells ahead in registers: the ncu source view of the previous version showed 32 % of the stall samples as long-scoreboard
 // waits on exactly these dependent loads (perm -> gids -> irp / fixed) and on the per-entry scatter-table loads; the table of
 // the most frequent position class (interior cells) is now kept in shared memory, as are the geometry-basis gradients.
-template <int P, int NCOMP, bool ATOMIC>
-__global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArgs F, int cells_in_launch) {
+// ELAST (NCOMP = 3 only): isotropic linear elasticity sigma = lambda tr(eps) I + 2 mu eps
+// (par_test_pb_bddc_linear_elasticity/.../sbm_irreducible_discrete_integration.i90:93-125):
+//   E[(i,a),(j,b)] = sum_q w detJ [ lambda G_i^a G_j^b + mu G_i^b G_j^a + delta_ab mu G_i . G_j ],  G = J^-1-mapped gradient,
+// i.e. for column (j,b) and row component a the same sum-factorised contraction with the flux
+//   t_k = w detJ [ lambda B_ak G_j^b + mu B_bk G_j^a + delta_ab mu sum_c B_ck G_j^c ],  B_rk = d xi_k / d x_r.
+template <int P, int NCOMP, bool ATOMIC, bool ELAST>
+__global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assemble_fast(FastArgs F, int cells_in_launch) {
+  static_assert(!ELAST || NCOMP == 3, "elasticity needs 3 components");
+  constexpr int DW = ELAST ? 10 : 6;                 // per quadrature point: B (9) + w detJ, or the symmetric D (6)
   constexpr int N1 = P + 1, NN = N1 * N1 * N1, NQ = NN, ND = NN * NCOMP;
   constexpr int CPW = NN <= 16 ? 32 / NN : 1;        // cells per warp (Q1: 4)
   constexpr int CPL = (NN + 31) / 32;                // columns per lane (Q3: 2)
@@ -253,7 +259,7 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
   const AsmArgs& A = F.a;
   __shared__ double s_B[N1 * N1], s_C[N1 * N1];      // 1-D tables for the lane-dependent factors
   __shared__ double s_gd[NQ * 24], s_qw[NQ];         // trilinear geometry gradients at the quadrature points, weights
-  __shared__ double s_D[WARPS * CPW][NQ][6];
+  __shared__ double s_D[WARPS * CPW][NQ][DW];
   __shared__ double s_fw[WARPS * CPW][NQ];
   __shared__ double s_gfix[WARPS * CPW][ND];
   __shared__ i64 s_base[WARPS * CPW][ND];
@@ -387,12 +393,20 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
           jacobian_at(X, s_gd + q * 24, inv, det);
           const double wd = det * s_qw[q];
           double* D = s_D[slot][q];
-          D[0] = wd * (inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0]);
-          D[1] = wd * (inv[0][0] * inv[0][1] + inv[1][0] * inv[1][1] + inv[2][0] * inv[2][1]);
-          D[2] = wd * (inv[0][0] * inv[0][2] + inv[1][0] * inv[1][2] + inv[2][0] * inv[2][2]);
-          D[3] = wd * (inv[0][1] * inv[0][1] + inv[1][1] * inv[1][1] + inv[2][1] * inv[2][1]);
-          D[4] = wd * (inv[0][1] * inv[0][2] + inv[1][1] * inv[1][2] + inv[2][1] * inv[2][2]);
-          D[5] = wd * (inv[0][2] * inv[0][2] + inv[1][2] * inv[1][2] + inv[2][2] * inv[2][2]);
+          if constexpr (ELAST) {
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+              for (int k = 0; k < 3; ++k) D[r * 3 + k] = inv[r][k];
+            D[9] = wd;
+          } else {
+            D[0] = wd * (inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0]);
+            D[1] = wd * (inv[0][0] * inv[0][1] + inv[1][0] * inv[1][1] + inv[2][0] * inv[2][1]);
+            D[2] = wd * (inv[0][0] * inv[0][2] + inv[1][0] * inv[1][2] + inv[2][0] * inv[2][2]);
+            D[3] = wd * (inv[0][1] * inv[0][1] + inv[1][1] * inv[1][1] + inv[2][1] * inv[2][1]);
+            D[4] = wd * (inv[0][1] * inv[0][2] + inv[1][1] * inv[1][2] + inv[2][1] * inv[2][2]);
+            D[5] = wd * (inv[0][2] * inv[0][2] + inv[1][2] * inv[1][2] + inv[2][2] * inv[2][2]);
+          }
           if (has_source) {
             double xq[3] = {0, 0, 0};
 #pragma unroll
@@ -424,46 +438,96 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : 3)) k_assemble_fast(FastArg
       for (int jj = 0; jj < CPL; ++jj) {
         const int j = j0 + 32 * jj;
         if (j >= NN) break;
-        double acc[NN];
-        column_sumfact<P>(s_D[slot], s_B, s_C, j, acc);
-        // --- element vector of row j: source term and strong Dirichlet columns (E is symmetric: E[j][i] = acc[i]) ---
-        double ev[NCOMP];
+        if constexpr (!ELAST) {
+          double acc[NN];
+          const double (*Dc)[DW] = s_D[slot];
+          column_sumfact<P>([&](int q, double g0, double g1, double g2, double& t0, double& t1, double& t2) {
+            const double* Dq = Dc[q];
+            t0 = Dq[0] * g0 + Dq[1] * g1 + Dq[2] * g2;
+            t1 = Dq[1] * g0 + Dq[3] * g1 + Dq[4] * g2;
+            t2 = Dq[2] * g0 + Dq[4] * g1 + Dq[5] * g2;
+          }, s_B, s_C, j, acc);
+          // --- element vector of row j: source term and strong Dirichlet columns (E is symmetric: E[j][i] = acc[i]) ---
+          double ev[NCOMP];
 #pragma unroll
-        for (int cc = 0; cc < NCOMP; ++cc) ev[cc] = 0.0;
-        if (has_source) {
-          const int j1 = j % N1, j2 = (j / N1) % N1, j3 = j / (N1 * N1);
-          double sacc = 0.0;
-#pragma unroll 1
-          for (int q = 0; q < NQ; ++q) {
-            const int q1 = q % N1, q2 = (q / N1) % N1, q3 = q / (N1 * N1);
-            sacc += s_fw[slot][q] * (s_B[q1 * N1 + j1] * s_B[q2 * N1 + j2] * s_B[q3 * N1 + j3]);
-          }
-          ev[0] = sacc;
-        }
-        if (any_dir) {
-#pragma unroll
-          for (int cc = 0; cc < NCOMP; ++cc) {
+          for (int cc = 0; cc < NCOMP; ++cc) ev[cc] = 0.0;
+          if (has_source) {
+            const int j1 = j % N1, j2 = (j / N1) % N1, j3 = j / (N1 * N1);
             double sacc = 0.0;
-#pragma unroll
-            for (int i = 0; i < NN; ++i) sacc += acc[i] * s_gfix[slot][cc * NN + i];
-            ev[cc] -= sacc;
+#pragma unroll 1
+            for (int q = 0; q < NQ; ++q) {
+              const int q1 = q % N1, q2 = (q / N1) % N1, q3 = q / (N1 * N1);
+              sacc += s_fw[slot][q] * (s_B[q1 * N1 + j1] * s_B[q2 * N1 + j2] * s_B[q3 * N1 + j3]);
+            }
+            ev[0] = sacc;
           }
-        }
-        // --- scatter through the precomputed map ---
+          if (any_dir) {
 #pragma unroll
-        for (int cc = 0; cc < NCOMP; ++cc) {
+            for (int cc = 0; cc < NCOMP; ++cc) {
+              double sacc = 0.0;
 #pragma unroll
-          for (int i = 0; i < NN; ++i) {
-            const int li = cc * NN + i;
-            const unsigned short rel = tab[li * ND + cc * NN + j];
-            if (rel != 0xFFFF) {
-              double* dst = A.val + (s_base[slot][li] + rel);
-              if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
+              for (int i = 0; i < NN; ++i) sacc += acc[i] * s_gfix[slot][cc * NN + i];
+              ev[cc] -= sacc;
             }
           }
-          const int g = s_gid[slot][cc * NN + j];
-          if (g > 0 && g <= A.n_free && ev[cc] != 0.0) {
-            if (ATOMIC) atomicAdd(&A.rhs[g - 1], ev[cc]); else A.rhs[g - 1] += ev[cc];
+          // --- scatter through the precomputed map ---
+#pragma unroll
+          for (int cc = 0; cc < NCOMP; ++cc) {
+#pragma unroll
+            for (int i = 0; i < NN; ++i) {
+              const int li = cc * NN + i;
+              const unsigned short rel = tab[li * ND + cc * NN + j];
+              if (rel != 0xFFFF) {
+                double* dst = A.val + (s_base[slot][li] + rel);
+                if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
+              }
+            }
+            const int g = s_gid[slot][cc * NN + j];
+            if (g > 0 && g <= A.n_free && ev[cc] != 0.0) {
+              if (ATOMIC) atomicAdd(&A.rhs[g - 1], ev[cc]); else A.rhs[g - 1] += ev[cc];
+            }
+          }
+        } else {
+          const double lam = A.lambda, mu = A.mu;
+          const double (*Bc)[DW] = s_D[slot];
+#pragma unroll 1
+          for (int b = 0; b < 3; ++b) {                 // column (j, b)
+            double evb = 0.0;
+#pragma unroll 1
+            for (int a = 0; a < 3; ++a) {               // rows (i, a)
+              double acc[NN];
+              column_sumfact<P>([&](int q, double g0, double g1, double g2, double& t0, double& t1, double& t2) {
+                const double* Bq = Bc[q];
+                const double G0 = Bq[0] * g0 + Bq[1] * g1 + Bq[2] * g2;      // physical gradient of phi_j
+                const double G1 = Bq[3] * g0 + Bq[4] * g1 + Bq[5] * g2;
+                const double G2 = Bq[6] * g0 + Bq[7] * g1 + Bq[8] * g2;
+                const double Ga = a == 0 ? G0 : (a == 1 ? G1 : G2), Gb = b == 0 ? G0 : (b == 1 ? G1 : G2);
+                const double lG = Bq[9] * lam * Gb, mG = Bq[9] * mu * Ga, md = a == b ? Bq[9] * mu : 0.0;
+                const double* Ba = Bq + 3 * a;
+                const double* Bb = Bq + 3 * b;
+                t0 = Ba[0] * lG + Bb[0] * mG + md * (Bq[0] * G0 + Bq[3] * G1 + Bq[6] * G2);
+                t1 = Ba[1] * lG + Bb[1] * mG + md * (Bq[1] * G0 + Bq[4] * G1 + Bq[7] * G2);
+                t2 = Ba[2] * lG + Bb[2] * mG + md * (Bq[2] * G0 + Bq[5] * G1 + Bq[8] * G2);
+              }, s_B, s_C, j, acc);
+              // strong Dirichlet columns through the symmetry E[(j,b),(i,a)] = E[(i,a),(j,b)]
+              if (any_dir) {
+#pragma unroll
+                for (int i = 0; i < NN; ++i) evb -= acc[i] * s_gfix[slot][a * NN + i];
+              }
+#pragma unroll
+              for (int i = 0; i < NN; ++i) {
+                const int li = a * NN + i;
+                const unsigned short rel = tab[li * ND + b * NN + j];
+                if (rel != 0xFFFF) {
+                  double* dst = A.val + (s_base[slot][li] + rel);
+                  if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
+                }
+              }
+            }
+            const int g = s_gid[slot][b * NN + j];
+            if (g > 0 && g <= A.n_free && evb != 0.0) {
+              if (ATOMIC) atomicAdd(&A.rhs[g - 1], evb); else A.rhs[g - 1] += evb;
+            }
           }
         }
       }
@@ -484,13 +548,13 @@ static int load_const_tables(const fb2_space_s* s) {
   return 0;
 }
 
-template <int P, int NCOMP>
+template <int P, int NCOMP, bool ELAST = false>
 static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_variant) {
   constexpr int NN = (P + 1) * (P + 1) * (P + 1), CPW = NN <= 16 ? 32 / NN : 1, WARPS = 4;
   FastArgs F = F0;
   cudaStream_t st = fb2_stream();
   int bps = 0;
-  FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_assemble_fast<P, NCOMP, true>, WARPS * 32, 0));
+  FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_assemble_fast<P, NCOMP, true, ELAST>, WARPS * 32, 0));
   if (bps < 1) bps = 1;
   auto grid_for = [&](int ncell) {
     i64 need = ((i64)ncell + WARPS * CPW - 1) / (WARPS * CPW), cap = (i64)fb2_num_sms() * bps;
@@ -499,14 +563,14 @@ static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_var
   if (scatter_variant == FB2_SCATTER_ATOMIC) {
     F.a.color = -1;
     const int ncell = s->m.n_local;
-    k_assemble_fast<P, NCOMP, true><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
+    k_assemble_fast<P, NCOMP, true, ELAST><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
   } else {
     for (int color = 0; color < 8; ++color) {
       F.a.color = color;
       int ncell = 1;
       for (int k = 0; k < 3; ++k) ncell *= (s->m.nloc[k] - ((color >> k) & 1) + 1) / 2;
       if (ncell == 0) continue;
-      k_assemble_fast<P, NCOMP, false><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
+      k_assemble_fast<P, NCOMP, false, ELAST><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
     }
   }
   FB2_CUDA(cudaGetLastError());
@@ -516,12 +580,15 @@ static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_var
 // returns 0 when the fast path ran, -1 when it does not apply (the caller uses the generic kernel), >0 on error
 int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant) {
   const fb2_space_s* s = A->s;
-  if (args.kind == FB2_KIND_ELASTICITY || s->rt.p > 3) return -1;
+  if (s->rt.p > 3) return -1;
+  if (args.kind == FB2_KIND_ELASTICITY && (s->rt.ncomp != 3 || s->rt.p > 2)) return -1;   // Q3 elasticity: generic kernel
   FB2_TRY(fb2_build_scatter_map(A));
   if (A->map_state != 1) return -1;
   FB2_TRY(load_const_tables(s));
   FastArgs F;
   F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs; F.common_tab = A->common_tab;
+  if (args.kind == FB2_KIND_ELASTICITY)
+    return s->rt.p == 1 ? launch_fast<1, 3, true>(F, s, scatter_variant) : launch_fast<2, 3, true>(F, s, scatter_variant);
   if (s->rt.p == 1) return s->rt.ncomp == 1 ? launch_fast<1, 1>(F, s, scatter_variant) : launch_fast<1, 3>(F, s, scatter_variant);
   if (s->rt.p == 2) return s->rt.ncomp == 1 ? launch_fast<2, 1>(F, s, scatter_variant) : launch_fast<2, 3>(F, s, scatter_variant);
   return s->rt.ncomp == 1 ? launch_fast<3, 1>(F, s, scatter_variant) : launch_fast<3, 3>(F, s, scatter_variant);

@@ -142,7 +142,7 @@ int fb2_csr_set_values(fb2_matrix_t A, const double* val_host);
 int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind, int func, const double* func_params,
                            const double* mat_params, int scatter_variant);
 /* assembly kernel variant: 0 = register-blocked contraction + precomputed cell-local -> CSR-slot scatter map where it
- * applies (Poisson / vector Laplacian, Q1-Q2; default), 1 = generic warp-per-cell kernel that searches ja (all kinds/orders) */
+ * applies (Poisson / vector Laplacian Q1-Q3, elasticity Q1-Q2; default), 1 = generic warp-per-cell kernel that searches ja (all kinds/orders) */
 int fb2_set_assembly_variant(int variant);
 /* y = A x : csr apply_body (csr_sparse_matrix.f90:626-672); par: + comm() (par_sparse_matrix.f90:739-762) */
 int fb2_spmv(fb2_matrix_t A, fb2_vector_t x, fb2_vector_t y);
