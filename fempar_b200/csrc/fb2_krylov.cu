@@ -334,6 +334,208 @@ static int gmres_solve(fb2_matrix_s* A, const double* dinv, const double* b, dou
   return 0;
 }
 
+// LU with partial pivoting of the k x k leading block (column-major, leading dimension ld) and solve: what
+// dgetrf/dgetrs do in lfom.f90:250-262 (LAPACK is third party; same algorithm, unblocked).  Returns false if singular.
+static bool lu_solve(const std::vector<double>& hh, int ld, int k, double* g) {
+  std::vector<double> a((size_t)k * k);
+  for (int j = 0; j < k; ++j)
+    for (int i = 0; i < k; ++i) a[(size_t)j * k + i] = hh[(size_t)j * ld + i];
+  for (int c = 0; c < k; ++c) {
+    int piv = c;
+    for (int i = c + 1; i < k; ++i)
+      if (fabs(a[(size_t)c * k + i]) > fabs(a[(size_t)c * k + piv])) piv = i;
+    if (a[(size_t)c * k + piv] == 0.0) return false;
+    if (piv != c) {
+      for (int j = 0; j < k; ++j) std::swap(a[(size_t)j * k + c], a[(size_t)j * k + piv]);
+      std::swap(g[c], g[piv]);
+    }
+    for (int i = c + 1; i < k; ++i) {
+      const double l = a[(size_t)c * k + i] / a[(size_t)c * k + c];
+      a[(size_t)c * k + i] = l;
+      for (int j = c + 1; j < k; ++j) a[(size_t)j * k + i] -= l * a[(size_t)j * k + c];
+      g[i] -= l * g[c];
+    }
+  }
+  for (int i = k - 1; i >= 0; --i) {
+    for (int j = i + 1; j < k; ++j) g[i] -= a[(size_t)j * k + i] * g[j];
+    g[i] /= a[(size_t)i * k + i];
+  }
+  return true;
+}
+
+// lfom.f90:124-330: left-preconditioned full orthogonalisation method; RES_RES / RES_RHS on the true residual.
+// Restated as written, including g(1) = the INITIAL preconditioned residual norm after a restart (lfom.f90:247).
+static int lfom_solve(fb2_matrix_s* A, const double* dinv, const double* b, double* x, const fb2_ils_params_t* prm, int dkrymax,
+                      int strat, int* iters, int* conv, double* err, double* hist) {
+  const i64 n = A->n;
+  const int stop = prm->stopping_criterium, maxit = prm->max_num_iterations;
+  FB2_CHECK(stop == FB2_STOP_RES_RES || stop == FB2_STOP_RES_RHS, "LFOM supports RES_RES and RES_RHS (lfom.f90:345-352)");
+  FB2_CHECK(strat == FB2_ORTHO_MGSRO || strat == FB2_ORTHO_ICGSRO, "unknown orthonormalisation strategy");
+  int m = dkrymax < maxit ? dkrymax : maxit;
+  if (m < 1) m = 1;
+  const int ld = m + 1;
+  KrylovWork W;
+  double *r, *z;
+  FB2_TRY(W.get(&r, n)); FB2_TRY(W.get(&z, n));
+  std::vector<double*> V((size_t)m + 1);
+  for (auto& p : V) FB2_TRY(W.get(&p, n));
+  std::vector<double> hh((size_t)ld * m, 0.0), g((size_t)m + 1, 0.0);
+  double rhs_norm = 0.0, res_norm = 0.0, res_2_norm = 0.0, res_norm_initial, tol, e;
+  if (stop == FB2_STOP_RES_RHS) FB2_TRY(nrm2(A, b, n, &rhs_norm));
+  FB2_TRY(fb2_dev_init(x, 0.0, n));
+  FB2_TRY(fb2_op_apply(A, x, r));
+  FB2_TRY(fb2_dev_axpby(r, 1.0, b, -1.0, n));
+  FB2_TRY(nrm2(A, r, n, &res_2_norm));
+  FB2_TRY(fb2_dev_apply_M(dinv, r, z, n));
+  FB2_TRY(nrm2(A, z, n, &res_norm));
+  res_norm_initial = res_norm;
+  tol = prm->rtol * (stop == FB2_STOP_RES_RES ? res_2_norm : rhs_norm) + prm->atol;
+  e = res_2_norm;
+  bool exit_loop = e <= tol, have_z = false, failed = false;
+  int it = 0, ierrc = 0;
+  while (!exit_loop && it < maxit && !failed) {
+    std::fill(hh.begin(), hh.end(), 0.0);
+    if (it != 0) {
+      FB2_TRY(fb2_op_apply(A, x, r));
+      FB2_TRY(fb2_dev_axpby(r, 1.0, b, -1.0, n));
+      FB2_TRY(fb2_dev_apply_M(dinv, r, z, n));
+      FB2_TRY(nrm2(A, z, n, &res_norm));
+    }
+    if (res_norm != 0.0) FB2_TRY(fb2_dev_scal(V[0], 1.0 / res_norm, z, n));
+    int kloc = 0;
+    while (!exit_loop && it < maxit && kloc < m) {
+      ++kloc; ++it;
+      FB2_TRY(fb2_op_apply(A, V[kloc - 1], r));
+      FB2_TRY(fb2_dev_apply_M(dinv, r, V[kloc], n));
+      double* col = &hh[(size_t)(kloc - 1) * ld];
+      if (strat == FB2_ORTHO_MGSRO) FB2_TRY(modified_gs_reorthonorm(A, kloc + 1, V.data(), n, col, &ierrc));
+      else FB2_TRY(iterative_gs_reorthonorm(A, kloc + 1, V.data(), n, col, &ierrc));
+      if (ierrc < 0) { exit_loop = true; break; }
+      std::fill(g.begin(), g.end(), 0.0);
+      g[0] = res_norm_initial;
+      if (!lu_solve(hh, ld, kloc, g.data())) { failed = true; break; }       // dgetrf info /= 0
+      FB2_CUDA(cudaMemcpyAsync(z, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, fb2_stream()));
+      FB2_TRY(multiaxpy(kloc, V.data(), g.data(), 1.0, z, n));
+      FB2_TRY(fb2_op_apply(A, z, r));
+      FB2_TRY(fb2_dev_axpby(r, 1.0, b, -1.0, n));
+      FB2_TRY(nrm2(A, r, n, &res_2_norm));
+      have_z = true;
+      e = res_2_norm;
+      if (hist) hist[it - 1] = e;
+      exit_loop = e <= tol;
+    }
+    if (failed || ierrc == -2) break;
+    if (have_z) FB2_CUDA(cudaMemcpyAsync(x, z, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, fb2_stream()));
+    exit_loop = e <= tol;
+  }
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  *iters = it; *conv = e <= tol ? 1 : 0; *err = e;
+  return 0;
+}
+
+// minres.f90:361-740: Paige & Saunders' MINRES as adapted in the reference (symmetric, possibly indefinite A; SPD M).
+// Only RES_RES is accepted (minres.f90:764-770); the test applied is phibar <= Anorm * ynorm * rtol + atol.
+static int minres_solve(fb2_matrix_s* A, const double* dinv, const double* b, double* x, const fb2_ils_params_t* prm,
+                        int* iters, int* conv, double* err, double* hist) {
+  const i64 n = A->n;
+  FB2_CHECK(prm->stopping_criterium == FB2_STOP_RES_RES, "MINRES supports RES_RES only (minres.f90:764-770)");
+  const double zero = 0.0, one = 1.0, ten = 10.0, eps = 2.220446049250313e-16;   // epsilon(1.0_rp)
+  const size_t bytes = sizeof(double) * (size_t)n;
+  cudaStream_t st = fb2_stream();
+  KrylovWork W;
+  double *r1, *r2, *v1, *v2, *y, *w, *w1, *w2;
+  FB2_TRY(W.get(&r1, n)); FB2_TRY(W.get(&r2, n)); FB2_TRY(W.get(&v1, n)); FB2_TRY(W.get(&v2, n));
+  FB2_TRY(W.get(&y, n)); FB2_TRY(W.get(&w, n)); FB2_TRY(W.get(&w1, n)); FB2_TRY(W.get(&w2, n));
+  int istop = 0, it = 0;
+  double Anorm = zero, Acond = zero, ynorm = zero, e = zero, tol = zero;
+  FB2_TRY(fb2_dev_init(x, 0.0, n));
+  FB2_TRY(fb2_op_apply(A, x, r1));
+  FB2_TRY(fb2_dev_axpby(r1, 1.0, b, -1.0, n));
+  FB2_TRY(fb2_dev_apply_M(dinv, r1, v1, n));
+  double beta1;
+  FB2_TRY(dot1(A, r1, v1, n, &beta1));
+  if (beta1 < zero) istop = 8;
+  else if (beta1 == zero) istop = 0;
+  else {
+    beta1 = sqrt(beta1);
+    double oldb = zero, beta = beta1, dbar = zero, epsln = zero, qrnorm = beta1, phibar = beta1, rhs1 = beta1, rhs2 = zero;
+    double tnorm2 = zero, ynorm2 = zero, cs = -one, sn = zero, gmax = zero, gmin = zero;
+    FB2_TRY(fb2_dev_init(w, 0.0, n));
+    FB2_TRY(fb2_dev_init(w2, 0.0, n));
+    FB2_CUDA(cudaMemcpyAsync(r2, r1, bytes, cudaMemcpyDeviceToDevice, st));
+    for (;;) {
+      ++it;
+      const double s = one / beta;
+      FB2_TRY(fb2_dev_scal(v2, s, v1, n));
+      FB2_TRY(fb2_op_apply(A, v2, y));
+      if (it >= 2) FB2_TRY(fb2_dev_axpby(y, -(beta / oldb), r1, 1.0, n));
+      double alpha;
+      FB2_TRY(dot1(A, v2, y, n, &alpha));
+      FB2_TRY(fb2_dev_axpby(y, -(alpha / beta), r2, 1.0, n));
+      std::swap(r1, r2);                                             // r1 = r2
+      FB2_CUDA(cudaMemcpyAsync(r2, y, bytes, cudaMemcpyDeviceToDevice, st));   // r2 = y
+      FB2_TRY(fb2_dev_apply_M(dinv, r2, v1, n));
+      oldb = beta;
+      FB2_TRY(dot1(A, r2, v1, n, &beta));
+      if (beta < zero) { istop = 6; break; }
+      beta = sqrt(beta);
+      tnorm2 = tnorm2 + alpha * alpha + oldb * oldb + beta * beta;
+      if (it == 1) {
+        if (beta / beta1 <= ten * eps) istop = -1;
+        gmax = fabs(alpha);
+        gmin = gmax;
+      }
+      const double oldeps = epsln;
+      const double delta = cs * dbar + sn * alpha;
+      const double gbar = sn * dbar - cs * alpha;
+      epsln = sn * beta;
+      dbar = -cs * beta;
+      const double gamma = sqrt(gbar * gbar + beta * beta);
+      cs = gbar / gamma;
+      sn = beta / gamma;
+      const double phi = cs * phibar;
+      phibar = sn * phibar;
+      const double denom = one / gamma;
+      {                                                              // w1 = w2 ; w2 = w ; w = (v - oldeps w1 - delta w2) * denom
+        double* t = w1; w1 = w2; w2 = w; w = t;
+        FB2_CUDA(cudaMemcpyAsync(w, v2, bytes, cudaMemcpyDeviceToDevice, st));
+        FB2_TRY(fb2_dev_axpby(w, -oldeps, w1, 1.0, n));
+        FB2_TRY(fb2_dev_axpby(w, -delta, w2, 1.0, n));
+        FB2_TRY(fb2_dev_scal(w, denom, w, n));
+      }
+      FB2_TRY(fb2_dev_axpby(x, phi, w, 1.0, n));
+      gmax = gmax > gamma ? gmax : gamma;
+      gmin = gmin < gamma ? gmin : gamma;
+      const double z = rhs1 / gamma;
+      ynorm2 = z * z + ynorm2;
+      rhs1 = rhs2 - delta * z;
+      rhs2 = -epsln * z;
+      Anorm = sqrt(tnorm2);
+      ynorm = sqrt(ynorm2);
+      const double epsx = Anorm * ynorm * eps, epsr = Anorm * ynorm * prm->rtol + prm->atol;
+      tol = epsr; e = phibar;
+      qrnorm = phibar;
+      Acond = gmax / gmin;
+      if (istop == 0) {
+        if (it >= prm->max_num_iterations) istop = 5;
+        if (Acond >= 0.1 / eps) istop = 4;
+        if (epsx >= beta1) istop = 3;
+        if (qrnorm <= epsx) istop = 2;
+        if (qrnorm <= epsr) istop = 1;
+      }
+      if (hist) hist[it - 1] = e;
+      if (istop != 0) break;
+    }
+  }
+  (void)tol;
+  FB2_CUDA(cudaStreamSynchronize(st));
+  fb2_record_phase("minres_istop", (double)istop);
+  fb2_record_phase("minres_Anorm", Anorm);
+  fb2_record_phase("minres_Acond", Acond);
+  *iters = it; *conv = (istop == 0 || istop == -1 || istop == 1 || istop == 2) ? 1 : 0; *err = e;
+  return 0;
+}
+
 // iterative_linear_solver_t%apply for every solver type on the device path (factory keys of
 // iterative_linear_solver_creational_methods_dictionary.f90:97-106): x = A^-1 b with x0 = 0
 extern "C" int fb2_ils_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, int ils_type,
@@ -361,8 +563,12 @@ extern "C" int fb2_ils_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, 
       return gmres_solve(A, d, b->d, x->d, prm, 'F', e.dkrymax, e.orthonorm_strat, num_iterations, did_converge, error_estimate, history);
     case FB2_ILS_LGMRES:
       return gmres_solve(A, d, b->d, x->d, prm, 'L', e.dkrymax, e.orthonorm_strat, num_iterations, did_converge, error_estimate, history);
+    case FB2_ILS_LFOM:
+      return lfom_solve(A, d, b->d, x->d, prm, e.dkrymax, e.orthonorm_strat, num_iterations, did_converge, error_estimate, history);
+    case FB2_ILS_MINRES:
+      return minres_solve(A, d, b->d, x->d, prm, num_iterations, did_converge, error_estimate, history);
     default: break;
   }
-  FB2_CHECK(false, "fb2_ils_solve: solver type not on the device path (LFOM, MINRES stay on the host)");
+  FB2_CHECK(false, "fb2_ils_solve: unknown solver type");
   return 2;
 }

@@ -188,7 +188,9 @@ enum {
   FB2_ILS_RICHARDSON = 2,  /* richardson.f90:101-205, RES_RES / RES_RHS */
   FB2_ILS_RGMRES = 3,      /* rgmres.f90:120-356, RES_NRMGIVEN_* */
   FB2_ILS_FGMRES = 4,      /* fgmres.f90:120-356, RES_NRMGIVEN_* */
-  FB2_ILS_LGMRES = 5       /* lgmres.f90:152-420, RES_NRMGIVEN_*, RES_RES, RES_RHS */
+  FB2_ILS_LGMRES = 5,      /* lgmres.f90:152-420, RES_NRMGIVEN_*, RES_RES, RES_RHS */
+  FB2_ILS_LFOM = 6,        /* lfom.f90:124-330, RES_RES / RES_RHS */
+  FB2_ILS_MINRES = 7       /* minres.f90:361-740, RES_RES; istop / Anorm / Acond via fb2_last_phase_ms("minres_istop" ...) */
 };
 enum { FB2_ORTHO_MGSRO = 0, FB2_ORTHO_ICGSRO = 1 };   /* ILS_ORTHONORM_STRAT: iterative_solver_utils.f90:46-106 / :128-196 */
 typedef struct {

@@ -310,3 +310,159 @@ def fgmres(A, M, b, rtol=1e-6, atol=0.0, maxit=1000, stop=RES_NRMGIVEN_RES_NRMGI
 
 def lgmres(A, M, b, rtol=1e-6, atol=0.0, maxit=1000, stop=RES_NRMGIVEN_RES_NRMGIVEN, dkrymax=30, strat=ICGSRO):
     return _gmres(A, M, b, rtol, atol, maxit, stop, dkrymax, strat, 'L')
+
+
+def lfom(A, M, b, rtol=1e-6, atol=0.0, maxit=1000, stop=RES_RES, dkrymax=30, strat=ICGSRO):
+    """lfom.f90:124-330: left-preconditioned full orthogonalisation method; every iteration solves H_k y = beta e_1 by LU with
+    partial pivoting (dgetrf/dgetrs: LAPACK, third party, version unpinned; numpy.linalg.solve is the same algorithm) and
+    forms the true residual.  Supports res_res, res_rhs.  NOTE restated as written: g(1) is the INITIAL preconditioned
+    residual norm also after a restart (lfom.f90:247), although the restarted basis is normalised with the current one."""
+    n = b.size
+    m = dkrymax
+    x = np.zeros(n)
+    V = [None] * (m + 1)
+    rhs_norm = _nrm2(b) if stop == RES_RHS else 0.0
+    r = b - A(x)
+    res_2_norm = _nrm2(r)
+    z = M(r)
+    res_norm = _nrm2(z)
+    res_norm_initial = res_norm
+    tol = rtol * (res_2_norm if stop == RES_RES else rhs_norm) + atol
+    err = res_2_norm
+    exit_loop = err <= tol
+    it, hist, ierrc = 0, [], 0
+    zsol = x.copy()
+    while not exit_loop and it < maxit:
+        hh = np.zeros((m + 1, m))
+        if it != 0:
+            r = b - A(x)
+            z = M(r)
+            res_norm = _nrm2(z)
+        V[0] = z / res_norm if res_norm != 0.0 else x.copy()
+        kloc = 0
+        while not exit_loop and it < maxit and kloc < m:
+            kloc += 1
+            it += 1
+            V[kloc] = M(A(V[kloc - 1]))
+            col = np.zeros(kloc + 1)
+            ierrc = _ortho(strat, kloc + 1, V, col)
+            hh[:kloc + 1, kloc - 1] = col
+            if ierrc < 0:
+                exit_loop = True
+                break
+            g = np.zeros(kloc)
+            g[0] = res_norm_initial
+            try:
+                y = np.linalg.solve(hh[:kloc, :kloc], g)
+            except np.linalg.LinAlgError:
+                return dict(x=x, iters=it, converged=False, err=float(err), history=np.array(hist))
+            zsol = x.copy()
+            for i in range(kloc):
+                zsol += y[i] * V[i]
+            res_2_norm = _nrm2(b - A(zsol))
+            err = res_2_norm
+            hist.append(err)
+            exit_loop = err <= tol
+        if ierrc == -2:
+            break
+        x = zsol.copy()
+        exit_loop = err <= tol
+    return dict(x=x, iters=it, converged=bool(err <= tol), err=float(err), history=np.array(hist))
+
+
+def minres(A, M, b, rtol=1e-6, atol=0.0, maxit=1000):
+    """minres.f90:361-740 (Paige & Saunders' MINRES as adapted in the reference; only res_res is accepted, and the test
+    actually applied is ||r_k||_inv(M) estimate phibar <= Anorm*ynorm*rtol + atol).  Returns istop as well."""
+    eps = np.finfo(np.float64).eps
+    x = np.zeros_like(b)
+    istop, it = 0, 0
+    Anorm = Acond = rnorm = ynorm = 0.0
+    hist = []
+    r1 = b - A(x)
+    v1 = M(r1)
+    beta1 = float(np.dot(r1, v1))
+    err, tol = 0.0, 0.0
+    if beta1 < 0.0:
+        istop = 8
+    elif beta1 == 0.0:
+        istop = 0
+    else:
+        beta1 = np.sqrt(beta1)
+        oldb, beta, dbar, epsln = 0.0, beta1, 0.0, 0.0
+        qrnorm = phibar = rhs1 = beta1
+        rhs2 = tnorm2 = ynorm2 = 0.0
+        cs, sn = -1.0, 0.0
+        w = np.zeros_like(b)
+        w2 = np.zeros_like(b)
+        r2 = r1.copy()
+        gmax = gmin = 0.0
+        while True:
+            it += 1
+            s = 1.0 / beta
+            v2 = s * v1
+            y = A(v2)
+            if it >= 2:
+                y = y - (beta / oldb) * r1
+            alpha = float(np.dot(v2, y))
+            y = y - (alpha / beta) * r2
+            r1 = r2.copy()
+            r2 = y.copy()
+            v1 = M(r2)
+            oldb = beta
+            beta = float(np.dot(r2, v1))
+            if beta < 0.0:
+                istop = 6
+                break
+            beta = np.sqrt(beta)
+            tnorm2 = tnorm2 + alpha ** 2 + oldb ** 2 + beta ** 2
+            if it == 1:
+                if beta / beta1 <= 10.0 * eps:
+                    istop = -1
+                gmax = abs(alpha)
+                gmin = gmax
+            oldeps = epsln
+            delta = cs * dbar + sn * alpha
+            gbar = sn * dbar - cs * alpha
+            epsln = sn * beta
+            dbar = -cs * beta
+            gamma = np.sqrt(gbar ** 2 + beta ** 2)
+            cs = gbar / gamma
+            sn = beta / gamma
+            phi = cs * phibar
+            phibar = sn * phibar
+            denom = 1.0 / gamma
+            w1 = w2.copy()
+            w2 = w.copy()
+            w = (v2 - oldeps * w1 - delta * w2) * denom
+            x = x + phi * w
+            gmax = max(gmax, gamma)
+            gmin = min(gmin, gamma)
+            z = rhs1 / gamma
+            ynorm2 = z ** 2 + ynorm2
+            rhs1 = rhs2 - delta * z
+            rhs2 = -epsln * z
+            Anorm = np.sqrt(tnorm2)
+            ynorm = np.sqrt(ynorm2)
+            epsx = Anorm * ynorm * eps
+            epsr = Anorm * ynorm * rtol + atol
+            tol, err = epsr, phibar
+            qrnorm = phibar
+            rnorm = qrnorm
+            Acond = gmax / gmin
+            if istop == 0:
+                if it >= maxit:
+                    istop = 5
+                if Acond >= 0.1 / eps:
+                    istop = 4
+                if epsx >= beta1:
+                    istop = 3
+                if qrnorm <= epsx:
+                    istop = 2
+                if qrnorm <= epsr:
+                    istop = 1
+            hist.append(err)
+            if istop != 0:
+                break
+    conv = istop in (0, -1, 1, 2)
+    return dict(x=x, iters=it, converged=bool(conv), err=float(err), history=np.array(hist), istop=istop,
+                Anorm=float(Anorm), Acond=float(Acond))

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 import scipy.sparse as sp
 
-from oracle.oracle import OracleSpace, KIND_POISSON, FUNC_SHARP_WAVE
+from oracle.oracle import OracleSpace, KIND_POISSON, FUNC_SHARP_WAVE  # noqa: F401
 from oracle import krylov_oracle as K
 
 pytestmark = pytest.mark.gpu
@@ -90,7 +90,66 @@ def test_default_stopping_criteria_and_unsupported(fb2, system):
     ils.set_type_from_string("RGMRES")
     assert ils.params[fb2.ILS_STOPPING_CRITERIUM] == "RES_NRMGIVEN_RES_NRMGIVEN"
     with pytest.raises(fb2.Fb2Error):
-        ils.set_type_from_string("MINRES")                      # stays on the host
+        ils.set_type_from_string("PARDISO")                     # not an iterative solver key
     ils, _ = None, None
     with pytest.raises(fb2.Fb2Error):                           # rgmres_supports_stopping_criteria (rgmres.f90:358-366)
         _run(fb2, system, "RGMRES", True, {fb2.ILS_STOPPING_CRITERIUM: "RES_RES"})
+
+
+@pytest.mark.parametrize("stop", [0, 1])
+@pytest.mark.parametrize("strat", ["ICGSRO", "MGSRO"])
+@pytest.mark.parametrize("dkry", [60, 10])
+def test_lfom(fb2, system, stop, strat, dkry):
+    """dkry = 10 exercises the restart exactly as the reference writes it (g(1) stays the initial norm, lfom.f90:247): both
+    sides stagnate the same way and stop at max_num_iterations."""
+    pl = {fb2.ILS_RTOL: 1e-9, fb2.ILS_MAX_NUM_ITERATIONS: 60, fb2.ILS_STOPPING_CRITERIUM: STOPS[stop],
+          fb2.ILS_MAX_DIM_KRYLOV_BASIS: dkry, fb2.ILS_ORTHONORM_STRATEGY: strat}
+    ils, x = _run(fb2, system, "LFOM", True, pl)
+    r = K.lfom(system["A"], system["Mj"], system["b"], rtol=1e-9, maxit=60, stop=stop, dkrymax=dkry,
+               strat=K.ICGSRO if strat == "ICGSRO" else K.MGSRO)
+    assert ils.converged() == r["converged"] and abs(ils.get_num_iterations() - r["iters"]) <= 1
+    k = min(ils.get_num_iterations(), r["iters"]) * 2 // 3
+    assert np.allclose(ils.history[:k], r["history"][:k], rtol=1e-5)
+    if r["converged"]:
+        assert np.max(np.abs(x - r["x"])) <= 1e-6 * np.max(np.abs(r["x"]))
+
+
+@pytest.mark.parametrize("prec", [True, False])
+def test_minres_spd(fb2, system, prec):
+    pl = {fb2.ILS_RTOL: 1e-10, fb2.ILS_MAX_NUM_ITERATIONS: 500}
+    ils, x = _run(fb2, system, "MINRES", prec, pl)
+    r = K.minres(system["A"], system["Mj"] if prec else system["Mi"], system["b"], rtol=1e-10, maxit=500)
+    _compare(ils, x, r)
+    assert int(system["op"].last_phase_ms("minres_istop")) == r["istop"]
+    assert abs(system["op"].last_phase_ms("minres_Anorm") - r["Anorm"]) <= 1e-8 * r["Anorm"]
+    # iteration limit: istop = 5, did_converge = .false.
+    ils, x = _run(fb2, system, "MINRES", prec, dict(pl, **{fb2.ILS_MAX_NUM_ITERATIONS: 6}))
+    r = K.minres(system["A"], system["Mj"] if prec else system["Mi"], system["b"], rtol=1e-10, maxit=6)
+    assert ils.get_num_iterations() == 6 and not ils.converged() and r["istop"] == 5
+    assert np.allclose(x, r["x"], rtol=1e-10, atol=1e-13)
+
+
+def test_minres_symmetric_indefinite_host_matrix(fb2):
+    """MINRES is the reference's solver for symmetric INDEFINITE operators: A - sigma I with sigma inside the spectrum,
+    handed over as a host-assembled CSR matrix."""
+    o = OracleSpace((5, 5, 5), order=2)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    n = o.num_free
+    A = sp.csr_matrix((o.val().copy(), (o.ja() - 1).copy(), o.irp().copy()), shape=(n, n))
+    ev = np.linalg.eigvalsh(A.toarray())
+    sigma = 0.5 * (ev[n // 3] + ev[n // 3 + 1])
+    As = (A - sigma * sp.identity(n)).tocsr()
+    As.sort_indices()
+    b = o.rhs().copy()
+    Ad = fb2.SparseMatrix(host_csr=(As.indptr + 1, As.indices + 1, As.data))
+    ils = fb2.IterativeLinearSolver()
+    ils.set_parameters_from_pl({fb2.ILS_TYPE: "MINRES", fb2.ILS_RTOL: 1e-10, fb2.ILS_MAX_NUM_ITERATIONS: 3000,
+                                fb2.ILS_TRACK_CONVERGENCE_HISTORY: True})
+    ils.set_operators(Ad, None)
+    vb, vx = fb2.ScalarArray(n=n), fb2.ScalarArray(n=n)
+    vb.set_entries(b)
+    ils.apply(vb, vx)
+    r = K.minres(lambda v: As @ v, lambda v: v.copy(), b, rtol=1e-10, maxit=3000)
+    assert ils.converged() and r["converged"] and abs(ils.get_num_iterations() - r["iters"]) <= 2
+    xs = np.linalg.solve(As.toarray(), b)
+    assert np.max(np.abs(vx.get_entries() - xs)) <= 1e-6 * np.max(np.abs(xs))

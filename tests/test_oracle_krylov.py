@@ -29,6 +29,8 @@ def test_all_solvers_reach_the_direct_solution():
             "fgmres": K.fgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20),
             "lgmres": K.lgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20),
             "lgmres_res_res": K.lgmres(Af, Mf, b, rtol=1e-10, maxit=1000, dkrymax=20, stop=K.RES_RES),
+            "lfom": K.lfom(Af, Mf, b, rtol=1e-10, maxit=200, dkrymax=200),
+            "minres": K.minres(Af, Mf, b, rtol=1e-12, maxit=1000),
             "richardson": K.richardson(Af, Mf, b, rtol=1e-8, maxit=50000, relaxation=0.9)}
     for name, r in runs.items():
         assert r["converged"], name
@@ -69,3 +71,15 @@ def test_givens_rotation_and_gram_schmidt_helpers():
         assert np.allclose(sum(hh[i] * V[i] for i in range(5)), w)          # w = V h
         V[4] = np.zeros(50)
         assert fn(5, V, hh) == -1                                           # zero input vector
+
+
+def test_minres_on_a_symmetric_indefinite_system():
+    A, dinv, b, xe, _ = _system()
+    n = A.shape[0]
+    ev = np.linalg.eigvalsh(A.toarray())
+    As = (A - 0.5 * (ev[n // 2] + ev[n // 2 + 1]) * sp.identity(n)).tocsr()
+    r = K.minres(lambda v: As @ v, lambda v: v.copy(), b, rtol=1e-11, maxit=5000)
+    xs = np.linalg.solve(As.toarray(), b)
+    assert r["converged"] and r["istop"] == 1
+    assert np.max(np.abs(r["x"] - xs)) <= 1e-6 * np.max(np.abs(xs))
+    assert np.all(np.diff(r["history"]) <= 1e-12)        # MINRES minimises the residual: monotone estimate
