@@ -137,7 +137,8 @@ def test_minres_symmetric_indefinite_host_matrix(fb2):
     n = o.num_free
     A = sp.csr_matrix((o.val().copy(), (o.ja() - 1).copy(), o.irp().copy()), shape=(n, n))
     ev = np.linalg.eigvalsh(A.toarray())
-    sigma = 0.5 * (ev[n // 3] + ev[n // 3 + 1])
+    k = n // 4 + int(np.argmax(np.diff(ev[n // 4:3 * n // 4])))     # widest spectral gap in the middle half
+    sigma = 0.5 * (ev[k] + ev[k + 1])
     As = (A - sigma * sp.identity(n)).tocsr()
     As.sort_indices()
     b = o.rhs().copy()
