@@ -83,6 +83,14 @@ _SIGS = {
                            C.POINTER(C.c_double), _VP],
     "fb2_ils_solve": [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(ILSParams), C.POINTER(ILSExtParams), C.POINTER(C.c_int),
                       C.POINTER(C.c_int), C.POINTER(C.c_double), _VP],
+    "fb2_comm_set_parts_per_rank": [C.c_int],
+    "fb2_vec_comm_multi": [C.c_int, _VP],
+    "fb2_vec_dot_multi": [C.c_int, _VP, _VP, C.POINTER(C.c_double)],
+    "fb2_spmv_multi": [C.c_int, _VP, _VP, _VP],
+    "fb2_jacobi_setup_multi": [C.c_int, _VP, _VP],
+    "fb2_pcg_solve_multi": [C.c_int, _VP, _VP, _VP, _VP, C.POINTER(ILSParams), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                            C.POINTER(C.c_double), _VP],
+    "fb2_pcg_iterate_multi": [C.c_int, _VP, _VP, _VP, _VP, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)],
     "fb2_pcg_iterate": [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)],
     "fb2_error_norms": [_VP, _VP, C.c_int, _VP, C.POINTER(C.c_double), C.POINTER(C.c_double)],
 }

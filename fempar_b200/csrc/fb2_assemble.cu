@@ -179,7 +179,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   a.kind = kind; a.sym = A->sym; a.fn = make_func(func, func_params);
   a.lambda = mat_params ? mat_params[0] : 0.0; a.mu = mat_params ? mat_params[1] : 1.0;
   // the scatter map is set-up (like the reference's COO->CSR compression it is paid once): build it before the timed region
-  if (g_asm_variant == 0 && kind != FB2_KIND_ELASTICITY && s->rt.p <= 3) FB2_TRY(fb2_build_scatter_map(A));
+  if (g_asm_variant == 0 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);

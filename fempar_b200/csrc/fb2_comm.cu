@@ -18,6 +18,17 @@ static int g_rank = 0, g_nranks = 1;
     }                                                                                             \
   } while (0)
 
+// Several sub-domains (parts) per process: part p (1-based, FEMPAR numbering) lives on rank (p-1)/parts_per_rank, e.g. the
+// 8-part layout of BASELINE config 3 on 2 or 4 GPUs.  With more than one part per rank the single-part entry points do no
+// communication; the *_multi entry points exchange all co-resident parts collectively.
+static int g_parts_per_rank = 1;
+static inline int rank_of_part(int part1) { return (part1 - 1) / g_parts_per_rank; }
+int fb2_comm_parts_per_rank() { return g_parts_per_rank; }
+extern "C" int fb2_comm_set_parts_per_rank(int k) {
+  FB2_CHECK(k >= 1, "parts per rank must be >= 1");
+  g_parts_per_rank = k;
+  return 0;
+}
 int fb2_comm_active() { return g_comm != nullptr; }
 int fb2_comm_nranks() { return g_nranks; }
 int fb2_comm_rank() { return g_rank; }
@@ -117,9 +128,9 @@ static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add, 
   if (ns > 0) k_pack<<<(ns + 255) / 256, 256, 0, s>>>(x, sidx, 0, ns, imp->d_snd_buf);
   FB2_NCCL(ncclGroupStart());
   for (size_t i = 0; i < rl.size(); ++i)
-    if (rp[i + 1] > rp[i]) FB2_NCCL(ncclRecv(imp->d_rcv_buf + rp[i], rp[i + 1] - rp[i], ncclDouble, rl[i] - 1, g_comm, s));
+    if (rp[i + 1] > rp[i]) FB2_NCCL(ncclRecv(imp->d_rcv_buf + rp[i], rp[i + 1] - rp[i], ncclDouble, rank_of_part(rl[i]), g_comm, s));
   for (size_t i = 0; i < sl.size(); ++i)
-    if (sp[i + 1] > sp[i]) FB2_NCCL(ncclSend(imp->d_snd_buf + sp[i], sp[i + 1] - sp[i], ncclDouble, sl[i] - 1, g_comm, s));
+    if (sp[i + 1] > sp[i]) FB2_NCCL(ncclSend(imp->d_snd_buf + sp[i], sp[i + 1] - sp[i], ncclDouble, rank_of_part(sl[i]), g_comm, s));
   FB2_NCCL(ncclGroupEnd());
   if (add) {
     // stage 1 always unpacks into unpack_idx; additions in neighbour-list order (the reference's order)
@@ -134,10 +145,84 @@ static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add, 
 //  stage 1: non-owners send their partial sums, the owner receives and adds   (rcv side = owner)
 //  stage 2: the owner sends the total, non-owners receive and overwrite
 int fb2_import_exchange_on(fb2_import_s* imp, double* d_vec, cudaStream_t stream) {
-  if (!g_comm || !imp) return 0;
+  if (!g_comm || !imp || g_parts_per_rank > 1) return 0;
   FB2_TRY(exchange_stage(imp, d_vec, false, true, stream));
   FB2_TRY(exchange_stage(imp, d_vec, true, false, stream));
   return 0;
 }
 int fb2_import_exchange(fb2_import_s* imp, double* d_vec) { return fb2_import_exchange_on(imp, d_vec, fb2_stream()); }
 
+
+// ------------------------------------------------------------------------------------------
+// comm() of the co-resident parts of this rank, collectively: messages between two parts of the same process are
+// device-to-device copies, the others one grouped ncclSend/ncclRecv.  NCCL matches the messages of a rank pair in issue
+// order, so both sides order them by (source part, destination part).
+// ------------------------------------------------------------------------------------------
+struct Msg { int peer, src, dst; double* ptr; int len; };
+static int exchange_stage_multi(int np, fb2_import_s* const* imps, const int* part_ids, double* const* xs, bool reverse,
+                                cudaStream_t s) {
+  std::vector<Msg> sends, recvs;
+  for (int i = 0; i < np; ++i) {
+    fb2_import_s* imp = imps[i];
+    const std::vector<int>& sp = reverse ? imp->rcv_ptrs : imp->snd_ptrs;
+    const int* sidx = reverse ? imp->d_unpack_idx : imp->d_pack_idx;
+    const int ns = sp.empty() ? 0 : sp.back();
+    if (ns > 0) k_pack<<<(ns + 255) / 256, 256, 0, s>>>(xs[i], sidx, 0, ns, imp->d_snd_buf);
+  }
+  for (int i = 0; i < np; ++i) {
+    fb2_import_s* imp = imps[i];
+    const std::vector<int>& sl = reverse ? imp->list_rcv : imp->list_snd;
+    const std::vector<int>& sp = reverse ? imp->rcv_ptrs : imp->snd_ptrs;
+    const std::vector<int>& rl = reverse ? imp->list_snd : imp->list_rcv;
+    const std::vector<int>& rp = reverse ? imp->snd_ptrs : imp->rcv_ptrs;
+    for (size_t a = 0; a < sl.size(); ++a) {
+      const int len = sp[a + 1] - sp[a];
+      if (len <= 0) continue;
+      const int nb = sl[a];
+      if (rank_of_part(nb) == g_rank) {
+        int j = -1;
+        for (int k = 0; k < np; ++k) if (part_ids[k] == nb) j = k;
+        FB2_CHECK(j >= 0, "a neighbour part of this rank is missing from the multi-part call");
+        fb2_import_s* dst = imps[j];
+        const std::vector<int>& drl = reverse ? dst->list_snd : dst->list_rcv;
+        const std::vector<int>& drp = reverse ? dst->snd_ptrs : dst->rcv_ptrs;
+        int b = -1;
+        for (size_t k = 0; k < drl.size(); ++k) if (drl[k] == part_ids[i]) b = (int)k;
+        FB2_CHECK(b >= 0 && drp[b + 1] - drp[b] == len, "inconsistent dof_import lists between two co-resident parts");
+        FB2_CUDA(cudaMemcpyAsync(dst->d_rcv_buf + drp[b], imp->d_snd_buf + sp[a], sizeof(double) * (size_t)len,
+                                 cudaMemcpyDeviceToDevice, s));
+      } else sends.push_back({rank_of_part(nb), part_ids[i], nb, imp->d_snd_buf + sp[a], len});
+    }
+    for (size_t a = 0; a < rl.size(); ++a) {
+      const int len = rp[a + 1] - rp[a];
+      if (len > 0 && rank_of_part(rl[a]) != g_rank) recvs.push_back({rank_of_part(rl[a]), rl[a], part_ids[i], imp->d_rcv_buf + rp[a], len});
+    }
+  }
+  auto by_pair = [](const Msg& x, const Msg& y) { return x.src != y.src ? x.src < y.src : x.dst < y.dst; };
+  std::sort(sends.begin(), sends.end(), by_pair);
+  std::sort(recvs.begin(), recvs.end(), by_pair);
+  if (!sends.empty() || !recvs.empty()) {
+    FB2_NCCL(ncclGroupStart());
+    for (const Msg& m : recvs) FB2_NCCL(ncclRecv(m.ptr, m.len, ncclDouble, m.peer, g_comm, s));
+    for (const Msg& m : sends) FB2_NCCL(ncclSend(m.ptr, m.len, ncclDouble, m.peer, g_comm, s));
+    FB2_NCCL(ncclGroupEnd());
+  }
+  for (int i = 0; i < np; ++i) {
+    fb2_import_s* imp = imps[i];
+    if (!reverse) {
+      if (imp->n_add_dst > 0)
+        k_unpack_add<<<(imp->n_add_dst + 255) / 256, 256, 0, s>>>(xs[i], imp->n_add_dst, imp->d_add_dst, imp->d_add_ptr, imp->d_add_pos, imp->d_rcv_buf);
+    } else {
+      const int nr = imp->snd_ptrs.empty() ? 0 : imp->snd_ptrs.back();
+      if (nr > 0) k_unpack<<<(nr + 255) / 256, 256, 0, s>>>(xs[i], imp->d_pack_idx, 0, nr, imp->d_rcv_buf);
+    }
+  }
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+int fb2_import_exchange_multi(int np, fb2_import_s* const* imps, const int* part_ids, double* const* xs, cudaStream_t s) {
+  if (!g_comm) return 0;
+  FB2_TRY(exchange_stage_multi(np, imps, part_ids, xs, false, s));
+  FB2_TRY(exchange_stage_multi(np, imps, part_ids, xs, true, s));
+  return 0;
+}

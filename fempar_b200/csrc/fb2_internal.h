@@ -173,6 +173,8 @@ int fb2_comm_rank();
 int fb2_allreduce_sum(double* d_buf, int count);           // in place, device buffer
 int fb2_import_exchange(fb2_import_s* imp, double* d_vec); // par_scalar_array%comm()
 int fb2_import_exchange_on(fb2_import_s* imp, double* d_vec, cudaStream_t stream);
+int fb2_import_exchange_multi(int np, fb2_import_s* const* imps, const int* part_ids, double* const* xs, cudaStream_t s);
+int fb2_comm_parts_per_rank();
 const double* fb2_import_weight(fb2_import_s* imp);
 void fb2_import_destroy(fb2_import_s* imp);
 int fb2_import_build_add_plan(fb2_import_s* imp);   // from imp->h_unpack_idx (0-based)

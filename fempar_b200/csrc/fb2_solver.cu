@@ -677,3 +677,260 @@ int fb2_dots_host(fb2_matrix_t A, int k, const double* const* xs, const double* 
   FB2_CUDA(fb2_memcpy(out, d_tmp, sizeof(double) * k, cudaMemcpyDeviceToHost));
   return 0;
 }
+
+// ==========================================================================================
+// Several sub-domains per process (fb2_comm_set_parts_per_rank): the par_* vector / operator / PCG entry points over
+// the list of co-resident parts.  Same kernels and the same device-resident CgState as the single-part path; every part
+// writes its partial sums into its own segment of the scratch buffer and one reduction sums all segments in a fixed order.
+// ==========================================================================================
+struct MultiCtx {
+  int np = 0;
+  std::vector<fb2_matrix_s*> A;
+  std::vector<fb2_import_s*> imp;
+  std::vector<int> part;
+  std::vector<const double*> w;
+};
+static int multi_ctx(int np, fb2_matrix_t* A, MultiCtx& C) {
+  FB2_CHECK(np >= 1 && A, "multi-part call without parts");
+  C.np = np; C.A.assign(A, A + np); C.imp.resize(np); C.part.resize(np); C.w.resize(np);
+  for (int i = 0; i < np; ++i) {
+    FB2_CHECK(A[i] && A[i]->s && A[i]->s->imp, "multi-part call: every matrix needs a par space (part_id > 0)");
+    FB2_CHECK(!A[i]->sym, "multi-part PCG uses full storage");
+    C.imp[i] = A[i]->s->imp; C.part[i] = A[i]->s->part_id;
+    C.w[i] = fb2_comm_active() ? fb2_import_weight(C.imp[i]) : nullptr;
+  }
+  return 0;
+}
+static int exchange_multi(const MultiCtx& C, double* const* xs, cudaStream_t s) {
+  return fb2_import_exchange_multi(C.np, C.imp.data(), C.part.data(), xs, s);
+}
+
+extern "C" int fb2_vec_comm_multi(int np, fb2_vector_t* v) {
+  FB2_CHECK(np >= 1 && v, "bad argument");
+  std::vector<fb2_import_s*> imp(np); std::vector<int> part(np); std::vector<double*> xs(np);
+  for (int i = 0; i < np; ++i) {
+    FB2_CHECK(v[i] && v[i]->s && v[i]->s->imp, "fb2_vec_comm_multi: vectors must belong to par spaces");
+    imp[i] = v[i]->s->imp; part[i] = v[i]->s->part_id; xs[i] = v[i]->d;
+  }
+  return fb2_import_exchange_multi(np, imp.data(), part.data(), xs.data(), fb2_stream());
+}
+// sum over the co-resident parts of the weighted local dots, then the all-reduce (par_scalar_array.f90:303-350)
+extern "C" int fb2_vec_dot_multi(int np, fb2_vector_t* x, fb2_vector_t* y, double* result) {
+  FB2_CHECK(np >= 1 && np <= 64 && x && y, "bad argument");
+  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
+  for (int i = 0; i < np; ++i) {
+    FB2_CHECK(x[i]->n == y[i]->n, "size mismatch");
+    FB2_TRY(fb2_dot_device(x[i]->d, y[i]->d, weight_of(x[i]), x[i]->n, d_tmp + 1 + i));
+  }
+  k_reduce_partials<<<1, 256, 0, fb2_stream()>>>(d_tmp + 1, np, 0, 1, d_tmp);
+  if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(d_tmp, 1));
+  FB2_CUDA(fb2_memcpy(result, d_tmp, sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+extern "C" int fb2_spmv_multi(int np, fb2_matrix_t* A, fb2_vector_t* x, fb2_vector_t* y) {
+  MultiCtx C;
+  FB2_TRY(multi_ctx(np, A, C));
+  std::vector<double*> ys(np);
+  for (int i = 0; i < np; ++i) {
+    FB2_CHECK(x[i]->n == A[i]->n && y[i]->n == A[i]->n, "size mismatch");
+    FB2_TRY(spmv_local(A[i], x[i]->d, y[i]->d, false, nullptr, nullptr));
+    ys[i] = y[i]->d;
+  }
+  FB2_TRY(exchange_multi(C, ys.data(), fb2_stream()));
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  return 0;
+}
+extern "C" int fb2_jacobi_setup_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv) {
+  MultiCtx C;
+  FB2_TRY(multi_ctx(np, A, C));
+  std::vector<double*> ds(np);
+  for (int i = 0; i < np; ++i) { FB2_TRY(fb2_extract_diagonal(A[i], dinv[i])); ds[i] = dinv[i]->d; }
+  FB2_TRY(exchange_multi(C, ds.data(), fb2_stream()));
+  for (int i = 0; i < np; ++i) FB2_TRY(fb2_vec_entrywise_invert(dinv[i]));
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  return 0;
+}
+
+struct MultiWork {
+  std::vector<CgWork> parts;
+  CgState* st = nullptr;
+  double* hist = nullptr;
+  int hist_cap = 0;
+};
+static MultiWork g_mwork;
+static int multi_workspace(const MultiCtx& C, int hist_len) {
+  MultiWork& M = g_mwork;
+  if ((int)M.parts.size() != C.np) {
+    for (CgWork& W : M.parts) { cudaFree(W.r); cudaFree(W.p); cudaFree(W.Ap); }
+    M.parts.assign(C.np, CgWork());
+  }
+  for (int i = 0; i < C.np; ++i) {
+    CgWork& W = M.parts[i];
+    if (W.n != C.A[i]->n) {
+      cudaFree(W.r); cudaFree(W.p); cudaFree(W.Ap);
+      const i64 n = C.A[i]->n;
+      FB2_TRY(fb2_dalloc(&W.r, (size_t)n)); FB2_TRY(fb2_dalloc(&W.p, (size_t)n)); FB2_TRY(fb2_dalloc(&W.Ap, (size_t)n));
+      W.n = n;
+    }
+  }
+  if (!M.st) FB2_TRY(fb2_dalloc(&M.st, 1));
+  if (hist_len > M.hist_cap) { cudaFree(M.hist); FB2_TRY(fb2_dalloc(&M.hist, (size_t)hist_len)); M.hist_cap = hist_len; }
+  return 0;
+}
+
+static int multi_cg_setup(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_t* b, fb2_vector_t* x, double rtol, double atol,
+                          int maxit, int stop) {
+  cudaStream_t s = fb2_stream();
+  MultiWork& M = g_mwork;
+  const int np = C.np;
+  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;      // [4][np] partial dots, then 4 sums at d_tmp + 4 np
+  for (int i = 0; i < np; ++i) {
+    CgWork& W = M.parts[i];
+    const i64 n = W.n;
+    const double* di = dinv ? dinv[i]->d : nullptr;
+    k_init<<<vec_grid(n), 256, 0, s>>>(x[i]->d, 0.0, n);
+    FB2_CUDA(cudaMemcpyAsync(W.r, b[i]->d, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    if (di) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, di, W.r, n);
+    else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    FB2_TRY(fb2_dot_device(W.r, W.p, C.w[i], n, d_tmp + 0 * np + i));
+    FB2_TRY(fb2_dot_device(W.r, W.r, C.w[i], n, d_tmp + 1 * np + i));
+    FB2_TRY(fb2_dot_device(b[i]->d, b[i]->d, C.w[i], n, d_tmp + 2 * np + i));
+    if (stop == FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN) {
+      if (di) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.Ap, di, b[i]->d, n);
+      FB2_TRY(fb2_dot_device(b[i]->d, di ? W.Ap : b[i]->d, C.w[i], n, d_tmp + 3 * np + i));
+    } else FB2_CUDA(cudaMemsetAsync(d_tmp + 3 * np + i, 0, sizeof(double), s));
+  }
+  k_reduce_partials<<<1, 256, 0, s>>>(d_tmp, np, np, 4, d_tmp + 4 * np);
+  if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(d_tmp + 4 * np, 4));
+  double h[4];
+  FB2_CUDA(fb2_memcpy(h, d_tmp + 4 * np, 4 * sizeof(double), cudaMemcpyDeviceToHost));
+  const double nr0 = sqrt(h[1]), nb = sqrt(h[2]);
+  double tol = 0.0, tol_extra = 0.0;
+  switch (stop) {
+    case FB2_STOP_DELTA_RHS: case FB2_STOP_RES_RHS: tol = rtol * nb + atol; break;
+    case FB2_STOP_DELTA_RHS_AND_RES_RHS: case FB2_STOP_DELTA_DELTA_AND_RES_RHS: tol = tol_extra = rtol * nb + atol; break;
+    case FB2_STOP_RES_RES: tol = rtol * nr0 + atol; break;
+    case FB2_STOP_DELTA_DELTA_AND_RES_RES: tol = tol_extra = rtol * nr0 + atol; break;
+    case FB2_STOP_DELTA_RHS_AND_RES_RES: tol = rtol * nb + atol; tol_extra = rtol * nr0 + atol; break;
+    case FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN: tol = rtol * sqrt(h[3]) + atol; break;
+    case FB2_STOP_RES_NRMGIVEN_RES_NRMGIVEN: tol = rtol * sqrt(h[0]) + atol; break;
+    default: break;
+  }
+  k_cg_init_state<<<1, 1, 0, s>>>(M.st, h[0], tol, tol_extra, rtol, atol, maxit, stop, g_cg_icg);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// one PCG iteration over all co-resident parts (overlapped par apply, see cg_enqueue_iteration)
+static int multi_cg_iteration(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_t* x, double* hist, cudaEvent_t ev0, cudaEvent_t ev1) {
+  cudaStream_t s = fb2_stream(), cs = fb2_comm_stream();
+  MultiWork& M = g_mwork;
+  const int np = C.np;
+  double* part = fb2_scratch_partials();
+  static cudaEvent_t ev_itf = nullptr, ev_halo = nullptr;
+  if (!ev_itf) { cudaEventCreateWithFlags(&ev_itf, cudaEventDisableTiming); cudaEventCreateWithFlags(&ev_halo, cudaEventDisableTiming); }
+  if (ev0) cudaEventRecord(ev0, s);
+  std::vector<i64> t_itf(np), row_itf(np);
+  std::vector<double*> aps(np);
+  for (int i = 0; i < np; ++i) {
+    CgWork& W = M.parts[i];
+    FB2_TRY(fb2_spmv_interface_split(C.A[i], C.A[i]->s->n_interior, &t_itf[i], &row_itf[i]));
+    FB2_TRY(fb2_spmv_stream_range(C.A[i], W.p, W.Ap, false, &M.st->done, t_itf[i], C.A[i]->spmv_ntiles, 0, nullptr, nullptr));
+    aps[i] = W.Ap;
+  }
+  FB2_CUDA(cudaEventRecord(ev_itf, s));
+  FB2_CUDA(cudaStreamWaitEvent(cs, ev_itf, 0));
+  FB2_TRY(exchange_multi(C, aps.data(), cs));
+  FB2_CUDA(cudaEventRecord(ev_halo, cs));
+  int off = 0;
+  for (int i = 0; i < np; ++i) {
+    CgWork& W = M.parts[i];
+    int g = 0;
+    FB2_TRY(fb2_spmv_stream_range(C.A[i], W.p, W.Ap, true, &M.st->done, 0, t_itf[i], g_par_chunk, part + off, &g));
+    off += g;
+  }
+  FB2_CUDA(cudaStreamWaitEvent(s, ev_halo, 0));
+  if (ev1) cudaEventRecord(ev1, s);
+  for (int i = 0; i < np; ++i) {
+    CgWork& W = M.parts[i];
+    const i64 n = W.n, r0 = row_itf[i];
+    if (r0 < n) {
+      int gd = reduce_grid(n - r0);
+      if (gd > 64) gd = 64;
+      k_dot<<<gd, 256, 0, s>>>(W.Ap + r0, W.p + r0, C.w[i] ? C.w[i] + r0 : nullptr, n - r0, part + off);
+      off += gd;
+    }
+  }
+  FB2_CHECK(off <= FB2_MAX_PARTIALS, "too many partial sums for the multi-part PCG");
+  k_reduce_partials<<<1, 1024, 0, s>>>(part, off, 0, 1, &M.st->App);
+  if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(&M.st->App, 1));
+  int off2 = 0;
+  for (int i = 0; i < np; ++i) {
+    CgWork& W = M.parts[i];
+    const int g2 = reduce_grid(W.n);
+    k_cg_update_xr<<<g2, 256, 0, s>>>(W.n, M.st, W.p, W.Ap, dinv ? dinv[i]->d : nullptr, C.w[i], x[i]->d, W.r, part + off2, FB2_MAX_PARTIALS);
+    off2 += g2;
+  }
+  k_reduce_partials<<<1, 256, 0, s>>>(part, off2, FB2_MAX_PARTIALS, 4, &M.st->rr);
+  if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(&M.st->rr, 4));
+  k_cg_scalars<<<1, 1, 0, s>>>(M.st, hist);
+  for (int i = 0; i < np; ++i) {
+    CgWork& W = M.parts[i];
+    k_cg_update_p<<<vec_grid(W.n), 256, 0, s>>>(W.n, M.st, W.r, dinv ? dinv[i]->d : nullptr, W.p);
+  }
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int fb2_pcg_solve_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, fb2_vector_t* b, fb2_vector_t* x,
+                                   const fb2_ils_params_t* prm, int* num_iterations, int* did_converge, double* error_estimate,
+                                   double* history) {
+  FB2_CHECK(b && x && prm, "null argument");
+  MultiCtx C;
+  FB2_TRY(multi_ctx(np, A, C));
+  for (int i = 0; i < np; ++i) FB2_CHECK(b[i]->n == A[i]->n && x[i]->n == A[i]->n && (!dinv || dinv[i]->n == A[i]->n), "size mismatch");
+  FB2_CHECK(prm->stopping_criterium >= FB2_STOP_RES_RES && prm->stopping_criterium <= FB2_STOP_DELTA_DELTA_AND_RES_RHS, "unknown stopping criterium");
+  const int maxit = prm->max_num_iterations;
+  const bool track = history != nullptr;
+  FB2_TRY(multi_workspace(C, track ? maxit : 0));
+  cudaStream_t s = fb2_stream();
+  FB2_TRY(multi_cg_setup(C, dinv, b, x, prm->rtol, prm->atol, maxit, prm->stopping_criterium));
+  const int every = prm->check_every > 0 ? prm->check_every : 8;
+  CgState h;
+  memset(&h, 0, sizeof(h));
+  int launched = 0;
+  while (launched < maxit) {
+    int chunk = every;
+    if (launched + chunk > maxit) chunk = maxit - launched;
+    for (int k = 0; k < chunk; ++k) FB2_TRY(multi_cg_iteration(C, dinv, x, track ? g_mwork.hist : nullptr, nullptr, nullptr));
+    launched += chunk;
+    FB2_CUDA(fb2_memcpy(&h, g_mwork.st, sizeof(CgState), cudaMemcpyDeviceToHost));
+    if (h.done) break;
+  }
+  *num_iterations = h.iter; *did_converge = h.converged; *error_estimate = h.err;
+  if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, g_mwork.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+extern "C" int fb2_pcg_iterate_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, fb2_vector_t* b, fb2_vector_t* x,
+                                     int n_iterations, double* ms_total, double* ms_spmv) {
+  FB2_CHECK(b && x && n_iterations > 0, "bad argument");
+  MultiCtx C;
+  FB2_TRY(multi_ctx(np, A, C));
+  FB2_TRY(multi_workspace(C, 0));
+  cudaStream_t s = fb2_stream();
+  FB2_TRY(multi_cg_setup(C, dinv, b, x, 0.0, -1.0, n_iterations + 1, FB2_STOP_RES_RES));
+  std::vector<cudaEvent_t> ev(2 * (size_t)n_iterations + 2);
+  for (auto& e : ev) cudaEventCreate(&e);
+  cudaEventRecord(ev[2 * n_iterations], s);
+  for (int k = 0; k < n_iterations; ++k) FB2_TRY(multi_cg_iteration(C, dinv, x, nullptr, ev[2 * k], ev[2 * k + 1]));
+  cudaEventRecord(ev[2 * n_iterations + 1], s);
+  FB2_CUDA(cudaStreamSynchronize(s));
+  float ms = 0, acc = 0;
+  cudaEventElapsedTime(&ms, ev[2 * n_iterations], ev[2 * n_iterations + 1]);
+  for (int k = 0; k < n_iterations; ++k) { float m1 = 0; cudaEventElapsedTime(&m1, ev[2 * k], ev[2 * k + 1]); acc += m1; }
+  for (auto& e : ev) cudaEventDestroy(e);
+  if (ms_total) *ms_total = ms;
+  if (ms_spmv) *ms_spmv = acc;
+  return 0;
+}

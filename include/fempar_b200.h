@@ -207,6 +207,22 @@ int fb2_ils_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_
 int fb2_pcg_iterate(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, int n_iterations,
                     double* ms_total, double* ms_spmv);
 
+/* ---- several sub-domains per process (BASELINE config 3: the 8-part layout on 2 or 4 GPUs) ----------------------------
+ * Part p (1-based) lives on rank (p-1)/parts_per_rank.  With parts_per_rank > 1 the single-part entry points above do NOT
+ * communicate (fb2_integrate_assemble leaves the local RHS); the *_multi entry points take the arrays of the np co-resident
+ * handles and do comm() / weighted dots / the PCG iteration over all of them collectively.  Same semantics as
+ * par_scalar_array%comm / %dot, par_sparse_matrix%apply, jacobi numerical_setup and cg_solve_body. */
+int fb2_comm_set_parts_per_rank(int parts_per_rank);
+int fb2_vec_comm_multi(int np, fb2_vector_t* v);
+int fb2_vec_dot_multi(int np, fb2_vector_t* x, fb2_vector_t* y, double* result);
+int fb2_spmv_multi(int np, fb2_matrix_t* A, fb2_vector_t* x, fb2_vector_t* y);
+int fb2_jacobi_setup_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv);
+int fb2_pcg_solve_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv /*NULL = identity*/, fb2_vector_t* b, fb2_vector_t* x,
+                        const fb2_ils_params_t* params, int* num_iterations, int* did_converge, double* error_estimate,
+                        double* history);
+int fb2_pcg_iterate_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, fb2_vector_t* b, fb2_vector_t* x, int n_iterations,
+                          double* ms_total, double* ms_spmv);
+
 /* ---- error norms: sqrt(sum_K int |grad(u-u_h)|^2), sqrt(int (u-u_h)^2) ----- */
 int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double* h1_seminorm,
                     double* l2_norm);

@@ -71,3 +71,15 @@ def test_par_pcg_nccl(world):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "PAR_NCCL_OK" in r.stdout
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_par_8_parts_on_fewer_gpus_nccl(world):
+    """BASELINE config 3: the 8-sub-domain layout on 2 and 4 GPUs (4 / 2 co-resident parts per process)."""
+    if _ngpus() < world:
+        pytest.skip("needs %d GPUs" % world)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+           "--master-port", str(29600 + world), os.path.join(ROOT, "tests", "par_multi_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "PAR_MULTI_OK" in r.stdout
