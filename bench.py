@@ -37,6 +37,8 @@ def parse():
     ap.add_argument("--scatter", type=int, default=0)
     ap.add_argument("--cpu-cells", type=int, default=48, help="cells per direction of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--subdomains", type=int, default=0,
+                    help="number of FEMPAR sub-domains (parts); 0 = 8 (2x2x2, BASELINE config 3) when --gpus is 2, 4 or 8, else 1")
     ap.add_argument("--spmv-variant", type=int, default=0, help="0 TMA-streamed tiles, 1 warp-per-row")
     ap.add_argument("--asm-variant", type=int, default=0, help="0 register-blocked contraction + scatter map, 1 generic kernel")
     return ap.parse_args()
@@ -162,24 +164,44 @@ def main():
     fb.init(local)
     fb._lib.check(fb._lib.lib().fb2_set_spmv_variant(a.spmv_variant))
     fb._lib.check(fb._lib.lib().fb2_set_assembly_variant(a.asm_variant))
-    parts = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
+    nsub = a.subdomains if a.subdomains else (8 if world > 1 else 1)
+    nsub = max(nsub, world)
+    parts = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[nsub]
+    assert nsub % world == 0, "--subdomains must be a multiple of --gpus"
+    ppr = nsub // world                     # co-resident sub-domains per process
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         fb.comm_init_from_torch(dist)
+    fb.comm_set_parts_per_rank(ppr)
     free_b, total_b = torch.cuda.mem_get_info()
     cells = pick_cells(a, free_b, a.order, world)
     N = [cells] * 3
+    multi = ppr > 1
     t0 = time.perf_counter()
-    space = fb.FeSpace(N, order=a.order, num_parts_x_dim=parts, part_id=(rank + 1 if world > 1 else 0))
+    if world == 1 and nsub == 1:
+        my_parts = [0]
+    else:
+        my_parts = list(range(rank * ppr + 1, rank * ppr + ppr + 1))
+    spaces = [fb.FeSpace(N, order=a.order, num_parts_x_dim=parts, part_id=q) for q in my_parts]
     t_space = time.perf_counter() - t0
-    op = fb.FeAffineOperator()
-    op.create(fb.csr_format, [False], [True], [1], space, fb.DiscreteIntegration(fb.poisson, fb.func_linear, None, None, a.scatter))
-    t_pattern_ms = op.last_phase_ms("pattern")
-    A = op.get_matrix()
-    n_loc, nnz_loc = space.num_free_dofs, A.nnz
-    M = fb.JacobiPreconditioner(); M.create(op); M.symbolic_setup()
-    ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG"); ils.set_operators(A, M)
-    x = space.create_dof_values()
+    ops, t_pattern_ms = [], 0.0
+    for sp in spaces:
+        o = fb.FeAffineOperator()
+        o.create(fb.csr_format, [False], [True], [1], sp, fb.DiscreteIntegration(fb.poisson, fb.func_linear, None, None, a.scatter))
+        t_pattern_ms += o.last_phase_ms("pattern")
+        ops.append(o)
+    space, op = spaces[0], ops[0]
+    As = [o.get_matrix() for o in ops]
+    A = As[0]
+    n_loc, nnz_loc = sum(sp.num_free_dofs for sp in spaces), sum(m.nnz for m in As)
+    ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG")
+    if multi:
+        dinvs = [sp.create_dof_values() for sp in spaces]
+        xs = [sp.create_dof_values() for sp in spaces]
+    else:
+        M = fb.JacobiPreconditioner(); M.create(op); M.symbolic_setup()
+        ils.set_operators(A, M)
+        x = space.create_dof_values()
 
     def sync_all():
         fb._lib.check(fb._lib.lib().fb2_device_synchronize())
@@ -188,6 +210,16 @@ def main():
             dist.barrier()
 
     def step():
+        if multi:
+            t_asm = 0.0
+            for o in ops:                                   # co-resident sub-domains are assembled one after the other
+                o.compute()
+                t_asm += o.last_phase_ms("integrate")
+            bs = [o.get_translation() for o in ops]
+            fb.vec_comm_multi(bs)                           # RHS comm()
+            fb.jacobi_setup_multi(As, dinvs)
+            t_tot, t_spmv = ils.iterate_multi(As, dinvs, bs, xs, a.cg_iters)
+            return t_asm, t_tot, t_spmv
         op.compute()
         t_asm = op.last_phase_ms("integrate")
         M.numerical_setup()
@@ -224,24 +256,39 @@ def main():
     asm_mdofs = n_free_global / (asm_t * 1e-3) / 1e6
 
     # e2e: the same PCG iterations through the C-ABI call with HOST buffers (H2D of b, D2H of x inside the timed region)
-    b_host = torch.empty(n_loc, dtype=torch.float64).pin_memory()
-    b_host.copy_(torch.from_numpy(op.get_translation().get_entries()))
-    x_host = torch.empty(n_loc, dtype=torch.float64).pin_memory()
     ils.set_parameters_from_pl({fb.ILS_RTOL: 0.0, fb.ILS_ATOL: -1.0, fb.ILS_MAX_NUM_ITERATIONS: a.cg_iters})
     ils.check_every = a.cg_iters
     ts = []
-    for k in range(3):
-        sync_all()
-        t0 = time.perf_counter()
-        ils.apply(b_host.numpy(), x_host.numpy())
-        fb._lib.check(fb._lib.lib().fb2_device_synchronize())
-        ts.append(time.perf_counter() - t0)
+    if multi:
+        b_hosts = [torch.from_numpy(o.get_translation().get_entries()).pin_memory() for o in ops]
+        x_hosts = [torch.empty(sp.num_free_dofs, dtype=torch.float64).pin_memory() for sp in spaces]
+        bs = [sp.create_dof_values() for sp in spaces]
+        for k in range(3):
+            sync_all()
+            t0 = time.perf_counter()
+            for bv, bh in zip(bs, b_hosts):
+                bv.set_entries(bh.numpy())                  # H2D
+            ils.apply_multi(As, dinvs, bs, xs)
+            for xv, xh in zip(xs, x_hosts):
+                fb._lib.check(fb._lib.lib().fb2_vec_get(xv.h, xh.data_ptr()))   # D2H
+            ts.append(time.perf_counter() - t0)
+    else:
+        b_host = torch.empty(n_loc, dtype=torch.float64).pin_memory()
+        b_host.copy_(torch.from_numpy(op.get_translation().get_entries()))
+        x_host = torch.empty(n_loc, dtype=torch.float64).pin_memory()
+        for k in range(3):
+            sync_all()
+            t0 = time.perf_counter()
+            ils.apply(b_host.numpy(), x_host.numpy())
+            fb._lib.check(fb._lib.lib().fb2_device_synchronize())
+            ts.append(time.perf_counter() - t0)
     te = torch.tensor([min(ts[1:])], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e = {"value": a.cg_iters * bytes_all / float(te.item()) / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(n_glob_rows * 8),
            "d2h_bytes_per_step": int(n_glob_rows * 8),
-           "what": "fb2_pcg_solve_host on every rank: H2D b + %d PCG iterations + D2H x (max over ranks)" % a.cg_iters}
+           "what": ("fb2_pcg_solve_host" if not multi else "fb2_vec_set + fb2_pcg_solve_multi + fb2_vec_get") +
+                   " on every rank: H2D b + %d PCG iterations + D2H x (max over ranks)" % a.cg_iters}
 
     if rank != 0:
         if world > 1:
@@ -271,7 +318,8 @@ def main():
             "config": {"workload": "3D Poisson Q%d hex %d^3 cells (%d free DOFs, %d nnz), u=x+y+z Dirichlet, Jacobi-PCG; "
                                    "step = integrate+assemble + Jacobi setup + %d PCG iterations"
                                    % (a.order, cells, n_free_global, int(nnz_glob), a.cg_iters),
-                       "parts": list(parts), "l2": "inputs larger than L2 (no flush needed)", "scatter": a.scatter},
+                       "parts": list(parts), "subdomains_per_gpu": ppr, "l2": "inputs larger than L2 (no flush needed)",
+                       "scatter": a.scatter},
             "assembly_mdof_per_s": asm_mdofs, "assembly_ms": asm_t, "pcg_ms_per_iteration": cg_t / a.cg_iters,
             "spmv_ms": spmv_t, "setup_ms": {"fe_space": t_space * 1e3, "csr_pattern": t_pattern_ms, "scatter_map": t_map_ms},
             "wall_ms_per_step": wall_t,
@@ -285,7 +333,7 @@ def main():
             # kernels of libfempar_b200.so per step: Dirichlet interpolation + memsets/assembly (3), Jacobi set-up (2), PCG set-up
             # (9), then per PCG iteration: serial 6 (SpMV, 2 partial reductions, x/r update, scalars, p update); par 14 (two
             # SpMV launches, 4 pack/unpack kernels, interface dot, reductions, updates; NCCL's own kernels not counted)
-            "gpu_launches": a.steps * (3 + 2 + 9 + (6 if world == 1 else 14) * a.cg_iters)}
+            "gpu_launches": a.steps * ((3 + 2) * ppr + 9 + (6 if (world == 1 and not multi) else 14 * ppr) * a.cg_iters)}
     if not a.no_cpu_baseline:
         r = cpu_reference_run(a.cpu_cells, a.order, a.cg_iters, 1, 0)
         line["cpu_baseline"] = {"value": r["spmv_gbs"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],

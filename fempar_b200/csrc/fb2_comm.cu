@@ -202,6 +202,7 @@ static int exchange_stage_multi(int np, fb2_import_s* const* imps, const int* pa
   std::sort(sends.begin(), sends.end(), by_pair);
   std::sort(recvs.begin(), recvs.end(), by_pair);
   if (!sends.empty() || !recvs.empty()) {
+    FB2_CHECK(g_comm != nullptr, "a neighbour part lives on another rank but fb2_comm_init was not called");
     FB2_NCCL(ncclGroupStart());
     for (const Msg& m : recvs) FB2_NCCL(ncclRecv(m.ptr, m.len, ncclDouble, m.peer, g_comm, s));
     for (const Msg& m : sends) FB2_NCCL(ncclSend(m.ptr, m.len, ncclDouble, m.peer, g_comm, s));
@@ -221,7 +222,7 @@ static int exchange_stage_multi(int np, fb2_import_s* const* imps, const int* pa
   return 0;
 }
 int fb2_import_exchange_multi(int np, fb2_import_s* const* imps, const int* part_ids, double* const* xs, cudaStream_t s) {
-  if (!g_comm) return 0;
+  // without a communicator every part must be co-resident (one process holding the whole partition)
   FB2_TRY(exchange_stage_multi(np, imps, part_ids, xs, false, s));
   FB2_TRY(exchange_stage_multi(np, imps, part_ids, xs, true, s));
   return 0;

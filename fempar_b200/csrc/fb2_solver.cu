@@ -697,7 +697,7 @@ static int multi_ctx(int np, fb2_matrix_t* A, MultiCtx& C) {
     FB2_CHECK(A[i] && A[i]->s && A[i]->s->imp, "multi-part call: every matrix needs a par space (part_id > 0)");
     FB2_CHECK(!A[i]->sym, "multi-part PCG uses full storage");
     C.imp[i] = A[i]->s->imp; C.part[i] = A[i]->s->part_id;
-    C.w[i] = fb2_comm_active() ? fb2_import_weight(C.imp[i]) : nullptr;
+    C.w[i] = fb2_import_weight(C.imp[i]);     // also without a communicator: co-resident parts replicate interface DOFs
   }
   return 0;
 }
@@ -720,7 +720,8 @@ extern "C" int fb2_vec_dot_multi(int np, fb2_vector_t* x, fb2_vector_t* y, doubl
   double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
   for (int i = 0; i < np; ++i) {
     FB2_CHECK(x[i]->n == y[i]->n, "size mismatch");
-    FB2_TRY(fb2_dot_device(x[i]->d, y[i]->d, weight_of(x[i]), x[i]->n, d_tmp + 1 + i));
+    FB2_CHECK(x[i]->s && x[i]->s->imp, "fb2_vec_dot_multi: vectors must belong to par spaces");
+    FB2_TRY(fb2_dot_device(x[i]->d, y[i]->d, fb2_import_weight(x[i]->s->imp), x[i]->n, d_tmp + 1 + i));
   }
   k_reduce_partials<<<1, 256, 0, fb2_stream()>>>(d_tmp + 1, np, 0, 1, d_tmp);
   if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(d_tmp, 1));

@@ -73,9 +73,9 @@ def test_par_pcg_nccl(world):
     assert "PAR_NCCL_OK" in r.stdout
 
 
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [1, 2, 4])
 def test_par_8_parts_on_fewer_gpus_nccl(world):
-    """BASELINE config 3: the 8-sub-domain layout on 2 and 4 GPUs (4 / 2 co-resident parts per process)."""
+    """BASELINE config 3: the 8-sub-domain layout on 1, 2 and 4 GPUs (8 / 4 / 2 co-resident parts per process)."""
     if _ngpus() < world:
         pytest.skip("needs %d GPUs" % world)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
