@@ -30,3 +30,11 @@ def test_bench_reference_arm_under_torchrun_world2():
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["cpu_baseline"]["kind"] == "port"
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["unit"] == "GB/s"
+
+
+def test_8_parts_on_2_ranks_over_gloo():
+    """Several sub-domains per process (BASELINE config 3 on fewer GPUs than parts): message ordering by (source part,
+    destination part) and local copies between co-resident parts, on the oracle's data."""
+    r = _torchrun(2, os.path.join(ROOT, "tests", "par_gloo_multi_worker.py"), port=29633)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "PAR_GLOO_MULTI_OK" in r.stdout
