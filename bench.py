@@ -213,14 +213,14 @@ def main():
         if multi:
             t_asm = 0.0
             for o in ops:                                   # co-resident sub-domains are assembled one after the other
-                o.compute()
+                o.force_compute()
                 t_asm += o.last_phase_ms("integrate")
             bs = [o.get_translation() for o in ops]
             fb.vec_comm_multi(bs)                           # RHS comm()
             fb.jacobi_setup_multi(As, dinvs)
             t_tot, t_spmv = ils.iterate_multi(As, dinvs, bs, xs, a.cg_iters)
             return t_asm, t_tot, t_spmv
-        op.compute()
+        op.force_compute()                                  # re-assembly into the fixed pattern every step
         t_asm = op.last_phase_ms("integrate")
         M.numerical_setup()
         t_tot, t_spmv = ils.iterate(op.get_translation(), x, a.cg_iters)

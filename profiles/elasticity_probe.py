@@ -13,7 +13,7 @@ for kind, name, mat in [(fb.vector_laplacian, "vector_laplacian", None), (fb.ela
         fb._lib.check(fb._lib.lib().fb2_set_assembly_variant(variant))
         ts = []
         for _ in range(4):
-            op.compute()
+            op.force_compute()
             ts.append(op.last_phase_ms("integrate"))
         t = min(ts[1:])
         print("%s Q2 x3 %d^3 (%d DOFs, %d nnz) variant %d: %.2f ms = %.0f MDOF/s" % (name, N, s.num_free_dofs, op.get_matrix().nnz,

@@ -261,3 +261,31 @@ def test_pcg_all_ten_stopping_criteria(fb2, stop, prec):
     k = min(ils.get_num_iterations(), r["iters"]) // 2
     assert np.allclose(ils.history[:k], r["history"][:k], rtol=1e-6)
     assert np.max(np.abs(x.get_entries() - r["x"])) <= 1e-6 * np.max(np.abs(r["x"]))
+
+
+def test_fe_affine_operator_state_machine_and_residual(fb2):
+    """fe_affine_operator_t: compute is a no-op once assembler_computed, force_compute re-assembles into the same pattern
+    (sbm_fe_affine_operator.i90:15-57); apply(x,y) = residual A x - b at the evaluation point (sbm_fe_operator.i90:435-467)."""
+    N, p = (5, 4, 3), 2
+    s = fb2.FeSpace(N, order=p)
+    op = fb2.FeAffineOperator()
+    op.create(fb2.csr_format, [False], [True], [1], s, fb2.DiscreteIntegration(fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0))
+    assert op.get_state() == "created" and op.is_linear()
+    op.compute()
+    assert op.get_state() == "assembler_computed"
+    v0 = op.get_matrix().get_values().copy()
+    op.get_matrix().init(7.0)                      # tamper: compute() must NOT re-assemble, force_compute() must
+    op.compute()
+    assert np.all(op.get_matrix().get_values() == 7.0)
+    op.force_compute()
+    assert np.allclose(op.get_matrix().get_values(), v0, rtol=1e-14, atol=1e-300)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    x = np.random.default_rng(5).standard_normal(s.num_free_dofs)
+    vx, vy = s.create_dof_values(), s.create_dof_values()
+    vx.set_entries(x)
+    op.apply(vx, vy)
+    ref = o.spmv(x) - o.rhs()
+    assert np.max(np.abs(vy.get_entries() - ref)) <= 1e-12 * np.max(np.abs(ref))
+    op.apply_add(vx, vy)
+    assert np.max(np.abs(vy.get_entries() - 2 * ref)) <= 1e-12 * np.max(np.abs(ref))
