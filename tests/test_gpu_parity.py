@@ -289,3 +289,28 @@ def test_fe_affine_operator_state_machine_and_residual(fb2):
     assert np.max(np.abs(vy.get_entries() - ref)) <= 1e-12 * np.max(np.abs(ref))
     op.apply_add(vx, vy)
     assert np.max(np.abs(vy.get_entries() - 2 * ref)) <= 1e-12 * np.max(np.abs(ref))
+
+
+def test_determinism_of_reductions_and_colored_scatter(fb2):
+    """the fused <Ap,p> and the vector reductions sum per-block partials in a fixed order, so two solves on the
+    same matrix are bitwise identical; the colored scatter variant (plain read-modify-write on one colour class at a time)
+    makes the assembled values bitwise reproducible too (the atomic variant is only reproducible to rounding)."""
+    N, p = (12, 11, 10), 2
+    s = fb2.FeSpace(N, order=p)
+    op = fb2.FeAffineOperator()
+    op.create(fb2.csr_format, [False], [True], [1], s, fb2.DiscreteIntegration(fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, fb2.scatter_colored))
+    op.compute()
+    v1, b1 = op.get_matrix().get_values().copy(), op.get_translation().get_entries().copy()
+    op.force_compute()
+    assert np.array_equal(op.get_matrix().get_values(), v1) and np.array_equal(op.get_translation().get_entries(), b1)
+    M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    sols, hists = [], []
+    for _ in range(2):
+        ils = fb2.IterativeLinearSolver()
+        ils.set_parameters_from_pl({fb2.ILS_TYPE: "CG", fb2.ILS_RTOL: 1e-10, fb2.ILS_MAX_NUM_ITERATIONS: 2000,
+                                    fb2.ILS_TRACK_CONVERGENCE_HISTORY: True})
+        ils.set_operators(op.get_tangent(), M)
+        x = s.create_dof_values()
+        ils.apply(op.get_translation(), x)
+        sols.append(x.get_entries().copy()); hists.append(ils.history.copy())
+    assert np.array_equal(sols[0], sols[1]) and np.array_equal(hists[0], hists[1])
