@@ -179,6 +179,7 @@ struct FastArgs {
   const int* cell_tab;
   const unsigned short* tabs;
   int common_tab;   // table id of the interior position class (-1: none); cached in shared memory by the kernel
+  int tile;         // (x,y) tile edge of the cell traversal of the atomic variant; 0 = lexicographic
 };
 
 // Column j of the element matrix by sum factorisation.  With q = (q1,q2,q3), i = (i1,i2,i3) and
@@ -293,10 +294,30 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
 #pragma unroll
   for (int k = 0; k < 3; ++k) { dN[k] = (double)A.g.N[k]; rN[k] = 1.0 / dN[k]; }
   // total-box position and lexicographic index of the ci-th cell of this launch
+  // Traversal order of the atomic variant: (x,y) tiles of T x T cell columns, each walked plane by plane in z, so that the
+  // matrix rows a cell shares with its z-neighbour are still in L2 when that neighbour scatters (a whole z-plane of config 2
+  // is 382 MB of values, three times the L2; a 32 x 32 tile plane is 6 MB).  Ragged last tiles are handled in closed form.
+  const int T = F.tile;
   auto cell_pos = [&](int ci, int* ijk) {
     int r = ci;
-    ijk[0] = r % cdim[0]; r /= cdim[0];
-    ijk[1] = r % cdim[1]; ijk[2] = r / cdim[1];
+    if (A.color < 0 && T > 0) {
+      const int nx = cdim[0], ny = cdim[1], nz = cdim[2];
+      const int row_cells = nx * T * nz;                    // every tile row but the last is T cells high
+      const int ty = r / row_cells;
+      r -= ty * row_cells;
+      const int wy = min(T, ny - ty * T);
+      const int tile_cells = T * wy * nz;                   // every tile of the row but the last is T cells wide
+      const int tx = r / tile_cells;
+      r -= tx * tile_cells;
+      const int wx = min(T, nx - tx * T);
+      const int plane = wx * wy;
+      ijk[2] = r / plane; r -= ijk[2] * plane;
+      const int yy = r / wx;
+      ijk[1] = ty * T + yy; ijk[0] = tx * T + (r - yy * wx);
+    } else {
+      ijk[0] = r % cdim[0]; r /= cdim[0];
+      ijk[1] = r % cdim[1]; ijk[2] = r / cdim[1];
+    }
 #pragma unroll
     for (int k = 0; k < 3; ++k) ijk[k] = (A.color < 0 ? ijk[k] : 2 * ijk[k] + coff[k]) + A.g.L[k];
     return ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
@@ -587,6 +608,7 @@ int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant)
   FB2_TRY(load_const_tables(s));
   FastArgs F;
   F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs; F.common_tab = A->common_tab;
+  F.tile = getenv("FB2_ASM_TILE") ? atoi(getenv("FB2_ASM_TILE")) : 32;
   if (args.kind == FB2_KIND_ELASTICITY)
     return s->rt.p == 1 ? launch_fast<1, 3, true>(F, s, scatter_variant) : launch_fast<2, 3, true>(F, s, scatter_variant);
   if (s->rt.p == 1) return s->rt.ncomp == 1 ? launch_fast<1, 1>(F, s, scatter_variant) : launch_fast<1, 3>(F, s, scatter_variant);
