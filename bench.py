@@ -334,7 +334,7 @@ def main():
             # (9), then per PCG iteration: serial 6 (SpMV, 2 partial reductions, x/r update, scalars, p update); par 14 (two
             # SpMV launches, 4 pack/unpack kernels, interface dot, reductions, updates; NCCL's own kernels not counted)
             "gpu_launches": a.steps * ((3 + 2) * ppr + 9 + (6 if (world == 1 and not multi) else 14 * ppr) * a.cg_iters)}
-    if not a.no_cpu_baseline:
+    if not a.no_cpu_baseline and world == 1:       # reported on rank 0 at N=1 only
         r = cpu_reference_run(a.cpu_cells, a.order, a.cg_iters, 1, 0)
         line["cpu_baseline"] = {"value": r["spmv_gbs"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
                                 "assembly_mdof_per_s": r["asm_mdofs"]}
