@@ -51,17 +51,21 @@ __global__ void __launch_bounds__(128) k_assemble_generic(AsmArgs A, int cells_i
     cdim[k] = A.color < 0 ? A.g.nloc[k] : (A.g.nloc[k] - coff[k] + 1) / 2;
   }
   for (int ci = blockIdx.x * warps + w; ci < cells_in_launch; ci += gridDim.x * warps) {
-    int ijk[3];
-    {
+    int c;
+    double X[8][3];
+    if (A.coords) {   // host-built space: cells in the caller's order, vertices uploaded
+      c = ci;
+      cell_vertices_from(A.coords, c, X);
+    } else {
+      int ijk[3];
       int r = ci;
       ijk[0] = r % cdim[0]; r /= cdim[0];
       ijk[1] = r % cdim[1]; ijk[2] = r / cdim[1];
       for (int k = 0; k < 3; ++k) ijk[k] = (A.color < 0 ? ijk[k] : 2 * ijk[k] + coff[k]) + A.g.L[k];
+      int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
+      c = A.perm ? A.perm[lex] : lex;
+      cell_vertices(A.g, ijk, X);
     }
-    int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
-    int c = A.perm ? A.perm[lex] : lex;
-    double X[8][3];
-    cell_vertices(A.g, ijk, X);
     // geometry at the quadrature points (lanes over q)
     for (int q = lane; q < nq; q += 32) {
       double inv[3][3], det;
@@ -173,13 +177,16 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   AsmArgs a;
   a.g = make_geom(s);
   a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = s->rt.ncomp; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
-  a.perm = s->d_perm; a.gids = s->d_gids; a.fixed = s->d_fixed;
+  a.perm = s->d_perm; a.gids = s->d_gids; a.coords = s->d_coords; a.fixed = s->d_fixed;
   a.qw = s->d_qw; a.phi = s->d_phi; a.dphi = s->d_dphi; a.gphi = s->d_gphi; a.gdphi = s->d_gdphi;
   a.irp = A->d_irp; a.ja = A->d_ja; a.val = A->d_val; a.rhs = rhs->d; a.n_free = A->n;
   a.kind = kind; a.sym = A->sym; a.fn = make_func(func, func_params);
   a.lambda = mat_params ? mat_params[0] : 0.0; a.mu = mat_params ? mat_params[1] : 1.0;
   // the scatter map is set-up (like the reference's COO->CSR compression it is paid once): build it before the timed region
-  if (g_asm_variant == 0 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
+  const bool host_built = s->d_coords != nullptr;   // no lattice: generic kernel, slots by binary search, atomic scatter
+  FB2_CHECK(s->d_gids != nullptr, "this space has no cell DOF lists (bare space): use fb2_assemble_batch");
+  if (host_built) scatter_variant = FB2_SCATTER_ATOMIC;
+  if (!host_built && g_asm_variant == 0 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
@@ -191,7 +198,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int bps = (int)(227 * 1024 / smem); if (bps < 1) bps = 1; if (bps > 8) bps = 8;
-  int fast_rc = g_asm_variant == 0 ? fb2_assemble_fast(A, a, scatter_variant) : -1;
+  int fast_rc = (g_asm_variant == 0 && !host_built) ? fb2_assemble_fast(A, a, scatter_variant) : -1;
   if (fast_rc > 0) return fast_rc;
   if (fast_rc == 0) {
   } else if (scatter_variant == FB2_SCATTER_ATOMIC) {
@@ -226,23 +233,35 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
 // ------------------------------------------------------------------------------------------
 // strong Dirichlet values by nodal interpolation (sbm_serial_fe_space.i90:997-1176)
 // ------------------------------------------------------------------------------------------
-__global__ void k_interp_dirichlet(CellGeom g, int p, int nn, int nd, int n_cells, const int* __restrict__ lex_of,
+// physical position of a Lagrange node of cell c (structured: closed form; host-built: trilinear map of the uploaded vertices)
+__device__ __forceinline__ void node_position(const CellGeom& g, const double* __restrict__ coords, const int* __restrict__ lex_of,
+                                              int c, int node, int p, double* x) {
+  int n1 = p + 1;
+  int in[3] = {node % n1, (node / n1) % n1, node / (n1 * n1)};
+  if (coords) {
+    double X[8][3], xi[3] = {(double)in[0] / (double)p, (double)in[1] / (double)p, (double)in[2] / (double)p};
+    cell_vertices_from(coords, c, X);
+    trilinear_point(X, xi, x);
+    return;
+  }
+  int lex = lex_of ? lex_of[c] : c;
+  int ijk[3] = {lex % g.ntot[0], (lex / g.ntot[0]) % g.ntot[1], lex / (g.ntot[0] * g.ntot[1])};
+  for (int k = 0; k < 3; ++k) {
+    double x0 = (double)(g.first[k] + ijk[k]) / (double)g.N[k], x1 = (double)(g.first[k] + ijk[k] + 1) / (double)g.N[k];
+    double sfrac = (double)in[k] / (double)p;
+    x[k] = (1.0 - sfrac) * x0 + sfrac * x1;
+  }
+}
+
+__global__ void k_interp_dirichlet(CellGeom g, const double* __restrict__ coords, int p, int nn, int nd, int n_cells, const int* __restrict__ lex_of,
                                    const int* __restrict__ gids, FuncPrm fn, double* fixed) {
   i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= (i64)n_cells * nd) return;
   int c = (int)(tid / nd), l = (int)(tid % nd);
   int gid = gids[tid];
   if (gid >= 0) return;
-  int lex = lex_of ? lex_of[c] : c;
-  int ijk[3] = {lex % g.ntot[0], (lex / g.ntot[0]) % g.ntot[1], lex / (g.ntot[0] * g.ntot[1])};
-  int node = l % nn, n1 = p + 1;
-  int in[3] = {node % n1, (node / n1) % n1, node / (n1 * n1)};
   double x[3];
-  for (int k = 0; k < 3; ++k) {
-    double x0 = (double)(g.first[k] + ijk[k]) / (double)g.N[k], x1 = (double)(g.first[k] + ijk[k] + 1) / (double)g.N[k];
-    double sfrac = (double)in[k] / (double)p;
-    x[k] = (1.0 - sfrac) * x0 + sfrac * x1;
-  }
+  node_position(g, coords, lex_of, c, l % nn, p, x);
   fixed[-gid - 1] = func_u(fn, x);
 }
 
@@ -250,7 +269,7 @@ extern "C" int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const
   if (s->n_dirichlet == 0) return 0;
   i64 total = (i64)s->m.n_cells * s->rt.ndofs;
   k_interp_dirichlet<<<(unsigned)((total + 255) / 256), 256, 0, fb2_stream()>>>(
-      make_geom(s), s->rt.p, s->rt.nnode, s->rt.ndofs, s->m.n_cells, s->d_lex_of, s->d_gids, make_func(func, func_params),
+      make_geom(s), s->d_coords, s->rt.p, s->rt.nnode, s->rt.ndofs, s->m.n_cells, s->d_lex_of, s->d_gids, make_func(func, func_params),
       s->d_fixed);
   FB2_CUDA(cudaGetLastError());
   FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
@@ -259,30 +278,22 @@ extern "C" int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const
 
 // nodal interpolation of an analytic scalar function into the FREE DOF values of an fe_function
 // (serial_fe_space_interpolate_scalar_function, sbm_serial_fe_space.i90:734-819); every component gets u
-__global__ void k_interp_free(CellGeom g, int p, int nn, int nd, int n_local, const int* __restrict__ lex_of,
+__global__ void k_interp_free(CellGeom g, const double* __restrict__ coords, int p, int nn, int nd, int n_local, const int* __restrict__ lex_of,
                               const int* __restrict__ gids, i64 n_free, FuncPrm fn, double* x_out) {
   i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= (i64)n_local * nd) return;
   int c = (int)(tid / nd), l = (int)(tid % nd);
   int gid = gids[tid];
   if (gid <= 0 || gid > n_free) return;
-  int lex = lex_of ? lex_of[c] : c;
-  int ijk[3] = {lex % g.ntot[0], (lex / g.ntot[0]) % g.ntot[1], lex / (g.ntot[0] * g.ntot[1])};
-  int node = l % nn, n1 = p + 1;
-  int in[3] = {node % n1, (node / n1) % n1, node / (n1 * n1)};
   double x[3];
-  for (int k = 0; k < 3; ++k) {
-    double x0 = (double)(g.first[k] + ijk[k]) / (double)g.N[k], x1 = (double)(g.first[k] + ijk[k] + 1) / (double)g.N[k];
-    double sfrac = (double)in[k] / (double)p;
-    x[k] = (1.0 - sfrac) * x0 + sfrac * x1;
-  }
+  node_position(g, coords, lex_of, c, l % nn, p, x);
   x_out[gid - 1] = func_u(fn, x);   // every cell sharing the node writes the same value
 }
 extern "C" int fb2_fe_space_interpolate(fb2_space_t s, int func, const double* func_params, fb2_vector_t x) {
   FB2_CHECK(s && x && x->n == s->n_free, "fb2_fe_space_interpolate: size mismatch");
   i64 total = (i64)s->m.n_local * s->rt.ndofs;
   if (total > 0)
-    k_interp_free<<<(unsigned)((total + 255) / 256), 256, 0, fb2_stream()>>>(make_geom(s), s->rt.p, s->rt.nnode, s->rt.ndofs,
+    k_interp_free<<<(unsigned)((total + 255) / 256), 256, 0, fb2_stream()>>>(make_geom(s), s->d_coords, s->rt.p, s->rt.nnode, s->rt.ndofs,
                                                                             s->m.n_local, s->d_lex_of, s->d_gids, s->n_free,
                                                                             make_func(func, func_params), x->d);
   FB2_CUDA(cudaGetLastError());
@@ -299,17 +310,23 @@ __global__ void k_error_norms(AsmArgs A, const double* __restrict__ x, int ncell
   double* w_u = sm + (size_t)w * nn;
   double e1 = 0.0, e0 = 0.0;
   for (int ci = blockIdx.x * warps + w; ci < ncells; ci += gridDim.x * warps) {
-    int ijk[3] = {ci % A.g.nloc[0] + A.g.L[0], (ci / A.g.nloc[0]) % A.g.nloc[1] + A.g.L[1],
-                  ci / (A.g.nloc[0] * A.g.nloc[1]) + A.g.L[2]};
-    int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
-    int c = A.perm ? A.perm[lex] : lex;
+    int c;
+    double X[8][3];
+    if (A.coords) {
+      c = ci;
+      cell_vertices_from(A.coords, c, X);
+    } else {
+      int ijk[3] = {ci % A.g.nloc[0] + A.g.L[0], (ci / A.g.nloc[0]) % A.g.nloc[1] + A.g.L[1],
+                    ci / (A.g.nloc[0] * A.g.nloc[1]) + A.g.L[2]};
+      int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
+      c = A.perm ? A.perm[lex] : lex;
+      cell_vertices(A.g, ijk, X);
+    }
     for (int l = lane; l < nn; l += 32) {
       int g = A.gids[(i64)c * A.nd + l];
       w_u[l] = g > 0 ? x[g - 1] : (g < 0 ? A.fixed[-g - 1] : 0.0);
     }
     __syncwarp();
-    double X[8][3];
-    cell_vertices(A.g, ijk, X);
     for (int q = lane; q < nq; q += 32) {
       double inv[3][3], det;
       jacobian_at(X, A.gdphi + q * 24, inv, det);
@@ -345,7 +362,7 @@ extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const do
   AsmArgs a;
   a.g = make_geom(s);
   a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = 1; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
-  a.perm = s->d_perm; a.gids = s->d_gids; a.fixed = s->d_fixed;
+  a.perm = s->d_perm; a.gids = s->d_gids; a.coords = s->d_coords; a.fixed = s->d_fixed;
   a.qw = s->d_qw; a.phi = s->d_phi; a.dphi = s->d_dphi; a.gphi = s->d_gphi; a.gdphi = s->d_gdphi;
   a.fn = make_func(func, func_params);
   double* d_out = fb2_scratch_partials();

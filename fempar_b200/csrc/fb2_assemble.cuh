@@ -59,6 +59,25 @@ __device__ __forceinline__ void cell_vertices(const CellGeom& g, const int* ijk,
     for (int k = 0; k < 3; ++k) X[a][k] = (double)(g.first[k] + ijk[k] + ((a >> k) & 1)) / (double)g.N[k];
 }
 
+// vertex coordinates of a cell of a host-built (unstructured) space
+__device__ __forceinline__ void cell_vertices_from(const double* __restrict__ coords, int c, double X[8][3]) {
+  const double* p = coords + (i64)c * 24;
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) X[a][k] = p[a * 3 + k];
+}
+// physical position of the reference point xi in [0,1]^3 under the trilinear cell map
+__device__ __forceinline__ void trilinear_point(const double X[8][3], const double* xi, double* x) {
+  x[0] = x[1] = x[2] = 0.0;
+#pragma unroll
+  for (int a = 0; a < 8; ++a) {
+    double w = ((a & 1) ? xi[0] : 1.0 - xi[0]) * ((a & 2) ? xi[1] : 1.0 - xi[1]) * ((a & 4) ? xi[2] : 1.0 - xi[2]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) x[k] += w * X[a][k];
+  }
+}
+
 // J(q) = sum_a x_a (x) gradN_a(q), inverse, |det| (sbm_cell_map.i90:272-296, sbm_cell_integrator.i90:448-561)
 __device__ __forceinline__ void jacobian_at(const double X[8][3], const double* __restrict__ gd /*[8][3]*/, double inv[3][3],
                                             double& det) {
@@ -88,6 +107,7 @@ struct AsmArgs {
   int p, nn, ncomp, nd, nq;
   const int* perm;       // lex -> local cell id (nullptr: identity)
   const int* gids;
+  const double* coords;  // host-built spaces: vertex coordinates [cell][8][3]; nullptr = structured closed form
   const double* fixed;
   const double *qw, *phi, *dphi, *gphi, *gdphi;
   const i64* irp;

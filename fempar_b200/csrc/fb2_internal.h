@@ -85,6 +85,7 @@ struct fb2_space_s {
   int* d_node_dof = nullptr; // [ncomp][lattice of the LOCAL cell box] -> gid
   int* d_dof_node = nullptr; // [n_free] -> comp * lattice_size + lattice node
   double* d_fixed = nullptr; // fixed_dof_values [n_dirichlet]
+  double* d_coords = nullptr;// host-built (unstructured) spaces only: vertex coordinates [n_cells][8][3], hex vertex order
   // reference tables on device
   double* d_qw = nullptr;    // [nq]
   double* d_phi = nullptr;   // [nq][nnode]
@@ -135,6 +136,8 @@ double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x
 #define FB2_MAX_PARTIALS 65536
 
 int fb2_build_scatter_map(fb2_matrix_s* A);
+int fb2_space_setup_reference_fe(fb2_space_s* s, int order, int ncomp);   // reference-FE tables, host + device (fb2_space.cu)
+int fb2_csr_graph_from_gids(fb2_matrix_s* A);                             // COO sort/unique graph (fb2_unstructured.cu)
 // primitives of fb2_solver.cu used by the host-driven Krylov solvers (fb2_krylov.cu)
 bool fb2_matrix_is_par(fb2_matrix_s* A);
 const double* fb2_matrix_weight(fb2_matrix_s* A);

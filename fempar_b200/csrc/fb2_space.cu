@@ -392,6 +392,22 @@ int fb2_build_node_maps(fb2_space_s* s) {
   return 0;
 }
 
+static int upload_ref_tables(fb2_space_s* s) {
+  auto up = [&](double** d, const std::vector<double>& h) -> int {
+    FB2_TRY(fb2_dalloc(d, h.size()));
+    FB2_CUDA(fb2_memcpy(*d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+    return 0;
+  };
+  FB2_TRY(up(&s->d_qw, s->h_qw)); FB2_TRY(up(&s->d_phi, s->h_phi)); FB2_TRY(up(&s->d_dphi, s->h_dphi));
+  FB2_TRY(up(&s->d_gphi, s->h_gphi)); FB2_TRY(up(&s->d_gdphi, s->h_gdphi));
+  return 0;
+}
+int fb2_space_setup_reference_fe(fb2_space_s* s, int order, int ncomp) {
+  FB2_CHECK(g_inited, "fb2_init was not called (no CUDA device, no CPU fallback)");
+  make_ref_tables(s, order, ncomp);
+  return upload_ref_tables(s);
+}
+
 extern "C" int fb2_fe_space_create(fb2_space_t* out, const int num_cells[3], const int num_parts[3], int part_id,
                                    int order, int num_components, uint32_t dirichlet_boundary_mask) {
   FB2_CHECK(g_inited, "fb2_init was not called (no CUDA device, no CPU fallback)");
@@ -473,13 +489,7 @@ extern "C" int fb2_fe_space_create(fb2_space_t* out, const int num_cells[3], con
   FB2_CUDA(cudaStreamSynchronize(st));
   cudaFree(cnt_free); cudaFree(cnt_dir); cudaFree(base_free); cudaFree(base_dir); cudaFree(own_mask); cudaFree(dirv_mask);
   // 3. reference tables to the device
-  auto up = [&](double** d, const std::vector<double>& h) -> int {
-    FB2_TRY(fb2_dalloc(d, h.size()));
-    FB2_CUDA(fb2_memcpy(*d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
-    return 0;
-  };
-  FB2_TRY(up(&s->d_qw, s->h_qw)); FB2_TRY(up(&s->d_phi, s->h_phi)); FB2_TRY(up(&s->d_dphi, s->h_dphi));
-  FB2_TRY(up(&s->d_gphi, s->h_gphi)); FB2_TRY(up(&s->d_gdphi, s->h_gdphi));
+  FB2_TRY(upload_ref_tables(s));
   FB2_TRY(fb2_dalloc(&s->d_fixed, (size_t)s->n_dirichlet));
   FB2_CUDA(cudaMemsetAsync(s->d_fixed, 0, sizeof(double) * (s->n_dirichlet ? s->n_dirichlet : 1), fb2_stream()));
   // 4. par layer: interface DOFs, dof_import, interior-then-interface renumbering
@@ -494,6 +504,7 @@ extern "C" int fb2_fe_space_create(fb2_space_t* out, const int num_cells[3], con
 extern "C" int fb2_fe_space_destroy(fb2_space_t s) {
   if (!s) return 0;
   cudaFree(s->d_perm); cudaFree(s->d_lex_of); cudaFree(s->d_gids); cudaFree(s->d_node_dof); cudaFree(s->d_dof_node);
+  cudaFree(s->d_coords);
   cudaFree(s->d_fixed); cudaFree(s->d_qw); cudaFree(s->d_phi); cudaFree(s->d_dphi); cudaFree(s->d_gphi); cudaFree(s->d_gdphi);
   if (s->imp) fb2_import_destroy(s->imp);
   delete s;
@@ -628,6 +639,17 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
   const i64 n = A->n;
+  if (s->d_coords) {   // host-built space: no lattice, the graph comes from the cell DOF lists
+    FB2_TRY(fb2_csr_graph_from_gids(A));
+    cudaEventRecord(e1, st);
+    FB2_CUDA(cudaStreamSynchronize(st));
+    float ms_u = 0;
+    cudaEventElapsedTime(&ms_u, e0, e1);
+    fb2_record_phase("pattern", ms_u);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *out = A;
+    return 0;
+  }
   i64* cnt;
   FB2_TRY(fb2_dalloc(&cnt, (size_t)n + 1));
   FB2_TRY(fb2_dalloc(&A->d_irp, (size_t)n + 72));  // padding: the SpMV bulk-copies irp slices of up to 66 entries per tile

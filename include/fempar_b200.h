@@ -111,6 +111,16 @@ int fb2_dof_import_get(fb2_space_t s, int32_t* list_rcv, int32_t* rcv_ptrs, int3
 /* ---- host-built FEMPAR objects handed to the device path (matrix-format, assembler and comm seams) ------ */
 /* a space that is only a number of local DOFs (unstructured meshes, other reference FEs: the reference numbers the DOFs) */
 int fb2_fe_space_create_bare(fb2_space_t* out, int64_t num_dofs);
+/* a space on an UNSTRUCTURED conforming hex mesh that the reference numbered itself: serial_fe_space_t's
+ * cell-wise DOF lists (ptr_dofs_x_fe / lst_dofs_gids, sbm_serial_fe_space.i90:2623-2875; here nd = ncomp*(order+1)^3 ids per
+ * cell, cell-local order of SURVEY A.3, >0 free, <0 strong Dirichlet, >num_free_dofs ghost-only) and the vertex coordinates
+ * of every cell, cell_coords[cell][vertex 0..7, x fastest][xyz].  Cells 0..num_local_cells-1 are integrated.  The device then
+ * builds the CSR graph from the lists (fb2_csr_create: all cell pairs, sort, compress -- base_sparse_matrix.f90:4479-4628),
+ * integrates with the per-cell Jacobians of the trilinear map (sbm_cell_map.i90:272-296, fb2_integrate_assemble), interpolates
+ * and computes error norms; fb2_dof_import_set attaches the par layer. */
+int fb2_fe_space_create_from_host(fb2_space_t* out, int32_t num_cells, int32_t num_local_cells, int order, int num_components,
+                                  const int32_t* lst_dofs_gids, const double* cell_coords, int64_t num_free_dofs,
+                                  int64_t num_dirichlet_dofs);
 /* attach the dof_import_t the reference computed (dof_import.f90:49-90; Fortran conventions: part ids, ptrs and local
  * DOF ids 1-based; weight may be NULL = 0 on every packed, i.e. non-owned, DOF) */
 int fb2_dof_import_set(fb2_space_t s, int32_t num_rcv, const int32_t* list_rcv, const int32_t* rcv_ptrs,
