@@ -186,7 +186,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   const bool host_built = s->d_coords != nullptr;   // no lattice: generic kernel, slots by binary search, atomic scatter
   FB2_CHECK(s->d_gids != nullptr, "this space has no cell DOF lists (bare space): use fb2_assemble_batch");
   if (host_built) scatter_variant = FB2_SCATTER_ATOMIC;
-  if (!host_built && g_asm_variant == 0 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
+  if (g_asm_variant == 0 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
@@ -198,7 +198,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int bps = (int)(227 * 1024 / smem); if (bps < 1) bps = 1; if (bps > 8) bps = 8;
-  int fast_rc = (g_asm_variant == 0 && !host_built) ? fb2_assemble_fast(A, a, scatter_variant) : -1;
+  int fast_rc = g_asm_variant == 0 ? fb2_assemble_fast(A, a, scatter_variant) : -1;
   if (fast_rc > 0) return fast_rc;
   if (fast_rc == 0) {
   } else if (scatter_variant == FB2_SCATTER_ATOMIC) {

@@ -92,7 +92,7 @@ __global__ void k_map_verify(int n_local, int nd, const int* __restrict__ gids, 
 }
 __global__ void k_map_assign(const int* __restrict__ bad_list, int n_bad, int first_tab, int* cell_tab) {
   int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < n_bad) cell_tab[bad_list[k]] = first_tab + k;
+  if (k < n_bad) cell_tab[bad_list ? bad_list[k] : k] = first_tab + k;   // bad_list == nullptr: identity (every cell)
 }
 
 int fb2_build_scatter_map(fb2_matrix_s* A) {
@@ -104,6 +104,32 @@ int fb2_build_scatter_map(fb2_matrix_s* A) {
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
+  if (s->d_coords) {   // host-numbered space: no position classes, one explicit table per cell (as for the "bad" cells below)
+    const size_t elems = (size_t)nd * nd;
+    if ((size_t)n_local * elems * 2 > ((size_t)4 << 30)) A->map_state = -1;
+    else {
+      int* d_ids;
+      FB2_TRY(fb2_dalloc(&A->d_cell_tab, (size_t)n_local));
+      FB2_TRY(fb2_dalloc(&d_ids, (size_t)n_local));
+      FB2_TRY(fb2_dalloc(&A->d_tabs, elems * n_local));
+      k_map_assign<<<(n_local + 255) / 256, 256, 0, st>>>(nullptr, n_local, 0, A->d_cell_tab);
+      FB2_CUDA(cudaMemcpyAsync(d_ids, A->d_cell_tab, sizeof(int) * (size_t)n_local, cudaMemcpyDeviceToDevice, st));
+      k_map_build<<<n_local, 256, 0, st>>>(d_ids, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym, A->d_tabs);
+      FB2_CUDA(cudaGetLastError());
+      FB2_CUDA(cudaStreamSynchronize(st));
+      cudaFree(d_ids);
+      A->n_class_tabs = 0; A->n_tabs = n_local; A->common_tab = -1; A->map_state = 1;
+    }
+    cudaEventRecord(e1, st);
+    cudaStreamSynchronize(st);
+    float ms_h = 0;
+    cudaEventElapsedTime(&ms_h, e0, e1);
+    fb2_record_phase("scatter_map", ms_h);
+    fb2_record_phase("scatter_map_class_tables", 0.0);
+    fb2_record_phase("scatter_map_tables", (double)A->n_tabs);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+  }
   CellGeom g = make_geom(s);
   int *d_rep, *d_class_of_key, *d_bad, *d_nbad, *d_reps;
   FB2_TRY(fb2_dalloc(&A->d_cell_tab, (size_t)n_local));
@@ -247,9 +273,12 @@ __device__ __forceinline__ void column_sumfact(TFun tfun, const double* __restri
 //   E[(i,a),(j,b)] = sum_q w detJ [ lambda G_i^a G_j^b + mu G_i^b G_j^a + delta_ab mu G_i . G_j ],  G = J^-1-mapped gradient,
 // i.e. for column (j,b) and row component a the same sum-factorised contraction with the flux
 //   t_k = w detJ [ lambda B_ak G_j^b + mu B_bk G_j^a + delta_ab mu sum_c B_ck G_j^c ],  B_rk = d xi_k / d x_r.
-template <int P, int NCOMP, bool ATOMIC, bool ELAST>
+// HOSTGEO: host-numbered space (fb2_unstructured.cu): cells in the caller's order, vertex coordinates read from memory, one
+// explicit scatter table per cell; a separate instantiation so that the structured kernels keep their register budget.
+template <int P, int NCOMP, bool ATOMIC, bool ELAST, bool HOSTGEO = false>
 __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assemble_fast(FastArgs F, int cells_in_launch) {
   static_assert(!ELAST || NCOMP == 3, "elasticity needs 3 components");
+  static_assert(!HOSTGEO || ATOMIC, "host-numbered spaces scatter with atomics");
   constexpr int DW = ELAST ? 10 : 6;                 // per quadrature point: B (9) + w detJ, or the symmetric D (6)
   constexpr int N1 = P + 1, NN = N1 * N1 * N1, NQ = NN, ND = NN * NCOMP;
   constexpr int CPW = NN <= 16 ? 32 / NN : 1;        // cells per warp (Q1: 4)
@@ -324,6 +353,7 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
   };
   auto cell_id = [&](int ci) {            // stage A: local cell id (one dependent load through perm in the par numbering)
     if (!lane_on || ci >= cells_in_launch) return -1;
+    if constexpr (HOSTGEO) return ci;
     int ijk[3];
     const int lex = cell_pos(ci, ijk);
     return A.perm ? A.perm[lex] : lex;
@@ -384,12 +414,13 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
     cNN = cell_id(ci + 3 * stride);                     // cell id of cell k+3
     if (on) {
       int ijk[3];
-      cell_pos(ci, ijk);
+      if constexpr (!HOSTGEO) cell_pos(ci, ijk);
       // vertex coordinates (first + ijk + {0,1}) / N (uniform_hex_mesh_generator.f90:608-635): the quotient is formed with the
       // precomputed reciprocal and one residual correction (q0 = a*y; r = fma(-q0, N, a); q = fma(r, y, q0)), which gives the
       // correctly rounded a/N in 3 DFMA-class operations instead of the ~25-instruction IEEE division sequence per coordinate
       double X[8][3];
-      if constexpr (P >= 3) cell_vertices(A.g, ijk, X);   // Q3 is at the 255-register limit: the two extra invariants spill
+      if constexpr (HOSTGEO) cell_vertices_from(A.coords, ci, X);
+      else if constexpr (P >= 3) cell_vertices(A.g, ijk, X);   // Q3 is at the 255-register limit: the two extra invariants spill
       else {
         double lohi[3][2];
 #pragma unroll
@@ -569,6 +600,21 @@ static int load_const_tables(const fb2_space_s* s) {
   return 0;
 }
 
+template <int P, int NCOMP, bool ELAST>
+static int launch_fast_host(const FastArgs& F0, const fb2_space_s* s) {
+  constexpr int NN = (P + 1) * (P + 1) * (P + 1), CPW = NN <= 16 ? 32 / NN : 1, WARPS = 4;
+  FastArgs F = F0;
+  F.a.color = -1; F.tile = 0;
+  int bps = 0;
+  FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_assemble_fast<P, NCOMP, true, ELAST, true>, WARPS * 32, 0));
+  if (bps < 1) bps = 1;
+  const int ncell = s->m.n_local;
+  i64 need = ((i64)ncell + WARPS * CPW - 1) / (WARPS * CPW), cap = (i64)fb2_num_sms() * bps;
+  k_assemble_fast<P, NCOMP, true, ELAST, true><<<(int)(need < cap ? need : cap), WARPS * 32, 0, fb2_stream()>>>(F, ncell);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
 template <int P, int NCOMP, bool ELAST = false>
 static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_variant) {
   constexpr int NN = (P + 1) * (P + 1) * (P + 1), CPW = NN <= 16 ? 32 / NN : 1, WARPS = 4;
@@ -609,6 +655,12 @@ int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant)
   FastArgs F;
   F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs; F.common_tab = A->common_tab;
   F.tile = getenv("FB2_ASM_TILE") ? atoi(getenv("FB2_ASM_TILE")) : 32;
+  if (s->d_coords) {   // host-numbered space
+    if (args.kind == FB2_KIND_ELASTICITY) return s->rt.p == 1 ? launch_fast_host<1, 3, true>(F, s) : launch_fast_host<2, 3, true>(F, s);
+    if (s->rt.ncomp != 1) return -1;
+    return s->rt.p == 1 ? launch_fast_host<1, 1, false>(F, s) : s->rt.p == 2 ? launch_fast_host<2, 1, false>(F, s)
+                                                                              : launch_fast_host<3, 1, false>(F, s);
+  }
   if (args.kind == FB2_KIND_ELASTICITY)
     return s->rt.p == 1 ? launch_fast<1, 3, true>(F, s, scatter_variant) : launch_fast<2, 3, true>(F, s, scatter_variant);
   if (s->rt.p == 1) return s->rt.ncomp == 1 ? launch_fast<1, 1>(F, s, scatter_variant) : launch_fast<1, 3>(F, s, scatter_variant);

@@ -21,6 +21,14 @@ def _close(a, b, rtol=1e-12):
     return np.max(np.abs(a - b)) <= rtol * max(np.max(np.abs(b)), 1e-300)
 
 
+@pytest.fixture(params=[0, 1], ids=["asm_fast", "asm_generic"], autouse=True)
+def asm_variant(request, fb2):
+    """0 = sum-factorised kernel with one explicit scatter table per cell, 1 = generic kernel searching ja."""
+    fb2._lib.check(fb2._lib.lib().fb2_set_assembly_variant(request.param))
+    yield request.param
+    fb2._lib.check(fb2._lib.lib().fb2_set_assembly_variant(0))
+
+
 def _operator(fb2, s, sym, kind=KIND_POISSON, func=FUNC_LINEAR, prm=None, mat=None):
     op = fb2.FeAffineOperator()
     op.create(fb2.csr_format, [sym], [True], [1], s, fb2.DiscreteIntegration(kind, func, prm, mat, fb2.scatter_atomic))
