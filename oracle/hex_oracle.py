@@ -144,3 +144,64 @@ def structured_cell_coords(N, warp=None):
     off = np.stack([a & 1, (a >> 1) & 1, (a >> 2) & 1], axis=1)
     X = (ijk[:, None, :] + off[None, :, :]) / float(N)
     return warp(X) if warp is not None else X
+
+
+def y_junction_mesh(n=2, nz=2):
+    """A genuinely unstructured conforming hex mesh: three quad blocks meeting at a valence-3 line (a 'Y' junction, the
+    building block of O-grids), each block n x n cells, extruded into nz layers.  Returns X [3 n^2 nz, 8, 3]."""
+    ang = lambda d: np.array([np.cos(np.deg2rad(d)), np.sin(np.deg2rad(d))])
+    C0 = np.zeros(2)
+    P = [ang(90), ang(210), ang(330)]
+    M = [ang(150), ang(270), ang(30)]                       # M[0] between P0 and P1, M[1] between P1 and P2, M[2] between P2, P0
+    blocks = [(C0, M[2], P[0], M[0]), (C0, M[0], P[1], M[1]), (C0, M[1], P[2], M[2])]   # counter-clockwise corners
+    cells = []
+    for (A, B, Cc, D) in blocks:
+        bil = lambda s, t: A * (1 - s) * (1 - t) + B * s * (1 - t) + D * (1 - s) * t + Cc * s * t
+        for k in range(nz):
+            for j in range(n):
+                for i in range(n):
+                    v = np.zeros((8, 3))
+                    for a in range(8):
+                        s, t, z = (i + (a & 1)) / n, (j + ((a >> 1) & 1)) / n, (k + ((a >> 2) & 1)) / nz
+                        v[a, :2] = bil(s, t)
+                        v[a, 2] = z
+                    cells.append(v)
+    return np.array(cells)
+
+
+def number_by_coordinates(p, X, ncomp=1, decimals=9):
+    """Conforming H1 numbering of any trilinear hex mesh: Lagrange nodes that coincide physically are one DOF, ids handed out
+    by first touch in cell order (cell-local node order); nodes of faces owned by a single cell are strong Dirichlet.
+    Returns gids [c, ncomp * (p+1)^3] (free > 0, Dirichlet < 0), n_free, n_dirichlet.  (The device accepts ANY numbering the
+    host supplies; this one only has to be conforming.)"""
+    xn = node_coordinates(p, X)
+    nc, nn, _ = xn.shape
+    key = np.round(xn.reshape(-1, 3), decimals)
+    _, first, inv = np.unique(key, axis=0, return_index=True, return_inverse=True)
+    inv = inv.reshape(-1)
+    order = np.argsort(np.argsort(first))                    # unique node -> rank by first touch
+    node = order[inv].reshape(nc, nn)
+    n1 = p + 1
+    loc = np.arange(nn)
+    ijk = np.stack([loc % n1, (loc // n1) % n1, loc // (n1 * n1)], axis=1)
+    faces = {}
+    face_nodes = []
+    for d in range(3):
+        for side in (0, p):
+            face_nodes.append(loc[ijk[:, d] == side])
+    for c in range(nc):
+        for f in face_nodes:
+            k = tuple(sorted(node[c, f]))
+            faces[k] = faces.get(k, 0) + 1
+    is_dir = np.zeros(order.size, dtype=bool)
+    for k, cnt in faces.items():
+        if cnt == 1:
+            is_dir[list(k)] = True
+    gids = np.zeros((nc, ncomp * nn), dtype=np.int32)
+    free_id = np.cumsum(~is_dir) * (~is_dir)                 # 1-based among free nodes (first-touch order)
+    dir_id = np.cumsum(is_dir) * is_dir
+    nf, ndir = int((~is_dir).sum()), int(is_dir.sum())
+    for cc in range(ncomp):
+        g = np.where(is_dir[node], -(dir_id[node] + cc * ndir), free_id[node] + cc * nf)
+        gids[:, cc * nn:(cc + 1) * nn] = g
+    return gids, ncomp * nf, ncomp * ndir

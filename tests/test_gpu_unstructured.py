@@ -157,3 +157,51 @@ def test_bad_arguments_fail_loudly(fb2):
     g[0, 0] = -3
     with pytest.raises(fb2.Fb2Error):
         fb2.HostNumberedFeSpace(1, 1, g, np.zeros((2, 8, 3)), 1, 2)             # Dirichlet id beyond the declared count
+
+
+@pytest.mark.parametrize("p", [1, 2, 3])
+def test_y_junction_unstructured_topology(fb2, p):
+    """a mesh no lattice describes (three blocks around a valence-3 line): graph + values against the hex oracle, patch test
+    through Jacobi-PCG, interpolation and error norms on the device."""
+    X = ho.y_junction_mesh(3, 2)
+    gids, nf, ndir = ho.number_by_coordinates(p, X)
+    s = fb2.HostNumberedFeSpace(p, 1, gids, X, nf, ndir)
+    op = _operator(fb2, s, False)
+    xn = ho.node_coordinates(p, X).sum(-1)
+    fixed = np.zeros(ndir)
+    fixed[-gids[gids < 0] - 1] = xn[gids < 0]
+    assert _close(s.get_fixed_dof_values(), fixed, 1e-14)
+    A, rhs = ho.assemble(p, 1, gids, X, nf, fixed)
+    irp, ja = op.get_matrix().get_pattern()
+    assert np.array_equal(irp - 1, A.indptr) and np.array_equal(ja - 1, A.indices)
+    assert _close(op.get_matrix().get_values(), A.data)
+    assert np.max(np.abs(op.get_translation().get_entries() - rhs)) <= 1e-12 * np.abs(rhs).max()
+    M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    ils = fb2.IterativeLinearSolver()
+    ils.set_parameters_from_pl({fb2.ILS_TYPE: "CG", fb2.ILS_RTOL: 1e-13, fb2.ILS_MAX_NUM_ITERATIONS: 2000})
+    ils.set_operators(op.get_tangent(), M)
+    x = s.create_dof_values()
+    ils.apply(op.get_translation(), x)
+    assert ils.converged()
+    exact = np.zeros(nf)
+    exact[gids[gids > 0] - 1] = xn[gids > 0]
+    assert np.max(np.abs(x.get_entries() - exact)) < 1e-9
+    xi = s.create_dof_values()
+    s.interpolate(FUNC_LINEAR, None, xi)
+    assert _close(xi.get_entries(), exact, 1e-14)
+    h1, l2 = s.error_norms(x, FUNC_LINEAR)
+    assert h1 < 1e-8 and l2 < 1e-9
+    op.free()
+
+
+def test_y_junction_elasticity(fb2):
+    X = ho.y_junction_mesh(2, 2)
+    gids, nf, ndir = ho.number_by_coordinates(2, X, ncomp=3)
+    s = fb2.HostNumberedFeSpace(2, 3, gids, X, nf, ndir)
+    op = _operator(fb2, s, False, kind=KIND_ELASTICITY, mat=[5.0 / 18.0, 5.0 / 12.0])
+    A, rhs = ho.assemble(2, 3, gids, X, nf, s.get_fixed_dof_values(), lam=5.0 / 18.0, mu=5.0 / 12.0)
+    irp, ja = op.get_matrix().get_pattern()
+    assert np.array_equal(irp - 1, A.indptr) and np.array_equal(ja - 1, A.indices)
+    assert _close(op.get_matrix().get_values(), A.data)
+    assert np.max(np.abs(op.get_translation().get_entries() - rhs)) <= 1e-12 * np.abs(rhs).max()
+    op.free()

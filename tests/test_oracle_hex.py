@@ -83,3 +83,24 @@ def test_distorted_patch_test(p):
     assert np.abs(x - exact).max() < 1e-11
     h1, l2 = ho.error_norms(p, gids, X, x, fixed, lambda q: q.sum(-1), lambda q: np.ones_like(q))
     assert h1 < 1e-10 and l2 < 1e-11
+
+
+@pytest.mark.parametrize("p", [1, 2])
+def test_y_junction_mesh_patch_test(p):
+    """unstructured topology (a line where three blocks meet): conforming numbering + exact reproduction of u = x+y+z."""
+    X = ho.y_junction_mesh(3, 2)
+    gids, nf, ndir = ho.number_by_coordinates(p, X)
+    assert nf > 0 and ndir > 0 and gids.max() == nf and gids.min() == -ndir
+    vol = ho.cell_geometry(p, X)[1].sum()
+    assert abs(vol - 1.5 * np.sqrt(3.0)) < 1e-12            # regular hexagon of circumradius 1, height 1
+    xn = ho.node_coordinates(p, X).sum(-1)
+    fixed = np.zeros(ndir)
+    fixed[-gids[gids < 0] - 1] = xn[gids < 0]
+    A, rhs = ho.assemble(p, 1, gids, X, nf, fixed)
+    assert abs(A - A.T).max() < 1e-13
+    x = spla.spsolve(A.tocsc(), rhs)
+    exact = np.zeros(nf)
+    exact[gids[gids > 0] - 1] = xn[gids > 0]
+    assert np.abs(x - exact).max() < 1e-11
+    valence = np.bincount(gids[:, 0][gids[:, 0] > 0])      # local node 0 of every block cell (i,j)=(0,0) is the junction line
+    assert valence.max() == 3
