@@ -100,6 +100,44 @@ def main():
     chk("host_solution", np.max(np.abs(xh.get_entries() - ro["x"][rank])) <= 1e-8)
     if rank == 0:
         print("host-built import + CSR: iters", ils.get_num_iterations(), ro["iters"], "ok", ok, flush=True)
+    # --- host-numbered par space: the oracle's per-part lst_dofs_gids (local + ghost cells, interior-then-
+    #     interface numbering), vertex coordinates by global cell id and dof_import_t are uploaded; affine coordinates must
+    #     reproduce the par oracle, warped coordinates must pass the patch test across the parts ---
+    from oracle import hex_oracle as ho
+    cg_ids = np.asarray(q.cells_gid()) - 1
+    warp = lambda X: X + 0.05 * np.sin(np.pi * X) * np.sin(np.pi * X[..., [1, 2, 0]])
+    for tag, wfun in (("affine", None), ("warped", warp)):
+        Xc = ho.structured_cell_coords(N[0], wfun)[cg_ids]
+        gl = q.lst_dofs_gids().copy()
+        hs = fb.HostNumberedFeSpace(p, 1, gl, Xc, q.num_free, q.num_dirichlet, num_local_cells=q.num_local_cells)
+        hs.set_dof_import(im["list_rcv"], im["rcv_ptrs"] + 1, im["unpack_idx"], im["list_snd"], im["snd_ptrs"] + 1, im["pack_idx"])
+        func, prm = (FUNC_SHARP_WAVE, WAVE) if wfun is None else (FUNC_LINEAR, None)
+        hop = fb.FeAffineOperator()
+        hop.create(fb.csr_format, [False], [True], [1], hs, fb.DiscreteIntegration(fb.poisson, func, prm))
+        hop.compute()
+        hM = fb.JacobiPreconditioner(); hM.create(hop); hM.numerical_setup()
+        ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG")
+        ils.set_parameters_from_pl({fb.ILS_RTOL: 1e-12, fb.ILS_MAX_NUM_ITERATIONS: 5000})
+        ils.set_operators(hop.get_tangent(), hM)
+        hx = hs.create_dof_values()
+        ils.apply(hop.get_translation(), hx)
+        if wfun is None:
+            hb = hop.get_translation().get_entries()
+            chk("hostnum_rhs", np.max(np.abs(hb - P.b[rank])) <= 1e-12 * np.max(np.abs(P.b[rank])))
+            chk("hostnum_dinv", np.max(np.abs(hM.inverse_diagonal.get_entries() - P.dinv[rank])) <= 1e-12 * np.max(np.abs(P.dinv[rank])))
+            chk("hostnum_iters", ils.converged() and abs(ils.get_num_iterations() - ro["iters"]) <= 1, (ils.get_num_iterations(), ro["iters"]))
+            chk("hostnum_solution", np.max(np.abs(hx.get_entries() - ro["x"][rank])) <= 1e-8)
+        else:
+            xn = ho.node_coordinates(p, Xc).sum(-1)
+            exact = np.zeros(q.num_free)
+            m = (gl > 0) & (gl <= q.num_free)
+            exact[gl[m] - 1] = xn[m]
+            chk("hostnum_patch", ils.converged() and np.max(np.abs(hx.get_entries() - exact)) <= 1e-9, np.max(np.abs(hx.get_entries() - exact)))
+            h1, l2 = hs.error_norms(hx, FUNC_LINEAR)
+            chk("hostnum_errors", h1 < 1e-8 and l2 < 1e-9, (h1, l2))
+        if rank == 0:
+            print("host-numbered par space", tag, "iters", ils.get_num_iterations(), "ok", ok, flush=True)
+        hop.free()
     # --- other Krylov solvers in the par layout: iteration counts and residual histories are invariant
     #     under the DOF renumbering of the partition, so the SERIAL restatement on the same mesh is the checker ---
     import scipy.sparse as sp
