@@ -120,6 +120,14 @@ struct fb2_matrix_s {
   i64* d_tile_row = nullptr;              // first row of every tile
   unsigned char* d_tile_nrows = nullptr;  // rows in the tile (<= spmv_R)
   size_t spmv_smem = 0;
+  // compressed column indices of the streaming SpMV (fb2_spmv.cu): per tile a dictionary of its distinct columns + one
+  // uint16 dictionary position per stored entry (10 B instead of 12 B per non-zero streamed from HBM)
+  int spmv_comp = 0;                        // 0 not built, 1 in use, -1 unavailable / switched off
+  int spmv_dcap = 0;                        // largest dictionary (entries, multiple of 4)
+  unsigned short* d_idx16 = nullptr;        // [nnz] position of ja[k] in the dictionary of its tile
+  int* d_dict = nullptr;                    // concatenated dictionaries, 0-based columns, each padded to 4 entries
+  i64* d_dict_ptr = nullptr;                // [ntiles + 1] offsets into d_dict
+  size_t spmv_smem_comp = 0;
   int owns_space = 0;                       // matrix created from host arrays without a space: it owns a bare one
   i64 spmv_t_itf = -1, spmv_row_itf = -1;   // interface split of the tile table (par overlap)
 };
@@ -150,6 +158,7 @@ int fb2_dots_host(fb2_matrix_s* A, int k, const double* const* xs, const double*
 void fb2_cg_set_icg(int on);
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 int fb2_spmv_prepare(fb2_matrix_s* A);
+void fb2_spmv_set_compress(bool on);   // dictionary-compressed column indices for matrices prepared from now on
 // tiles [t0, t1) only; chunk = 0: persistent CTAs striding over the range, chunk > 0: one CTA per `chunk` consecutive tiles
 // (short-lived CTAs, so that a higher-priority stream gets SM resources while the launch is running)
 int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, i64 t0, i64 t1,

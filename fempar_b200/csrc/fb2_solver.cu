@@ -137,7 +137,12 @@ static int g_spmv_variant = 0;   // 0: TMA-streamed tiles (fb2_spmv.cu), 1: warp
 // interior tiles per short-lived CTA (FB2_PAR_CHUNK)
 static int g_par_overlap = getenv("FB2_PAR_OVERLAP") ? atoi(getenv("FB2_PAR_OVERLAP")) : 1;
 static int g_par_chunk = getenv("FB2_PAR_CHUNK") ? atoi(getenv("FB2_PAR_CHUNK")) : 64;
-extern "C" int fb2_set_spmv_variant(int v) { g_spmv_variant = v; return 0; }
+extern "C" int fb2_set_spmv_variant(int v) {
+  // 2 = streamed tiles with dictionary-compressed column indices, for matrices whose first SpMV comes after this call
+  fb2_spmv_set_compress(v == 2);
+  g_spmv_variant = v == 2 ? 0 : v;
+  return 0;
+}
 
 static int spmv_grid(i64 n, int warps_per_block) {
   i64 b = (n + warps_per_block - 1) / warps_per_block;

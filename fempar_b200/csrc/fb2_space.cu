@@ -692,6 +692,7 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
 extern "C" int fb2_csr_destroy(fb2_matrix_t A) {
   if (!A) return 0;
   cudaFree(A->d_irp); cudaFree(A->d_ja); cudaFree(A->d_val); cudaFree(A->d_cell_tab); cudaFree(A->d_tabs); cudaFree(A->d_tile_row); cudaFree(A->d_tile_nrows);
+  cudaFree(A->d_idx16); cudaFree(A->d_dict); cudaFree(A->d_dict_ptr);
   if (A->owns_space) fb2_fe_space_destroy(A->s);
   delete A;
   return 0;

@@ -49,22 +49,34 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // the "full" one with the byte count of the three bulk copies (val, ja, irp slice).  The 8 consumer
 // warps never synchronise with each other: each owns R/8 rows of every tile, gathers x, reduces its
 // rows inside TPR-lane groups and releases the stage with one arrive per warp.
-template <bool FUSE_DOT>
-__global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* __restrict__ irp, const int* __restrict__ ja,
+// COMP: the column indices are streamed as uint16 positions in a per-tile dictionary of distinct columns (built once by
+// fb2_spmv_compress): 10 B + ~0.5 B of dictionary per non-zero instead of 12 B.  `ja` then points at the uint16 stream, the
+// element range of a tile is aligned to 8 entries (16-byte bulk copies), and the products are formed in the same order, so y
+// is bit-identical to the uncompressed kernel.
+template <bool FUSE_DOT, bool COMP>
+__global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* __restrict__ irp, const void* __restrict__ ja_any,
                                                              const double* __restrict__ val, const double* __restrict__ x,
                                                              double* __restrict__ y, double* partials, const int* done_flag,
                                                              int R, int cap, i64 ntiles, int STAGES,
                                                              const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
-                                                             int chunk) {
+                                                             int chunk, const int* __restrict__ dict, const i64* __restrict__ dict_ptr,
+                                                             int dcap) {
+  constexpr int IB = COMP ? 2 : 4;                       // bytes per streamed column index
+  constexpr i64 AL = COMP ? 7 : 3;                       // element-range alignment mask
+  const int* ja = (const int*)ja_any;
+  const unsigned short* ja16 = (const unsigned short*)ja_any;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full_bar[SPMV_MAX_STAGES], empty_bar[SPMV_MAX_STAGES];
   __shared__ i64 s_e0a[SPMV_MAX_STAGES], s_r0[SPMV_MAX_STAGES];
-  __shared__ int s_nr[SPMV_MAX_STAGES];
+  __shared__ int s_nr[SPMV_MAX_STAGES], s_nd[SPMV_MAX_STAGES];
   __shared__ double s_red[32];
   if (done_flag && *done_flag) return;
   const int tid = threadIdx.x;
   const size_t irp_bytes = (size_t)(R + 2) * 8;
-  const size_t stage_bytes = (size_t)cap * 12 + irp_bytes;
+  const size_t dict_off = (size_t)cap * (8 + IB);
+  const size_t xs_off = dict_off + (COMP ? (size_t)dcap * 4 : 0);      // COMP: x gathered once per dictionary entry
+  const size_t irp_off = xs_off + (COMP ? (size_t)dcap * 8 : 0);
+  const size_t stage_bytes = irp_off + irp_bytes;
   // tiles of this CTA: persistent (chunk == 0): blockIdx.x, blockIdx.x + gridDim.x, ... ; chunked: `chunk` consecutive tiles
   const i64 t_first = chunk ? (i64)blockIdx.x * chunk : (i64)blockIdx.x;
   const i64 t_step = chunk ? 1 : (i64)gridDim.x;
@@ -79,27 +91,36 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
     // ---------------- producer warp ----------------
     if (tid == SPMV_CONSUMERS) {
       i64 t = t_first;
-      i64 e0 = 0, e1 = 0, r0 = 0;
+      i64 e0 = 0, e1 = 0, r0 = 0, d0 = 0, d1 = 0;
       int nr = 0;
-      if (t < t_end) { r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr]; }
+      if (t < t_end) {
+        r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr];
+        if (COMP) { d0 = dict_ptr[t]; d1 = dict_ptr[t + 1]; }
+      }
       for (int it = 0; t < t_end; t += t_step, ++it) {
         const int s = it % STAGES;
         // prefetch the row / element range of the next tile before blocking on the empty barrier
-        i64 tn = t + t_step, ne0 = 0, ne1 = 0, nr0 = 0;
+        i64 tn = t + t_step, ne0 = 0, ne1 = 0, nr0 = 0, nd0 = 0, nd1 = 0;
         int nnr = 0;
-        if (tn < t_end) { nr0 = tile_row[tn]; nnr = tile_nrows[tn]; ne0 = irp[nr0]; ne1 = irp[nr0 + nnr]; }
+        if (tn < t_end) {
+          nr0 = tile_row[tn]; nnr = tile_nrows[tn]; ne0 = irp[nr0]; ne1 = irp[nr0 + nnr];
+          if (COMP) { nd0 = dict_ptr[tn]; nd1 = dict_ptr[tn + 1]; }
+        }
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
         unsigned char* base = smem_raw + s * stage_bytes;
-        const i64 e0a = e0 & ~(i64)3;
-        const uint32_t cnt4 = (uint32_t)((e1 - e0a + 3) & ~(i64)3);
-        s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr;
-        mbar_expect_tx(&full_bar[s], cnt4 * 12u + (uint32_t)irp_bytes);
-        bulk_g2s(base + (size_t)cap * 12, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
+        const i64 e0a = e0 & ~AL;
+        const uint32_t cnt4 = (uint32_t)((e1 - e0a + AL) & ~AL);
+        const uint32_t dbytes = COMP ? (uint32_t)(d1 - d0) * 4u : 0u;
+        s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0);
+        mbar_expect_tx(&full_bar[s], cnt4 * (uint32_t)(8 + IB) + dbytes + (uint32_t)irp_bytes);
+        bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
         if (cnt4) {
           bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
-          bulk_g2s(base + (size_t)cap * 8, ja + e0a, cnt4 * 4u, &full_bar[s]);
+          if (COMP) bulk_g2s(base + (size_t)cap * 8, ja16 + e0a, cnt4 * 2u, &full_bar[s]);
+          else bulk_g2s(base + (size_t)cap * 8, ja + e0a, cnt4 * 4u, &full_bar[s]);
         }
-        e0 = ne0; e1 = ne1; r0 = nr0; nr = nnr;
+        if (COMP && dbytes) bulk_g2s(base + dict_off, dict + d0, dbytes, &full_bar[s]);
+        e0 = ne0; e1 = ne1; r0 = nr0; nr = nnr; d0 = nd0; d1 = nd1;
       }
     }
     return;
@@ -117,7 +138,20 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
     const unsigned char* base = smem_raw + s * stage_bytes;
     const double* sv = (const double*)base;
     const int* sj = (const int*)(base + (size_t)cap * 8);
-    const i64* s_irp = (const i64*)(base + (size_t)cap * 12);
+    const unsigned short* sj16 = (const unsigned short*)(base + (size_t)cap * 8);
+    const int* sd = (const int*)(base + dict_off);
+    const i64* s_irp = (const i64*)(base + irp_off);
+    // COMP: the consumer warps gather x once per DISTINCT column of the tile into shared memory (7-9x fewer gathers than
+    // entries); the inner loop then reads shared memory only.  One named barrier per tile; the per-stage buffer is safe to
+    // rewrite STAGES tiles later because every warp has passed the barriers of the tiles in between.
+    double* xs = (double*)(base + xs_off);
+    if (COMP) {
+      const int nd = s_nd[s];
+      for (int d = tid; d < nd; d += SPMV_CONSUMERS) xs[d] = x[sd[d]];
+      asm volatile("bar.sync 2, %0;" ::"r"(SPMV_CONSUMERS) : "memory");
+    }
+    // x value of the k-th staged entry
+    auto xat = [&](int k) -> double { if (COMP) return xs[sj16[k]]; else return x[sj[k] - 1]; };
     const i64 e0a = s_e0a[s];
     double acc = 0.0;
     const bool live = row < s_nr[s];
@@ -125,7 +159,7 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
       const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
       int k = b + sub;
       for (; k + 3 * TPR < e; k += 4 * TPR) {
-        const double x0 = x[sj[k] - 1], x1 = x[sj[k + TPR] - 1], x2 = x[sj[k + 2 * TPR] - 1], x3 = x[sj[k + 3 * TPR] - 1];
+        const double x0 = xat(k), x1 = xat(k + TPR), x2 = xat(k + 2 * TPR), x3 = xat(k + 3 * TPR);
         acc += sv[k] * x0;
         acc += sv[k + TPR] * x1;
         acc += sv[k + 2 * TPR] * x2;
@@ -135,8 +169,7 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
         // tail of up to 3 entries per lane as ONE masked batch, so that its gathers are in flight together
         const int k1 = k + TPR, k2 = k + 2 * TPR;
         const bool p1 = k1 < e, p2 = k2 < e;
-        const int c0 = sj[k], c1 = p1 ? sj[k1] : c0, c2 = p2 ? sj[k2] : c0;
-        const double x0 = x[c0 - 1], x1 = x[c1 - 1], x2 = x[c2 - 1];
+        const double x0 = xat(k), x1 = p1 ? xat(k1) : 0.0, x2 = p2 ? xat(k2) : 0.0;
         acc += sv[k] * x0;
         if (p1) acc += sv[k1] * x1;
         if (p2) acc += sv[k2] * x2;
@@ -194,6 +227,134 @@ __global__ void k_tile_fill(i64 n, const i64* __restrict__ irp, int R, int cap, 
   for (i64 a = r0; a < r1; a += rows, ++o) { tile_row[o] = a; tile_nrows[o] = (unsigned char)(min(a + rows, r1) - a); }
 }
 
+// ---- compressed column indices: per tile the sorted distinct columns (dictionary) + a uint16 position per entry ----
+#define DICT_SORT_MAX 4096
+template <bool FILL>
+__global__ void __launch_bounds__(256) k_tile_dict(const i64* __restrict__ irp, const int* __restrict__ ja,
+                                                   const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
+                                                   i64* cnt, int* maxcnt, const i64* __restrict__ dict_ptr, int* dict,
+                                                   unsigned short* idx16) {
+  __shared__ int sb[DICT_SORT_MAX], su[DICT_SORT_MAX];
+  __shared__ int s_scan[256];
+  const int tid = threadIdx.x;
+  const i64 t = blockIdx.x;
+  const i64 r0 = tile_row[t];
+  const i64 e0 = irp[r0], e1 = irp[r0 + tile_nrows[t]];
+  const int m = (int)(e1 - e0);
+  int np2 = 256;
+  while (np2 < m) np2 <<= 1;
+  for (int i = tid; i < np2; i += 256) sb[i] = i < m ? ja[e0 + i] - 1 : 0x7fffffff;
+  __syncthreads();
+  for (int k = 2; k <= np2; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < np2; i += 256) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const int a = sb[i], b = sb[ixj];
+          if ((a > b) == ((i & k) == 0)) { sb[i] = b; sb[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  // ordered compaction of the distinct values: each thread owns a contiguous chunk
+  const int per = np2 / 256, lo = tid * per;
+  int heads = 0;
+  for (int i = lo; i < lo + per; ++i) heads += (i < m && (i == 0 || sb[i] != sb[i - 1])) ? 1 : 0;
+  s_scan[tid] = heads;
+  __syncthreads();
+  for (int o = 1; o < 256; o <<= 1) {            // Hillis-Steele inclusive scan
+    const int v = tid >= o ? s_scan[tid - o] : 0;
+    __syncthreads();
+    s_scan[tid] += v;
+    __syncthreads();
+  }
+  const int nu = s_scan[255];
+  int pos = s_scan[tid] - heads;
+  for (int i = lo; i < lo + per; ++i)
+    if (i < m && (i == 0 || sb[i] != sb[i - 1])) su[pos++] = sb[i];
+  __syncthreads();
+  const int nu4 = (nu + 3) & ~3;
+  if (!FILL) {
+    if (tid == 0) { cnt[t] = nu4; atomicMax(maxcnt, nu4); }
+    return;
+  }
+  const i64 d0 = dict_ptr[t];
+  for (int i = tid; i < nu4; i += 256) dict[d0 + i] = su[i < nu ? i : nu - 1];
+  for (int i = tid; i < m; i += 256) {
+    const int c = ja[e0 + i] - 1;
+    int a = 0, b = nu;
+    while (a < b) { const int mid = (a + b) >> 1; if (su[mid] < c) a = mid + 1; else b = mid; }
+    idx16[e0 + i] = (unsigned short)a;
+  }
+}
+
+// Off by default: measured SLOWER than the plain int32 stream on B200 (Q2 256^3: 21.9 vs 19.3 ms per SpMV although 12 % fewer
+// bytes move, profiles/r1_spmv_compress_probe.txt) -- the gather phase and its barrier put a global-latency bubble at the
+// head of every tile that 4 CTAs per SM do not hide.  Kept behind fb2_set_spmv_variant(2) / FB2_SPMV_COMPRESS=1 as the
+// starting point for a pipelined gather.
+static int g_compress = getenv("FB2_SPMV_COMPRESS") ? atoi(getenv("FB2_SPMV_COMPRESS")) : 0;
+void fb2_spmv_set_compress(bool on) { g_compress = on ? 1 : 0; }
+static int spmv_compress(fb2_matrix_s* A, int capbuf, int R, int STAGES) {
+  const int enabled = g_compress;
+  A->spmv_comp = -1;
+  const i64 nt = A->spmv_ntiles;
+  if (!enabled || nt == 0 || capbuf > DICT_SORT_MAX || nt > 0x7fffffffLL) return 0;
+  cudaStream_t st = fb2_stream();
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  i64* cnt; int* d_max;
+  FB2_TRY(fb2_dalloc(&cnt, (size_t)nt + 1)); FB2_TRY(fb2_dalloc(&d_max, 1));
+  FB2_TRY(fb2_dalloc(&A->d_dict_ptr, (size_t)nt + 1));
+  FB2_CUDA(cudaMemsetAsync(cnt + nt, 0, sizeof(i64), st));
+  FB2_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), st));
+  k_tile_dict<false><<<(unsigned)nt, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, cnt, d_max, nullptr, nullptr, nullptr);
+  FB2_CUDA(cudaGetLastError());
+  {
+    void* tmp = nullptr; size_t bytes = 0;
+    FB2_CUDA(cub::DeviceScan::ExclusiveSum(tmp, bytes, cnt, A->d_dict_ptr, nt + 1, st));
+    FB2_CUDA(cudaMalloc(&tmp, bytes ? bytes : 1));
+    cudaError_t e = cub::DeviceScan::ExclusiveSum(tmp, bytes, cnt, A->d_dict_ptr, nt + 1, st);
+    cudaStreamSynchronize(st);
+    cudaFree(tmp);
+    FB2_CUDA(e);
+  }
+  i64 total = 0; int dcap = 0;
+  FB2_CUDA(fb2_memcpy(&total, A->d_dict_ptr + nt, sizeof(i64), cudaMemcpyDeviceToHost));
+  FB2_CUDA(fb2_memcpy(&dcap, d_max, sizeof(int), cudaMemcpyDeviceToHost));
+  cudaFree(cnt); cudaFree(d_max);
+  const size_t smem = ((size_t)capbuf * 10 + (size_t)dcap * 12 + (size_t)(R + 2) * 8) * STAGES;
+  // worth it only when the dictionaries are small next to the 2 B per entry they save, and the stage still fits
+  bool ok = dcap > 0 && dcap <= 2048 && smem <= 200 * 1024 && (double)total * 4.0 < 0.5 * 2.0 * (double)A->nnz;
+  if (ok) {
+    // the extra streams are optional: when HBM is short the uncompressed kernel stays in use
+    if (cudaMalloc((void**)&A->d_idx16, sizeof(unsigned short) * ((size_t)A->nnz + 16)) != cudaSuccess) { cudaGetLastError(); A->d_idx16 = nullptr; ok = false; }
+    else if (cudaMalloc((void**)&A->d_dict, sizeof(int) * ((size_t)total + 4)) != cudaSuccess) { cudaGetLastError(); A->d_dict = nullptr; ok = false; }
+  }
+  if (!ok) {
+    cudaFree(A->d_idx16); cudaFree(A->d_dict_ptr); A->d_idx16 = nullptr; A->d_dict_ptr = nullptr;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+  }
+  FB2_CUDA(cudaMemsetAsync(A->d_idx16, 0, sizeof(unsigned short) * ((size_t)A->nnz + 16), st));
+  FB2_CUDA(cudaMemsetAsync(A->d_dict, 0, sizeof(int) * ((size_t)total + 4), st));
+  k_tile_dict<true><<<(unsigned)nt, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, nullptr, nullptr, A->d_dict_ptr, A->d_dict, A->d_idx16);
+  FB2_CUDA(cudaGetLastError());
+  A->spmv_dcap = dcap; A->spmv_smem_comp = smem;
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaEventRecord(e1, st);
+  FB2_CUDA(cudaStreamSynchronize(st));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  fb2_record_phase("spmv_compress", ms);
+  fb2_record_phase("spmv_dict_entries", (double)total);
+  fb2_record_phase("spmv_dict_cap", (double)dcap);
+  A->spmv_comp = 1;
+  return 0;
+}
+
 // choose the tile geometry once per matrix
 int fb2_spmv_prepare(fb2_matrix_s* A) {
   if (A->spmv_cap > 0 || A->n == 0) return 0;
@@ -234,16 +395,17 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   size_t smem = stage * STAGES;
   FB2_CHECK(smem <= 200 * 1024, "SpMV tile does not fit in shared memory");
   A->spmv_R = R; A->spmv_cap = capbuf; A->spmv_ntiles = ntiles; A->spmv_smem = smem; A->spmv_stages = STAGES;
-  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int bps = 0;
-  FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_stream<true>, SPMV_THREADS, smem));
+  FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_stream<true, false>, SPMV_THREADS, smem));
   if (bps < 1) bps = 1;
   i64 grid = (i64)fb2_num_sms() * bps;
   if (grid > ntiles) grid = ntiles;
   if (grid > FB2_MAX_PARTIALS) grid = FB2_MAX_PARTIALS;
   A->spmv_grid = (int)grid;
   fb2_record_phase("spmv_R", R); fb2_record_phase("spmv_tiles", (double)ntiles); fb2_record_phase("spmv_ctas_per_sm", bps);
+  FB2_TRY(spmv_compress(A, capbuf, R, STAGES));
   return 0;
 }
 
@@ -255,14 +417,18 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
   cudaStream_t st = fb2_stream();
   if (chunk && (nt + chunk - 1) / chunk > FB2_MAX_PARTIALS / 2) chunk = (int)((nt + FB2_MAX_PARTIALS / 2 - 1) / (FB2_MAX_PARTIALS / 2));
   i64 grid = chunk ? (nt + chunk - 1) / chunk : (nt < A->spmv_grid ? nt : (i64)A->spmv_grid);
-  if (fuse_dot)
-    k_spmv_stream<true><<<(unsigned)grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, partials, done_flag,
-                                                                             A->spmv_R, A->spmv_cap, nt, A->spmv_stages,
-                                                                             A->d_tile_row + t0, A->d_tile_nrows + t0, chunk);
-  else
-    k_spmv_stream<false><<<(unsigned)grid, SPMV_THREADS, A->spmv_smem, st>>>(A->n, A->d_irp, A->d_ja, A->d_val, x, y, nullptr, done_flag,
-                                                                              A->spmv_R, A->spmv_cap, nt, A->spmv_stages,
-                                                                              A->d_tile_row + t0, A->d_tile_nrows + t0, chunk);
+#define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                                   \
+  k_spmv_stream<FD, CP><<<(unsigned)grid, SPMV_THREADS, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
+                                                                    done_flag, A->spmv_R, A->spmv_cap, nt, A->spmv_stages,   \
+                                                                    A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP)
+  if (A->spmv_comp == 1) {
+    if (fuse_dot) SPMV_LAUNCH(true, true, A->d_idx16, A->spmv_smem_comp, A->d_dict, A->d_dict_ptr + t0, A->spmv_dcap);
+    else SPMV_LAUNCH(false, true, A->d_idx16, A->spmv_smem_comp, A->d_dict, A->d_dict_ptr + t0, A->spmv_dcap);
+  } else {
+    if (fuse_dot) SPMV_LAUNCH(true, false, A->d_ja, A->spmv_smem, nullptr, nullptr, 0);
+    else SPMV_LAUNCH(false, false, A->d_ja, A->spmv_smem, nullptr, nullptr, 0);
+  }
+#undef SPMV_LAUNCH
   FB2_CUDA(cudaGetLastError());
   if (grid_out) *grid_out = (int)grid;
   return 0;

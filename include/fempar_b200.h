@@ -156,7 +156,9 @@ int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind, int func,
 int fb2_set_assembly_variant(int variant);
 /* y = A x : csr apply_body (csr_sparse_matrix.f90:626-672); par: + comm() (par_sparse_matrix.f90:739-762) */
 int fb2_spmv(fb2_matrix_t A, fb2_vector_t x, fb2_vector_t y);
-/* SpMV kernel variant: 0 = TMA-streamed row tiles (default), 1 = warp-per-row (kept for ncu comparison) */
+/* SpMV kernel variant: 0 = TMA-streamed row tiles (default), 1 = warp-per-row (kept for ncu comparison), 2 = streamed tiles
+ * with per-tile dictionary + uint16 column indices (10.6 instead of 12 B per non-zero; bit-identical results; measured slower,
+ * experimental; applies to matrices whose first SpMV comes after the call) */
 int fb2_set_spmv_variant(int variant);
 int fb2_extract_diagonal(fb2_matrix_t A, fb2_vector_t d);   /* csr_sparse_matrix.f90:4231-4256 */
 

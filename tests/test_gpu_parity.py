@@ -314,3 +314,37 @@ def test_determinism_of_reductions_and_colored_scatter(fb2):
         ils.apply(op.get_translation(), x)
         sols.append(x.get_entries().copy()); hists.append(ils.history.copy())
     assert np.array_equal(sols[0], sols[1]) and np.array_equal(hists[0], hists[1])
+
+
+@pytest.mark.parametrize("N,p", [((9, 8, 7), 2), ((12, 12, 12), 1), ((5, 5, 4), 3)])
+def test_spmv_kernel_variants_agree(fb2, N, p):
+    """variant 0 = TMA-streamed tiles, 1 = warp per row, 2 = streamed tiles with dictionary-compressed uint16 column indices:
+    2 forms the same products in the same order (bit-identical y and fused <Ap,p>, same PCG history), 1 agrees to rounding."""
+    ys, hist = {}, {}
+    lib = fb2._lib.lib()
+    try:
+        for v in (0, 2, 1):
+            fb2._lib.check(lib.fb2_set_spmv_variant(v))
+            s, op = _assemble(fb2, N, p, 1, KIND_POISSON, FUNC_SHARP_WAVE, WAVE, None, 1)   # coloured scatter: the same matrix bits every time
+            x = np.random.default_rng(11).standard_normal(s.num_free_dofs)
+            vx, vy = s.create_dof_values(), s.create_dof_values()
+            vx.set_entries(x)
+            op.get_matrix().apply(vx, vy)
+            ys[v] = vy.get_entries()
+            M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+            ils = fb2.IterativeLinearSolver()
+            ils.set_parameters_from_pl({fb2.ILS_TYPE: "CG", fb2.ILS_RTOL: 1e-10, fb2.ILS_MAX_NUM_ITERATIONS: 500,
+                                        fb2.ILS_TRACK_CONVERGENCE_HISTORY: True})
+            ils.set_operators(op.get_tangent(), M)
+            sol = s.create_dof_values()
+            ils.apply(op.get_translation(), sol)
+            assert ils.converged()
+            hist[v] = (ils.get_num_iterations(), sol.get_entries())
+            if v == 2:
+                assert op.last_phase_ms("spmv_dict_cap") > 0          # the compressed stream was really built
+            op.free()
+    finally:
+        fb2._lib.check(lib.fb2_set_spmv_variant(0))
+    assert np.array_equal(ys[0], ys[2])
+    assert hist[0][0] == hist[2][0] and np.array_equal(hist[0][1], hist[2][1])
+    assert _close(ys[1], ys[0]) and abs(hist[1][0] - hist[0][0]) <= 1
