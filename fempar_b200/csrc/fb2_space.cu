@@ -630,6 +630,70 @@ __global__ void k_row_fill(int p, int ncomp, int M0, int M1, int M2, i64 lat_siz
   }
 }
 
+// Same rows, sorted in registers: lane l holds candidates l*KPL .. l*KPL+KPL-1; bitonic network with in-lane exchanges for
+// distances < KPL and warp shuffles above (no shared memory, no __syncwarp): rows of up to 32*KPL candidates.
+template <int KPL>
+__global__ void __launch_bounds__(128) k_row_fill_reg(int p, int ncomp, int M0, int M1, int M2, i64 lat_size, i64 n, int sym,
+                                                      const int* __restrict__ dof_node, const int* __restrict__ node_dof,
+                                                      const i64* __restrict__ irp, int* __restrict__ ja) {
+  constexpr int SORT_N = 32 * KPL;
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int M[3] = {M0, M1, M2};
+  for (i64 r = (i64)blockIdx.x * warps + w; r < n; r += (i64)gridDim.x * warps) {
+    int lo[3], hi[3];
+    const i64 lat = dof_node[r] % lat_size;
+    row_box(p, M, lat, lo, hi);
+    const int b0 = hi[0] - lo[0] + 1, b1 = hi[1] - lo[1] + 1, b2 = hi[2] - lo[2] + 1;
+    const int nb = b0 * b1 * b2, ncand = nb * ncomp;
+    int v[KPL];
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) {
+      const int e = lane * KPL + i;
+      int g = 0x7fffffff;
+      if (e < ncand) {
+        const int comp = e / nb, q = e - comp * nb;
+        const int a0 = lo[0] + q % b0, a1 = lo[1] + (q / b0) % b1, a2 = lo[2] + q / (b0 * b1);
+        const int c = node_dof[comp * lat_size + a0 + (i64)M0 * (a1 + (i64)M1 * a2)];
+        if (c > 0 && c <= n && (!sym || c >= r + 1)) g = c;
+      }
+      v[i] = g;
+    }
+#pragma unroll
+    for (int k = 2; k <= SORT_N; k <<= 1) {
+#pragma unroll
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        if (j >= KPL) {
+          const int lj = j / KPL;
+#pragma unroll
+          for (int i = 0; i < KPL; ++i) {
+            const int idx = lane * KPL + i;
+            const int other = __shfl_xor_sync(0xffffffffu, v[i], lj);
+            const bool up = (idx & k) == 0, lower = (idx & j) == 0;
+            v[i] = (lower == up) ? min(v[i], other) : max(v[i], other);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < KPL; ++i) {
+            if ((i & j) == 0) {
+              const int i2 = i | j;
+              const bool up = ((lane * KPL + i) & k) == 0;
+              const int a = v[i], b = v[i2];
+              if ((a > b) == up) { v[i] = b; v[i2] = a; }
+            }
+          }
+        }
+      }
+    }
+    const i64 start = irp[r];
+    const int cnt = (int)(irp[r + 1] - start);
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) {
+      const int e = lane * KPL + i;
+      if (e < cnt) ja[start + e] = v[i];
+    }
+  }
+}
+
 extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_storage) {
   FB2_CHECK(s != nullptr, "null space");
   fb2_matrix_s* A = new fb2_matrix_s();
@@ -672,12 +736,20 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
   k_row_fill<SN><<<blocks, threads, (threads / 32) * SN * sizeof(int), st>>>(p, ncomp, s->Mlat[0], s->Mlat[1], s->Mlat[2], \
                                                                              s->lat_size, n, A->sym, s->d_dof_node,      \
                                                                              s->d_node_dof, A->d_irp, A->d_ja)
-    if (maxrow <= 32) LAUNCH_FILL(32);
+    static const int fill_variant = getenv("FB2_ROW_FILL") ? atoi(getenv("FB2_ROW_FILL")) : 1;   // 0: shared-memory sort
+#define LAUNCH_FILL_REG(K)                                                                                               \
+  k_row_fill_reg<K><<<fb2_num_sms() * 16, 128, 0, st>>>(p, ncomp, s->Mlat[0], s->Mlat[1], s->Mlat[2], s->lat_size, n, A->sym, \
+                                                        s->d_dof_node, s->d_node_dof, A->d_irp, A->d_ja)
+    if (fill_variant && maxrow <= 32) LAUNCH_FILL_REG(1);
+    else if (fill_variant && maxrow <= 128) LAUNCH_FILL_REG(4);
+    else if (fill_variant && maxrow <= 512) LAUNCH_FILL_REG(16);
+    else if (maxrow <= 32) LAUNCH_FILL(32);
     else if (maxrow <= 128) LAUNCH_FILL(128);
     else if (maxrow <= 512) LAUNCH_FILL(512);
     else if (maxrow <= 1024) LAUNCH_FILL(1024);
     else { FB2_CHECK(maxrow <= 2048, "row too long"); LAUNCH_FILL(2048); }
 #undef LAUNCH_FILL
+#undef LAUNCH_FILL_REG
   }
   FB2_CUDA(cudaGetLastError());
   cudaEventRecord(e1, st);
