@@ -39,6 +39,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 #define SPMV_CONSUMERS 256
 #define SPMV_THREADS (SPMV_CONSUMERS + 32)
 #define SPMV_MAX_STAGES 8
+#define SPMV_DS 512   // compressed variant: distinct columns of a tile staged in shared memory (larger dictionaries stay global)
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -54,7 +55,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // element range of a tile is aligned to 8 entries (16-byte bulk copies), and the products are formed in the same order, so y
 // is bit-identical to the uncompressed kernel.
 template <bool FUSE_DOT, bool COMP>
-__global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* __restrict__ irp, const void* __restrict__ ja_any,
+__global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i64* __restrict__ irp, const void* __restrict__ ja_any,
                                                              const double* __restrict__ val, const double* __restrict__ x,
                                                              double* __restrict__ y, double* partials, const int* done_flag,
                                                              int R, int cap, i64 ntiles, int STAGES,
@@ -69,13 +70,17 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
   __shared__ uint64_t full_bar[SPMV_MAX_STAGES], empty_bar[SPMV_MAX_STAGES];
   __shared__ i64 s_e0a[SPMV_MAX_STAGES], s_r0[SPMV_MAX_STAGES];
   __shared__ int s_nr[SPMV_MAX_STAGES], s_nd[SPMV_MAX_STAGES];
+  __shared__ i64 s_d0[SPMV_MAX_STAGES];
   __shared__ double s_red[32];
   if (done_flag && *done_flag) return;
   const int tid = threadIdx.x;
   const size_t irp_bytes = (size_t)(R + 2) * 8;
-  const size_t dict_off = (size_t)cap * (8 + IB);
-  const size_t xs_off = dict_off + (COMP ? (size_t)dcap * 4 : 0);      // COMP: x gathered once per dictionary entry
-  const size_t irp_off = xs_off + (COMP ? (size_t)dcap * 8 : 0);
+  // COMP: one region of SPMV_DS doubles per stage: the dictionary lands in its upper half (TMA), is read into registers, and
+  // the x values gathered through it then overwrite the region in place (x gathered once per distinct column of the tile)
+  const size_t xs_off = (size_t)cap * (8 + IB);
+  const size_t dict_off = xs_off + (size_t)SPMV_DS * 4;
+  const size_t irp_off = xs_off + (COMP ? (size_t)SPMV_DS * 8 : 0);
+  (void)dcap;
   const size_t stage_bytes = irp_off + irp_bytes;
   // tiles of this CTA: persistent (chunk == 0): blockIdx.x, blockIdx.x + gridDim.x, ... ; chunked: `chunk` consecutive tiles
   const i64 t_first = chunk ? (i64)blockIdx.x * chunk : (i64)blockIdx.x;
@@ -110,8 +115,9 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
         unsigned char* base = smem_raw + s * stage_bytes;
         const i64 e0a = e0 & ~AL;
         const uint32_t cnt4 = (uint32_t)((e1 - e0a + AL) & ~AL);
-        const uint32_t dbytes = COMP ? (uint32_t)(d1 - d0) * 4u : 0u;
-        s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0);
+        // a dictionary that does not fit the region is not staged: the consumers then go through it in global memory
+        const uint32_t dbytes = (COMP && d1 - d0 <= SPMV_DS) ? (uint32_t)(d1 - d0) * 4u : 0u;
+        s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0); s_d0[s] = d0;
         mbar_expect_tx(&full_bar[s], cnt4 * (uint32_t)(8 + IB) + dbytes + (uint32_t)irp_bytes);
         bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
         if (cnt4) {
@@ -145,13 +151,26 @@ __global__ void __launch_bounds__(SPMV_THREADS) k_spmv_stream(i64 n, const i64* 
     // entries); the inner loop then reads shared memory only.  One named barrier per tile; the per-stage buffer is safe to
     // rewrite STAGES tiles later because every warp has passed the barriers of the tiles in between.
     double* xs = (double*)(base + xs_off);
+    bool big = false;
+    const int* dict_g = nullptr;
     if (COMP) {
       const int nd = s_nd[s];
-      for (int d = tid; d < nd; d += SPMV_CONSUMERS) xs[d] = x[sd[d]];
-      asm volatile("bar.sync 2, %0;" ::"r"(SPMV_CONSUMERS) : "memory");
+      big = nd > SPMV_DS;
+      dict_g = dict + s_d0[s];
+      if (!big) {
+        static_assert(SPMV_DS <= 2 * SPMV_CONSUMERS, "two dictionary entries per consumer thread");
+        const int c0 = tid < nd ? sd[tid] : -1, c1 = tid + SPMV_CONSUMERS < nd ? sd[tid + SPMV_CONSUMERS] : -1;
+        asm volatile("bar.sync 2, %0;" ::"r"(SPMV_CONSUMERS) : "memory");   // every entry is in a register before the overwrite
+        if (c0 >= 0) xs[tid] = x[c0];
+        if (c1 >= 0) xs[tid + SPMV_CONSUMERS] = x[c1];
+        asm volatile("bar.sync 2, %0;" ::"r"(SPMV_CONSUMERS) : "memory");
+      }
     }
     // x value of the k-th staged entry
-    auto xat = [&](int k) -> double { if (COMP) return xs[sj16[k]]; else return x[sj[k] - 1]; };
+    auto xat = [&](int k) -> double {
+      if (COMP) return big ? x[dict_g[sj16[k]]] : xs[sj16[k]];
+      else return x[sj[k] - 1];
+    };
     const i64 e0a = s_e0a[s];
     double acc = 0.0;
     const bool live = row < s_nr[s];
@@ -288,10 +307,10 @@ __global__ void __launch_bounds__(256) k_tile_dict(const i64* __restrict__ irp, 
   }
 }
 
-// Off by default: measured SLOWER than the plain int32 stream on B200 (Q2 256^3: 21.9 vs 19.3 ms per SpMV although 12 % fewer
-// bytes move, profiles/r1_spmv_compress_probe.txt) -- the gather phase and its barrier put a global-latency bubble at the
-// head of every tile that 4 CTAs per SM do not hide.  Kept behind fb2_set_spmv_variant(2) / FB2_SPMV_COMPRESS=1 as the
-// starting point for a pipelined gather.
+// Off by default: at parity with the plain int32 stream on B200, not faster (Q2 256^3: 19.46 vs 19.04 ms per SpMV although
+// 11 % fewer bytes move, profiles/r1_spmv_compress_probe.txt) -- the gather phase and its two barriers per tile cost what the
+// bytes save while only two stages are in flight.  Kept behind fb2_set_spmv_variant(2) / FB2_SPMV_COMPRESS=1 as the starting
+// point for a deeper ring of the small streams.
 static int g_compress = getenv("FB2_SPMV_COMPRESS") ? atoi(getenv("FB2_SPMV_COMPRESS")) : 0;
 void fb2_spmv_set_compress(bool on) { g_compress = on ? 1 : 0; }
 static int spmv_compress(fb2_matrix_s* A, int capbuf, int R, int STAGES) {
@@ -323,9 +342,9 @@ static int spmv_compress(fb2_matrix_s* A, int capbuf, int R, int STAGES) {
   FB2_CUDA(fb2_memcpy(&total, A->d_dict_ptr + nt, sizeof(i64), cudaMemcpyDeviceToHost));
   FB2_CUDA(fb2_memcpy(&dcap, d_max, sizeof(int), cudaMemcpyDeviceToHost));
   cudaFree(cnt); cudaFree(d_max);
-  const size_t smem = ((size_t)capbuf * 10 + (size_t)dcap * 12 + (size_t)(R + 2) * 8) * STAGES;
+  const size_t smem = ((size_t)capbuf * 10 + (size_t)SPMV_DS * 8 + (size_t)(R + 2) * 8) * STAGES;
   // worth it only when the dictionaries are small next to the 2 B per entry they save, and the stage still fits
-  bool ok = dcap > 0 && dcap <= 2048 && smem <= 200 * 1024 && (double)total * 4.0 < 0.5 * 2.0 * (double)A->nnz;
+  bool ok = dcap > 0 && smem <= 200 * 1024 && (double)total * 4.0 < 0.5 * 2.0 * (double)A->nnz;
   if (ok) {
     // the extra streams are optional: when HBM is short the uncompressed kernel stays in use
     if (cudaMalloc((void**)&A->d_idx16, sizeof(unsigned short) * ((size_t)A->nnz + 16)) != cudaSuccess) { cudaGetLastError(); A->d_idx16 = nullptr; ok = false; }
