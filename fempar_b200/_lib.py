@@ -47,6 +47,8 @@ _SIGS = {
     "fb2_dof_import_get": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP],
     "fb2_csr_create": [C.POINTER(_VP), _VP, C.c_int],
     "fb2_csr_destroy": [_VP],
+    "fb2_fe_space_get_quadrature_points": [_VP, _VP],
+    "fb2_fe_space_set_source_values": [_VP, _VP],
     "fb2_fe_space_create_bare": [C.POINTER(_VP), C.c_int64],
     "fb2_fe_space_create_from_host": [C.POINTER(_VP), C.c_int32, C.c_int32, C.c_int, C.c_int, _VP, _VP, C.c_int64, C.c_int64],
     "fb2_dof_import_set": [_VP, C.c_int32, _VP, _VP, _VP, C.c_int32, _VP, _VP, _VP, _VP],

@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(128) k_assemble_generic(AsmArgs A, int cells_i
       double xq[3] = {0, 0, 0};
       for (int a = 0; a < 8; ++a)
         for (int k = 0; k < 3; ++k) xq[k] += s_gphi[q * 8 + a] * X[a][k];
-      w_fw[q] = (A.kind == FB2_KIND_POISSON) ? wd * func_f(A.fn, xq) : 0.0;
+      w_fw[q] = (A.kind == FB2_KIND_POISSON) ? wd * (A.src_qp ? A.src_qp[(i64)c * nq + q] : func_f(A.fn, xq)) : 0.0;
     }
     for (int l = lane; l < nd; l += 32) {
       int g = A.gids[(i64)c * nd + l];
@@ -178,6 +178,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   a.g = make_geom(s);
   a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = s->rt.ncomp; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
   a.perm = s->d_perm; a.gids = s->d_gids; a.coords = s->d_coords; a.fixed = s->d_fixed;
+  a.src_qp = kind == FB2_KIND_POISSON ? s->d_src_qp : nullptr;
   a.qw = s->d_qw; a.phi = s->d_phi; a.dphi = s->d_dphi; a.gphi = s->d_gphi; a.gdphi = s->d_gdphi;
   a.irp = A->d_irp; a.ja = A->d_ja; a.val = A->d_val; a.rhs = rhs->d; a.n_free = A->n;
   a.kind = kind; a.sym = A->sym; a.fn = make_func(func, func_params);
@@ -301,6 +302,50 @@ extern "C" int fb2_fe_space_interpolate(fb2_space_t s, int func, const double* f
 }
 
 // ------------------------------------------------------------------------------------------
+// user source term: the integrand seam for an arbitrary f (discrete_integration_t%integrate_galerkin evaluates
+// source_term%get_value_space at quadrature_points_coordinates, tutorial_01_..._modules.f90:100-118): the host asks for the
+// physical quadrature points of the local cells, evaluates its own function there and hands the samples back
+// ------------------------------------------------------------------------------------------
+__global__ void k_quad_points(CellGeom g, const double* __restrict__ coords, const int* __restrict__ lex_of, int n_local, int nq,
+                              const double* __restrict__ gphi, double* __restrict__ out) {
+  i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (i64)n_local * nq) return;
+  const int c = (int)(tid / nq), q = (int)(tid % nq);
+  double X[8][3];
+  if (coords) cell_vertices_from(coords, c, X);
+  else {
+    const int lex = lex_of ? lex_of[c] : c;
+    int ijk[3] = {lex % g.ntot[0], (lex / g.ntot[0]) % g.ntot[1], lex / (g.ntot[0] * g.ntot[1])};
+    cell_vertices(g, ijk, X);
+  }
+  double xq[3] = {0, 0, 0};
+  for (int a = 0; a < 8; ++a)
+    for (int k = 0; k < 3; ++k) xq[k] += gphi[q * 8 + a] * X[a][k];
+  for (int k = 0; k < 3; ++k) out[tid * 3 + k] = xq[k];
+}
+extern "C" int fb2_fe_space_get_quadrature_points(fb2_space_t s, double* host_out) {
+  FB2_CHECK(s && host_out && s->d_gphi, "fb2_fe_space_get_quadrature_points: bad argument (bare space?)");
+  const i64 total = (i64)s->m.n_local * s->rt.nq;
+  if (total == 0) return 0;
+  double* d;
+  FB2_TRY(fb2_dalloc(&d, (size_t)total * 3));
+  k_quad_points<<<(unsigned)((total + 255) / 256), 256, 0, fb2_stream()>>>(make_geom(s), s->d_coords, s->d_lex_of, s->m.n_local,
+                                                                          s->rt.nq, s->d_gphi, d);
+  FB2_CUDA(cudaGetLastError());
+  FB2_CUDA(fb2_memcpy(host_out, d, sizeof(double) * (size_t)total * 3, cudaMemcpyDeviceToHost));
+  cudaFree(d);
+  return 0;
+}
+extern "C" int fb2_fe_space_set_source_values(fb2_space_t s, const double* host_in) {
+  FB2_CHECK(s && s->d_gphi, "fb2_fe_space_set_source_values: bad argument (bare space?)");
+  const size_t total = (size_t)s->m.n_local * s->rt.nq;
+  if (!host_in) { cudaFree(s->d_src_qp); s->d_src_qp = nullptr; return 0; }   // back to the analytic selector
+  if (!s->d_src_qp) FB2_TRY(fb2_dalloc(&s->d_src_qp, total));
+  if (total) FB2_CUDA(fb2_memcpy(s->d_src_qp, host_in, sizeof(double) * total, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // error norms (tutorial_01_..._modules.f90:611-661; ErrorNorms/): warp per cell, lanes over q
 // ------------------------------------------------------------------------------------------
 __global__ void k_error_norms(AsmArgs A, const double* __restrict__ x, int ncells, double* out /*[2]*/) {
@@ -362,7 +407,7 @@ extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const do
   AsmArgs a;
   a.g = make_geom(s);
   a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = 1; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
-  a.perm = s->d_perm; a.gids = s->d_gids; a.coords = s->d_coords; a.fixed = s->d_fixed;
+  a.perm = s->d_perm; a.gids = s->d_gids; a.coords = s->d_coords; a.fixed = s->d_fixed; a.src_qp = nullptr;
   a.qw = s->d_qw; a.phi = s->d_phi; a.dphi = s->d_dphi; a.gphi = s->d_gphi; a.gdphi = s->d_gdphi;
   a.fn = make_func(func, func_params);
   double* d_out = fb2_scratch_partials();

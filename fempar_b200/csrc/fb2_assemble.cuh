@@ -109,6 +109,7 @@ struct AsmArgs {
   const int* gids;
   const double* coords;  // host-built spaces: vertex coordinates [cell][8][3]; nullptr = structured closed form
   const double* fixed;
+  const double* src_qp;  // user source term at the quadrature points [local cell][q] (nullptr: the analytic selector `fn`)
   const double *qw, *phi, *dphi, *gphi, *gdphi;
   const i64* irp;
   const int* ja;

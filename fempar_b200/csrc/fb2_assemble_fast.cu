@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
     coff[k] = A.color < 0 ? 0 : (A.color >> k) & 1;
     cdim[k] = A.color < 0 ? A.g.nloc[k] : (A.g.nloc[k] - coff[k] + 1) / 2;
   }
-  const bool has_source = A.kind == FB2_KIND_POISSON && A.fn.kind == FB2_FUNC_SHARP_WAVE;
+  const bool has_source = A.kind == FB2_KIND_POISSON && (A.fn.kind == FB2_FUNC_SHARP_WAVE || A.src_qp != nullptr);
   const int stride = gridDim.x * WARPS * CPW;
   double dN[3], rN[3];
 #pragma unroll
@@ -414,7 +414,8 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
     cNN = cell_id(ci + 3 * stride);                     // cell id of cell k+3
     if (on) {
       int ijk[3];
-      if constexpr (!HOSTGEO) cell_pos(ci, ijk);
+      int lex_cur = ci;
+      if constexpr (!HOSTGEO) lex_cur = cell_pos(ci, ijk);
       // vertex coordinates (first + ijk + {0,1}) / N (uniform_hex_mesh_generator.f90:608-635): the quotient is formed with the
       // precomputed reciprocal and one residual correction (q0 = a*y; r = fma(-q0, N, a); q = fma(r, y, q0)), which gives the
       // correctly rounded a/N in 3 DFMA-class operations instead of the ~25-instruction IEEE division sequence per coordinate
@@ -460,12 +461,17 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
             D[5] = wd * (inv[0][2] * inv[0][2] + inv[1][2] * inv[1][2] + inv[2][2] * inv[2][2]);
           }
           if (has_source) {
-            double xq[3] = {0, 0, 0};
+            if (A.src_qp) {   // user samples, indexed by the local cell id
+              const int c_cur = HOSTGEO ? ci : (A.perm ? A.perm[lex_cur] : lex_cur);
+              s_fw[slot][q] = wd * A.src_qp[(i64)c_cur * NQ + q];
+            } else {
+              double xq[3] = {0, 0, 0};
 #pragma unroll
-            for (int a = 0; a < 8; ++a)
+              for (int a = 0; a < 8; ++a)
 #pragma unroll
-              for (int k = 0; k < 3; ++k) xq[k] += A.gphi[q * 8 + a] * X[a][k];
-            s_fw[slot][q] = wd * func_f(A.fn, xq);
+                for (int k = 0; k < 3; ++k) xq[k] += A.gphi[q * 8 + a] * X[a][k];
+              s_fw[slot][q] = wd * func_f(A.fn, xq);
+            }
           }
         }
       }

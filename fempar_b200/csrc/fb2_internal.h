@@ -85,6 +85,7 @@ struct fb2_space_s {
   int* d_node_dof = nullptr; // [ncomp][lattice of the LOCAL cell box] -> gid
   int* d_dof_node = nullptr; // [n_free] -> comp * lattice_size + lattice node
   double* d_fixed = nullptr; // fixed_dof_values [n_dirichlet]
+  double* d_src_qp = nullptr;// optional user source term sampled at the quadrature points [n_local][nq] (scalar Poisson)
   double* d_coords = nullptr;// host-built (unstructured) spaces only: vertex coordinates [n_cells][8][3], hex vertex order
   // reference tables on device
   double* d_qw = nullptr;    // [nq]

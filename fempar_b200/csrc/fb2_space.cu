@@ -504,7 +504,7 @@ extern "C" int fb2_fe_space_create(fb2_space_t* out, const int num_cells[3], con
 extern "C" int fb2_fe_space_destroy(fb2_space_t s) {
   if (!s) return 0;
   cudaFree(s->d_perm); cudaFree(s->d_lex_of); cudaFree(s->d_gids); cudaFree(s->d_node_dof); cudaFree(s->d_dof_node);
-  cudaFree(s->d_coords);
+  cudaFree(s->d_coords); cudaFree(s->d_src_qp);
   cudaFree(s->d_fixed); cudaFree(s->d_qw); cudaFree(s->d_phi); cudaFree(s->d_dphi); cudaFree(s->d_gphi); cudaFree(s->d_gdphi);
   if (s->imp) fb2_import_destroy(s->imp);
   delete s;

@@ -99,6 +99,13 @@ int fb2_fe_space_interpolate_dirichlet(fb2_space_t s, int func, const double* fu
 /* free DOF values of an fe_function by nodal interpolation of the analytic function:
  * serial_fe_space_interpolate_scalar_function, sbm_serial_fe_space.i90:734-819 (x has num_free_dofs entries) */
 int fb2_fe_space_interpolate(fb2_space_t s, int func, const double* func_params, fb2_vector_t x);
+/* user source term of the scalar Poisson integrand (the `source_term%get_value_space(quad_coords(qpoint), ...)` calls of
+ * integrate_galerkin, tutorial_01_..._modules.f90:100-118): get the physical quadrature points of the local cells
+ * (host_out[num_local_cells][nq][3], cells in lst_dofs_gids order, q index x fastest), evaluate any f there on the host and
+ * set the samples (host_in[num_local_cells][nq]); fb2_integrate_assemble then uses them instead of the analytic selector.
+ * host_in = NULL switches back. */
+int fb2_fe_space_get_quadrature_points(fb2_space_t s, double* host_out);
+int fb2_fe_space_set_source_values(fb2_space_t s, const double* host_in);
 int fb2_fe_space_get_fixed_values(fb2_space_t s, double* host_out);
 int fb2_fe_space_set_fixed_values(fb2_space_t s, const double* host_in);
 

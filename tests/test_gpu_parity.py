@@ -348,3 +348,44 @@ def test_spmv_kernel_variants_agree(fb2, N, p):
     assert np.array_equal(ys[0], ys[2])
     assert hist[0][0] == hist[2][0] and np.array_equal(hist[0][1], hist[2][1])
     assert _close(ys[1], ys[0]) and abs(hist[1][0] - hist[0][0]) <= 1
+
+
+def _wave_source(x, alpha=200.0, r=0.7, c=-0.05):
+    """f = -lap(u) of the tutorial_01 sharp circular wave, evaluated on the host (what a user integrand would do)."""
+    d2 = (x - c) ** 2
+    t1 = d2.sum(-1); s = np.sqrt(t1); t2 = s - r; w = alpha ** 2 * t2 ** 2 + 1.0
+    res = 0.0
+    for k in range(3):
+        res = res - (alpha / (s * w) - alpha * d2[..., k] / (t1 * s * w) - 2 * alpha ** 3 * d2[..., k] * t2 / (t1 * w * w))
+    return res
+
+
+@pytest.mark.parametrize("N,p", [((6, 5, 4), 1), ((5, 4, 3), 2), ((3, 3, 2), 3)])
+def test_user_source_term_sampled_at_quadrature_points(fb2, asm_variant, N, p):
+    """integrand seam for an arbitrary f: quadrature points from the device, f evaluated on the host, samples handed back;
+    with the tutorial's f this must reproduce the built-in analytic source, and the RHS is linear in the samples."""
+    s, op = _assemble(fb2, N, p, 1, KIND_POISSON, FUNC_SHARP_WAVE, WAVE, None, 0)
+    b_ref = op.get_translation().get_entries()
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=0)
+    assert _close(b_ref, o.rhs())
+    xq = s.get_quadrature_points()
+    assert xq.shape == (s.num_local_cells, (p + 1) ** 3, 3) and xq.min() > 0.0 and xq.max() < 1.0
+    f = _wave_source(xq)
+    s.set_source_values(f)
+    op.force_compute()
+    b1 = op.get_translation().get_entries()
+    assert np.max(np.abs(b1 - b_ref)) <= 1e-11 * np.max(np.abs(b_ref))
+    s.set_source_values(np.zeros_like(f))
+    op.force_compute()
+    b0 = op.get_translation().get_entries()                      # Dirichlet lifting only
+    s.set_source_values(-2.5 * f)
+    op.force_compute()
+    b2 = op.get_translation().get_entries()
+    assert np.max(np.abs((b2 - b0) + 2.5 * (b1 - b0))) <= 1e-11 * np.max(np.abs(b_ref))
+    s.set_source_values(None)                                    # back to the analytic selector
+    op.force_compute()
+    assert _close(op.get_translation().get_entries(), b_ref, 1e-13)
+    with pytest.raises(fb2.Fb2Error):
+        s.set_source_values(np.zeros(3))
+    op.free()

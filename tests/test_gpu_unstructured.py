@@ -205,3 +205,20 @@ def test_y_junction_elasticity(fb2):
     assert _close(op.get_matrix().get_values(), A.data)
     assert np.max(np.abs(op.get_translation().get_entries() - rhs)) <= 1e-12 * np.abs(rhs).max()
     op.free()
+
+
+@pytest.mark.parametrize("p", [1, 2])
+def test_user_source_term_on_distorted_mesh(fb2, p):
+    """quadrature points of a host-numbered space follow the trilinear map; a host-evaluated source gives the hex oracle's RHS."""
+    X = ho.y_junction_mesh(3, 2)
+    gids, nf, ndir = ho.number_by_coordinates(p, X)
+    s = fb2.HostNumberedFeSpace(p, 1, gids, X, nf, ndir)
+    xq = s.get_quadrature_points()
+    assert np.max(np.abs(xq - ho.cell_geometry(p, X)[0])) < 1e-14
+    src = lambda x: np.sin(3.0 * x[..., 0]) * np.cos(2.0 * x[..., 1]) + x[..., 2] ** 2
+    s.set_source_values(src(xq))
+    op = _operator(fb2, s, False)
+    A, rhs = ho.assemble(p, 1, gids, X, nf, s.get_fixed_dof_values(), source=src)
+    assert _close(op.get_matrix().get_values(), A.data)
+    assert np.max(np.abs(op.get_translation().get_entries() - rhs)) <= 1e-12 * np.abs(rhs).max()
+    op.free()
