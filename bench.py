@@ -323,12 +323,17 @@ def main():
             "assembly_mdof_per_s": asm_mdofs, "assembly_ms": asm_t, "pcg_ms_per_iteration": cg_t / a.cg_iters,
             "spmv_ms": spmv_t, "setup_ms": {"fe_space": t_space * 1e3, "csr_pattern": t_pattern_ms, "scatter_map": t_map_ms},
             "wall_ms_per_step": wall_t,
-            "roofline": {"bound": "hbm", "kernel": "k_spmv_stream<true> (TMA-streamed CSR row tiles, short-lived CTAs over 32 tiles, fused <Ap,p>)" if a.spmv_variant == 0 else "k_spmv<true> (warp-per-row)", "achieved": achieved,
+            "roofline": {"bound": "hbm", "kernel": "k_spmv_stream<true,false> (TMA-streamed CSR row tiles, short-lived CTAs over 32 tiles, fused <Ap,p>)" if a.spmv_variant == 0 else "k_spmv<true> (warp-per-row)", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": per_gpu_bytes,
+                         "frac_of_nominal_8000_GBps": achieved / 8000.0,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650"},
             "roofline_assembly": {"bound": "hbm", "kernel": "k_assemble_fast<2,1,atomic>" if (a.asm_variant == 0 and a.order <= 2) else "k_assemble_generic", "achieved": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9,
                                   "peak": peak, "unit": "GB/s", "frac": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9 / peak},
+            # BLAS-1 traffic of one PCG iteration: the reference's unfused vector TBPs move 18 n doubles, the fused
+            # kernels here 11 n (x/r update with four partial dots: 4 reads + 2 writes + dinv; p update: 3 reads + 1 write)
+            "pcg_vector_bytes_per_iteration": {"reference_unfused": int(18 * 8 * n_glob_rows), "fused": int(11 * 8 * n_glob_rows),
+                                               "measured_ms": (cg_t / a.cg_iters) - spmv_t},
             "clocks": clk.summary(), "e2e": e2e,
             # kernels of libfempar_b200.so per step: Dirichlet interpolation + memsets/assembly (3), Jacobi set-up (2), PCG set-up
             # (9), then per PCG iteration: serial 6 (SpMV, 2 partial reductions, x/r update, scalars, p update); par 14 (two
