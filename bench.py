@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--subdomains", type=int, default=0,
                     help="number of FEMPAR sub-domains (parts); 0 = 8 (2x2x2, BASELINE config 3) when --gpus is 2, 4 or 8, else 1")
-    ap.add_argument("--spmv-variant", type=int, default=0, help="0 TMA-streamed tiles, 1 warp-per-row")
+    ap.add_argument("--spmv-variant", type=int, default=0, help="0 TMA-streamed tiles, 1 warp-per-row, 2 streamed tiles with dictionary-compressed column indices")
     ap.add_argument("--asm-variant", type=int, default=0, help="0 register-blocked contraction + scatter map, 1 generic kernel")
     return ap.parse_args()
 

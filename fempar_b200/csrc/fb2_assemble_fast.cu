@@ -663,7 +663,8 @@ int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant)
   F.tile = getenv("FB2_ASM_TILE") ? atoi(getenv("FB2_ASM_TILE")) : 32;
   if (s->d_coords) {   // host-numbered space
     if (args.kind == FB2_KIND_ELASTICITY) return s->rt.p == 1 ? launch_fast_host<1, 3, true>(F, s) : launch_fast_host<2, 3, true>(F, s);
-    if (s->rt.ncomp != 1) return -1;
+    if (s->rt.ncomp != 1)   // vector Laplacian
+      return s->rt.p == 1 ? launch_fast_host<1, 3, false>(F, s) : s->rt.p == 2 ? launch_fast_host<2, 3, false>(F, s) : -1;
     return s->rt.p == 1 ? launch_fast_host<1, 1, false>(F, s) : s->rt.p == 2 ? launch_fast_host<2, 1, false>(F, s)
                                                                               : launch_fast_host<3, 1, false>(F, s);
   }

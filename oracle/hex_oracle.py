@@ -72,14 +72,20 @@ def cell_geometry(p, X):
     return xq, det * qw[None, :], g, phi
 
 
-def element_matrices(p, X, ncomp=1, lam=0.0, mu=1.0):
-    """element matrices [c, nd, nd]; ncomp = 1: Poisson; ncomp = 3: linear elasticity, component-major DOF blocks."""
+def element_matrices(p, X, ncomp=1, lam=0.0, mu=1.0, vector_laplacian=False):
+    """element matrices [c, nd, nd]; ncomp = 1: Poisson; ncomp = 3: linear elasticity, or the vector Laplacian (the scalar
+    matrix on the three diagonal blocks, explicit zeros elsewhere: vector_poisson_discrete_integration.f90:62-140);
+    component-major DOF blocks."""
     xq, wd, g, phi = cell_geometry(p, X)
     if ncomp == 1:
         return np.einsum("cq,cqak,cqbk->cab", wd, g, g)
     nn = g.shape[2]
     K = np.zeros((X.shape[0], 3 * nn, 3 * nn))
     dot = np.einsum("cq,cqak,cqbk->cab", wd, g, g)
+    if vector_laplacian:
+        for ci in range(3):
+            K[:, ci * nn:(ci + 1) * nn, ci * nn:(ci + 1) * nn] = dot
+        return K
     for ci in range(3):
         for cj in range(3):
             blk = lam * np.einsum("cq,cqa,cqb->cab", wd, g[..., ci], g[..., cj]) + \
@@ -96,9 +102,9 @@ def node_coordinates(p, X):
     return np.einsum("na,cak->cnk", _tensor(G, G, G), X)
 
 
-def assemble(p, ncomp, gids, X, n_free, fixed=None, source=None, lam=0.0, mu=1.0, sym=False):
-    """CSR matrix (ascending columns, duplicates summed) and RHS of the local cells given as (gids [c, nd], X [c, 8, 3])."""
-    K = element_matrices(p, X, ncomp, lam, mu)
+def assemble(p, ncomp, gids, X, n_free, fixed=None, source=None, lam=0.0, mu=1.0, sym=False, vector_laplacian=False):
+    """CSR matrix (ascending columns, duplicates summed, explicit zeros kept) and RHS of the local cells (gids [c, nd], X [c, 8, 3])."""
+    K = element_matrices(p, X, ncomp, lam, mu, vector_laplacian)
     nc, nd = gids.shape
     rhs = np.zeros(n_free)
     if source is not None:

@@ -222,3 +222,18 @@ def test_user_source_term_on_distorted_mesh(fb2, p):
     assert _close(op.get_matrix().get_values(), A.data)
     assert np.max(np.abs(op.get_translation().get_entries() - rhs)) <= 1e-12 * np.abs(rhs).max()
     op.free()
+
+
+@pytest.mark.parametrize("p", [1, 2])
+def test_y_junction_vector_laplacian(fb2, p):
+    from oracle.oracle import KIND_VECTOR_LAPLACIAN
+    X = ho.y_junction_mesh(2, 2)
+    gids, nf, ndir = ho.number_by_coordinates(p, X, ncomp=3)
+    s = fb2.HostNumberedFeSpace(p, 3, gids, X, nf, ndir)
+    op = _operator(fb2, s, False, kind=KIND_VECTOR_LAPLACIAN)
+    A, rhs = ho.assemble(p, 3, gids, X, nf, s.get_fixed_dof_values(), vector_laplacian=True)
+    irp, ja = op.get_matrix().get_pattern()
+    assert np.array_equal(irp - 1, A.indptr) and np.array_equal(ja - 1, A.indices)
+    assert _close(op.get_matrix().get_values(), A.data)
+    assert np.max(np.abs(op.get_translation().get_entries() - rhs)) <= 1e-12 * np.abs(rhs).max()
+    op.free()

@@ -104,3 +104,15 @@ def test_y_junction_mesh_patch_test(p):
     assert np.abs(x - exact).max() < 1e-11
     valence = np.bincount(gids[:, 0][gids[:, 0] > 0])      # local node 0 of every block cell (i,j)=(0,0) is the junction line
     assert valence.max() == 3
+
+
+def test_affine_vector_laplacian_matches_pinned_oracle():
+    from oracle.oracle import KIND_VECTOR_LAPLACIAN
+    N = 3
+    o = OracleSpace([N] * 3, order=2, ncomp=3)
+    o.assemble(KIND_VECTOR_LAPLACIAN, FUNC_LINEAR, None, None, sym=False, route=1)
+    A, rhs = ho.assemble(2, 3, o.lst_dofs_gids().copy(), ho.structured_cell_coords(N), o.num_free, o.fixed().copy(),
+                         vector_laplacian=True)
+    assert np.array_equal(A.indptr, o.irp()) and np.array_equal(A.indices + 1, o.ja())     # explicit zeros kept on both sides
+    assert np.abs(A.data - o.val()).max() <= 1e-12 * np.abs(o.val()).max()
+    assert np.abs(rhs - o.rhs()).max() <= 1e-12 * max(1.0, np.abs(o.rhs()).max())
