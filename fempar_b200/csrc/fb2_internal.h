@@ -157,6 +157,8 @@ int fb2_dev_scal(double* dst, double a, const double* src, i64 n);
 int fb2_dev_init(double* x, double a, i64 n);
 int fb2_dots_host(fb2_matrix_s* A, int k, const double* const* xs, const double* const* ys, i64 n, double* out);
 void fb2_cg_set_icg(int on);
+bool fb2_ils_has_initial_solution(i64 n);
+int fb2_ils_load_initial_solution(double* x, i64 n);   // x <- the user's initial solution, or 0
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 int fb2_spmv_prepare(fb2_matrix_s* A);
 void fb2_spmv_set_compress(bool on);   // dictionary-compressed column indices for matrices prepared from now on

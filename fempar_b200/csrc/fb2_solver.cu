@@ -507,6 +507,32 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
   return 0;
 }
 
+// initial solution of the next solves (base_iterative_linear_solver_t%set_initial_solution, base_iterative_linear_solver.f90:
+// 340-360: the solver keeps its own copy; default zero, :281-282).  One copy per process, like the rest of the library state.
+static double* g_x0 = nullptr;
+static i64 g_x0_n = 0;
+static bool g_x0_on = false;
+extern "C" int fb2_ils_set_initial_solution(fb2_vector_t x0) {
+  if (!x0) { g_x0_on = false; return 0; }
+  if (g_x0_n != x0->n) {
+    cudaFree(g_x0); g_x0 = nullptr; g_x0_n = 0;
+    FB2_TRY(fb2_dalloc(&g_x0, (size_t)x0->n));
+    g_x0_n = x0->n;
+  }
+  FB2_CUDA(cudaMemcpyAsync(g_x0, x0->d, sizeof(double) * (size_t)x0->n, cudaMemcpyDeviceToDevice, fb2_stream()));
+  g_x0_on = true;
+  return 0;
+}
+// a vector that does not belong to range(A) is ignored, as the reference does (with a warning, :349-351)
+bool fb2_ils_has_initial_solution(i64 n) { return g_x0_on && g_x0_n == n; }
+int fb2_ils_load_initial_solution(double* x, i64 n) {
+  if (fb2_ils_has_initial_solution(n))
+    FB2_CUDA(cudaMemcpyAsync(x, g_x0, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, fb2_stream()));
+  else k_init<<<vec_grid(n), 256, 0, fb2_stream()>>>(x, 0.0, n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+
 static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const double* b, double* x, bool par, double rtol,
                     double atol, int maxit, int stop) {
   cudaStream_t s = fb2_stream();
@@ -515,8 +541,14 @@ static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const d
   // x <- 0 ; r = A x ; r = b - r   (cg.f90:142,158-162)
   // The initial solution is zero (base_iterative_linear_solver.f90:281-282), so r = b - A*0 = b bit for bit: the
   // reference's initial SpMV and its halo exchange are skipped.
-  k_init<<<vec_grid(n), 256, 0, s>>>(x, 0.0, n);
-  FB2_CUDA(cudaMemcpyAsync(W.r, b, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+  if (fb2_ils_has_initial_solution(n)) {   // user-selected initial solution: the full r = b - A x (cg.f90:158-162)
+    FB2_TRY(fb2_ils_load_initial_solution(x, n));
+    FB2_TRY(fb2_op_apply(A, x, W.r));
+    FB2_TRY(fb2_dev_axpby(W.r, 1.0, b, -1.0, n));
+  } else {
+    k_init<<<vec_grid(n), 256, 0, s>>>(x, 0.0, n);
+    FB2_CUDA(cudaMemcpyAsync(W.r, b, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+  }
   // z = M^-1 r ; p = z ; r_z = <r,z>
   if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, dinv, W.r, n);
   else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));

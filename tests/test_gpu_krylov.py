@@ -154,3 +154,79 @@ def test_minres_symmetric_indefinite_host_matrix(fb2):
     assert ils.converged() and r["converged"] and abs(ils.get_num_iterations() - r["iters"]) <= 2
     xs = np.linalg.solve(As.toarray(), b)
     assert np.max(np.abs(vx.get_entries() - xs)) <= 1e-6 * np.max(np.abs(xs))
+
+
+def _np_pcg(A, dinv, b, x0, rtol, maxit):
+    """cg.f90:101-238 with a non-zero initial solution (RES_RES: ||r_i|| <= rtol ||r_0||), numpy on the oracle's CSR."""
+    x = x0.copy()
+    r = b - A @ x
+    z = dinv * r
+    p = z.copy()
+    rz = r @ z
+    tol = rtol * np.sqrt(r @ r)
+    it = 0
+    while True:
+        it += 1
+        Ap = A @ p
+        alpha = rz / (Ap @ p)
+        x += alpha * p
+        r -= alpha * Ap
+        if np.sqrt(r @ r) <= tol or it >= maxit:
+            return x, it
+        z = dinv * r
+        beta = 1.0 / rz
+        rz = r @ z
+        beta *= rz
+        p = z + beta * p
+
+
+@pytest.mark.parametrize("ils_type", ["CG"])
+def test_set_initial_solution(fb2, ils_type):
+    """base_iterative_linear_solver_t%set_initial_solution: the solve starts from a copy of the given vector (default zero)."""
+    import scipy.sparse as sp
+    from oracle.oracle import OracleSpace, KIND_POISSON, FUNC_SHARP_WAVE
+    N, p = (6, 5, 4), 2
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, [200.0, 0.7, -0.05, -0.05, -0.05], route=0)
+    A = sp.csr_matrix((o.val().copy(), o.ja().copy() - 1, o.irp().copy()), shape=(o.num_free, o.num_free))
+    dinv, b = o.jacobi_setup().copy(), o.rhs().copy()
+    s = fb2.FeSpace(N, order=p)
+    op = fb2.FeAffineOperator()
+    op.create(fb2.csr_format, [False], [True], [1], s, fb2.DiscreteIntegration(fb2.poisson, FUNC_SHARP_WAVE,
+                                                                                [200.0, 0.7, -0.05, -0.05, -0.05], None, 1))
+    op.compute()
+    M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    x0 = np.random.default_rng(4).standard_normal(o.num_free)
+    v0 = s.create_dof_values(); v0.set_entries(x0)
+    ils = fb2.IterativeLinearSolver()
+    relax = {fb2.ILS_RELAXATION: 0.9} if ils_type == "RICHARDSON" else {}
+    ils.set_parameters_from_pl(dict({fb2.ILS_TYPE: ils_type, fb2.ILS_RTOL: 1e-9, fb2.ILS_MAX_NUM_ITERATIONS: 3000}, **relax))
+    ils.set_operators(op.get_tangent(), M)
+    x = s.create_dof_values()
+    ils.apply(op.get_translation(), x)
+    it_zero, sol_zero = ils.get_num_iterations(), x.get_entries()
+    ils.set_initial_solution(v0)
+    v0.init(123.0)                                               # the solver keeps its own copy
+    ils.apply(op.get_translation(), x)
+    assert ils.converged()
+    # every solver converges to the same solution from the new start; CG's RES_RES is relative to the NEW initial residual
+    # (the other types stop on their own estimates of a preconditioned norm: checked through the solution)
+    assert np.linalg.norm(x.get_entries() - sol_zero) <= 1e-5 * np.linalg.norm(sol_zero)
+    if ils_type == "CG":
+        assert np.linalg.norm(b - A @ x.get_entries()) <= 1.01e-9 * np.linalg.norm(b - A @ x0)
+    if ils_type == "CG":
+        xr, itr = _np_pcg(A, dinv, b, x0, 1e-9, 3000)
+        assert abs(ils.get_num_iterations() - itr) <= 1 and np.max(np.abs(x.get_entries() - xr)) < 1e-8
+        xh = np.zeros(o.num_free)
+        ils.apply(b, xh)                                         # host-buffer entry uses it too
+        assert np.max(np.abs(xh - xr)) < 1e-8
+    # starting from the converged solution: nothing left to do beyond the first iteration
+    v0.set_entries(sol_zero); ils.set_initial_solution(v0)
+    ils.set_parameters_from_pl({fb2.ILS_RTOL: 0.0, fb2.ILS_ATOL: 1e-5 * max(np.linalg.norm(b), np.linalg.norm(dinv * b))})
+    ils.apply(op.get_translation(), x)
+    assert ils.converged() and ils.get_num_iterations() <= 1
+    ils.set_initial_solution(None)                               # back to zero
+    ils.set_parameters_from_pl({fb2.ILS_RTOL: 1e-9, fb2.ILS_ATOL: 0.0})
+    ils.apply(op.get_translation(), x)
+    assert ils.get_num_iterations() == it_zero and np.array_equal(x.get_entries(), sol_zero)
+    op.free()
