@@ -180,7 +180,7 @@ def _np_pcg(A, dinv, b, x0, rtol, maxit):
         p = z + beta * p
 
 
-@pytest.mark.parametrize("ils_type", ["CG"])
+@pytest.mark.parametrize("ils_type", ["CG", "RGMRES", "MINRES", "RICHARDSON"])
 def test_set_initial_solution(fb2, ils_type):
     """base_iterative_linear_solver_t%set_initial_solution: the solve starts from a copy of the given vector (default zero)."""
     import scipy.sparse as sp
