@@ -163,7 +163,9 @@ static size_t generic_smem_bytes(const fb2_space_s* s, int warps) {
 }
 
 int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant);  // fb2_assemble_fast.cu
-static int g_asm_variant = 0;   // 0: fast path where it applies, 1: always the generic kernel (kept for ncu comparison)
+static int g_asm_variant = 0;   // 0: fast paths where they apply, 1: always the generic kernel (kept for ncu comparison),
+                                // 2: sum-factorised scatter kernel only (no row-owner gather)
+int fb2_assembly_variant() { return g_asm_variant; }
 extern "C" int fb2_set_assembly_variant(int v) { g_asm_variant = v; return 0; }
 
 extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind, int func, const double* func_params,
@@ -187,7 +189,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   const bool host_built = s->d_coords != nullptr;   // no lattice: generic kernel, slots by binary search, atomic scatter
   FB2_CHECK(s->d_gids != nullptr, "this space has no cell DOF lists (bare space): use fb2_assemble_batch");
   if (host_built) scatter_variant = FB2_SCATTER_ATOMIC;
-  if (g_asm_variant == 0 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
+  if (g_asm_variant != 1 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
@@ -199,7 +201,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int bps = (int)(227 * 1024 / smem); if (bps < 1) bps = 1; if (bps > 8) bps = 8;
-  int fast_rc = g_asm_variant == 0 ? fb2_assemble_fast(A, a, scatter_variant) : -1;
+  int fast_rc = g_asm_variant != 1 ? fb2_assemble_fast(A, a, scatter_variant) : -1;
   if (fast_rc > 0) return fast_rc;
   if (fast_rc == 0) {
   } else if (scatter_variant == FB2_SCATTER_ATOMIC) {

@@ -14,7 +14,7 @@
 // (3) Scatter: RED.ADD.F64 (atomic variant) or plain read-modify-write on one colour class (colored variant)
 //     into val[slot]; strong Dirichlet columns go to the RHS (sbm_fe_cell_iterator.i90:1610-1637).
 #include <stdlib.h>
-#include "fb2_assemble.cuh"
+#include "fb2_sumfact.cuh"
 
 // ------------------------------------------------------------------------------------------
 // scatter map
@@ -195,74 +195,17 @@ int fb2_build_scatter_map(fb2_matrix_s* A) {
 // ------------------------------------------------------------------------------------------
 // integration + scatter
 // ------------------------------------------------------------------------------------------
-// 1-D Lagrange values B[q][i] and derivatives C[q][i] at the 1-D Gauss points, orders 1..3.  Every index below is
-// a compile-time constant after unrolling, so these become constant-bank / uniform-register operands of DFMA.
-__constant__ double c_B1[3][16];
-__constant__ double c_C1[3][16];
-
 struct FastArgs {
   AsmArgs a;
   const int* cell_tab;
   const unsigned short* tabs;
   int common_tab;   // table id of the interior position class (-1: none); cached in shared memory by the kernel
   int tile;         // (x,y) tile edge of the cell traversal of the atomic variant; 0 = lexicographic
+  // row-owner hybrid (fb2_assemble_rows.cu): only the listed cells are visited (total-box lexicographic ids, nullptr = all
+  // local cells) and rows whose bit is set in row_fast are left alone (the gather kernel writes them completely)
+  const int* cell_list;
+  const unsigned* row_fast;
 };
-
-// Column j of the element matrix by sum factorisation.  With q = (q1,q2,q3), i = (i1,i2,i3) and
-// t(q) = w detJ J^-1 J^-T(q) grad_ref phi_j(q):
-//   E[i][j] = sum_q  C[q1][i1] B[q2][i2] B[q3][i3] t0 + B[q1][i1] C[q2][i2] B[q3][i3] t1 + B[q1][i1] B[q2][i2] C[q3][i3] t2
-// contracted direction by direction: 9 (t) + 9 (x) + 9 (y) + 6 (z) FMA per quadrature point for p = 2, i.e. 891 DFMA
-// per column instead of the 2430 of the dense q-loop, and no table traffic in the inner loop.
-// tfun(q, g0, g1, g2, t0, t1, t2) maps the reference gradient of phi_j at quadrature point q to the flux t(q)
-template <int P, class TFun>
-__device__ __forceinline__ void column_sumfact(TFun tfun, const double* __restrict__ sB,
-                                               const double* __restrict__ sC, int j, double* __restrict__ acc) {
-  constexpr int N1 = P + 1, NN = N1 * N1 * N1;
-  const int j1 = j % N1, j2 = (j / N1) % N1, j3 = j / (N1 * N1);
-#pragma unroll
-  for (int i = 0; i < NN; ++i) acc[i] = 0.0;
-#pragma unroll
-  for (int q3 = 0; q3 < N1; ++q3) {
-    const double b3 = sB[q3 * N1 + j3], c3 = sC[q3 * N1 + j3];
-    double w01[N1 * N1], w2[N1 * N1];
-#pragma unroll
-    for (int k = 0; k < N1 * N1; ++k) { w01[k] = 0.0; w2[k] = 0.0; }
-#pragma unroll
-    for (int q2 = 0; q2 < N1; ++q2) {
-      const double b2 = sB[q2 * N1 + j2], c2 = sC[q2 * N1 + j2];
-      const double m0 = b2 * b3, m1 = c2 * b3, m2 = b2 * c3;   // grad_ref phi_j = (c1 m0, b1 m1, b1 m2)
-      double a0[N1], a1[N1], a2[N1];
-#pragma unroll
-      for (int k = 0; k < N1; ++k) { a0[k] = 0.0; a1[k] = 0.0; a2[k] = 0.0; }
-#pragma unroll
-      for (int q1 = 0; q1 < N1; ++q1) {
-        const int q = q1 + N1 * (q2 + N1 * q3);
-        const double b1 = sB[q1 * N1 + j1], c1 = sC[q1 * N1 + j1];
-        const double g0 = c1 * m0, g1 = b1 * m1, g2 = b1 * m2;
-        double t0, t1, t2;
-        tfun(q, g0, g1, g2, t0, t1, t2);
-#pragma unroll
-        for (int i1 = 0; i1 < N1; ++i1) {
-          a0[i1] = fma(c_C1[P - 1][q1 * N1 + i1], t0, a0[i1]);
-          a1[i1] = fma(c_B1[P - 1][q1 * N1 + i1], t1, a1[i1]);
-          a2[i1] = fma(c_B1[P - 1][q1 * N1 + i1], t2, a2[i1]);
-        }
-      }
-#pragma unroll
-      for (int i2 = 0; i2 < N1; ++i2)
-#pragma unroll
-        for (int i1 = 0; i1 < N1; ++i1) {
-          w01[i1 + N1 * i2] = fma(c_B1[P - 1][q2 * N1 + i2], a0[i1], fma(c_C1[P - 1][q2 * N1 + i2], a1[i1], w01[i1 + N1 * i2]));
-          w2[i1 + N1 * i2] = fma(c_B1[P - 1][q2 * N1 + i2], a2[i1], w2[i1 + N1 * i2]);
-        }
-    }
-#pragma unroll
-    for (int i3 = 0; i3 < N1; ++i3)
-#pragma unroll
-      for (int k = 0; k < N1 * N1; ++k)
-        acc[k + N1 * N1 * i3] = fma(c_B1[P - 1][q3 * N1 + i3], w01[k], fma(c_C1[P - 1][q3 * N1 + i3], w2[k], acc[k + N1 * N1 * i3]));
-  }
-}
 
 // Per-cell input data (cell id through perm, DOF ids, row starts, Dirichlet values, table id) is software-pipelined three
 // cells ahead in registers: the ncu source view of the previous version showed 32 % of the stall samples as long-scoreboard
@@ -329,6 +272,13 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
   const int T = F.tile;
   auto cell_pos = [&](int ci, int* ijk) {
     int r = ci;
+    if (F.cell_list) {
+      const int lex = F.cell_list[ci];
+      ijk[0] = lex % A.g.ntot[0];
+      const int rr = lex / A.g.ntot[0];
+      ijk[1] = rr % A.g.ntot[1]; ijk[2] = rr / A.g.ntot[1];
+      return lex;
+    }
     if (A.color < 0 && T > 0) {
       const int nx = cdim[0], ny = cdim[1], nz = cdim[2];
       const int row_cells = nx * T * nz;                    // every tile row but the last is T cells high
@@ -371,7 +321,9 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
   auto load_rows = [&](const int* gid, i64* base, double* fix) {   // stage C
 #pragma unroll
     for (int g = 0; g < G; ++g) {
-      base[g] = (gid[g] > 0 && gid[g] <= A.n_free) ? A.irp[gid[g] - 1] : -1;
+      bool mine = gid[g] > 0 && gid[g] <= A.n_free;
+      if (mine && F.row_fast) mine = !((F.row_fast[(gid[g] - 1) >> 5] >> ((gid[g] - 1) & 31)) & 1u);
+      base[g] = mine ? A.irp[gid[g] - 1] : -1;
       fix[g] = gid[g] < 0 ? A.fixed[-gid[g] - 1] : 0.0;
     }
   };
@@ -535,13 +487,13 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
             for (int i = 0; i < NN; ++i) {
               const int li = cc * NN + i;
               const unsigned short rel = tab[li * ND + cc * NN + j];
-              if (rel != 0xFFFF) {
+              if (rel != 0xFFFF && s_base[slot][li] >= 0) {
                 double* dst = A.val + (s_base[slot][li] + rel);
                 if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
               }
             }
             const int g = s_gid[slot][cc * NN + j];
-            if (g > 0 && g <= A.n_free && ev[cc] != 0.0) {
+            if (g > 0 && g <= A.n_free && ev[cc] != 0.0 && s_base[slot][cc * NN + j] >= 0) {
               if (ATOMIC) atomicAdd(&A.rhs[g - 1], ev[cc]); else A.rhs[g - 1] += ev[cc];
             }
           }
@@ -576,14 +528,14 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
               for (int i = 0; i < NN; ++i) {
                 const int li = a * NN + i;
                 const unsigned short rel = tab[li * ND + b * NN + j];
-                if (rel != 0xFFFF) {
+                if (rel != 0xFFFF && s_base[slot][li] >= 0) {
                   double* dst = A.val + (s_base[slot][li] + rel);
                   if (ATOMIC) atomicAdd(dst, acc[i]); else *dst += acc[i];
                 }
               }
             }
             const int g = s_gid[slot][b * NN + j];
-            if (g > 0 && g <= A.n_free && evb != 0.0) {
+            if (g > 0 && g <= A.n_free && evb != 0.0 && s_base[slot][b * NN + j] >= 0) {
               if (ATOMIC) atomicAdd(&A.rhs[g - 1], evb); else A.rhs[g - 1] += evb;
             }
           }
@@ -592,18 +544,6 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
     }
     __syncwarp();
   }
-}
-
-static int g_const_loaded[4] = {0, 0, 0, 0};
-static int load_const_tables(const fb2_space_s* s) {
-  const int p = s->rt.p;
-  if (g_const_loaded[p]) return 0;
-  double b[16] = {0}, c[16] = {0};
-  for (size_t k = 0; k < s->h_b1d.size(); ++k) { b[k] = s->h_b1d[k]; c[k] = s->h_c1d[k]; }
-  FB2_CUDA(cudaMemcpyToSymbol(c_B1, b, sizeof(b), sizeof(b) * (p - 1)));
-  FB2_CUDA(cudaMemcpyToSymbol(c_C1, c, sizeof(c), sizeof(c) * (p - 1)));
-  g_const_loaded[p] = 1;
-  return 0;
 }
 
 template <int P, int NCOMP, bool ELAST>

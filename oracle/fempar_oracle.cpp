@@ -21,6 +21,8 @@
 // =====================================================================================
 #include <algorithm>
 #include <array>
+#include <atomic>
+#include <chrono>
 #include <cassert>
 #include <cmath>
 #include <cstdint>
@@ -1106,4 +1108,138 @@ int fo_nq(void* h) { return ((Space*)h)->fe.nq; }
 int fo_hw_threads() { int n = int(std::thread::hardware_concurrency()); return n > 0 ? n : 1; }
 int fo_set_threads(void* h, int nt) { ((Space*)h)->nthreads = nt > 0 ? nt : 1; return 0; }
 int fo_num_threads(void* h) { return ((Space*)h)->nthreads; }
+// -------------------------------------------------------------------------------------
+// The reference's MPI path with every rank a host thread (BASELINE.md 3 variant 2):
+// one Space per part, sub-assembled local matrices, and per PCG iteration
+//   par_sparse_matrix apply  = local matvec + comm      LinearAlgebra/SparseMatrix/par_sparse_matrix.f90:739-762
+//   par_scalar_array%comm    = 2-stage neighbour exchange LinearAlgebra/Vector/par_scalar_array.f90:498-533
+//                              (pack_rp / unpack_rp, Tools/mpi_context.f90:522-639: here mailboxes in shared memory
+//                               with a barrier where MPI would wait)
+//   par dot / nrm2           = weighted local dot + l1_sum  par_scalar_array.f90:303-350 (mpi_context.f90:384: allreduce)
+//   cg_solve_body            LinearAlgebra/IterativeLinearSolver/cg.f90:101-238 (RES_RES, fixed number of iterations)
+// out[0] assembly seconds/step (max over ranks), out[1] seconds per apply (matvec + comm), out[2] seconds of the PCG loop/step,
+// out[3] |b|_2, out[4] |r|_2 after the last iteration, out[5] sum of the assembled diagonal, out[6] Jacobi set-up seconds/step
+// -------------------------------------------------------------------------------------
+namespace {
+struct SpinBarrier {
+  std::atomic<int> count{0}, gen{0};
+  int n = 1;
+  void wait() {
+    int g = gen.load(std::memory_order_acquire);
+    if (count.fetch_add(1, std::memory_order_acq_rel) == n - 1) { count.store(0, std::memory_order_relaxed); gen.fetch_add(1, std::memory_order_release); }
+    else { int spins = 0; while (gen.load(std::memory_order_acquire) == g) { if (++spins > 2000) std::this_thread::yield(); } }
+  }
+};
+}
+int fo_par_run(void** hs, int np, int kind, int func, const double* fprm, const double* mat, int cg_iters, int steps, int warmup,
+               double* out) {
+  std::vector<Space*> S(np);
+  for (int p = 0; p < np; ++p) S[p] = (Space*)hs[p];
+  // mailbox (p -> q) positions: stage 1 uses the send lists, stage 2 the receive lists
+  std::vector<std::vector<std::vector<double>>> box1(np), box2(np);
+  std::vector<std::vector<int>> slot_of_snd(np), slot_of_rcv(np);   // for receiver p: index of p in the sender's list
+  for (int p = 0; p < np; ++p) {
+    box1[p].resize(S[p]->list_snd.size()); box2[p].resize(S[p]->list_rcv.size());
+    for (size_t i = 0; i < S[p]->list_snd.size(); ++i) box1[p][i].resize(S[p]->snd_ptrs[i + 1] - S[p]->snd_ptrs[i]);
+    for (size_t i = 0; i < S[p]->list_rcv.size(); ++i) box2[p][i].resize(S[p]->rcv_ptrs[i + 1] - S[p]->rcv_ptrs[i]);
+  }
+  auto find_in = [](const std::vector<int>& lst, int part) { for (size_t i = 0; i < lst.size(); ++i) if (lst[i] == part) return int(i); return -1; };
+  SpinBarrier bar; bar.n = np;
+  std::vector<double> red(size_t(np) * 2 * 8, 0.0);
+  std::vector<double> t_asm(np, 0.0), t_app(np, 0.0), t_cg(np, 0.0), t_jac(np, 0.0), chk(8, 0.0);
+  auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  auto body = [&](int p) {
+    Space& s = *S[p];
+    const int n = s.n_free;
+    if (s.weight.size() != size_t(n)) s.weight.assign(n, 1.0);   // serial space: every DOF is owned
+    int red_flip = 0;
+    auto comm = [&](double* x) {
+      for (size_t i = 0; i < s.list_snd.size(); ++i)
+        for (int k = s.snd_ptrs[i], o = 0; k < s.snd_ptrs[i + 1]; ++k, ++o) box1[p][i][o] = x[s.pack_idx[k] - 1];
+      bar.wait();
+      for (size_t i = 0; i < s.list_rcv.size(); ++i) {        // the owner adds, neighbour by neighbour in list order
+        const int q = s.list_rcv[i] - 1, j = find_in(S[q]->list_snd, p + 1);
+        const std::vector<double>& b = box1[q][j];
+        for (int k = s.rcv_ptrs[i], o = 0; k < s.rcv_ptrs[i + 1]; ++k, ++o) x[s.unpack_idx[k] - 1] += b[o];
+      }
+      for (size_t i = 0; i < s.list_rcv.size(); ++i)
+        for (int k = s.rcv_ptrs[i], o = 0; k < s.rcv_ptrs[i + 1]; ++k, ++o) box2[p][i][o] = x[s.unpack_idx[k] - 1];
+      bar.wait();
+      for (size_t i = 0; i < s.list_snd.size(); ++i) {        // the owner's total comes back
+        const int q = s.list_snd[i] - 1, j = find_in(S[q]->list_rcv, p + 1);
+        const std::vector<double>& b = box2[q][j];
+        for (int k = s.snd_ptrs[i], o = 0; k < s.snd_ptrs[i + 1]; ++k, ++o) x[s.pack_idx[k] - 1] = b[o];
+      }
+    };
+    auto allsum = [&](const double* loc, int cnt, double* glob) {
+      double* base = &red[size_t(red_flip) * np * 8];
+      for (int k = 0; k < cnt; ++k) base[size_t(p) * 8 + k] = loc[k];
+      bar.wait();
+      for (int k = 0; k < cnt; ++k) { double t = 0; for (int q = 0; q < np; ++q) t += base[size_t(q) * 8 + k]; glob[k] = t; }
+      red_flip ^= 1;
+    };
+    auto wdot = [&](const double* a, const double* b) {
+      double l = 0; for (int i = 0; i < n; ++i) l += s.weight[i] * a[i] * b[i];
+      double g; allsum(&l, 1, &g); return g;
+    };
+    Func f = make_func(s.m.d, func, fprm);
+    std::vector<double> b(n), x(n), r(n), z(n), pp(n), Ap(n), d(n);
+    for (int it = 0; it < warmup + steps; ++it) {
+      bar.wait();
+      double t0 = now();
+      s.assemble(kind, f, mat, false, 1);
+      bar.wait();
+      double t1 = now();
+      std::copy(s.rhs.begin(), s.rhs.end(), b.begin());
+      comm(b.data());                                        // par_sparse_assembler.f90:171-176
+      bar.wait();
+      double t1b = now();
+      s.jacobi_setup();                                      // local diagonal (inverted), comm on the diagonal itself
+      double dsum = 0;
+      for (int i = 0; i < n; ++i) d[i] = 1.0 / s.dinv[i];
+      comm(d.data());
+      for (int i = 0; i < n; ++i) { dsum += s.weight[i] * d[i]; d[i] = 1.0 / d[i]; }
+      bar.wait();
+      double t2 = now(), tapp = 0;
+      std::fill(x.begin(), x.end(), 0.0);
+      s.spmv(x.data(), r.data()); comm(r.data());
+      for (int i = 0; i < n; ++i) r[i] = b[i] - r[i];
+      for (int i = 0; i < n; ++i) z[i] = d[i] * r[i];
+      double r_z = wdot(r.data(), z.data());
+      pp = z;
+      for (int k = 0; k < cg_iters; ++k) {
+        double ta = now();
+        s.spmv(pp.data(), Ap.data()); comm(Ap.data());
+        bar.wait();
+        tapp += now() - ta;
+        double App = wdot(Ap.data(), pp.data());
+        double alpha = App != 0.0 ? r_z / App : 0.0;
+        for (int i = 0; i < n; ++i) x[i] += alpha * pp[i];
+        for (int i = 0; i < n; ++i) r[i] -= alpha * Ap[i];
+        (void)wdot(r.data(), r.data());                      // RES_RES: |r|_2 every iteration
+        for (int i = 0; i < n; ++i) z[i] = d[i] * r[i];
+        double beta = 1.0 / r_z;
+        r_z = wdot(r.data(), z.data());
+        beta *= r_z;
+        for (int i = 0; i < n; ++i) pp[i] = z[i] + beta * pp[i];
+      }
+      bar.wait();
+      double t3 = now();
+      if (it >= warmup) { t_asm[p] += t1 - t0; t_jac[p] += t2 - t1b; t_cg[p] += t3 - t2; t_app[p] += tapp / std::max(cg_iters, 1); }
+      double c0 = wdot(b.data(), b.data()), c1 = wdot(r.data(), r.data()), c2;
+      allsum(&dsum, 1, &c2);
+      if (p == 0) { chk[0] = std::sqrt(c0); chk[1] = std::sqrt(c1); chk[2] = c2; }
+    }
+  };
+  std::vector<std::thread> th;
+  for (int p = 0; p < np; ++p) th.emplace_back(body, p);
+  for (auto& t : th) t.join();
+  out[0] = *std::max_element(t_asm.begin(), t_asm.end()) / std::max(steps, 1);
+  out[1] = *std::max_element(t_app.begin(), t_app.end()) / std::max(steps, 1);
+  out[2] = *std::max_element(t_cg.begin(), t_cg.end()) / std::max(steps, 1);
+  out[3] = chk[0]; out[4] = chk[1]; out[5] = chk[2];
+  out[6] = *std::max_element(t_jac.begin(), t_jac.end()) / std::max(steps, 1);
+  return 0;
+}
+
 }

@@ -137,3 +137,18 @@ class ParOracle:
             h1 += a * a
             l2 += b * b
         return np.sqrt(h1), np.sqrt(l2)
+
+
+def par_run_threads(spaces, kind=KIND_POISSON, func=FUNC_LINEAR, fprm=None, mat=None, cg_iters=25, steps=1, warmup=0):
+    """The reference's MPI path with every rank a host thread (fo_par_run in fempar_oracle.cpp): sub-assembled parts,
+    2-stage neighbour exchange through shared-memory mailboxes, weighted dots + all-reduce, `cg_iters` Jacobi-PCG iterations.
+    Returns seconds per step/apply and the checksums |b|, |r|, sum diag(A)."""
+    import ctypes as C
+    L = spaces[0].L
+    hs = (C.c_void_p * len(spaces))(*[s.h for s in spaces])
+    a, pa = OracleSpace._prm(fprm)
+    m, pm = OracleSpace._prm(mat)
+    out = np.zeros(8)
+    L.fo_par_run(hs, len(spaces), int(kind), int(func), C.c_void_p(pa), C.c_void_p(pm), int(cg_iters), int(steps), int(warmup),
+                 C.c_void_p(out.ctypes.data))
+    return dict(assembly_s=out[0], apply_s=out[1], pcg_s=out[2], jacobi_s=out[6], b_nrm2=out[3], r_nrm2=out[4], diag_sum=out[5])

@@ -59,3 +59,34 @@ def test_two_part_split_is_half_half():
     a, b = P.imp
     assert a["pack_idx"].size == 4 and a["unpack_idx"].size == 5
     assert b["unpack_idx"].size == 4 and b["pack_idx"].size == 5
+
+
+@pytest.mark.parametrize("N,p,parts", [((8, 8, 8), 2, (2, 2, 2)), ((8, 8, 8), 1, (4, 2, 1)), ((6, 6, 6), 2, (1, 1, 1))])
+def test_threads_as_ranks_run_matches_numpy_par_oracle(N, p, parts):
+    """fo_par_run (the timed MPI-layout CPU baseline of bench.py: one host thread per rank, mailbox exchange, weighted dots)
+    leaves the same |b|, |r| after 25 PCG iterations and assembled diagonal as the numpy restatement of the par layer."""
+    from oracle.par_oracle import par_run_threads
+    nparts = int(np.prod(parts))
+    if nparts == 1:
+        s = OracleSpace(N, order=p)
+        r = par_run_threads([s], cg_iters=25)
+        s.assemble(KIND_POISSON, FUNC_LINEAR, route=1)
+        b = s.rhs().copy()
+        dinv = s.jacobi_setup()
+        c = s.cg(prec=1, rtol=0.0, atol=-1.0, maxit=25)
+        res = b - s.spmv(c["x"])
+        ref = (np.linalg.norm(b), np.linalg.norm(res), float(np.sum(1.0 / dinv)))
+    else:
+        P = ParOracle(N, order=p, parts=parts)
+        r = par_run_threads(P.spaces, cg_iters=25)
+        b = P.assemble(KIND_POISSON, FUNC_LINEAR)
+        P.jacobi_setup()
+        c = P.cg(prec=1, rtol=0.0, atol=-1.0, maxit=25)
+        Ax = P.spmv([v.copy() for v in c["x"]])
+        res = [bv - av for bv, av in zip(b, Ax)]
+        ref = (np.sqrt(P.dot(b, b)), np.sqrt(P.dot(res, res)),
+               float(sum(np.dot(i["weight"], 1.0 / d) for i, d in zip(P.imp, P.dinv))))
+    assert abs(r["b_nrm2"] - ref[0]) <= 1e-12 * ref[0]
+    assert abs(r["r_nrm2"] - ref[1]) <= 1e-8 * max(ref[1], 1e-12) + 1e-14
+    assert abs(r["diag_sum"] - ref[2]) <= 1e-12 * ref[2]
+    assert r["assembly_s"] > 0 and r["apply_s"] > 0 and r["pcg_s"] > 0
