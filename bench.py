@@ -391,6 +391,10 @@ def main():
         except Exception:
             return None
     t_map_ms, t_gather_ms = phase("scatter_map"), phase("gather_plan")
+    spmv_info = {"tiles": phase("spmv_tiles"), "tiles_in_pattern_class": phase("spmv_tiles_in_class"),
+                 "pattern_classes": phase("spmv_classes"), "classes_setup_ms": phase("spmv_classes_ms")}
+    asm_info = {"owner_cells_gather": phase("gather_fast_cells"), "cells_scatter": phase("gather_slow_cells"),
+                "rows_scatter": phase("gather_slow_rows")}
     asm_ms, cg_ms, spmv_ms, jac_ms = [], [], [], []
     with ClockSampler(local) as clk:
         t0 = time.perf_counter()
@@ -519,6 +523,9 @@ def main():
     except Exception:
         pass
     per_gpu_bytes = spmv_bytes(n_loc, nnz_loc)
+    class_share = 0.0
+    if a.spmv_variant == 0 and spmv_info["tiles"] and spmv_info["tiles_in_pattern_class"] is not None and ppr == 1:
+        class_share = spmv_info["tiles_in_pattern_class"] / spmv_info["tiles"]
     achieved = per_gpu_bytes / (np.mean(spmv_ms) / a.cg_iters * 1e-3) / 1e9
     asm_bytes = nnz_loc * 8 + n_loc * 8
     try:
@@ -540,7 +547,9 @@ def main():
             "assembly_mdof_per_s": asm_mdofs, "assembly_ms": asm_t, "jacobi_setup_ms": jac_t,
             "pcg_ms_per_iteration": cg_t / a.cg_iters, "spmv_ms": spmv_t,
             "ms_per_step_parts": {"assembly": asm_t, "jacobi_setup": jac_t, "pcg": cg_t},
-            "setup_ms": {"fe_space": space_t, "csr_pattern": pattern_t, "scatter_map": t_map_ms, "gather_plan": t_gather_ms},
+            "setup_ms": {"fe_space": space_t, "csr_pattern": pattern_t, "scatter_map": t_map_ms, "gather_plan": t_gather_ms,
+                         "spmv_pattern_classes": spmv_info["classes_setup_ms"]},
+            "spmv_tiles": spmv_info, "assembly_cells": asm_info,
             # one-shot create -> compute -> solve (what every reference driver does): set-up + the first (cold) step
             "cold_start_ms": space_t + pattern_t + first_t,
             "wall_ms_per_step": wall_t, "checksum": checksum,
@@ -548,6 +557,9 @@ def main():
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": per_gpu_bytes,
                          "frac_of_nominal_8000_GBps": achieved / 8000.0,
+                         # tiles of a verified pattern class stream no column indices: what the kernel actually has to move
+                         "streamed_bytes_per_launch_estimate": per_gpu_bytes - 4.0 * nnz_loc * class_share,
+                         "streamed_GBps": (per_gpu_bytes - 4.0 * nnz_loc * class_share) / (np.mean(spmv_ms) / a.cg_iters * 1e-3) / 1e9,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650"},
             "roofline_assembly": {"bound": "hbm", "kernel": asm_kernel_label(a, ncomp),
                                   "achieved": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",

@@ -162,7 +162,7 @@ static size_t generic_smem_bytes(const fb2_space_s* s, int warps) {
   return sizeof(double) * ((size_t)nq * nn * 4 + nq + nq * 32 + per_warp * warps);
 }
 
-int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant);  // fb2_assemble_fast.cu
+int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant, bool rows_path);  // fb2_assemble_fast.cu
 static int g_asm_variant = 0;   // 0: fast paths where they apply, 1: always the generic kernel (kept for ncu comparison),
                                 // 2: sum-factorised scatter kernel only (no row-owner gather)
 int fb2_assembly_variant() { return g_asm_variant; }
@@ -190,10 +190,18 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   FB2_CHECK(s->d_gids != nullptr, "this space has no cell DOF lists (bare space): use fb2_assemble_batch");
   if (host_built) scatter_variant = FB2_SCATTER_ATOMIC;
   if (g_asm_variant != 1 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
+  // row-owner gather path (scalar Q2 Laplacian on structured parts): plan + verification are set-up as well
+  bool rows_path = false;
+  if (g_asm_variant == 0 && scatter_variant == FB2_SCATTER_ATOMIC && !host_built) {
+    FB2_TRY(fb2_rows_prepare(A, kind));
+    rows_path = A->rows_state == 1 && A->map_state == 1;
+  }
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   cudaEventRecord(e0, st);
-  FB2_CUDA(cudaMemsetAsync(A->d_val, 0, sizeof(double) * (size_t)A->nnz, st));
+  // rows written completely by the gather kernel need no zero fill: only the rows left to the scatter kernel are cleared
+  if (rows_path) FB2_TRY(fb2_rows_zero_slow(A));
+  else FB2_CUDA(cudaMemsetAsync(A->d_val, 0, sizeof(double) * (size_t)A->nnz, st));
   FB2_CUDA(cudaMemsetAsync(rhs->d, 0, sizeof(double) * (size_t)rhs->n, st));
   const int warps = 4, threads = warps * 32;
   size_t smem = generic_smem_bytes(s, warps);
@@ -201,7 +209,7 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   FB2_CUDA(cudaFuncSetAttribute(k_assemble_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int bps = (int)(227 * 1024 / smem); if (bps < 1) bps = 1; if (bps > 8) bps = 8;
-  int fast_rc = g_asm_variant != 1 ? fb2_assemble_fast(A, a, scatter_variant) : -1;
+  int fast_rc = g_asm_variant != 1 ? fb2_assemble_fast(A, a, scatter_variant, rows_path) : -1;
   if (fast_rc > 0) return fast_rc;
   if (fast_rc == 0) {
   } else if (scatter_variant == FB2_SCATTER_ATOMIC) {

@@ -231,7 +231,10 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
   constexpr bool TABCACHE = ND * ND * 2 <= 16384;    // scalar Q1-Q3 and vector Q1/Q2
   const AsmArgs& A = F.a;
   __shared__ double s_B[N1 * N1], s_C[N1 * N1];      // 1-D tables for the lane-dependent factors
-  __shared__ double s_gd[NQ * 24], s_qw[NQ];         // trilinear geometry gradients at the quadrature points, weights
+  // trilinear geometry gradients at the quadrature points (stride 26 doubles = 20 words mod 32: lanes are consecutive q
+  // and read 16 bytes each; a stride of 24 doubles put them on two bank groups -- 15.8 wavefronts per LDS.128, ncu round 2), weights
+  __shared__ __align__(16) double s_gd[NQ * 26];
+  __shared__ double s_qw[NQ];
   __shared__ double s_D[WARPS * CPW][NQ][DW];
   __shared__ double s_fw[WARPS * CPW][NQ];
   __shared__ double s_gfix[WARPS * CPW][ND];
@@ -246,7 +249,7 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
   const bool lane_on = lane < CPW * NN || CPL > 1;
   const int slot = w * CPW + (lane_on ? sub : 0);
   if (threadIdx.x < N1 * N1) { s_B[threadIdx.x] = c_B1[P - 1][threadIdx.x]; s_C[threadIdx.x] = c_C1[P - 1][threadIdx.x]; }
-  for (int e = threadIdx.x; e < NQ * 24; e += blockDim.x) s_gd[e] = A.gdphi[e];
+  for (int e = threadIdx.x; e < NQ * 24; e += blockDim.x) s_gd[(e / 24) * 26 + e % 24] = A.gdphi[e];
   for (int e = threadIdx.x; e < NQ; e += blockDim.x) s_qw[e] = A.qw[e];
   const bool have_cache = TABCACHE && F.common_tab >= 0;
   if (have_cache) {
@@ -395,7 +398,7 @@ __global__ void __launch_bounds__(128, (P == 3 ? 2 : (ELAST ? 2 : 3))) k_assembl
         if (q < NQ) {
           // --- lane as quadrature point: D(q) = w detJ J^-1 J^-T (sbm_cell_map.i90:272-296), source term ---
           double inv[3][3], det;
-          jacobian_at(X, s_gd + q * 24, inv, det);
+          jacobian_at(X, s_gd + q * 26, inv, det);
           const double wd = det * s_qw[q];
           double* D = s_D[slot][q];
           if constexpr (ELAST) {
@@ -562,7 +565,7 @@ static int launch_fast_host(const FastArgs& F0, const fb2_space_s* s) {
 }
 
 template <int P, int NCOMP, bool ELAST = false>
-static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_variant) {
+static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_variant, int n_listed = -1) {
   constexpr int NN = (P + 1) * (P + 1) * (P + 1), CPW = NN <= 16 ? 32 / NN : 1, WARPS = 4;
   FastArgs F = F0;
   cudaStream_t st = fb2_stream();
@@ -575,8 +578,8 @@ static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_var
   };
   if (scatter_variant == FB2_SCATTER_ATOMIC) {
     F.a.color = -1;
-    const int ncell = s->m.n_local;
-    k_assemble_fast<P, NCOMP, true, ELAST><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
+    const int ncell = n_listed >= 0 ? n_listed : s->m.n_local;   // listed cells only (row-owner hybrid) or every local cell
+    if (ncell > 0) k_assemble_fast<P, NCOMP, true, ELAST><<<grid_for(ncell), WARPS * 32, 0, st>>>(F, ncell);
   } else {
     for (int color = 0; color < 8; ++color) {
       F.a.color = color;
@@ -591,7 +594,8 @@ static int launch_fast(const FastArgs& F0, const fb2_space_s* s, int scatter_var
 }
 
 // returns 0 when the fast path ran, -1 when it does not apply (the caller uses the generic kernel), >0 on error
-int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant) {
+int fb2_rows_launch(fb2_matrix_s* A, const AsmArgs& a);   // fb2_assemble_rows.cu
+int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant, bool rows_path) {
   const fb2_space_s* s = A->s;
   if (s->rt.p > 3) return -1;
   if (args.kind == FB2_KIND_ELASTICITY && (s->rt.ncomp != 3 || s->rt.p > 2)) return -1;   // Q3 elasticity: generic kernel
@@ -601,6 +605,12 @@ int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant)
   FastArgs F;
   F.a = args; F.cell_tab = A->d_cell_tab; F.tabs = A->d_tabs; F.common_tab = A->common_tab;
   F.tile = getenv("FB2_ASM_TILE") ? atoi(getenv("FB2_ASM_TILE")) : 32;
+  F.cell_list = nullptr; F.row_fast = nullptr;
+  if (rows_path) {   // verified owner cells: rows written once by the gather kernel; the rest: scatter over the cells touching them
+    FB2_TRY(fb2_rows_launch(A, args));
+    F.cell_list = A->d_slow_cells; F.row_fast = A->d_row_fast;
+    return launch_fast<2, 1>(F, s, FB2_SCATTER_ATOMIC, A->n_slow_cells);
+  }
   if (s->d_coords) {   // host-numbered space
     if (args.kind == FB2_KIND_ELASTICITY) return s->rt.p == 1 ? launch_fast_host<1, 3, true>(F, s) : launch_fast_host<2, 3, true>(F, s);
     if (s->rt.ncomp != 1)   // vector Laplacian

@@ -24,6 +24,7 @@
 // Replaces, like the scatter kernel, the triple loop of the user plugin + fe_cell_iterator%assembly
 // (tutorial_01_..._modules.f90:114-128, sbm_fe_cell_iterator.i90:1610-1637, base_sparse_matrix.f90:3469-3513).
 #include <cub/cub.cuh>
+#include <thrust/iterator/counting_iterator.h>
 #include <stdlib.h>
 #include "fb2_sumfact.cuh"
 
@@ -32,12 +33,6 @@ namespace {
 constexpr int TY = 4, TZ = 4;            // owner-cell columns per CTA (pencil cross-section)
 constexpr int GY = TY + 1, GZ = TZ + 1;  // geometry cells per x-slab
 
-template <int P>
-struct RowsTraits {
-  static constexpr int N1 = P + 1, NN = N1 * N1 * N1, NQ = NN;
-  static constexpr int NROWS = P * P * P;                          // rows of an owner cell
-  static constexpr int CHUNK = (3 * P - 1 + 0) * 0 + 0;            // (unused)
-};
 __host__ __device__ constexpr int rows_chunk(int P) {   // entries of the chunk: per direction P-1 nodes with P+1 columns, 1 with 2P+1
   int w = (P - 1) * (P + 1) + (2 * P + 1);
   return w * w * w;
@@ -82,15 +77,18 @@ __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
   double* s_D = smem;                                          // [2][SA]
   double* s_stage = s_D + 2 * SA;                              // [WARPS][CH]
   double* s_fw = s_stage + WARPS * CH;                         // [2][GY*GZ][NQ] (SRC only)
-  double* s_gd = s_fw + (SRC ? 2 * GY * GZ * NQ : 0);          // [NQ][24]
-  double* s_gp = s_gd + NQ * 24;                               // [NQ][8] (SRC only, analytic f)
-  double* s_qw = s_gp + (SRC ? NQ * 8 : 0);                    // [NQ]
+  // strides 26 / 10 doubles (= 20 words mod 32): lanes are consecutive quadrature points and read 16 bytes each, so the 8
+  // lanes of a quarter warp cover the 32 banks once; with strides of 24 / 8 doubles they met on two bank groups (ncu: 15.8
+  // wavefronts per LDS.128 in jacobian_at, 35 % of all shared-memory wavefronts of the kernel)
+  double* s_gd = s_fw + (SRC ? 2 * GY * GZ * NQ : 0);          // [NQ][26]
+  double* s_gp = s_gd + NQ * 26;                               // [NQ][10] (SRC only, analytic f)
+  double* s_qw = s_gp + (SRC ? NQ * 10 : 0);                    // [NQ]
   double* s_B = s_qw + NQ;                                     // [N1*N1]
   double* s_C = s_B + N1 * N1;
   unsigned short* s_plan = (unsigned short*)(s_C + N1 * N1);   // [NN][NN]
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  for (int e = tid; e < NQ * 24; e += blockDim.x) s_gd[e] = R.gdphi[e];
-  if (SRC) for (int e = tid; e < NQ * 8; e += blockDim.x) s_gp[e] = R.gphi[e];
+  for (int e = tid; e < NQ * 24; e += blockDim.x) s_gd[(e / 24) * 26 + e % 24] = R.gdphi[e];
+  if (SRC) for (int e = tid; e < NQ * 8; e += blockDim.x) s_gp[(e / 8) * 10 + e % 8] = R.gphi[e];
   for (int e = tid; e < NQ; e += blockDim.x) s_qw[e] = R.qw[e];
   if (tid < N1 * N1) { s_B[tid] = c_B1[P - 1][tid]; s_C[tid] = c_C1[P - 1][tid]; }
   for (int e = tid; e < NN * NN; e += blockDim.x) s_plan[e] = R.plan[e];
@@ -129,7 +127,7 @@ __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) X[a][k] = lohi[k][(a >> k) & 1];
       double inv[3][3], det;
-      jacobian_at(X, s_gd + q * 24, inv, det);
+      jacobian_at(X, s_gd + q * 26, inv, det);
       const double wd = det * s_qw[q];
       double* D = Dslab + gy * SB + gz * SC + q * 6;
       D[0] = wd * (inv[0][0] * inv[0][0] + inv[1][0] * inv[1][0] + inv[2][0] * inv[2][0]);
@@ -149,7 +147,7 @@ __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
 #pragma unroll
           for (int a = 0; a < 8; ++a)
 #pragma unroll
-            for (int k = 0; k < 3; ++k) xq[k] += s_gp[q * 8 + a] * X[a][k];
+            for (int k = 0; k < 3; ++k) xq[k] += s_gp[q * 10 + a] * X[a][k];
           f = func_f(R.fn, xq);
         }
         s_fw[((xs & 1) * GY * GZ + cell) * NQ + q] = wd * f;
@@ -204,7 +202,7 @@ __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
           u2 = Db.x * g0 + Dd.x * g1 + Dd.y * g2;
         }, s_B, s_C, irow, acc);
         if (SRC) {
-          const double* fw = s_fw + ((((xs + d0) & 1) * GY + (oy + d1)) + GY * 0) * 0 + ((((xs + d0) & 1) * GY * GZ) + (oy + d1) + GY * (oz + d2)) * NQ;
+          const double* fw = s_fw + ((((xs + d0) & 1) * GY * GZ) + (oy + d1) + GY * (oz + d2)) * NQ;
           const int i1 = irow % N1, i2 = (irow / N1) % N1, i3 = irow / (N1 * N1);
 #pragma unroll 1
           for (int q = 0; q < NQ; ++q) {
@@ -408,7 +406,7 @@ template <int P>
 size_t rows_smem_bytes(bool src) {
   constexpr int N1 = P + 1, NN = N1 * N1 * N1, NQ = NN, CH = rows_chunk(P);
   constexpr int SC = NQ * 6, SB = GZ * SC + 10, SA = GY * SB + 4;
-  size_t d = 2 * (size_t)SA + 8 * (size_t)CH + (src ? 2 * GY * GZ * NQ + NQ * 8 : 0) + NQ * 24 + NQ + 2 * N1 * N1;
+  size_t d = 2 * (size_t)SA + 8 * (size_t)CH + (src ? 2 * GY * GZ * NQ + NQ * 10 : 0) + NQ * 26 + NQ + 2 * N1 * N1;
   return d * sizeof(double) + (size_t)NN * NN * sizeof(unsigned short) + 16;
 }
 
@@ -427,7 +425,7 @@ int fb2_rows_prepare(fb2_matrix_s* A, int kind) {
   const int n_local = s->m.n_local;
   for (int k = 0; k < 3; ++k) if (s->m.nloc[k] < 8) return 0;   // no deep-interior representative
   if (n_local == 0 || A->n < 64) return 0;
-  constexpr int P = 2, N1 = 3, NN = 27;
+  constexpr int P = 2, NN = 27;
   cudaStream_t st = fb2_stream();
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -478,7 +476,7 @@ int fb2_rows_prepare(fb2_matrix_s* A, int kind) {
       FB2_TRY(fb2_dalloc(&A->d_slow_rows, (size_t)n_slow_rows_max + 1));
       {
         void* tmp = nullptr; size_t bytes = 0;
-        cub::CountingInputIterator<i64> it(0);
+        thrust::counting_iterator<i64> it(0);
         FB2_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, it, flag, A->d_slow_rows, d_cnt, A->n, st));
         FB2_CUDA(cudaMalloc(&tmp, bytes ? bytes : 1));
         FB2_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, it, flag, A->d_slow_rows, d_cnt, A->n, st));

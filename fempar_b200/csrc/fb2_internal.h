@@ -115,6 +115,17 @@ struct fb2_matrix_s {
   unsigned short* d_tabs = nullptr;   // [n_tabs][nd*nd] relative slots, 0xFFFF = entry not stored
   int common_tab = -1;                // table id of the interior position class
   int n_tabs = 0, n_class_tabs = 0, map_state = 0;   // map_state: 0 not built, 1 built, -1 unavailable (search fallback)
+  // row-owner gather assembly (fb2_assemble_rows.cu): owner cells whose chunk of rows verified against the plan are written by
+  // plain stores; the remaining ("slow") rows are zeroed and accumulated by the scatter kernel over the cells touching them
+  int rows_state = 0;                     // 0 not built, 1 usable, -1 unavailable
+  unsigned short* d_rows_plan = nullptr;  // [units][columns] chunk-relative slots
+  unsigned char rows_row_of_node[32] = {0};
+  i64* d_chunk_base = nullptr;            // [n_local] irp of the owner cell's first row, -1: not a verified owner cell
+  unsigned* d_row_fast = nullptr;         // bit per row: written by the gather kernel
+  i64* d_slow_rows = nullptr;             // the other rows, ascending
+  int* d_slow_cells = nullptr;            // total-box lexicographic ids of the cells touching a slow row, ascending
+  i64 n_fast_cells = 0, n_slow_rows = 0;
+  int n_slow_cells = 0;
   // SpMV tile geometry (fb2_spmv.cu)
   int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0;
   i64 spmv_ntiles = 0;
@@ -129,6 +140,13 @@ struct fb2_matrix_s {
   int* d_dict = nullptr;                    // concatenated dictionaries, 0-based columns, each padded to 4 entries
   i64* d_dict_ptr = nullptr;                // [ntiles + 1] offsets into d_dict
   size_t spmv_smem_comp = 0;
+  // pattern classes of the streaming SpMV (fb2_spmv.cu): tiles whose columns are r0 + class deltas read neither ja nor gather x
+  int spmv_cls = 0;                         // 0 not built, 1 in use, -1 unavailable / switched off
+  int spmv_ncls = 0;
+  i64 spmv_tiles_in_class = 0;
+  unsigned char* d_tile_class = nullptr;    // [ntiles] class id, 0xFF: none
+  void* d_cls_desc = nullptr;               // SpmvClassDesc[ncls]
+  unsigned short* d_cls_idx = nullptr;      // [ncls][spmv_cap] x-window position of every staged entry
   int owns_space = 0;                       // matrix created from host arrays without a space: it owns a bare one
   i64 spmv_t_itf = -1, spmv_row_itf = -1;   // interface split of the tile table (par overlap)
 };
@@ -145,6 +163,9 @@ double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x
 #define FB2_MAX_PARTIALS 65536
 
 int fb2_build_scatter_map(fb2_matrix_s* A);
+int fb2_rows_prepare(fb2_matrix_s* A, int kind);     // fb2_assemble_rows.cu: plan + per-cell verification (set-up)
+int fb2_rows_zero_slow(fb2_matrix_s* A);
+int fb2_assembly_variant();
 int fb2_space_setup_reference_fe(fb2_space_s* s, int order, int ncomp);   // reference-FE tables, host + device (fb2_space.cu)
 int fb2_csr_graph_from_gids(fb2_matrix_s* A);                             // COO sort/unique graph (fb2_unstructured.cu)
 // primitives of fb2_solver.cu used by the host-driven Krylov solvers (fb2_krylov.cu)
@@ -161,7 +182,8 @@ bool fb2_ils_has_initial_solution(i64 n);
 int fb2_ils_load_initial_solution(double* x, i64 n);   // x <- the user's initial solution, or 0
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 int fb2_spmv_prepare(fb2_matrix_s* A);
-void fb2_spmv_set_compress(bool on);   // dictionary-compressed column indices for matrices prepared from now on
+void fb2_spmv_set_compress(bool on);
+void fb2_spmv_set_classes(bool on);      // pattern-class tiles for matrices prepared from now on (default on)   // dictionary-compressed column indices for matrices prepared from now on
 // tiles [t0, t1) only; chunk = 0: persistent CTAs striding over the range, chunk > 0: one CTA per `chunk` consecutive tiles
 // (short-lived CTAs, so that a higher-priority stream gets SM resources while the launch is running)
 int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, i64 t0, i64 t1,

@@ -140,6 +140,7 @@ static int g_par_chunk = getenv("FB2_PAR_CHUNK") ? atoi(getenv("FB2_PAR_CHUNK"))
 extern "C" int fb2_set_spmv_variant(int v) {
   // 2 = streamed tiles with dictionary-compressed column indices, for matrices whose first SpMV comes after this call
   fb2_spmv_set_compress(v == 2);
+  fb2_spmv_set_classes(v != 3);
   g_spmv_variant = (v == 2 || v == 3) ? 0 : v;   // 3: streamed tiles reading ja for every tile (fb2_spmv.cu)
   return 0;
 }

@@ -6,6 +6,8 @@
 // consecutive rows is the contiguous element range [irp[r0], irp[r0+R]) of both.  Algorithmic bytes
 // per row tile: 12 B per non-zero + 24 B per row (irp, y, x).
 #include <stdlib.h>
+#include <algorithm>
+#include <vector>
 #include <cub/cub.cuh>
 #include "fb2_internal.h"
 
@@ -45,6 +47,24 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// ---- pattern classes (index-free tiles) ----
+// On a structured part most row tiles are translated copies of a few patterns: the columns of tile t are r0 + delta_k with the
+// same deltas for every tile of its class (DOF ids are affine in the lattice position away from the boundary).  For such a
+// tile neither ja nor x gathers are needed: the class descriptor lists the <= 31 contiguous column segments [r0 + delta,
+// r0 + delta + len) the tile touches -- the producer warp bulk-copies them from x (L2-resident: neighbouring tiles share them)
+// into an "x window" in the stage -- and a uint16 window position per entry (class constant, copied from an L2-resident
+// table).  HBM traffic of a class tile: 8 B per non-zero instead of 12 B, and the consumers read shared memory only.
+// The class of a tile is never assumed: fb2_spmv_build_classes compares every tile entry by entry with the representative
+// of its class and checks the segment bounds; everything else streams ja as before.  Products are formed in the same
+// order from the same operands, so y is bit-identical to the ja path (tests: test_midsize_spmv_variants_bitwise).
+struct SpmvClassDesc {
+  int nseg, idx_bytes, x_bytes, pad;
+  int delta[32];   // first column of the segment relative to the first row of the tile (even, so 16-byte aligned in x)
+  int len[32];     // doubles, even
+  int off[32];     // position of the segment in the window, doubles
+};
+#define SPMV_NOCLASS 0xFF
+
 // Persistent block over tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  Warp 8 is the TMA producer
 // (one elected lane): it runs STAGES tiles ahead, waiting on the per-stage "empty" mbarrier and arming
 // the "full" one with the byte count of the three bulk copies (val, ja, irp slice).  The 8 consumer
@@ -61,7 +81,9 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
                                                              int R, int cap, i64 ntiles, int STAGES,
                                                              const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
                                                              int chunk, const int* __restrict__ dict, const i64* __restrict__ dict_ptr,
-                                                             int dcap) {
+                                                             int dcap, const unsigned char* __restrict__ tile_class,
+                                                             const SpmvClassDesc* __restrict__ cls_desc,
+                                                             const unsigned short* __restrict__ cls_idx) {
   constexpr int IB = COMP ? 2 : 4;                       // bytes per streamed column index
   constexpr i64 AL = COMP ? 7 : 3;                       // element-range alignment mask
   const int* ja = (const int*)ja_any;
@@ -69,7 +91,7 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full_bar[SPMV_MAX_STAGES], empty_bar[SPMV_MAX_STAGES];
   __shared__ i64 s_e0a[SPMV_MAX_STAGES], s_r0[SPMV_MAX_STAGES];
-  __shared__ int s_nr[SPMV_MAX_STAGES], s_nd[SPMV_MAX_STAGES];
+  __shared__ int s_nr[SPMV_MAX_STAGES], s_nd[SPMV_MAX_STAGES], s_cls[SPMV_MAX_STAGES], s_xoff[SPMV_MAX_STAGES];
   __shared__ i64 s_d0[SPMV_MAX_STAGES];
   __shared__ double s_red[32];
   if (done_flag && *done_flag) return;
@@ -94,40 +116,68 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
 
   if (tid >= SPMV_CONSUMERS) {
     // ---------------- producer warp ----------------
-    if (tid == SPMV_CONSUMERS) {
-      i64 t = t_first;
-      i64 e0 = 0, e1 = 0, r0 = 0, d0 = 0, d1 = 0;
-      int nr = 0;
-      if (t < t_end) {
-        r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr];
-        if (COMP) { d0 = dict_ptr[t]; d1 = dict_ptr[t + 1]; }
-      }
-      for (int it = 0; t < t_end; t += t_step, ++it) {
-        const int s = it % STAGES;
+    // lane 0 keeps the tile bookkeeping and issues the val / ja (or class index table) / irp copies; for a class tile the
+    // other lanes issue one x-segment copy each
+    const int plane = tid - SPMV_CONSUMERS;
+    i64 t = t_first;
+    i64 e0 = 0, e1 = 0, r0 = 0, d0 = 0, d1 = 0;
+    int nr = 0, cls = SPMV_NOCLASS;
+    if (plane == 0 && t < t_end) {
+      r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr];
+      if (COMP) { d0 = dict_ptr[t]; d1 = dict_ptr[t + 1]; }
+      if (!COMP && tile_class) cls = tile_class[t];
+    }
+    for (int it = 0; t < t_end; t += t_step, ++it) {
+      const int s = it % STAGES;
+      unsigned char* base = smem_raw + s * stage_bytes;
+      i64 ne0 = 0, ne1 = 0, nr0 = 0, nd0 = 0, nd1 = 0;
+      int nnr = 0, ncls = SPMV_NOCLASS;
+      if (plane == 0) {
         // prefetch the row / element range of the next tile before blocking on the empty barrier
-        i64 tn = t + t_step, ne0 = 0, ne1 = 0, nr0 = 0, nd0 = 0, nd1 = 0;
-        int nnr = 0;
+        const i64 tn = t + t_step;
         if (tn < t_end) {
           nr0 = tile_row[tn]; nnr = tile_nrows[tn]; ne0 = irp[nr0]; ne1 = irp[nr0 + nnr];
           if (COMP) { nd0 = dict_ptr[tn]; nd1 = dict_ptr[tn + 1]; }
+          if (!COMP && tile_class) ncls = tile_class[tn];
         }
         mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
-        unsigned char* base = smem_raw + s * stage_bytes;
         const i64 e0a = e0 & ~AL;
         const uint32_t cnt4 = (uint32_t)((e1 - e0a + AL) & ~AL);
         // a dictionary that does not fit the region is not staged: the consumers then go through it in global memory
         const uint32_t dbytes = (COMP && d1 - d0 <= SPMV_DS) ? (uint32_t)(d1 - d0) * 4u : 0u;
-        s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0); s_d0[s] = d0;
-        mbar_expect_tx(&full_bar[s], cnt4 * (uint32_t)(8 + IB) + dbytes + (uint32_t)irp_bytes);
-        bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
-        if (cnt4) {
-          bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
-          if (COMP) bulk_g2s(base + (size_t)cap * 8, ja16 + e0a, cnt4 * 2u, &full_bar[s]);
-          else bulk_g2s(base + (size_t)cap * 8, ja + e0a, cnt4 * 4u, &full_bar[s]);
+        s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0); s_d0[s] = d0; s_cls[s] = cls;
+        if (!COMP && cls != SPMV_NOCLASS) {
+          const SpmvClassDesc& D = cls_desc[cls];
+          s_xoff[s] = D.idx_bytes;
+          mbar_expect_tx(&full_bar[s], cnt4 * 8u + (uint32_t)D.idx_bytes + (uint32_t)D.x_bytes + (uint32_t)irp_bytes);
+          bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
+          if (cnt4) bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
+          bulk_g2s(base + (size_t)cap * 8, cls_idx + (size_t)cls * cap, (uint32_t)D.idx_bytes, &full_bar[s]);
+        } else {
+          mbar_expect_tx(&full_bar[s], cnt4 * (uint32_t)(8 + IB) + dbytes + (uint32_t)irp_bytes);
+          bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
+          if (cnt4) {
+            bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
+            if (COMP) bulk_g2s(base + (size_t)cap * 8, ja16 + e0a, cnt4 * 2u, &full_bar[s]);
+            else bulk_g2s(base + (size_t)cap * 8, ja + e0a, cnt4 * 4u, &full_bar[s]);
+          }
+          if (COMP && dbytes) bulk_g2s(base + dict_off, dict + d0, dbytes, &full_bar[s]);
         }
-        if (COMP && dbytes) bulk_g2s(base + dict_off, dict + d0, dbytes, &full_bar[s]);
-        e0 = ne0; e1 = ne1; r0 = nr0; nr = nnr; d0 = nd0; d1 = nd1;
       }
+      if (!COMP && tile_class) {
+        // x window of a class tile: lane l copies segment l - 1 (the barrier was armed by lane 0 above)
+        const int c_now = __shfl_sync(0xffffffffu, cls, 0);
+        if (c_now != SPMV_NOCLASS) {
+          const i64 r_now = __shfl_sync(0xffffffffu, r0, 0);
+          const SpmvClassDesc& D = cls_desc[c_now];
+          if (plane >= 1 && plane <= D.nseg) {
+            const int g = plane - 1;
+            bulk_g2s(base + (size_t)cap * 8 + (size_t)D.idx_bytes + (size_t)D.off[g] * 8, x + (r_now + D.delta[g]), (uint32_t)D.len[g] * 8u,
+                     &full_bar[s]);
+          }
+        }
+      }
+      e0 = ne0; e1 = ne1; r0 = nr0; nr = nnr; d0 = nd0; d1 = nd1; cls = ncls;
     }
     return;
   }
@@ -166,10 +216,13 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
         asm volatile("bar.sync 2, %0;" ::"r"(SPMV_CONSUMERS) : "memory");
       }
     }
+    // class tile: uint16 window positions where ja would be, the x window right behind them
+    const bool in_class = !COMP && tile_class && s_cls[s] != SPMV_NOCLASS;
+    const double* sxw = (const double*)(base + (size_t)cap * 8 + (in_class ? s_xoff[s] : 0));
     // x value of the k-th staged entry
     auto xat = [&](int k) -> double {
       if (COMP) return big ? x[dict_g[sj16[k]]] : xs[sj16[k]];
-      else return x[sj[k] - 1];
+      else return in_class ? sxw[sj16[k]] : x[sj[k] - 1];
     };
     const i64 e0a = s_e0a[s];
     double acc = 0.0;
@@ -374,6 +427,249 @@ static int spmv_compress(fb2_matrix_s* A, int capbuf, int R, int STAGES) {
   return 0;
 }
 
+
+// ---- pattern classes: signature hash per tile, the most frequent signatures become classes, every tile is then compared
+// entry by entry with the representative of its class ----
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+  z += 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+// warp per tile: order-independent sum of position-keyed hashes of (row lengths, column deltas), seeded by (rows, shift)
+__global__ void k_tile_hash(i64 ntiles, const i64* __restrict__ irp, const int* __restrict__ ja, const i64* __restrict__ tile_row,
+                            const unsigned char* __restrict__ tile_nrows, unsigned long long* hash, int* tile_id) {
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (i64 t = (i64)blockIdx.x * warps + w; t < ntiles; t += (i64)gridDim.x * warps) {
+    const i64 r0 = tile_row[t];
+    const int nr = tile_nrows[t];
+    const i64 e0 = irp[r0], e1 = irp[r0 + nr];
+    unsigned long long h = 0;
+    for (int r = lane; r < nr; r += 32) h += mix64(((unsigned long long)(0x40000000u + r) << 32) ^ (unsigned long long)(irp[r0 + r + 1] - irp[r0 + r]));
+    for (i64 k = e0 + lane; k < e1; k += 32)
+      h += mix64(((unsigned long long)(k - e0) << 32) ^ (unsigned long long)(unsigned)(ja[k] - 1 - (int)r0));
+    for (int o = 16; o > 0; o >>= 1) h += __shfl_down_sync(0xffffffffu, h, o);
+    if (lane == 0) {
+      hash[t] = mix64(h ^ ((unsigned long long)nr << 8) ^ (unsigned long long)(e0 & 3));
+      tile_id[t] = (int)t;
+    }
+  }
+}
+
+#define SPMV_CLS_MAX 250
+#define SPMV_SEG_GAP 8
+// block per class: segments of the representative tile's distinct columns and the window position of every entry
+__global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp, const int* __restrict__ ja,
+                                                     const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
+                                                     const int* __restrict__ rep, int cap, SpmvClassDesc* desc,
+                                                     unsigned short* cls_idx, int* valid) {
+  __shared__ int sb[DICT_SORT_MAX], su[DICT_SORT_MAX];
+  __shared__ int s_scan[256];
+  __shared__ SpmvClassDesc D;
+  __shared__ int s_ok;
+  const int tid = threadIdx.x, c = blockIdx.x;
+  const i64 t = rep[c];
+  const i64 r0 = tile_row[t];
+  const i64 e0 = irp[r0], e1 = irp[r0 + tile_nrows[t]];
+  const int m = (int)(e1 - e0), shift = (int)(e0 & 3);
+  int np2 = 256;
+  while (np2 < m) np2 <<= 1;
+  for (int i = tid; i < np2; i += 256) sb[i] = i < m ? ja[e0 + i] - 1 - (int)r0 : 0x7fffffff;
+  __syncthreads();
+  for (int k = 2; k <= np2; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < np2; i += 256) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const int a = sb[i], b = sb[ixj];
+          if ((a > b) == ((i & k) == 0)) { sb[i] = b; sb[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  const int per = np2 / 256, lo = tid * per;
+  int heads = 0;
+  for (int i = lo; i < lo + per; ++i) heads += (i < m && (i == 0 || sb[i] != sb[i - 1])) ? 1 : 0;
+  s_scan[tid] = heads;
+  __syncthreads();
+  for (int o = 1; o < 256; o <<= 1) {
+    const int v = tid >= o ? s_scan[tid - o] : 0;
+    __syncthreads();
+    s_scan[tid] += v;
+    __syncthreads();
+  }
+  const int nu = s_scan[255];
+  int pos = s_scan[tid] - heads;
+  for (int i = lo; i < lo + per; ++i)
+    if (i < m && (i == 0 || sb[i] != sb[i - 1])) su[pos++] = sb[i];
+  __syncthreads();
+  if (tid == 0) {
+    // greedy runs of the sorted distinct deltas; starts rounded down and lengths rounded up to even (16-byte bulk copies)
+    int nseg = 0, total = 0, ok = m > 0;
+    const int idx_n = (shift + m + 7) & ~7;
+    const int xw_cap = (cap * 4 - idx_n * 2) / 8;
+    int i = 0;
+    while (ok && i < nu) {
+      const int start = su[i] & ~1;
+      int last = su[i];
+      ++i;
+      while (i < nu && su[i] - last <= SPMV_SEG_GAP) { last = su[i]; ++i; }
+      const int len = (last - start + 2) & ~1;
+      if (nseg >= 31) { ok = 0; break; }
+      D.delta[nseg] = start; D.len[nseg] = len; D.off[nseg] = total;
+      total += len; ++nseg;
+    }
+    if (total > xw_cap || total > 0xFFFF || idx_n > cap) ok = 0;
+    D.nseg = nseg; D.idx_bytes = idx_n * 2; D.x_bytes = total * 8; D.pad = 0;
+    for (int g = nseg; g < 32; ++g) { D.delta[g] = 0; D.len[g] = 0; D.off[g] = 0; }
+    s_ok = ok;
+  }
+  __syncthreads();
+  unsigned short* out = cls_idx + (size_t)c * cap;
+  for (int i = tid; i < cap; i += 256) {
+    unsigned short v = 0;
+    const int k = i - shift;
+    if (s_ok && k >= 0 && k < m) {
+      const int d = ja[e0 + k] - 1 - (int)r0;
+      int g = 0;
+      while (g + 1 < D.nseg && D.delta[g + 1] <= d) ++g;
+      v = (unsigned short)(D.off[g] + d - D.delta[g]);
+    }
+    out[i] = v;
+  }
+  if (tid < (int)(sizeof(SpmvClassDesc) / sizeof(int))) ((int*)&desc[c])[tid] = ((const int*)&D)[tid];
+  if (tid == 0) valid[c] = s_ok;
+}
+
+// warp per tile: exact comparison with the representative of the class with the same hash, and segment bounds
+__global__ void k_tile_classify(i64 ntiles, i64 n, const i64* __restrict__ irp, const int* __restrict__ ja,
+                                const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
+                                const unsigned long long* __restrict__ hash, int ncls, const unsigned long long* __restrict__ cls_hash,
+                                const int* __restrict__ rep, const int* __restrict__ valid, const SpmvClassDesc* __restrict__ desc,
+                                unsigned char* tile_class, unsigned long long* n_in_class) {
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (i64 t = (i64)blockIdx.x * warps + w; t < ntiles; t += (i64)gridDim.x * warps) {
+    const unsigned long long h = hash[t];
+    int c = -1;
+    for (int k = lane; k < ncls; k += 32) if (cls_hash[k] == h && valid[k]) c = k;
+    for (int o = 16; o > 0; o >>= 1) c = max(c, __shfl_xor_sync(0xffffffffu, c, o));
+    bool same = c >= 0;
+    if (same) {
+      const i64 tr = rep[c], r0 = tile_row[t], q0 = tile_row[tr];
+      const int nr = tile_nrows[t];
+      const i64 e0 = irp[r0], e1 = irp[r0 + nr], f0 = irp[q0], f1 = irp[q0 + tile_nrows[tr]];
+      same = nr == tile_nrows[tr] && (e1 - e0) == (f1 - f0) && (e0 & 3) == (f0 & 3);
+      if (same) {
+        for (int r = lane; r < nr; r += 32) same = same && (irp[r0 + r + 1] - irp[r0 + r]) == (irp[q0 + r + 1] - irp[q0 + r]);
+        const int m = (int)(e1 - e0);
+        for (int k = lane; k < m; k += 32) same = same && (ja[e0 + k] - (int)r0) == (ja[f0 + k] - (int)q0);
+        const SpmvClassDesc& D = desc[c];
+        if (lane < D.nseg) same = same && r0 + D.delta[lane] >= 0 && r0 + D.delta[lane] + D.len[lane] <= n;
+      }
+    }
+    same = __all_sync(0xffffffffu, same);
+    if (lane == 0) {
+      tile_class[t] = same ? (unsigned char)c : (unsigned char)SPMV_NOCLASS;
+      if (same) atomicAdd(n_in_class, 1ULL);
+    }
+  }
+}
+
+static int g_spmv_classes = getenv("FB2_SPMV_CLASSES") ? atoi(getenv("FB2_SPMV_CLASSES")) : 1;
+void fb2_spmv_set_classes(bool on) { g_spmv_classes = on ? 1 : 0; }
+
+static int spmv_build_classes(fb2_matrix_s* A) {
+  A->spmv_cls = -1;
+  const i64 nt = A->spmv_ntiles;
+  if (!g_spmv_classes || nt < 64 || nt > 0x7fffffffLL || A->spmv_cap > DICT_SORT_MAX) return 0;
+  cudaStream_t st = fb2_stream();
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  unsigned long long *hash, *hash_s, *uniq;
+  int *tid, *tid_s, *counts, *d_nruns;
+  FB2_TRY(fb2_dalloc(&hash, (size_t)nt)); FB2_TRY(fb2_dalloc(&hash_s, (size_t)nt)); FB2_TRY(fb2_dalloc(&uniq, (size_t)nt));
+  FB2_TRY(fb2_dalloc(&tid, (size_t)nt)); FB2_TRY(fb2_dalloc(&tid_s, (size_t)nt)); FB2_TRY(fb2_dalloc(&counts, (size_t)nt));
+  FB2_TRY(fb2_dalloc(&d_nruns, 1));
+  k_tile_hash<<<fb2_num_sms() * 8, 256, 0, st>>>(nt, A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, hash, tid);
+  FB2_CUDA(cudaGetLastError());
+  {
+    void* tmp = nullptr; size_t bytes = 0;
+    FB2_CUDA(cub::DeviceRadixSort::SortPairs(tmp, bytes, hash, hash_s, tid, tid_s, (int)nt, 0, 64, st));
+    FB2_CUDA(cudaMalloc(&tmp, bytes ? bytes : 1));
+    FB2_CUDA(cub::DeviceRadixSort::SortPairs(tmp, bytes, hash, hash_s, tid, tid_s, (int)nt, 0, 64, st));
+    FB2_CUDA(cudaStreamSynchronize(st));
+    cudaFree(tmp);
+    tmp = nullptr; bytes = 0;
+    FB2_CUDA(cub::DeviceRunLengthEncode::Encode(tmp, bytes, hash_s, uniq, counts, d_nruns, (int)nt, st));
+    FB2_CUDA(cudaMalloc(&tmp, bytes ? bytes : 1));
+    FB2_CUDA(cub::DeviceRunLengthEncode::Encode(tmp, bytes, hash_s, uniq, counts, d_nruns, (int)nt, st));
+    FB2_CUDA(cudaStreamSynchronize(st));
+    cudaFree(tmp);
+  }
+  int nruns = 0;
+  FB2_CUDA(fb2_memcpy(&nruns, d_nruns, sizeof(int), cudaMemcpyDeviceToHost));
+  std::vector<unsigned long long> h_uniq((size_t)nruns);
+  std::vector<int> h_cnt((size_t)nruns);
+  if (nruns) {
+    FB2_CUDA(fb2_memcpy(h_uniq.data(), uniq, sizeof(unsigned long long) * (size_t)nruns, cudaMemcpyDeviceToHost));
+    FB2_CUDA(fb2_memcpy(h_cnt.data(), counts, sizeof(int) * (size_t)nruns, cudaMemcpyDeviceToHost));
+  }
+  // the most frequent signatures (at least 16 tiles each), at most SPMV_CLS_MAX
+  std::vector<i64> first((size_t)nruns);
+  i64 acc = 0;
+  for (int k = 0; k < nruns; ++k) { first[k] = acc; acc += h_cnt[k]; }
+  std::vector<int> order;
+  for (int k = 0; k < nruns; ++k) if (h_cnt[k] >= 16) order.push_back(k);
+  std::sort(order.begin(), order.end(), [&](int a, int b) { return h_cnt[a] != h_cnt[b] ? h_cnt[a] > h_cnt[b] : a < b; });
+  if ((int)order.size() > SPMV_CLS_MAX) order.resize(SPMV_CLS_MAX);
+  const int ncls = (int)order.size();
+  int rc = 0;
+  if (ncls > 0) {
+    std::vector<unsigned long long> h_ch((size_t)ncls);
+    std::vector<int> h_rep((size_t)ncls);
+    std::vector<int> h_first((size_t)ncls);
+    for (int c = 0; c < ncls; ++c) { h_ch[c] = h_uniq[order[c]]; h_first[c] = (int)first[order[c]]; }
+    // representative = first tile of the run in the sorted order
+    std::vector<int> h_tid_first((size_t)ncls);
+    for (int c = 0; c < ncls; ++c) FB2_CUDA(fb2_memcpy(&h_rep[c], tid_s + h_first[c], sizeof(int), cudaMemcpyDeviceToHost));
+    unsigned long long* d_ch;
+    int *d_rep, *d_valid;
+    unsigned long long* d_nin;
+    FB2_TRY(fb2_dalloc(&d_ch, (size_t)ncls)); FB2_TRY(fb2_dalloc(&d_rep, (size_t)ncls)); FB2_TRY(fb2_dalloc(&d_valid, (size_t)ncls));
+    FB2_TRY(fb2_dalloc(&d_nin, 1));
+    FB2_TRY(fb2_dalloc(&A->d_cls_desc, (size_t)ncls * sizeof(SpmvClassDesc)));
+    FB2_TRY(fb2_dalloc(&A->d_cls_idx, (size_t)ncls * A->spmv_cap + 8));
+    FB2_TRY(fb2_dalloc(&A->d_tile_class, (size_t)nt));
+    FB2_CUDA(fb2_memcpy(d_ch, h_ch.data(), sizeof(unsigned long long) * (size_t)ncls, cudaMemcpyHostToDevice));
+    FB2_CUDA(fb2_memcpy(d_rep, h_rep.data(), sizeof(int) * (size_t)ncls, cudaMemcpyHostToDevice));
+    FB2_CUDA(cudaMemsetAsync(d_nin, 0, sizeof(unsigned long long), st));
+    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap,
+                                        (SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, d_valid);
+    k_tile_classify<<<fb2_num_sms() * 8, 256, 0, st>>>(nt, A->n, A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, hash, ncls, d_ch,
+                                                        d_rep, d_valid, (const SpmvClassDesc*)A->d_cls_desc, A->d_tile_class, d_nin);
+    unsigned long long h_nin = 0;
+    FB2_CUDA(cudaMemcpyAsync(&h_nin, d_nin, sizeof(h_nin), cudaMemcpyDeviceToHost, st));
+    FB2_CUDA(cudaStreamSynchronize(st));
+    if (cudaGetLastError() != cudaSuccess) rc = 1;
+    A->spmv_ncls = ncls; A->spmv_tiles_in_class = (i64)h_nin;
+    if (rc == 0 && h_nin * 4 >= (unsigned long long)nt) A->spmv_cls = 1;   // worth the extra branch: a quarter of the tiles or more
+    cudaFree(d_ch); cudaFree(d_rep); cudaFree(d_valid); cudaFree(d_nin);
+  }
+  cudaFree(hash); cudaFree(hash_s); cudaFree(uniq); cudaFree(tid); cudaFree(tid_s); cudaFree(counts); cudaFree(d_nruns);
+  cudaEventRecord(e1, st);
+  FB2_CUDA(cudaStreamSynchronize(st));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  fb2_record_phase("spmv_classes_ms", ms);
+  fb2_record_phase("spmv_classes", (double)A->spmv_ncls);
+  fb2_record_phase("spmv_tiles_in_class", (double)A->spmv_tiles_in_class);
+  fb2_record_phase("spmv_signatures", (double)nruns);
+  if (rc) { fb2_set_error("SpMV class construction failed"); return 1; }
+  return 0;
+}
+
 // choose the tile geometry once per matrix
 int fb2_spmv_prepare(fb2_matrix_s* A) {
   if (A->spmv_cap > 0 || A->n == 0) return 0;
@@ -425,6 +721,7 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   A->spmv_grid = (int)grid;
   fb2_record_phase("spmv_R", R); fb2_record_phase("spmv_tiles", (double)ntiles); fb2_record_phase("spmv_ctas_per_sm", bps);
   FB2_TRY(spmv_compress(A, capbuf, R, STAGES));
+  if (A->spmv_comp != 1) FB2_TRY(spmv_build_classes(A));
   return 0;
 }
 
@@ -436,10 +733,13 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
   cudaStream_t st = fb2_stream();
   if (chunk && (nt + chunk - 1) / chunk > FB2_MAX_PARTIALS / 2) chunk = (int)((nt + FB2_MAX_PARTIALS / 2 - 1) / (FB2_MAX_PARTIALS / 2));
   i64 grid = chunk ? (nt + chunk - 1) / chunk : (nt < A->spmv_grid ? nt : (i64)A->spmv_grid);
+  // class tiles bulk-copy segments of x: they need a 16-byte aligned x (always true for library vectors, not for views)
+  const unsigned char* tcls = (A->spmv_cls == 1 && (((uintptr_t)x) & 15) == 0) ? A->d_tile_class + t0 : nullptr;
 #define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                                   \
   k_spmv_stream<FD, CP><<<(unsigned)grid, SPMV_THREADS, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
                                                                     done_flag, A->spmv_R, A->spmv_cap, nt, A->spmv_stages,   \
-                                                                    A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP)
+                                                                    A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP, \
+                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx)
   if (A->spmv_comp == 1) {
     if (fuse_dot) SPMV_LAUNCH(true, true, A->d_idx16, A->spmv_smem_comp, A->d_dict, A->d_dict_ptr + t0, A->spmv_dcap);
     else SPMV_LAUNCH(false, true, A->d_idx16, A->spmv_smem_comp, A->d_dict, A->d_dict_ptr + t0, A->spmv_dcap);
