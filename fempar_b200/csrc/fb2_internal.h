@@ -103,8 +103,10 @@ struct fb2_space_s {
   struct fb2_import_s* imp = nullptr;
 };
 
+struct fb2_solver_ws;
 struct fb2_matrix_s {
   fb2_space_s* s = nullptr;
+  fb2_solver_ws* ws = nullptr;   // solver workspace of this operator (fb2_solver.cu)
   int sym = 0;
   i64 n = 0, nnz = 0;
   i64* d_irp = nullptr;   // 0-based offsets, n+1
@@ -178,8 +180,9 @@ int fb2_dev_scal(double* dst, double a, const double* src, i64 n);
 int fb2_dev_init(double* x, double a, i64 n);
 int fb2_dots_host(fb2_matrix_s* A, int k, const double* const* xs, const double* const* ys, i64 n, double* out);
 void fb2_cg_set_icg(int on);
-bool fb2_ils_has_initial_solution(i64 n);
-int fb2_ils_load_initial_solution(double* x, i64 n);   // x <- the user's initial solution, or 0
+bool fb2_ils_has_initial_solution(fb2_matrix_s* A);
+int fb2_ils_load_initial_solution(fb2_matrix_s* A, double* x);   // x <- the initial solution set on this operator, or 0
+void fb2_solver_ws_free(fb2_matrix_s* A);
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 int fb2_spmv_prepare(fb2_matrix_s* A);
 void fb2_spmv_set_compress(bool on);

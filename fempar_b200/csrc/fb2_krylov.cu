@@ -198,7 +198,7 @@ static int richardson_solve(fb2_matrix_s* A, const double* dinv, const double* b
   FB2_TRY(W.get(&r, n)); FB2_TRY(W.get(&z, n));
   double rhs_norm = 0.0, res_norm, tol;
   if (stop == FB2_STOP_RES_RHS) FB2_TRY(nrm2(A, b, n, &rhs_norm));
-  FB2_TRY(fb2_ils_load_initial_solution(x, n));   // zero unless set_initial_solution was called
+  FB2_TRY(fb2_ils_load_initial_solution(A, x));   // zero unless set_initial_solution was called
   FB2_TRY(fb2_op_apply(A, x, r));
   FB2_TRY(fb2_dev_axpby(r, 1.0, b, -1.0, n));
   FB2_TRY(nrm2(A, r, n, &res_norm));
@@ -251,7 +251,7 @@ static int gmres_solve(fb2_matrix_s* A, const double* dinv, const double* b, dou
   // NOTE lgmres.f90:190-192 evaluates ||b|| only for res_nrmgiven_rhs_nrmgiven although res_rhs uses it (:217): here ||b||
   // is evaluated for res_rhs too (the evident intent; the reference reads an unset variable)
   if (stop == FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN || stop == FB2_STOP_RES_RHS) FB2_TRY(nrm2(A, b, n, &rhs_norm));
-  FB2_TRY(fb2_ils_load_initial_solution(x, n));   // zero unless set_initial_solution was called
+  FB2_TRY(fb2_ils_load_initial_solution(A, x));   // zero unless set_initial_solution was called
   FB2_TRY(fb2_op_apply(A, x, r));
   FB2_TRY(fb2_dev_axpby(r, 1.0, b, -1.0, n));
   FB2_TRY(nrm2(A, r, n, &res_norm));
@@ -382,7 +382,7 @@ static int lfom_solve(fb2_matrix_s* A, const double* dinv, const double* b, doub
   std::vector<double> hh((size_t)ld * m, 0.0), g((size_t)m + 1, 0.0);
   double rhs_norm = 0.0, res_norm = 0.0, res_2_norm = 0.0, res_norm_initial, tol, e;
   if (stop == FB2_STOP_RES_RHS) FB2_TRY(nrm2(A, b, n, &rhs_norm));
-  FB2_TRY(fb2_ils_load_initial_solution(x, n));   // zero unless set_initial_solution was called
+  FB2_TRY(fb2_ils_load_initial_solution(A, x));   // zero unless set_initial_solution was called
   FB2_TRY(fb2_op_apply(A, x, r));
   FB2_TRY(fb2_dev_axpby(r, 1.0, b, -1.0, n));
   FB2_TRY(nrm2(A, r, n, &res_2_norm));
@@ -448,7 +448,7 @@ static int minres_solve(fb2_matrix_s* A, const double* dinv, const double* b, do
   FB2_TRY(W.get(&y, n)); FB2_TRY(W.get(&w, n)); FB2_TRY(W.get(&w1, n)); FB2_TRY(W.get(&w2, n));
   int istop = 0, it = 0;
   double Anorm = zero, Acond = zero, ynorm = zero, e = zero, tol = zero;
-  FB2_TRY(fb2_ils_load_initial_solution(x, n));   // zero unless set_initial_solution was called
+  FB2_TRY(fb2_ils_load_initial_solution(A, x));   // zero unless set_initial_solution was called
   FB2_TRY(fb2_op_apply(A, x, r1));
   FB2_TRY(fb2_dev_axpby(r1, 1.0, b, -1.0, n));
   FB2_TRY(fb2_dev_apply_M(dinv, r1, v1, n));

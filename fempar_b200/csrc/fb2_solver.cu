@@ -430,32 +430,57 @@ struct CgWork {
   CgState* st = nullptr;
   int hist_cap = 0;
 };
-static CgWork g_work;
-static int cg_workspace(i64 n, int hist_len) {
-  if (g_work.n != n) {
-    cudaFree(g_work.r); cudaFree(g_work.p); cudaFree(g_work.Ap);
-    FB2_TRY(fb2_dalloc(&g_work.r, (size_t)n)); FB2_TRY(fb2_dalloc(&g_work.p, (size_t)n)); FB2_TRY(fb2_dalloc(&g_work.Ap, (size_t)n));
-    g_work.n = n;
+// Solver state lives in the matrix handle (re-entrant across handles): Krylov work vectors, the device-resident
+// CgState, the convergence history, the user's initial solution and the staging vectors of the host-buffer entry point.
+// Two operators of different size can be solved alternately without re-allocation or cross-talk.
+struct fb2_solver_ws {
+  CgWork w;
+  double* x0 = nullptr;
+  i64 x0_n = 0;
+  bool x0_on = false;
+  fb2_vector_t vb = nullptr, vx = nullptr;
+};
+static fb2_solver_ws* ws_of(fb2_matrix_t A) {
+  if (!A->ws) A->ws = new fb2_solver_ws();
+  return A->ws;
+}
+static CgWork& work_of(fb2_matrix_t A) { return ws_of(A)->w; }
+void fb2_solver_ws_free(fb2_matrix_s* A) {
+  if (!A->ws) return;
+  CgWork& W = A->ws->w;
+  cudaFree(W.r); cudaFree(W.p); cudaFree(W.Ap); cudaFree(W.hist); cudaFree(W.st); cudaFree(A->ws->x0);
+  if (A->ws->vb) { fb2_vec_destroy(A->ws->vb); fb2_vec_destroy(A->ws->vx); }
+  delete A->ws;
+  A->ws = nullptr;
+}
+static int cg_workspace(fb2_matrix_t A, int hist_len) {
+  CgWork& W = work_of(A);
+  const i64 n = A->n;
+  if (W.n != n) {
+    cudaFree(W.r); cudaFree(W.p); cudaFree(W.Ap);
+    FB2_TRY(fb2_dalloc(&W.r, (size_t)n)); FB2_TRY(fb2_dalloc(&W.p, (size_t)n)); FB2_TRY(fb2_dalloc(&W.Ap, (size_t)n));
+    W.n = n;
   }
-  if (!g_work.st) FB2_TRY(fb2_dalloc(&g_work.st, 1));
-  if (hist_len > g_work.hist_cap) {
-    cudaFree(g_work.hist);
-    FB2_TRY(fb2_dalloc(&g_work.hist, (size_t)hist_len));
-    g_work.hist_cap = hist_len;
+  if (!W.st) FB2_TRY(fb2_dalloc(&W.st, 1));
+  if (hist_len > W.hist_cap) {
+    cudaFree(W.hist);
+    FB2_TRY(fb2_dalloc(&W.hist, (size_t)hist_len));
+    W.hist_cap = hist_len;
   }
   return 0;
 }
-extern "C" int fb2_pcg_free_workspace(void) {
-  cudaFree(g_work.r); cudaFree(g_work.p); cudaFree(g_work.Ap); cudaFree(g_work.hist); cudaFree(g_work.st);
-  g_work = CgWork();
+// the work vectors belong to the matrix handles (released by fb2_csr_destroy, or earlier through this call)
+extern "C" int fb2_csr_free_solver_workspace(fb2_matrix_t A) {
+  if (A) fb2_solver_ws_free(A);
   return 0;
 }
+extern "C" int fb2_pcg_free_workspace(void) { return 0; }   // kept for ABI compatibility: nothing is process-global any more
 
 // one PCG iteration enqueued on the stream
 static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double* w, double* x, bool par, double* hist,
                                 cudaEvent_t ev_spmv0, cudaEvent_t ev_spmv1) {
   cudaStream_t s = fb2_stream();
-  CgWork& W = g_work;
+  CgWork& W = work_of(A);
   double* part = fb2_scratch_partials();
   const i64 n = A->n;
   int g = 0;
@@ -508,27 +533,29 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
   return 0;
 }
 
-// initial solution of the next solves (base_iterative_linear_solver_t%set_initial_solution, base_iterative_linear_solver.f90:
-// 340-360: the solver keeps its own copy; default zero, :281-282).  One copy per process, like the rest of the library state.
-static double* g_x0 = nullptr;
-static i64 g_x0_n = 0;
-static bool g_x0_on = false;
-extern "C" int fb2_ils_set_initial_solution(fb2_vector_t x0) {
-  if (!x0) { g_x0_on = false; return 0; }
-  if (g_x0_n != x0->n) {
-    cudaFree(g_x0); g_x0 = nullptr; g_x0_n = 0;
-    FB2_TRY(fb2_dalloc(&g_x0, (size_t)x0->n));
-    g_x0_n = x0->n;
+// initial solution of the next solves on this operator (base_iterative_linear_solver_t%set_initial_solution,
+// base_iterative_linear_solver.f90:340-360: the solver keeps its own copy; default zero, :281-282).  Keyed on the matrix
+// handle; NULL switches back to the zero default.
+extern "C" int fb2_csr_set_initial_solution(fb2_matrix_t A, fb2_vector_t x0) {
+  FB2_CHECK(A, "null matrix");
+  fb2_solver_ws* S = ws_of(A);
+  if (!x0) { S->x0_on = false; return 0; }
+  // a vector that does not belong to range(A) is ignored, as the reference does (with a warning, :349-351)
+  if (x0->n != A->n) { S->x0_on = false; return 0; }
+  if (S->x0_n != x0->n) {
+    cudaFree(S->x0); S->x0 = nullptr; S->x0_n = 0;
+    FB2_TRY(fb2_dalloc(&S->x0, (size_t)x0->n));
+    S->x0_n = x0->n;
   }
-  FB2_CUDA(cudaMemcpyAsync(g_x0, x0->d, sizeof(double) * (size_t)x0->n, cudaMemcpyDeviceToDevice, fb2_stream()));
-  g_x0_on = true;
+  FB2_CUDA(cudaMemcpyAsync(S->x0, x0->d, sizeof(double) * (size_t)x0->n, cudaMemcpyDeviceToDevice, fb2_stream()));
+  S->x0_on = true;
   return 0;
 }
-// a vector that does not belong to range(A) is ignored, as the reference does (with a warning, :349-351)
-bool fb2_ils_has_initial_solution(i64 n) { return g_x0_on && g_x0_n == n; }
-int fb2_ils_load_initial_solution(double* x, i64 n) {
-  if (fb2_ils_has_initial_solution(n))
-    FB2_CUDA(cudaMemcpyAsync(x, g_x0, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, fb2_stream()));
+bool fb2_ils_has_initial_solution(fb2_matrix_t A) { return A->ws && A->ws->x0_on && A->ws->x0_n == A->n; }
+int fb2_ils_load_initial_solution(fb2_matrix_t A, double* x) {
+  const i64 n = A->n;
+  if (fb2_ils_has_initial_solution(A))
+    FB2_CUDA(cudaMemcpyAsync(x, A->ws->x0, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, fb2_stream()));
   else k_init<<<vec_grid(n), 256, 0, fb2_stream()>>>(x, 0.0, n);
   FB2_CUDA(cudaGetLastError());
   return 0;
@@ -537,13 +564,13 @@ int fb2_ils_load_initial_solution(double* x, i64 n) {
 static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const double* b, double* x, bool par, double rtol,
                     double atol, int maxit, int stop) {
   cudaStream_t s = fb2_stream();
-  CgWork& W = g_work;
+  CgWork& W = work_of(A);
   const i64 n = A->n;
   // x <- 0 ; r = A x ; r = b - r   (cg.f90:142,158-162)
   // The initial solution is zero (base_iterative_linear_solver.f90:281-282), so r = b - A*0 = b bit for bit: the
   // reference's initial SpMV and its halo exchange are skipped.
-  if (fb2_ils_has_initial_solution(n)) {   // user-selected initial solution: the full r = b - A x (cg.f90:158-162)
-    FB2_TRY(fb2_ils_load_initial_solution(x, n));
+  if (fb2_ils_has_initial_solution(A)) {   // user-selected initial solution: the full r = b - A x (cg.f90:158-162)
+    FB2_TRY(fb2_ils_load_initial_solution(A, x));
     FB2_TRY(fb2_op_apply(A, x, W.r));
     FB2_TRY(fb2_dev_axpby(W.r, 1.0, b, -1.0, n));
   } else {
@@ -593,7 +620,8 @@ extern "C" int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, 
   const bool par = A->s->imp && fb2_comm_active();
   const double* w = par ? fb2_import_weight(A->s->imp) : nullptr;
   const bool track = history != nullptr;
-  FB2_TRY(cg_workspace(A->n, track ? maxit : 0));
+  FB2_TRY(cg_workspace(A, track ? maxit : 0));
+  CgWork& W = work_of(A);
   cudaStream_t s = fb2_stream();
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -607,9 +635,9 @@ extern "C" int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, 
     int chunk = every;
     if (launched + chunk > maxit) chunk = maxit - launched;
     for (int k = 0; k < chunk; ++k)
-      FB2_TRY(cg_enqueue_iteration(A, dinv ? dinv->d : nullptr, w, x->d, par, track ? g_work.hist : nullptr, nullptr, nullptr));
+      FB2_TRY(cg_enqueue_iteration(A, dinv ? dinv->d : nullptr, w, x->d, par, track ? W.hist : nullptr, nullptr, nullptr));
     launched += chunk;
-    FB2_CUDA(cudaMemcpyAsync(&h, g_work.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
+    FB2_CUDA(cudaMemcpyAsync(&h, W.st, sizeof(CgState), cudaMemcpyDeviceToHost, s));
     FB2_CUDA(cudaStreamSynchronize(s));
     if (h.done) break;
   }
@@ -622,14 +650,15 @@ extern "C" int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, 
   *num_iterations = h.iter;
   *did_converge = h.converged;
   *error_estimate = h.err;
-  if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, g_work.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
+  if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, W.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
   return 0;
 }
 
 extern "C" int fb2_pcg_solve_host(fb2_matrix_t A, fb2_vector_t dinv, const double* b_host, double* x_host,
                                   const fb2_ils_params_t* prm, int* num_iterations, int* did_converge, double* error_estimate,
                                   double* history) {
-  static fb2_vector_t vb = nullptr, vx = nullptr;
+  FB2_CHECK(A && b_host && x_host, "null argument");
+  fb2_vector_t &vb = ws_of(A)->vb, &vx = ws_of(A)->vx;   // staging vectors owned by the matrix handle
   if (!vb || vb->n != A->n) {
     if (vb) { fb2_vec_destroy(vb); fb2_vec_destroy(vx); }
     FB2_TRY(fb2_vec_create_n(&vb, A->n));
@@ -647,7 +676,7 @@ extern "C" int fb2_pcg_iterate(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b
   FB2_CHECK(A && b && x && n_iterations > 0, "bad argument");
   const bool par = A->s->imp && fb2_comm_active();
   const double* w = par ? fb2_import_weight(A->s->imp) : nullptr;
-  FB2_TRY(cg_workspace(A->n, 0));
+  FB2_TRY(cg_workspace(A, 0));
   cudaStream_t s = fb2_stream();
   // tolerance -1: never converges, so exactly n_iterations full iterations run
   FB2_TRY(cg_setup(A, dinv ? dinv->d : nullptr, w, b->d, x->d, par, 0.0, -1.0, n_iterations + 1, FB2_STOP_RES_RES));
@@ -790,41 +819,31 @@ extern "C" int fb2_jacobi_setup_multi(int np, fb2_matrix_t* A, fb2_vector_t* din
   return 0;
 }
 
+// the co-resident parts use the work vectors of their own matrices; the shared device state and history are those of the
+// first matrix of the list
 struct MultiWork {
-  std::vector<CgWork> parts;
+  std::vector<CgWork*> parts;
   CgState* st = nullptr;
   double* hist = nullptr;
-  int hist_cap = 0;
 };
-static MultiWork g_mwork;
-static int multi_workspace(const MultiCtx& C, int hist_len) {
-  MultiWork& M = g_mwork;
-  if ((int)M.parts.size() != C.np) {
-    for (CgWork& W : M.parts) { cudaFree(W.r); cudaFree(W.p); cudaFree(W.Ap); }
-    M.parts.assign(C.np, CgWork());
-  }
+static int multi_workspace(const MultiCtx& C, int hist_len, MultiWork& M) {
+  M.parts.resize(C.np);
   for (int i = 0; i < C.np; ++i) {
-    CgWork& W = M.parts[i];
-    if (W.n != C.A[i]->n) {
-      cudaFree(W.r); cudaFree(W.p); cudaFree(W.Ap);
-      const i64 n = C.A[i]->n;
-      FB2_TRY(fb2_dalloc(&W.r, (size_t)n)); FB2_TRY(fb2_dalloc(&W.p, (size_t)n)); FB2_TRY(fb2_dalloc(&W.Ap, (size_t)n));
-      W.n = n;
-    }
+    FB2_CHECK(!fb2_ils_has_initial_solution(C.A[i]), "the multi-part PCG starts from zero: clear the initial solution of the parts");
+    FB2_TRY(cg_workspace(C.A[i], i == 0 ? hist_len : 0));
+    M.parts[i] = &work_of(C.A[i]);
   }
-  if (!M.st) FB2_TRY(fb2_dalloc(&M.st, 1));
-  if (hist_len > M.hist_cap) { cudaFree(M.hist); FB2_TRY(fb2_dalloc(&M.hist, (size_t)hist_len)); M.hist_cap = hist_len; }
+  M.st = M.parts[0]->st; M.hist = M.parts[0]->hist;
   return 0;
 }
 
-static int multi_cg_setup(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_t* b, fb2_vector_t* x, double rtol, double atol,
-                          int maxit, int stop) {
+static int multi_cg_setup(const MultiCtx& C, MultiWork& M, fb2_vector_t* dinv, fb2_vector_t* b, fb2_vector_t* x, double rtol,
+                          double atol, int maxit, int stop) {
   cudaStream_t s = fb2_stream();
-  MultiWork& M = g_mwork;
   const int np = C.np;
   double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;      // [4][np] partial dots, then 4 sums at d_tmp + 4 np
   for (int i = 0; i < np; ++i) {
-    CgWork& W = M.parts[i];
+    CgWork& W = *M.parts[i];
     const i64 n = W.n;
     const double* di = dinv ? dinv[i]->d : nullptr;
     k_init<<<vec_grid(n), 256, 0, s>>>(x[i]->d, 0.0, n);
@@ -861,9 +880,9 @@ static int multi_cg_setup(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_t* b
 }
 
 // one PCG iteration over all co-resident parts (overlapped par apply, see cg_enqueue_iteration)
-static int multi_cg_iteration(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_t* x, double* hist, cudaEvent_t ev0, cudaEvent_t ev1) {
+static int multi_cg_iteration(const MultiCtx& C, MultiWork& M, fb2_vector_t* dinv, fb2_vector_t* x, double* hist, cudaEvent_t ev0,
+                              cudaEvent_t ev1) {
   cudaStream_t s = fb2_stream(), cs = fb2_comm_stream();
-  MultiWork& M = g_mwork;
   const int np = C.np;
   double* part = fb2_scratch_partials();
   static cudaEvent_t ev_itf = nullptr, ev_halo = nullptr;
@@ -872,7 +891,7 @@ static int multi_cg_iteration(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_
   std::vector<i64> t_itf(np), row_itf(np);
   std::vector<double*> aps(np);
   for (int i = 0; i < np; ++i) {
-    CgWork& W = M.parts[i];
+    CgWork& W = *M.parts[i];
     FB2_TRY(fb2_spmv_interface_split(C.A[i], C.A[i]->s->n_interior, &t_itf[i], &row_itf[i]));
     FB2_TRY(fb2_spmv_stream_range(C.A[i], W.p, W.Ap, false, &M.st->done, t_itf[i], C.A[i]->spmv_ntiles, 0, nullptr, nullptr));
     aps[i] = W.Ap;
@@ -883,7 +902,7 @@ static int multi_cg_iteration(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_
   FB2_CUDA(cudaEventRecord(ev_halo, cs));
   int off = 0;
   for (int i = 0; i < np; ++i) {
-    CgWork& W = M.parts[i];
+    CgWork& W = *M.parts[i];
     int g = 0;
     FB2_TRY(fb2_spmv_stream_range(C.A[i], W.p, W.Ap, true, &M.st->done, 0, t_itf[i], g_par_chunk, part + off, &g));
     off += g;
@@ -891,7 +910,7 @@ static int multi_cg_iteration(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_
   FB2_CUDA(cudaStreamWaitEvent(s, ev_halo, 0));
   if (ev1) cudaEventRecord(ev1, s);
   for (int i = 0; i < np; ++i) {
-    CgWork& W = M.parts[i];
+    CgWork& W = *M.parts[i];
     const i64 n = W.n, r0 = row_itf[i];
     if (r0 < n) {
       int gd = reduce_grid(n - r0);
@@ -905,7 +924,7 @@ static int multi_cg_iteration(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_
   if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(&M.st->App, 1));
   int off2 = 0;
   for (int i = 0; i < np; ++i) {
-    CgWork& W = M.parts[i];
+    CgWork& W = *M.parts[i];
     const int g2 = reduce_grid(W.n);
     k_cg_update_xr<<<g2, 256, 0, s>>>(W.n, M.st, W.p, W.Ap, dinv ? dinv[i]->d : nullptr, C.w[i], x[i]->d, W.r, part + off2, FB2_MAX_PARTIALS);
     off2 += g2;
@@ -914,7 +933,7 @@ static int multi_cg_iteration(const MultiCtx& C, fb2_vector_t* dinv, fb2_vector_
   if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(&M.st->rr, 4));
   k_cg_scalars<<<1, 1, 0, s>>>(M.st, hist);
   for (int i = 0; i < np; ++i) {
-    CgWork& W = M.parts[i];
+    CgWork& W = *M.parts[i];
     k_cg_update_p<<<vec_grid(W.n), 256, 0, s>>>(W.n, M.st, W.r, dinv ? dinv[i]->d : nullptr, W.p);
   }
   FB2_CUDA(cudaGetLastError());
@@ -931,9 +950,9 @@ extern "C" int fb2_pcg_solve_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, 
   FB2_CHECK(prm->stopping_criterium >= FB2_STOP_RES_RES && prm->stopping_criterium <= FB2_STOP_DELTA_DELTA_AND_RES_RHS, "unknown stopping criterium");
   const int maxit = prm->max_num_iterations;
   const bool track = history != nullptr;
-  FB2_TRY(multi_workspace(C, track ? maxit : 0));
-  cudaStream_t s = fb2_stream();
-  FB2_TRY(multi_cg_setup(C, dinv, b, x, prm->rtol, prm->atol, maxit, prm->stopping_criterium));
+  MultiWork M;
+  FB2_TRY(multi_workspace(C, track ? maxit : 0, M));
+  FB2_TRY(multi_cg_setup(C, M, dinv, b, x, prm->rtol, prm->atol, maxit, prm->stopping_criterium));
   const int every = prm->check_every > 0 ? prm->check_every : 8;
   CgState h;
   memset(&h, 0, sizeof(h));
@@ -941,13 +960,13 @@ extern "C" int fb2_pcg_solve_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, 
   while (launched < maxit) {
     int chunk = every;
     if (launched + chunk > maxit) chunk = maxit - launched;
-    for (int k = 0; k < chunk; ++k) FB2_TRY(multi_cg_iteration(C, dinv, x, track ? g_mwork.hist : nullptr, nullptr, nullptr));
+    for (int k = 0; k < chunk; ++k) FB2_TRY(multi_cg_iteration(C, M, dinv, x, track ? M.hist : nullptr, nullptr, nullptr));
     launched += chunk;
-    FB2_CUDA(fb2_memcpy(&h, g_mwork.st, sizeof(CgState), cudaMemcpyDeviceToHost));
+    FB2_CUDA(fb2_memcpy(&h, M.st, sizeof(CgState), cudaMemcpyDeviceToHost));
     if (h.done) break;
   }
   *num_iterations = h.iter; *did_converge = h.converged; *error_estimate = h.err;
-  if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, g_mwork.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
+  if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, M.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
   return 0;
 }
 
@@ -956,13 +975,14 @@ extern "C" int fb2_pcg_iterate_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv
   FB2_CHECK(b && x && n_iterations > 0, "bad argument");
   MultiCtx C;
   FB2_TRY(multi_ctx(np, A, C));
-  FB2_TRY(multi_workspace(C, 0));
+  MultiWork M;
+  FB2_TRY(multi_workspace(C, 0, M));
   cudaStream_t s = fb2_stream();
-  FB2_TRY(multi_cg_setup(C, dinv, b, x, 0.0, -1.0, n_iterations + 1, FB2_STOP_RES_RES));
+  FB2_TRY(multi_cg_setup(C, M, dinv, b, x, 0.0, -1.0, n_iterations + 1, FB2_STOP_RES_RES));
   std::vector<cudaEvent_t> ev(2 * (size_t)n_iterations + 2);
   for (auto& e : ev) cudaEventCreate(&e);
   cudaEventRecord(ev[2 * n_iterations], s);
-  for (int k = 0; k < n_iterations; ++k) FB2_TRY(multi_cg_iteration(C, dinv, x, nullptr, ev[2 * k], ev[2 * k + 1]));
+  for (int k = 0; k < n_iterations; ++k) FB2_TRY(multi_cg_iteration(C, M, dinv, x, nullptr, ev[2 * k], ev[2 * k + 1]));
   cudaEventRecord(ev[2 * n_iterations + 1], s);
   FB2_CUDA(cudaStreamSynchronize(s));
   float ms = 0, acc = 0;

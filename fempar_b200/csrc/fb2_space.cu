@@ -763,6 +763,7 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
 }
 extern "C" int fb2_csr_destroy(fb2_matrix_t A) {
   if (!A) return 0;
+  fb2_solver_ws_free(A);
   cudaFree(A->d_irp); cudaFree(A->d_ja); cudaFree(A->d_val); cudaFree(A->d_cell_tab); cudaFree(A->d_tabs); cudaFree(A->d_tile_row); cudaFree(A->d_tile_nrows);
   cudaFree(A->d_idx16); cudaFree(A->d_dict); cudaFree(A->d_dict_ptr);
   cudaFree(A->d_tile_class); cudaFree(A->d_cls_desc); cudaFree(A->d_cls_idx);

@@ -227,6 +227,9 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
     const i64 e0a = s_e0a[s];
     double acc = 0.0;
     const bool live = row < s_nr[s];
+    // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
+    double xrow = 0.0;
+    if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
     if (live) {
       const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
       int k = b + sub;
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
     for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
     if (sub == 0 && live) {
       y[r0 + row] = acc;
-      if (FUSE_DOT) dacc += acc * x[r0 + row];
+      if (FUSE_DOT) dacc += acc * xrow;
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty_bar[s]);
@@ -725,6 +728,20 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   return 0;
 }
 
+// drops the tile table and the pattern classes: the next apply prepares again (with the FB2_SPMV_* environment of that
+// moment).  Used by the tuning sweeps under profiles/.
+extern "C" int fb2_csr_spmv_reset(fb2_matrix_t A) {
+  FB2_CHECK(A, "null matrix");
+  FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  cudaFree(A->d_tile_row); cudaFree(A->d_tile_nrows); cudaFree(A->d_tile_class); cudaFree(A->d_cls_desc); cudaFree(A->d_cls_idx);
+  cudaFree(A->d_idx16); cudaFree(A->d_dict); cudaFree(A->d_dict_ptr);
+  A->d_tile_row = nullptr; A->d_tile_nrows = nullptr; A->d_tile_class = nullptr; A->d_cls_desc = nullptr; A->d_cls_idx = nullptr;
+  A->d_idx16 = nullptr; A->d_dict = nullptr; A->d_dict_ptr = nullptr;
+  A->spmv_R = A->spmv_cap = A->spmv_grid = A->spmv_stages = 0; A->spmv_ntiles = 0; A->spmv_smem = 0;
+  A->spmv_comp = 0; A->spmv_cls = 0; A->spmv_ncls = 0; A->spmv_tiles_in_class = 0; A->spmv_t_itf = -1; A->spmv_row_itf = -1;
+  return 0;
+}
+
 int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, i64 t0, i64 t1,
                           int chunk, double* partials, int* grid_out) {
   FB2_TRY(fb2_spmv_prepare(A));
@@ -757,7 +774,7 @@ int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, 
   FB2_TRY(fb2_spmv_prepare(A));
   // short-lived CTAs over 32 consecutive tiles beat persistent striding CTAs (dynamic balance, contiguous streams per CTA):
   // profiles/r1_spmv_chunk_sweep.txt
-  static int chunk = getenv("FB2_SPMV_CHUNK") ? atoi(getenv("FB2_SPMV_CHUNK")) : 32;
+  const int chunk = getenv("FB2_SPMV_CHUNK") ? atoi(getenv("FB2_SPMV_CHUNK")) : 32;
   return fb2_spmv_stream_range(A, x, y, fuse_dot, done_flag, 0, A->spmv_ntiles, chunk, fb2_scratch_partials(), grid_out);
 }
 

@@ -190,14 +190,21 @@ int fb2_vec_comm(fb2_vector_t v);                          /* par_scalar_array%c
 /* ---- Jacobi (jacobi_preconditioner.f90:356-412) and CG (cg.f90:101-238) ---------------------- */
 /* dinv = 1 ./ comm(diag(A)) */
 int fb2_jacobi_setup(fb2_matrix_t A, fb2_vector_t dinv);
-/* Solve A x = b from the initial solution (zero by default, see fb2_ils_set_initial_solution).  dinv == NULL -> identity preconditioner.  history may be NULL; else
+/* Solve A x = b from the initial solution (zero by default, see fb2_csr_set_initial_solution).  dinv == NULL -> identity preconditioner.  history may be NULL; else
  * must hold max_num_iterations doubles.  num_iterations counts loop SpMVs exactly like cg.f90.      */
 int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_t x, const fb2_ils_params_t* params,
                   int* num_iterations, int* did_converge, double* error_estimate, double* history);
-/* base_iterative_linear_solver_t%set_initial_solution (base_iterative_linear_solver.f90:340-360): the solves that follow
- * (fb2_pcg_solve, fb2_pcg_solve_host, fb2_ils_solve) start from a copy of x0 instead of zero; NULL = back to zero.  A vector of
- * another size is ignored like the reference ignores one outside range(A).  The *_multi entry points always start from zero. */
-int fb2_ils_set_initial_solution(fb2_vector_t x0);
+/* base_iterative_linear_solver_t%set_initial_solution (base_iterative_linear_solver.f90:340-360): the solves ON THIS OPERATOR
+ * that follow (fb2_pcg_solve, fb2_pcg_solve_host, fb2_ils_solve) start from a copy of x0 instead of zero; NULL = back to zero.
+ * The copy, like the Krylov work vectors, the device-resident convergence state and the staging vectors of the host-buffer
+ * entry point, belongs to the matrix handle: solves on different operators never share state (re-entrant across handles).
+ * A vector of another size is ignored like the reference ignores one outside range(A).  The *_multi entry points start from
+ * zero and reject parts with an initial solution set. */
+int fb2_csr_set_initial_solution(fb2_matrix_t A, fb2_vector_t x0);
+/* drops the SpMV tile table / pattern classes of the matrix; the next apply prepares them again (tuning sweeps) */
+int fb2_csr_spmv_reset(fb2_matrix_t A);
+/* releases the solver workspace of the operator early (fb2_csr_destroy does it too) */
+int fb2_csr_free_solver_workspace(fb2_matrix_t A);
 /* the same through HOST buffers (what iterative_linear_solver%apply sees from Fortran arrays):
  * H2D of b, solve, D2H of x inside the call. */
 int fb2_pcg_solve_host(fb2_matrix_t A, fb2_vector_t dinv, const double* b_host, double* x_host,

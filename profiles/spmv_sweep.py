@@ -1,0 +1,39 @@
+"""SpMV tile-geometry sweep on one matrix (profiles/): for every (R, STAGES, CAP, CHUNK) the tile table and pattern classes are
+rebuilt (fb2_csr_spmv_reset) and the SpMV launches inside 12 PCG iterations are timed with CUDA events (fb2_pcg_iterate).
+usage: python profiles/spmv_sweep.py [cells] [order]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import fempar_b200 as fb  # noqa: E402
+
+cells = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+order = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+fb.init(0)
+L = fb._lib.lib()
+s = fb.FeSpace([cells] * 3, order=order)
+op = fb.FeAffineOperator()
+op.create(fb.csr_format, [False], [True], [1], s, fb.DiscreteIntegration(fb.poisson, fb.func_linear))
+op.compute()
+A = op.get_matrix()
+M = fb.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG"); ils.set_operators(A, M)
+x = s.create_dof_values()
+bytes_alg = A.nnz * 12 + A.num_rows * 24
+combos = [(32, 2, 2304, 32), (32, 3, 2304, 32), (32, 2, 2304, 64), (16, 2, 1152, 64), (16, 3, 1152, 64), (16, 4, 1152, 64),
+          (16, 6, 1152, 64), (16, 4, 1152, 128), (8, 4, 576, 128), (8, 8, 576, 128), (64, 2, 4608, 16), (32, 4, 2304, 32)]
+if order != 2:
+    combos = [(16, 2, 2304, 32), (16, 3, 2304, 32), (8, 4, 1152, 64), (8, 6, 1152, 64), (16, 4, 2304, 32)]
+for R, st, cap, chunk in combos:
+    os.environ["FB2_SPMV_R"], os.environ["FB2_SPMV_STAGES"], os.environ["FB2_SPMV_CAP"], os.environ["FB2_SPMV_CHUNK"] = \
+        str(R), str(st), str(cap), str(chunk)
+    try:
+        fb._lib.check(L.fb2_csr_spmv_reset(A.h))
+        ils.iterate(op.get_translation(), x, 3)
+        t, ts = ils.iterate(op.get_translation(), x, 12)
+        ms = ts / 12
+        print("R=%-3d stages=%d cap=%-5d chunk=%-4d  spmv %.3f ms  %.0f GB/s algorithmic  tiles_in_class %.0f / %.0f  ctas/sm %.0f" % (
+            R, st, cap, chunk, ms, bytes_alg / ms / 1e6, op.last_phase_ms("spmv_tiles_in_class"), op.last_phase_ms("spmv_tiles"),
+            op.last_phase_ms("spmv_ctas_per_sm")), flush=True)
+    except Exception as e:   # a geometry that does not fit is reported, not fatal
+        print("R=%d stages=%d cap=%d chunk=%d: %s" % (R, st, cap, chunk, e), flush=True)
