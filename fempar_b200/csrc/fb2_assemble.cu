@@ -237,7 +237,8 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   fb2_record_phase("integrate", ms);
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   // par: assemble the RHS across parts (par_sparse_assembler.f90:171-176)
-  if (s->imp && fb2_comm_active()) FB2_TRY(fb2_import_exchange(s->imp, rhs->d));
+  // (with several sub-domains per process the caller assembles the RHS of all co-resident parts with fb2_vec_comm_multi)
+  if (s->imp && fb2_comm_active() && fb2_comm_parts_per_rank() == 1) FB2_TRY(fb2_import_exchange(s->imp, rhs->d));
   return 0;
 }
 

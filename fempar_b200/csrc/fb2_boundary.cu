@@ -109,7 +109,9 @@ extern "C" int fb2_csr_create_from_host(fb2_matrix_t* out, fb2_space_t space, in
   int *d_bad, h_bad = 0;
   FB2_TRY(fb2_dalloc(&d_bad, 1));
   FB2_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
-  if (n) k_check_csr<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, A->d_irp, A->d_ja, n + (space->n_free_ghost > 0 ? space->n_free_ghost : 0), d_bad);
+  if (n) // the local matrix of the reference is square over the local DOFs (every vector has n entries): columns beyond n would make
+  // the SpMV kernels gather past the end of x
+  k_check_csr<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, A->d_irp, A->d_ja, n, d_bad);
   FB2_CUDA(fb2_memcpy(&h_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost));
   cudaFree(d_bad); cudaFree(d_irp32);
   if (h_bad) { fb2_csr_destroy(A); FB2_CHECK(false, "fb2_csr_create_from_host: irp not monotone or ja not strictly ascending / out of range"); }
@@ -136,7 +138,7 @@ extern "C" int fb2_csr_initialize_values(fb2_matrix_t A, double alpha) {
 // (sbm_fe_cell_iterator.i90:1610-1637) is applied first: elvec -= elmat(:,j) * g(-id_j) for negative column ids.
 // ------------------------------------------------------------------------------------------
 __global__ void k_assemble_batch(int ncell, int nd, const int* __restrict__ dofs, const double* __restrict__ elmat,
-                                 const double* __restrict__ elvec, const double* __restrict__ fixed, i64 n, int sym,
+                                 const double* __restrict__ elvec, const double* __restrict__ fixed, i64 num_fixed, i64 n, int sym,
                                  const i64* __restrict__ irp, const int* __restrict__ ja, double* val, double* rhs, int* missing) {
   const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int c = blockIdx.x * warps + w; c < ncell; c += gridDim.x * warps) {
@@ -148,7 +150,13 @@ __global__ void k_assemble_batch(int ncell, int nd, const int* __restrict__ dofs
         const int gi = g[i], gj = g[j];
         if (gi < 1 || gi > n) continue;
         const double v = E[e];
-        if (gj < 0) { if (fixed && rhs) atomicAdd(&rhs[gi - 1], -v * fixed[-gj - 1]); continue; }
+        if (gj < 0) {
+          if (fixed && rhs) {
+            if (-(i64)gj > num_fixed) *missing = 2;           // Dirichlet id beyond the fixed values handed over
+            else atomicAdd(&rhs[gi - 1], -v * fixed[-gj - 1]);
+          }
+          continue;
+        }
         if (gj < 1 || gj > n || (sym && gi > gj)) continue;
         const i64 b = irp[gi - 1], end = irp[gi];
         i64 lo = b, hi = end;
@@ -184,11 +192,12 @@ extern "C" int fb2_assemble_batch(fb2_matrix_t A, fb2_vector_t rhs, int32_t num_
   }
   int blocks = (num_cells + 7) / 8;
   if (blocks > fb2_num_sms() * 8) blocks = fb2_num_sms() * 8;
-  k_assemble_batch<<<blocks, 256, 0, st>>>(num_cells, num_dofs_per_cell, d_dofs, d_mat, d_vec, d_fix, A->n, A->sym, A->d_irp,
+  k_assemble_batch<<<blocks, 256, 0, st>>>(num_cells, num_dofs_per_cell, d_dofs, d_mat, d_vec, d_fix, d_fix ? num_fixed : 0, A->n, A->sym, A->d_irp,
                                            A->d_ja, A->d_val, rhs ? rhs->d : nullptr, d_missing);
   FB2_CUDA(cudaGetLastError());
   FB2_CUDA(fb2_memcpy(&h_missing, d_missing, sizeof(int), cudaMemcpyDeviceToHost));
   cudaFree(d_dofs); cudaFree(d_missing); cudaFree(d_mat); cudaFree(d_vec); cudaFree(d_fix);
+  FB2_CHECK(h_missing != 2, "fb2_assemble_batch: a strong-Dirichlet id is beyond num_fixed");
   FB2_CHECK(h_missing == 0, "fb2_assemble_batch: an element entry has no slot in the CSR graph");
   return 0;
 }

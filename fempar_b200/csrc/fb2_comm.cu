@@ -145,7 +145,10 @@ static int exchange_stage(fb2_import_s* imp, double* x, bool reverse, bool add, 
 //  stage 1: non-owners send their partial sums, the owner receives and adds   (rcv side = owner)
 //  stage 2: the owner sends the total, non-owners receive and overwrite
 int fb2_import_exchange_on(fb2_import_s* imp, double* d_vec, cudaStream_t stream) {
-  if (!g_comm || !imp || g_parts_per_rank > 1) return 0;
+  if (!g_comm || !imp) return 0;
+  // several sub-domains per process: a single part cannot exchange on its own (its neighbours may live in this process);
+  // the *_multi entry points run the exchange collectively.  Returning 0 here would leave interface values unassembled.
+  FB2_CHECK(g_parts_per_rank == 1, "single-part par entry point called with several sub-domains per rank: use the *_multi entry points");
   FB2_TRY(exchange_stage(imp, d_vec, false, true, stream));
   FB2_TRY(exchange_stage(imp, d_vec, true, false, stream));
   return 0;

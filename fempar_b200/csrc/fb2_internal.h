@@ -129,7 +129,7 @@ struct fb2_matrix_s {
   i64 n_fast_cells = 0, n_slow_rows = 0;
   int n_slow_cells = 0;
   // SpMV tile geometry (fb2_spmv.cu)
-  int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0;
+  int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0, spmv_nc = 0;   // nc: consumer threads per CTA
   i64 spmv_ntiles = 0;
   i64* d_tile_row = nullptr;              // first row of every tile
   unsigned char* d_tile_nrows = nullptr;  // rows in the tile (<= spmv_R)

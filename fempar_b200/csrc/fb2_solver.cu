@@ -282,6 +282,8 @@ static const double* weight_of(fb2_vector_t v) {
 }
 extern "C" int fb2_vec_dot(fb2_vector_t x, fb2_vector_t y, double* result) {
   FB2_CHECK(x->n == y->n, "size mismatch");
+  FB2_CHECK(!(weight_of(x) && fb2_comm_active() && fb2_comm_parts_per_rank() > 1),
+            "fb2_vec_dot on one of several sub-domains per rank: use fb2_vec_dot_multi");
   double* d_res = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
   FB2_TRY(fb2_dot_device(x->d, y->d, weight_of(x), x->n, d_res));
   if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(d_res, 1));

@@ -36,10 +36,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+// wait with a suspend-time hint: the thread may be parked by the hardware instead of spinning through the issue slots
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAITP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n"
+      "@P1 bra DONEP;\n"
+      "bra LAB_WAITP;\n"
+      "DONEP:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity), "r"(20000u)
+      : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-#define SPMV_CONSUMERS 256
-#define SPMV_THREADS (SPMV_CONSUMERS + 32)
 #define SPMV_MAX_STAGES 8
 #define SPMV_DS 512   // compressed variant: distinct columns of a tile staged in shared memory (larger dictionaries stay global)
 
@@ -74,8 +86,11 @@ struct SpmvClassDesc {
 // fb2_spmv_compress): 10 B + ~0.5 B of dictionary per non-zero instead of 12 B.  `ja` then points at the uint16 stream, the
 // element range of a tile is aligned to 8 entries (16-byte bulk copies), and the products are formed in the same order, so y
 // is bit-identical to the uncompressed kernel.
-template <bool FUSE_DOT, bool COMP>
-__global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i64* __restrict__ irp, const void* __restrict__ ja_any,
+// NC consumer threads (256 or 128) + the producer warp.  With pattern-class tiles the consumers read shared memory only and the
+// per-tile bookkeeping of every warp (barrier wait, row bounds, reduction, release: ~150 instructions, half of the stall
+// samples in the ncu capture of round 2) is what limits them: 4 warps with 16 entries per lane and tile instead of 8 with 8.
+template <bool FUSE_DOT, bool COMP, int NC>
+__global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __restrict__ irp, const void* __restrict__ ja_any,
                                                              const double* __restrict__ val, const double* __restrict__ x,
                                                              double* __restrict__ y, double* partials, const int* done_flag,
                                                              int R, int cap, i64 ntiles, int STAGES,
@@ -109,16 +124,16 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
   const i64 t_step = chunk ? 1 : (i64)gridDim.x;
   const i64 t_end = chunk ? min(t_first + chunk, ntiles) : ntiles;
   if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], SPMV_CONSUMERS / 32); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NC / 32); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
 
-  if (tid >= SPMV_CONSUMERS) {
+  if (tid >= NC) {
     // ---------------- producer warp ----------------
     // lane 0 keeps the tile bookkeeping and issues the val / ja (or class index table) / irp copies; for a class tile the
     // other lanes issue one x-segment copy each
-    const int plane = tid - SPMV_CONSUMERS;
+    const int plane = tid - NC;
     i64 t = t_first;
     i64 e0 = 0, e1 = 0, r0 = 0, d0 = 0, d1 = 0;
     int nr = 0, cls = SPMV_NOCLASS;
@@ -140,7 +155,7 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
           if (COMP) { nd0 = dict_ptr[tn]; nd1 = dict_ptr[tn + 1]; }
           if (!COMP && tile_class) ncls = tile_class[tn];
         }
-        mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+        mbar_wait_parked(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
         const i64 e0a = e0 & ~AL;
         const uint32_t cnt4 = (uint32_t)((e1 - e0a + AL) & ~AL);
         // a dictionary that does not fit the region is not staged: the consumers then go through it in global memory
@@ -182,7 +197,7 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
     return;
   }
   // ---------------- consumer warps ----------------
-  const int TPR = SPMV_CONSUMERS / R;   // lanes per row: 4..32, power of two
+  const int TPR = NC / R;   // lanes per row: 4..32, power of two
   const int row = tid / TPR, sub = tid - row * TPR;
   const int lane = tid & 31, w = tid >> 5;
   double dacc = 0.0;
@@ -208,12 +223,12 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
       big = nd > SPMV_DS;
       dict_g = dict + s_d0[s];
       if (!big) {
-        static_assert(SPMV_DS <= 2 * SPMV_CONSUMERS, "two dictionary entries per consumer thread");
-        const int c0 = tid < nd ? sd[tid] : -1, c1 = tid + SPMV_CONSUMERS < nd ? sd[tid + SPMV_CONSUMERS] : -1;
-        asm volatile("bar.sync 2, %0;" ::"r"(SPMV_CONSUMERS) : "memory");   // every entry is in a register before the overwrite
+        static_assert(!COMP || SPMV_DS <= 2 * NC, "two dictionary entries per consumer thread");
+        const int c0 = tid < nd ? sd[tid] : -1, c1 = tid + NC < nd ? sd[tid + NC] : -1;
+        asm volatile("bar.sync 2, %0;" ::"r"(NC) : "memory");   // every entry is in a register before the overwrite
         if (c0 >= 0) xs[tid] = x[c0];
-        if (c1 >= 0) xs[tid + SPMV_CONSUMERS] = x[c1];
-        asm volatile("bar.sync 2, %0;" ::"r"(SPMV_CONSUMERS) : "memory");
+        if (c1 >= 0) xs[tid + NC] = x[c1];
+        asm volatile("bar.sync 2, %0;" ::"r"(NC) : "memory");
       }
     }
     // class tile: uint16 window positions where ja would be, the x window right behind them
@@ -230,7 +245,12 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
     // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
     double xrow = 0.0;
     if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
-    if (live) {
+    if (live && in_class) {
+      // shared memory only: a plain strided loop (no gather latency to batch against)
+      const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
+#pragma unroll 4
+      for (int k = b + sub; k < e; k += TPR) acc += sv[k] * sxw[sj16[k]];
+    } else if (live) {
       const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
       int k = b + sub;
       for (; k + 3 * TPR < e; k += 4 * TPR) {
@@ -255,6 +275,9 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
       y[r0 + row] = acc;
       if (FUSE_DOT) dacc += acc * xrow;
     }
+    // COMP: the consumers wrote xs[] through the generic proxy into a region the producer's next bulk copy (async proxy)
+    // overwrites: order the two proxies before releasing the stage
+    if (COMP) fence_proxy_async();
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty_bar[s]);
   }
@@ -262,10 +285,10 @@ __global__ void __launch_bounds__(SPMV_THREADS, 4) k_spmv_stream(i64 n, const i6
     // deterministic block sum over the consumer warps (named barrier 1: the producer warp has exited)
     for (int o = 16; o > 0; o >>= 1) dacc += __shfl_down_sync(0xffffffffu, dacc, o);
     if (lane == 0) s_red[w] = dacc;
-    asm volatile("bar.sync 1, %0;" ::"r"(SPMV_CONSUMERS) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"r"(NC) : "memory");
     if (tid == 0) {
       double r = 0.0;
-      for (int i = 0; i < SPMV_CONSUMERS / 32; ++i) r += s_red[i];
+      for (int i = 0; i < NC / 32; ++i) r += s_red[i];
       partials[blockIdx.x] = r;
     }
   }
@@ -416,8 +439,9 @@ static int spmv_compress(fb2_matrix_s* A, int capbuf, int R, int STAGES) {
   k_tile_dict<true><<<(unsigned)nt, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, nullptr, nullptr, A->d_dict_ptr, A->d_dict, A->d_idx16);
   FB2_CUDA(cudaGetLastError());
   A->spmv_dcap = dcap; A->spmv_smem_comp = smem;
-  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // (the attribute is per kernel, not per matrix: always the largest value any matrix may ask for)
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, true, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   cudaEventRecord(e1, st);
   FB2_CUDA(cudaStreamSynchronize(st));
   float ms = 0;
@@ -713,10 +737,20 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   size_t smem = stage * STAGES;
   FB2_CHECK(smem <= 200 * 1024, "SpMV tile does not fit in shared memory");
   A->spmv_R = R; A->spmv_cap = capbuf; A->spmv_ntiles = ntiles; A->spmv_smem = smem; A->spmv_stages = STAGES;
-  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // consumer threads: 128 (4 warps) when R rows leave at least 4 lanes per row, else 256; FB2_SPMV_CONSUMERS overrides
+  int nc = 256;
+  if (getenv("FB2_SPMV_CONSUMERS")) nc = atoi(getenv("FB2_SPMV_CONSUMERS"));
+  if (g_compress) nc = 256;   // the dictionary variant stages two entries per consumer thread
+  FB2_CHECK((nc == 128 || nc == 256) && nc / R >= 1 && nc / R <= 32, "bad FB2_SPMV_CONSUMERS");
+  A->spmv_nc = nc;
+  // the attribute is per kernel, not per matrix (two matrices with different R must not lower each other's limit)
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, false, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, false, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   int bps = 0;
-  FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_stream<true, false>, SPMV_THREADS, smem));
+  if (nc == 128) FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_stream<true, false, 128>, nc + 32, smem));
+  else FB2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_stream<true, false, 256>, nc + 32, smem));
   if (bps < 1) bps = 1;
   i64 grid = (i64)fb2_num_sms() * bps;
   if (grid > ntiles) grid = ntiles;
@@ -738,7 +772,7 @@ extern "C" int fb2_csr_spmv_reset(fb2_matrix_t A) {
   A->d_tile_row = nullptr; A->d_tile_nrows = nullptr; A->d_tile_class = nullptr; A->d_cls_desc = nullptr; A->d_cls_idx = nullptr;
   A->d_idx16 = nullptr; A->d_dict = nullptr; A->d_dict_ptr = nullptr;
   A->spmv_R = A->spmv_cap = A->spmv_grid = A->spmv_stages = 0; A->spmv_ntiles = 0; A->spmv_smem = 0;
-  A->spmv_comp = 0; A->spmv_cls = 0; A->spmv_ncls = 0; A->spmv_tiles_in_class = 0; A->spmv_t_itf = -1; A->spmv_row_itf = -1;
+  A->spmv_nc = 0; A->spmv_comp = 0; A->spmv_cls = 0; A->spmv_ncls = 0; A->spmv_tiles_in_class = 0; A->spmv_t_itf = -1; A->spmv_row_itf = -1;
   return 0;
 }
 
@@ -752,11 +786,16 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
   i64 grid = chunk ? (nt + chunk - 1) / chunk : (nt < A->spmv_grid ? nt : (i64)A->spmv_grid);
   // class tiles bulk-copy segments of x: they need a 16-byte aligned x (always true for library vectors, not for views)
   const unsigned char* tcls = (A->spmv_cls == 1 && (((uintptr_t)x) & 15) == 0) ? A->d_tile_class + t0 : nullptr;
-#define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                                   \
-  k_spmv_stream<FD, CP><<<(unsigned)grid, SPMV_THREADS, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
+#define SPMV_LAUNCH_NC(FD, CP, NCT, JA, SMEM, DICT, DPTR, DCAP)                                                                   \
+  k_spmv_stream<FD, CP, NCT><<<(unsigned)grid, NCT + 32, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
                                                                     done_flag, A->spmv_R, A->spmv_cap, nt, A->spmv_stages,   \
                                                                     A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP, \
                                                                     CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx)
+#define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                   \
+  do {                                                                                                    \
+    if (!CP && A->spmv_nc == 128) SPMV_LAUNCH_NC(FD, false, 128, JA, SMEM, DICT, DPTR, DCAP);             \
+    else SPMV_LAUNCH_NC(FD, CP, 256, JA, SMEM, DICT, DPTR, DCAP);                                         \
+  } while (0)
   if (A->spmv_comp == 1) {
     if (fuse_dot) SPMV_LAUNCH(true, true, A->d_idx16, A->spmv_smem_comp, A->d_dict, A->d_dict_ptr + t0, A->spmv_dcap);
     else SPMV_LAUNCH(false, true, A->d_idx16, A->spmv_smem_comp, A->d_dict, A->d_dict_ptr + t0, A->spmv_dcap);
@@ -765,6 +804,7 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
     else SPMV_LAUNCH(false, false, A->d_ja, A->spmv_smem, nullptr, nullptr, 0);
   }
 #undef SPMV_LAUNCH
+#undef SPMV_LAUNCH_NC
   FB2_CUDA(cudaGetLastError());
   if (grid_out) *grid_out = (int)grid;
   return 0;

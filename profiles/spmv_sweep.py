@@ -20,18 +20,21 @@ M = fb.JacobiPreconditioner(); M.create(op); M.numerical_setup()
 ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG"); ils.set_operators(A, M)
 x = s.create_dof_values()
 bytes_alg = A.nnz * 12 + A.num_rows * 24
-combos = [(32, 2, 2304, 32), (32, 3, 2304, 32), (32, 2, 2304, 64), (16, 2, 1152, 64), (16, 3, 1152, 64), (16, 4, 1152, 64),
-          (16, 6, 1152, 64), (16, 4, 1152, 128), (8, 4, 576, 128), (8, 8, 576, 128), (64, 2, 4608, 16), (32, 4, 2304, 32)]
+# (R, STAGES, CAP, CHUNK, CONSUMERS); round-2 call 4 showed 2 stages x 4 CTAs/SM ahead of deeper rings and smaller tiles
+combos = [(32, 2, 2304, 32, 256), (32, 2, 2304, 32, 128), (32, 2, 2304, 64, 128), (32, 2, 2304, 16, 128), (32, 2, 2176, 32, 128),
+          (32, 2, 2304, 32, 256)]
 if order != 2:
-    combos = [(16, 2, 2304, 32), (16, 3, 2304, 32), (8, 4, 1152, 64), (8, 6, 1152, 64), (16, 4, 2304, 32)]
-for R, st, cap, chunk in combos:
+    combos = [(16, 2, 2304, 32, 256), (16, 2, 2304, 32, 128), (16, 2, 2304, 64, 128)]
+for R, st, cap, chunk, nc in combos:
     os.environ["FB2_SPMV_R"], os.environ["FB2_SPMV_STAGES"], os.environ["FB2_SPMV_CAP"], os.environ["FB2_SPMV_CHUNK"] = \
         str(R), str(st), str(cap), str(chunk)
+    os.environ["FB2_SPMV_CONSUMERS"] = str(nc)
     try:
         fb._lib.check(L.fb2_csr_spmv_reset(A.h))
         ils.iterate(op.get_translation(), x, 3)
         t, ts = ils.iterate(op.get_translation(), x, 12)
         ms = ts / 12
+        print("nc=%d " % nc, end="")
         print("R=%-3d stages=%d cap=%-5d chunk=%-4d  spmv %.3f ms  %.0f GB/s algorithmic  tiles_in_class %.0f / %.0f  ctas/sm %.0f" % (
             R, st, cap, chunk, ms, bytes_alg / ms / 1e6, op.last_phase_ms("spmv_tiles_in_class"), op.last_phase_ms("spmv_tiles"),
             op.last_phase_ms("spmv_ctas_per_sm")), flush=True)
