@@ -99,6 +99,7 @@ _SIGS = {
     "fb2_pcg_iterate_multi": [C.c_int, _VP, _VP, _VP, _VP, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)],
     "fb2_pcg_iterate": [_VP, _VP, _VP, _VP, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)],
     "fb2_error_norms": [_VP, _VP, C.c_int, _VP, C.POINTER(C.c_double), C.POINTER(C.c_double)],
+    "fb2_error_norms_all": [_VP, _VP, C.c_int, _VP, C.c_double, _VP],
 }
 EXPORTED_SYMBOLS = sorted(list(_SIGS) + ["fb2_last_error_string", "fb2_version", "fb2_vec_device_ptr"])
 

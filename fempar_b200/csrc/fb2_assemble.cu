@@ -357,14 +357,20 @@ extern "C" int fb2_fe_space_set_source_values(fb2_space_t s, const double* host_
 }
 
 // ------------------------------------------------------------------------------------------
-// error norms (tutorial_01_..._modules.f90:611-661; ErrorNorms/): warp per cell, lanes over q
+// error norms of u - u_h for a scalar field (Integration/ErrorNorms/error_norms.f90:160-221,
+// sbm_error_norms_scalar.i90:114-232; tutorial_01_..._modules.f90:611-661): warp per cell, lanes over q.
+// One pass accumulates the cell contributions of every norm type:
+//   out[0] sum e w (mean)   out[1] sum |e| w (l1)   out[2] sum e^2 w (l2, h1)   out[3] sum |e|^p w (lp, w1p)
+//   out[4] max |e| (linfty, w1infty)   out[5] sum |grad e|^2 w (h1 semi)   out[6] sum (|grad e|^2)^(p/2) w (w1p semi)
+//   out[7] max_k |d_k e| (w1infty semi);   w = detJ * quadrature weight.  Maxima of non-negative doubles are taken on their bit
+//   patterns (monotone), sums with FP64 atomics (order-dependent in the last bits, like the reference's MPI reduction).
 // ------------------------------------------------------------------------------------------
-__global__ void k_error_norms(AsmArgs A, const double* __restrict__ x, int ncells, double* out /*[2]*/) {
+__global__ void k_error_norms(AsmArgs A, const double* __restrict__ x, int ncells, double expo, double* out /*[8]*/) {
   extern __shared__ double sm[];
   const int nq = A.nq, nn = A.nn;
   const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double* w_u = sm + (size_t)w * nn;
-  double e1 = 0.0, e0 = 0.0;
+  double a_mean = 0.0, a_l1 = 0.0, a_l2 = 0.0, a_lp = 0.0, a_max = 0.0, a_h1 = 0.0, a_w1p = 0.0, a_gmax = 0.0;
   for (int ci = blockIdx.x * warps + w; ci < ncells; ci += gridDim.x * warps) {
     int c;
     double X[8][3];
@@ -398,23 +404,41 @@ __global__ void k_error_norms(AsmArgs A, const double* __restrict__ x, int ncell
       for (int i = 0; i < 3; ++i) {
         double gh = inv[i][0] * gr[0] + inv[i][1] * gr[1] + inv[i][2] * gr[2];
         d2 += (gu[i] - gh) * (gu[i] - gh);
+        a_gmax = fmax(a_gmax, fabs(gu[i] - gh));
       }
-      e1 += wd * d2;
-      double du = func_u(A.fn, xq) - uh;
-      e0 += wd * du * du;
+      const double du = func_u(A.fn, xq) - uh;
+      a_mean += wd * du; a_l1 += wd * fabs(du); a_l2 += wd * du * du; a_lp += wd * pow(fabs(du), expo);
+      a_max = fmax(a_max, fabs(du));
+      a_h1 += wd * d2; a_w1p += wd * pow(d2, 0.5 * expo);
     }
     __syncwarp();
   }
   for (int o = 16; o > 0; o >>= 1) {
-    e1 += __shfl_down_sync(0xffffffffu, e1, o);
-    e0 += __shfl_down_sync(0xffffffffu, e0, o);
+    a_mean += __shfl_down_sync(0xffffffffu, a_mean, o); a_l1 += __shfl_down_sync(0xffffffffu, a_l1, o);
+    a_l2 += __shfl_down_sync(0xffffffffu, a_l2, o); a_lp += __shfl_down_sync(0xffffffffu, a_lp, o);
+    a_h1 += __shfl_down_sync(0xffffffffu, a_h1, o); a_w1p += __shfl_down_sync(0xffffffffu, a_w1p, o);
+    a_max = fmax(a_max, __shfl_down_sync(0xffffffffu, a_max, o)); a_gmax = fmax(a_gmax, __shfl_down_sync(0xffffffffu, a_gmax, o));
   }
-  if (lane == 0) { atomicAdd(&out[0], e1); atomicAdd(&out[1], e0); }
+  if (lane == 0) {
+    atomicAdd(&out[0], a_mean); atomicAdd(&out[1], a_l1); atomicAdd(&out[2], a_l2); atomicAdd(&out[3], a_lp);
+    atomicAdd(&out[5], a_h1); atomicAdd(&out[6], a_w1p);
+    atomicMax((unsigned long long*)&out[4], (unsigned long long)__double_as_longlong(a_max));
+    atomicMax((unsigned long long*)&out[7], (unsigned long long)__double_as_longlong(a_gmax));
+  }
 }
 
-extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double* h1_seminorm,
-                               double* l2_norm) {
+int fb2_allreduce_max(double* d_buf, int count);   // fb2_comm.cu
+
+// error_norms_scalar_t%compute for every norm type of error_norms.f90:41-54 that applies to an H1 scalar field.
+// norms[11] = mean, l1, l2, lp, linfty, h1_seminorm, h1, w1p_seminorm, w1p, w1infty_seminorm, w1infty; `exponent` as the
+// optional argument of compute (<= 0: the reference's default 2.0, error_norms.f90:308-331).  finalize_norm (:174-221) is
+// restated as written, including `norm = norm**exponent` for the p-norms.
+extern "C" int fb2_error_norms_all(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double exponent,
+                                   double norms[11]) {
+  FB2_CHECK(s && x && norms, "null argument");
   FB2_CHECK(s->rt.ncomp == 1, "error norms are implemented for scalar fields");
+  FB2_CHECK(s->d_gids != nullptr, "this space has no cell DOF lists (bare space)");
+  const double expo = exponent > 0.0 ? exponent : 2.0;
   AsmArgs a;
   a.g = make_geom(s);
   a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = 1; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
@@ -423,20 +447,43 @@ extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const do
   a.fn = make_func(func, func_params);
   double* d_out = fb2_scratch_partials();
   cudaStream_t st = fb2_stream();
-  FB2_CUDA(cudaMemsetAsync(d_out, 0, 2 * sizeof(double), st));
+  FB2_CUDA(cudaMemsetAsync(d_out, 0, 8 * sizeof(double), st));
   int warps = 4, blocks = fb2_num_sms() * 8;
-  k_error_norms<<<blocks, warps * 32, warps * a.nn * sizeof(double), st>>>(a, x->d, s->m.n_local, d_out);
+  k_error_norms<<<blocks, warps * 32, warps * a.nn * sizeof(double), st>>>(a, x->d, s->m.n_local, expo, d_out);
   FB2_CUDA(cudaGetLastError());
-  double h[2];
-  FB2_CUDA(cudaMemcpyAsync(h, d_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-  FB2_CUDA(cudaStreamSynchronize(st));
+  double h[8];
   if (fb2_comm_active()) {
-    // local cells partition the mesh: plain sum over parts
-    FB2_TRY(fb2_allreduce_sum(d_out, 2));
-    FB2_CUDA(cudaMemcpyAsync(h, d_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-    FB2_CUDA(cudaStreamSynchronize(st));
+    // local cells partition the mesh: l1_sum of the sums, l1_max of the maxima (error_norms.f90:188-207); the two maxima are
+    // moved next to each other for one max-reduction
+    double* d_mx = d_out + 8;
+    FB2_CUDA(cudaMemcpyAsync(d_mx, d_out + 4, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    FB2_CUDA(cudaMemcpyAsync(d_mx + 1, d_out + 7, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    FB2_TRY(fb2_allreduce_sum(d_out, 8));
+    FB2_TRY(fb2_allreduce_max(d_mx, 2));
+    FB2_CUDA(cudaMemcpyAsync(d_out + 4, d_mx, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    FB2_CUDA(cudaMemcpyAsync(d_out + 7, d_mx + 1, sizeof(double), cudaMemcpyDeviceToDevice, st));
   }
-  *h1_seminorm = sqrt(h[0]);
-  *l2_norm = sqrt(h[1]);
+  FB2_CUDA(cudaMemcpyAsync(h, d_out, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  FB2_CUDA(cudaStreamSynchronize(st));
+  norms[0] = h[0];                          // mean_norm
+  norms[1] = h[1];                          // l1_norm
+  norms[2] = sqrt(h[2]);                    // l2_norm
+  norms[3] = pow(h[3], expo);               // lp_norm        (norm**exponent, as written)
+  norms[4] = h[4];                          // linfty_norm
+  norms[5] = sqrt(h[5]);                    // h1_seminorm
+  norms[6] = sqrt(h[2] + h[5]);             // h1_norm
+  norms[7] = pow(h[6], expo);               // w1p_seminorm
+  norms[8] = pow(h[3] + h[6], expo);        // w1p_norm
+  norms[9] = h[7];                          // w1infty_seminorm
+  norms[10] = h[4] + h[7];                  // w1infty_norm   (l1_max of the values + l1_max of the gradients)
+  return 0;
+}
+
+extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double* h1_seminorm,
+                               double* l2_norm) {
+  double all[11];
+  FB2_TRY(fb2_error_norms_all(s, x, func, func_params, 2.0, all));
+  *h1_seminorm = all[5];
+  *l2_norm = all[2];
   return 0;
 }

@@ -61,6 +61,13 @@ int fb2_allreduce_sum(double* d_buf, int count) {
   return 0;
 }
 
+// environment%l1_max (mpi_context.f90 max_scalar_rp analogue)
+int fb2_allreduce_max(double* d_buf, int count) {
+  if (!g_comm) return 0;
+  FB2_NCCL(ncclAllReduce(d_buf, d_buf, count, ncclDouble, ncclMax, g_comm, fb2_stream()));
+  return 0;
+}
+
 // ------------------------------------------------------------------------------------------
 // dof_import on the device
 // ------------------------------------------------------------------------------------------

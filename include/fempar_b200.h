@@ -256,6 +256,22 @@ int fb2_pcg_iterate_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, fb2_vecto
 /* ---- error norms: sqrt(sum_K int |grad(u-u_h)|^2), sqrt(int (u-u_h)^2) ----- */
 int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double* h1_seminorm,
                     double* l2_norm);
+/* error_norms_scalar_t%compute for the eleven norm types par_test_poisson checks (par_test_poisson_driver.f90:557-589;
+ * Integration/ErrorNorms/error_norms.f90:41-54,160-221, sbm_error_norms_scalar.i90:114-232):
+ * norms[] = mean, l1, l2, lp, linfty, h1_seminorm, h1, w1p_seminorm, w1p, w1infty_seminorm, w1infty.
+ * exponent <= 0 selects the reference's default 2.0; in par the sums / maxima are all-reduced (l1_sum / l1_max). */
+#define FB2_NORM_MEAN 0
+#define FB2_NORM_L1 1
+#define FB2_NORM_L2 2
+#define FB2_NORM_LP 3
+#define FB2_NORM_LINFTY 4
+#define FB2_NORM_H1_SEMI 5
+#define FB2_NORM_H1 6
+#define FB2_NORM_W1P_SEMI 7
+#define FB2_NORM_W1P 8
+#define FB2_NORM_W1INFTY_SEMI 9
+#define FB2_NORM_W1INFTY 10
+int fb2_error_norms_all(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double exponent, double norms[11]);
 
 #ifdef __cplusplus
 }

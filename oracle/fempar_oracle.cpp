@@ -1019,6 +1019,52 @@ struct Space {
     }
     *h1semi = std::sqrt(e1); *l2 = std::sqrt(e0);
   }
+
+  // error_norms_scalar_t%compute for the eleven norm types of par_test_poisson's check_solution
+  // (Tests/Par/par_test_poisson/modules/par_test_poisson_driver.f90:557-589):
+  //   cell contributions   Integration/ErrorNorms/sbm_error_norms_scalar.i90:187-232
+  //   update_norm          Integration/ErrorNorms/error_norms.f90:160-172 (sum, or max for the *infty norms)
+  //   finalize_norm        error_norms.f90:174-221 (restated as written: the p-norms end with norm**exponent)
+  //   default exponent 2   error_norms.f90:308-331
+  // acc[8] = the un-finalised sums / maxima of THIS part (mean, l1, l2, lp, max|e|, h1, w1p, max|d_k e|), so that a multi-part
+  // caller can l1_sum / l1_max them before finalising; out[11] = mean, l1, l2, lp, linfty, h1_semi, h1, w1p_semi, w1p,
+  // w1infty_semi, w1infty of this part alone.
+  void errors_all(const double* x, const Func& fn, double expo, double* acc, double* out) const {
+    const int nd = fe.ndofs, nn = fe.nnode;
+    std::vector<double> detj(fe.nq), grad(size_t(fe.nq) * nn * 3), xq(size_t(fe.nq) * 3), ul(nd);
+    for (int k = 0; k < 8; ++k) acc[k] = 0.0;
+    for (int c = 0; c < m.n_local; ++c) {
+      cell_geometry(c, detj.data(), grad.data(), xq.data());
+      for (int l = 0; l < nd; ++l) {
+        int g = gids[size_t(c) * nd + l];
+        ul[l] = g > 0 ? x[g - 1] : fixed[-g - 1];
+      }
+      double cv[5] = {0, 0, 0, 0, 0}, cg[3] = {0, 0, 0};
+      for (int q = 0; q < fe.nq; ++q) {
+        const double factor = detj[q] * fe.qw[q];
+        double gu[3] = {0, 0, 0}, uh = 0, gh[3] = {0, 0, 0};
+        fn.grad_u(&xq[q * 3], gu);
+        for (int a = 0; a < nn; ++a) {
+          uh += ul[a] * fe.phi[size_t(q) * nn + a];
+          for (int k = 0; k < m.d; ++k) gh[k] += ul[a] * grad[(size_t(q) * nn + a) * 3 + k];
+        }
+        const double e = fn.u(&xq[q * 3]) - uh;
+        double g2 = 0;
+        for (int k = 0; k < m.d; ++k) { g2 += (gu[k] - gh[k]) * (gu[k] - gh[k]); cg[2] = std::max(cg[2], std::fabs(gu[k] - gh[k])); }
+        cv[0] += e * factor; cv[1] += std::fabs(e) * factor; cv[2] += e * e * factor; cv[3] += std::pow(std::fabs(e), expo) * factor;
+        cv[4] = std::max(cv[4], std::fabs(e));
+        cg[0] += g2 * factor; cg[1] += std::pow(g2, expo / 2.0) * factor;
+      }
+      acc[0] += cv[0]; acc[1] += cv[1]; acc[2] += cv[2]; acc[3] += cv[3]; acc[4] = std::max(acc[4], cv[4]);
+      acc[5] += cg[0]; acc[6] += cg[1]; acc[7] = std::max(acc[7], cg[2]);
+    }
+    finalize_norms(acc, expo, out);
+  }
+  static void finalize_norms(const double* a, double expo, double* out) {
+    out[0] = a[0]; out[1] = a[1]; out[2] = std::sqrt(a[2]); out[3] = std::pow(a[3], expo); out[4] = a[4];
+    out[5] = std::sqrt(a[5]); out[6] = std::sqrt(a[2] + a[5]); out[7] = std::pow(a[6], expo); out[8] = std::pow(a[3] + a[6], expo);
+    out[9] = a[7]; out[10] = a[4] + a[7];
+  }
 };
 
 } // namespace fo
@@ -1073,6 +1119,11 @@ int fo_errors(void* h, const double* x, int func, const double* fprm, double* h1
   Space* s = (Space*)h; Func f = make_func(s->m.d, func, fprm);
   s->errors(x, f, h1semi, l2); return 0;
 }
+int fo_errors_all(void* h, const double* x, int func, const double* fprm, double expo, double* acc8, double* out11) {
+  Space* s = (Space*)h; Func f = make_func(s->m.d, func, fprm);
+  s->errors_all(x, f, expo > 0 ? expo : 2.0, acc8, out11); return 0;
+}
+int fo_finalize_norms(const double* acc8, double expo, double* out11) { Space::finalize_norms(acc8, expo > 0 ? expo : 2.0, out11); return 0; }
 // element matrix of one cell (column-major nd x nd) and element vector, before Dirichlet elimination
 int fo_element(void* h, int cell, int kind, int func, const double* fprm, const double* mat, double* elmat, double* elvec) {
   Space* s = (Space*)h; Func f = make_func(s->m.d, func, fprm);

@@ -172,6 +172,28 @@ class OracleSpace:
         self.L.fo_errors(self.h, C.c_void_p(x.ctypes.data), func, C.c_void_p(pa), C.byref(h1), C.byref(l2))
         return h1.value, l2.value
 
+    NORM_NAMES = ("mean_norm", "l1_norm", "l2_norm", "lp_norm", "linfty_norm", "h1_seminorm", "h1_norm", "w1p_seminorm", "w1p_norm",
+                  "w1infty_seminorm", "w1infty_norm")
+
+    def errors_all(self, x, func=FUNC_LINEAR, fprm=None, exponent=None):
+        """the eleven norms of par_test_poisson's check_solution for this part: (dict of finalised norms, raw accumulators[8])"""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        a, pa = self._prm(fprm)
+        acc, out = np.zeros(8), np.zeros(11)
+        self.L.fo_errors_all(self.h, C.c_void_p(x.ctypes.data), func, C.c_void_p(pa), C.c_double(exponent or 0.0),
+                             C.c_void_p(acc.ctypes.data), C.c_void_p(out.ctypes.data))
+        return dict(zip(self.NORM_NAMES, out)), acc
+
+    @classmethod
+    def finalize_norms(cls, accs, exponent=None):
+        """l1_sum / l1_max of the per-part accumulators, then finalize_norm (error_norms.f90:174-221)"""
+        accs = np.asarray(accs, dtype=np.float64).reshape(-1, 8)
+        tot = accs.sum(axis=0)
+        tot[4], tot[7] = accs[:, 4].max(), accs[:, 7].max()
+        out = np.zeros(11)
+        lib().fo_finalize_norms(C.c_void_p(tot.ctypes.data), C.c_double(exponent or 0.0), C.c_void_p(out.ctypes.data))
+        return dict(zip(cls.NORM_NAMES, out))
+
     def element(self, cell, kind=KIND_POISSON, func=FUNC_LINEAR, fprm=None, mat=None):
         nd = self.ndofs_per_cell
         a, pa = self._prm(fprm)

@@ -389,3 +389,26 @@ def test_user_source_term_sampled_at_quadrature_points(fb2, asm_variant, N, p):
     with pytest.raises(fb2.Fb2Error):
         s.set_source_values(np.zeros(3))
     op.free()
+
+
+@pytest.mark.parametrize("N,p,func,prm", [((6, 6, 6), 2, FUNC_SHARP_WAVE, WAVE), ((5, 4, 3), 3, FUNC_SHARP_WAVE, WAVE), ((8, 8, 8), 1, FUNC_LINEAR, None)])
+@pytest.mark.parametrize("exponent", [None, 3])
+def test_eleven_error_norms_match_oracle(fb2, N, p, func, prm, exponent):
+    """error_norms_scalar_t%compute for the norm types par_test_poisson checks (par_test_poisson_driver.f90:557-589)"""
+    s, op = _assemble(fb2, N, p, 1, fb2.poisson, func, prm, None, 0)
+    o = OracleSpace(N, order=p)
+    o.assemble(KIND_POISSON, func, prm, route=1)
+    o.jacobi_setup()
+    r = o.cg(prec=1, rtol=1e-12, maxit=5000)
+    x = s.create_dof_values()
+    x.set_entries(r["x"])
+    got = s.error_norms_all(x, func, prm, exponent)
+    want, _ = o.errors_all(r["x"], func, prm, exponent)
+    assert list(got) == list(want) == list(fb2.ERROR_NORM_NAMES)
+    scale = max(abs(v) for v in want.values())
+    for k in want:
+        assert abs(got[k] - want[k]) <= 1e-9 * max(abs(want[k]), 1e-12 * scale) + 1e-13, (k, got[k], want[k])
+    h1, l2 = s.error_norms(x, func, prm)
+    assert abs(h1 - want["h1_seminorm"]) <= 1e-9 * abs(want["h1_seminorm"]) + 1e-13 and abs(l2 - want["l2_norm"]) <= 1e-9 * abs(want["l2_norm"]) + 1e-13
+    if func == FUNC_LINEAR:                       # the reference's acceptance bar
+        assert all(abs(v) < 1e-4 for v in got.values())

@@ -22,9 +22,11 @@ def _system(fb2, N, p, func, prm):
     return s, op, M, o
 
 
-def _solver(fb2, op, M, rtol=1e-10, track=True):
+def _solver(fb2, op, M, rtol=1e-10, track=True, stop=None):
     ils = fb2.IterativeLinearSolver(); ils.set_type_from_string("CG")
     ils.set_parameters_from_pl({fb2.ILS_RTOL: rtol, fb2.ILS_MAX_NUM_ITERATIONS: 500, fb2.ILS_TRACK_CONVERGENCE_HISTORY: track})
+    if stop is not None:
+        ils.set_parameters_from_pl({fb2.ILS_STOPPING_CRITERIUM: stop})
     ils.set_operators(op.get_tangent(), M)
     return ils
 
@@ -59,9 +61,10 @@ def test_initial_solution_is_per_operator(fb2):
     """an initial solution set for one operator must not leak into the solves of another one of the SAME size"""
     s1, op1, M1, o1 = _system(fb2, (6, 6, 6), 2, FUNC_SHARP_WAVE, WAVE)
     s2, op2, M2, o2 = _system(fb2, (6, 6, 6), 2, FUNC_LINEAR, None)
-    r1 = o1.cg(prec=1, rtol=1e-10, maxit=500)
-    r2 = o2.cg(prec=1, rtol=1e-10, maxit=500)
-    ils1, ils2 = _solver(fb2, op1, M1, track=False), _solver(fb2, op2, M2, track=False)
+    # RES_RHS: the tolerance is relative to |b|, so a warm start from the converged solution stops at once
+    r1 = o1.cg(prec=1, rtol=1e-10, maxit=500, stop=1)
+    r2 = o2.cg(prec=1, rtol=1e-10, maxit=500, stop=1)
+    ils1, ils2 = _solver(fb2, op1, M1, track=False, stop=fb2.res_rhs), _solver(fb2, op2, M2, track=False, stop=fb2.res_rhs)
     x1, x2 = s1.create_dof_values(), s2.create_dof_values()
     ils1.apply(op1.get_translation(), x1)
     n_cold = ils1.get_num_iterations()
