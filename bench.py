@@ -340,6 +340,7 @@ def main():
     A = As[0]
     n_loc, nnz_loc = sum(sp.num_free_dofs for sp in spaces), sum(m.nnz for m in As)
     ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG")
+    ils.set_parameters_from_pl({fb.ILS_OUTPUT_FREQUENCY: 0})      # no convergence log inside the timed regions
     if multi:
         dinvs = [sp.create_dof_values() for sp in spaces]
         xs = [sp.create_dof_values() for sp in spaces]

@@ -183,6 +183,7 @@ void fb2_cg_set_icg(int on);
 bool fb2_ils_has_initial_solution(fb2_matrix_s* A);
 int fb2_ils_load_initial_solution(fb2_matrix_s* A, double* x);   // x <- the initial solution set on this operator, or 0
 void fb2_solver_ws_free(fb2_matrix_s* A);
+void fb2_solver_record_convergence(fb2_matrix_s* A, double tol, double err, int iters);   // for the host-driven Krylov solvers
 int fb2_spmv_stream(fb2_matrix_s* A, const double* x, double* y, bool fuse_dot, const int* done_flag, int* grid_out);
 int fb2_spmv_prepare(fb2_matrix_s* A);
 void fb2_spmv_set_compress(bool on);

@@ -217,6 +217,7 @@ static int richardson_solve(fb2_matrix_s* A, const double* dinv, const double* b
     did = e <= tol;
   }
   *iters = it; *conv = did ? 1 : 0; *err = e;
+  fb2_solver_record_convergence(A, tol, e, it);
   return 0;
 }
 
@@ -331,6 +332,7 @@ static int gmres_solve(fb2_matrix_s* A, const double* dinv, const double* b, dou
   }
   FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
   *iters = it; *conv = e <= tol ? 1 : 0; *err = e;
+  fb2_solver_record_convergence(A, tol, e, it);
   return 0;
 }
 
@@ -430,6 +432,7 @@ static int lfom_solve(fb2_matrix_s* A, const double* dinv, const double* b, doub
   }
   FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
   *iters = it; *conv = e <= tol ? 1 : 0; *err = e;
+  fb2_solver_record_convergence(A, tol, e, it);
   return 0;
 }
 
@@ -527,7 +530,7 @@ static int minres_solve(fb2_matrix_s* A, const double* dinv, const double* b, do
       if (istop != 0) break;
     }
   }
-  (void)tol;
+  fb2_solver_record_convergence(A, tol, e, it);
   FB2_CUDA(cudaStreamSynchronize(st));
   fb2_record_phase("minres_istop", (double)istop);
   fb2_record_phase("minres_Anorm", Anorm);

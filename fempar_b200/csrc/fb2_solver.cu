@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(256) k_cg_update_xr(i64 n, CgState* st, const 
   }
 }
 // convergence bookkeeping: cg.f90:208-226 and update_convergence_data_and_evaluate_stopping_criteria :331-407 (all ten criteria)
-__global__ void k_cg_scalars(CgState* st, double* hist) {
+__global__ void k_cg_scalars(CgState* st, double* hist, double* hist_extra) {
   if (st->done) return;
   st->iter += 1;
   const int crit = st->crit;
@@ -402,6 +402,8 @@ __global__ void k_cg_scalars(CgState* st, double* hist) {
     st->err_extra = sqrt(st->rr);
     conv = st->err_extra <= st->tol_extra;
   }
+  // the 2nd criterion's estimate as the reference's per-iteration line prints it: updated only when the 1st one is met
+  if (hist_extra) hist_extra[st->iter - 1] = st->err_extra;
   st->converged = conv ? 1 : 0;
   if (conv || st->iter >= st->maxit) { st->done = 1; return; }
   st->beta = st->icg ? (1.0 / st->rz) * (st->rz_new - st->r2z) : st->rz_new / st->rz;   // icg.f90:216-222 / cg.f90:220-226
@@ -441,6 +443,8 @@ struct fb2_solver_ws {
   i64 x0_n = 0;
   bool x0_on = false;
   fb2_vector_t vb = nullptr, vx = nullptr;
+  double last[4] = {0, 0, 0, 0};   // rhs_convergence_test, rhs_extra_convergence_test, error estimates of the last solve
+  int last_iters = 0, last_tracked = 0;
 };
 static fb2_solver_ws* ws_of(fb2_matrix_t A) {
   if (!A->ws) A->ws = new fb2_solver_ws();
@@ -466,7 +470,7 @@ static int cg_workspace(fb2_matrix_t A, int hist_len) {
   if (!W.st) FB2_TRY(fb2_dalloc(&W.st, 1));
   if (hist_len > W.hist_cap) {
     cudaFree(W.hist);
-    FB2_TRY(fb2_dalloc(&W.hist, (size_t)hist_len));
+    FB2_TRY(fb2_dalloc(&W.hist, 2 * (size_t)hist_len));   // error estimates of the 1st criterion, then of the 2nd
     W.hist_cap = hist_len;
   }
   return 0;
@@ -529,7 +533,7 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
   k_cg_update_xr<<<g2, 256, 0, s>>>(n, W.st, W.p, W.Ap, dinv, w, x, W.r, part, FB2_MAX_PARTIALS);
   k_reduce_partials<<<1, 256, 0, s>>>(part, g2, FB2_MAX_PARTIALS, 4, &W.st->rr);   // rr, rz_new, pp, r2z are adjacent
   if (par) FB2_TRY(fb2_allreduce_sum(&W.st->rr, 4));
-  k_cg_scalars<<<1, 1, 0, s>>>(W.st, hist);
+  k_cg_scalars<<<1, 1, 0, s>>>(W.st, hist, hist ? hist + W.hist_cap : nullptr);
   k_cg_update_p<<<vec_grid(n), 256, 0, s>>>(n, W.st, W.r, dinv, W.p);
   FB2_CUDA(cudaGetLastError());
   return 0;
@@ -653,7 +657,29 @@ extern "C" int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, 
   *did_converge = h.converged;
   *error_estimate = h.err;
   if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, W.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
+  fb2_solver_ws* S = ws_of(A);
+  S->last[0] = h.tol; S->last[1] = h.tol_extra; S->last[2] = h.err; S->last[3] = h.err_extra;
+  S->last_iters = h.iter; S->last_tracked = track ? 1 : 0;
   return 0;
+}
+
+// what print_convergence_history_{header,new_line,footer} need beyond the history itself
+// (base_iterative_linear_solver.f90:584-676): out[4] = rhs_convergence_test, rhs_extra_convergence_test,
+// error_estimate_convergence_test, error_estimate_extra_convergence_test of the last solve on this operator; history_extra
+// (may be NULL; needs a solve that tracked the history) = the 2nd criterion's estimate per iteration
+extern "C" int fb2_csr_get_convergence_data(fb2_matrix_t A, double out[4], double* history_extra) {
+  FB2_CHECK(A && out, "null argument");
+  fb2_solver_ws* S = ws_of(A);
+  for (int k = 0; k < 4; ++k) out[k] = S->last[k];
+  if (history_extra && S->last_iters > 0) {
+    FB2_CHECK(S->last_tracked && S->w.hist, "the last solve did not track its convergence history");
+    FB2_CUDA(fb2_memcpy(history_extra, S->w.hist + S->w.hist_cap, sizeof(double) * S->last_iters, cudaMemcpyDeviceToHost));
+  }
+  return 0;
+}
+void fb2_solver_record_convergence(fb2_matrix_s* A, double tol, double err, int iters) {
+  fb2_solver_ws* S = ws_of(A);
+  S->last[0] = tol; S->last[1] = 0.0; S->last[2] = err; S->last[3] = 0.0; S->last_iters = iters; S->last_tracked = 0;
 }
 
 extern "C" int fb2_pcg_solve_host(fb2_matrix_t A, fb2_vector_t dinv, const double* b_host, double* x_host,
@@ -933,7 +959,7 @@ static int multi_cg_iteration(const MultiCtx& C, MultiWork& M, fb2_vector_t* din
   }
   k_reduce_partials<<<1, 256, 0, s>>>(part, off2, FB2_MAX_PARTIALS, 4, &M.st->rr);
   if (fb2_comm_active()) FB2_TRY(fb2_allreduce_sum(&M.st->rr, 4));
-  k_cg_scalars<<<1, 1, 0, s>>>(M.st, hist);
+  k_cg_scalars<<<1, 1, 0, s>>>(M.st, hist, hist ? hist + M.parts[0]->hist_cap : nullptr);
   for (int i = 0; i < np; ++i) {
     CgWork& W = *M.parts[i];
     k_cg_update_p<<<vec_grid(W.n), 256, 0, s>>>(W.n, M.st, W.r, dinv ? dinv[i]->d : nullptr, W.p);
@@ -969,6 +995,9 @@ extern "C" int fb2_pcg_solve_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, 
   }
   *num_iterations = h.iter; *did_converge = h.converged; *error_estimate = h.err;
   if (track && h.iter > 0) FB2_CUDA(fb2_memcpy(history, M.hist, sizeof(double) * h.iter, cudaMemcpyDeviceToHost));
+  fb2_solver_ws* S = ws_of(C.A[0]);      // convergence data of the collective solve: kept with the first part
+  S->last[0] = h.tol; S->last[1] = h.tol_extra; S->last[2] = h.err; S->last[3] = h.err_extra;
+  S->last_iters = h.iter; S->last_tracked = track ? 1 : 0;
   return 0;
 }
 

@@ -619,7 +619,7 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
     if (s_ok && k >= 0 && k < m) {
       const int d = ja[e0 + k] - 1 - (int)r0;
       int g = 0;
-      while (g + 1 < D.nseg && D.delta[g + 1] <= d) ++g;
+      while (g + 2 < D.nseg && D.delta[g + 1] <= d) ++g;      // column segments only: the last segment is the tile's own rows
       v = (unsigned short)(D.off[g] + d - D.delta[g]);
     }
     out[i] = v;

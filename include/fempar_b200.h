@@ -201,6 +201,12 @@ int fb2_pcg_solve(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b, fb2_vector_
  * A vector of another size is ignored like the reference ignores one outside range(A).  The *_multi entry points start from
  * zero and reject parts with an initial solution set. */
 int fb2_csr_set_initial_solution(fb2_matrix_t A, fb2_vector_t x0);
+/* what the reference's convergence log needs beyond the history (print_convergence_history_header / _new_line / _footer,
+ * base_iterative_linear_solver.f90:584-676): out[4] = rhs_convergence_test, rhs_extra_convergence_test,
+ * error_estimate_convergence_test, error_estimate_extra_convergence_test of the LAST solve on this operator; history_extra
+ * (NULL, or num_iterations doubles; needs a solve with history != NULL) = the estimate of the second criterion per iteration
+ * for the four DELTA_*_AND_RES_* criteria. */
+int fb2_csr_get_convergence_data(fb2_matrix_t A, double out[4], double* history_extra);
 /* drops the SpMV tile table / pattern classes of the matrix; the next apply prepares them again (tuning sweeps) */
 int fb2_csr_spmv_reset(fb2_matrix_t A);
 /* releases the solver workspace of the operator early (fb2_csr_destroy does it too) */

@@ -412,3 +412,42 @@ def test_eleven_error_norms_match_oracle(fb2, N, p, func, prm, exponent):
     assert abs(h1 - want["h1_seminorm"]) <= 1e-9 * abs(want["h1_seminorm"]) + 1e-13 and abs(l2 - want["l2_norm"]) <= 1e-9 * abs(want["l2_norm"]) + 1e-13
     if func == FUNC_LINEAR:                       # the reference's acceptance bar
         assert all(abs(v) < 1e-4 for v in got.values())
+
+
+def test_convergence_log_in_reference_format(fb2):
+    """header / per-iteration line / footer of base_iterative_linear_solver.f90:584-676, ILS_OUTPUT_FREQUENCY and ILS_LUOUT"""
+    import io
+    import re
+    s, op = _assemble(fb2, (6, 6, 6), 2, 1, fb2.poisson, FUNC_SHARP_WAVE, WAVE, None, 0)
+    M = fb2.JacobiPreconditioner(); M.create(op); M.numerical_setup()
+    o = OracleSpace((6, 6, 6), order=2)
+    o.assemble(KIND_POISSON, FUNC_SHARP_WAVE, WAVE, route=1)
+    o.jacobi_setup()
+    es = r"  [ -]\d\.\d{9}E[+-]\d{2}"
+    for stop, ostop, two in ((fb2.res_res, 0, False), (fb2.delta_rhs_and_res_rhs, 7, True)):
+        r = o.cg(prec=1, rtol=1e-8, maxit=500, stop=ostop, history=True)
+        buf = io.StringIO()
+        ils = fb2.IterativeLinearSolver(); ils.set_type_from_string("CG")
+        ils.set_parameters_from_pl({fb2.ILS_RTOL: 1e-8, fb2.ILS_MAX_NUM_ITERATIONS: 500, fb2.ILS_STOPPING_CRITERIUM: stop,
+                                    fb2.ILS_OUTPUT_FREQUENCY: 5, fb2.ILS_LUOUT: buf})
+        ils.set_operators(op.get_tangent(), M)
+        x = s.create_dof_values()
+        ils.apply(op.get_translation(), x)
+        lines = buf.getvalue().splitlines()
+        it = ils.get_num_iterations()
+        assert abs(it - r["iters"]) <= 1
+        cols = 4 if two else 2
+        assert lines[0] == "CG:   " + "Iteration" + "".join("  " + "%15s" % t for t in ("Error Estimate", "Tolerance") * (cols // 2))
+        body = lines[1:-2]
+        want_iters = [i for i in range(1, it + 1) if i % 5 == 0 or i == it]
+        assert [int(ln[6:15]) for ln in body] == want_iters
+        for ln in body:
+            assert re.fullmatch(r"CG:   [ \d]{9}" + es * cols, ln), ln
+        k = want_iters[0]
+        assert abs(float(body[0][15:33]) - r["history"][k - 1]) <= 1e-6 * r["history"][k - 1]
+        assert re.fullmatch(r"CG converged to " + es + (r" [ -]\d\.\d{9}E[+-]\d{2}" if two else "") + r"  in  [ \d]{9}  iterations\. ", lines[-2]), lines[-2]
+        assert lines[-1].startswith("Last iteration error estimate" + ("s: " if two else ": "))
+    ils.set_parameters_from_pl({fb2.ILS_OUTPUT_FREQUENCY: 0})
+    buf.truncate(0); buf.seek(0)
+    ils.apply(op.get_translation(), x)
+    assert buf.getvalue() == ""
