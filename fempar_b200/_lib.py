@@ -80,6 +80,10 @@ _SIGS = {
     "fb2_vec_axpby": [_VP, C.c_double, _VP, C.c_double],
     "fb2_vec_dot": [_VP, _VP, C.POINTER(C.c_double)],
     "fb2_vec_nrm2": [_VP, C.POINTER(C.c_double)],
+    "fb2_vec_local_dot": [_VP, _VP, C.POINTER(C.c_double)],
+    "fb2_vec_nullify_non_owned_dofs": [_VP],
+    "fb2_vec_extract_subvector": [_VP, C.c_int32, _VP, _VP],
+    "fb2_vec_insert_subvector": [_VP, C.c_int32, _VP, _VP],
     "fb2_vec_entrywise_product": [_VP, _VP, _VP],
     "fb2_vec_entrywise_invert": [_VP],
     "fb2_vec_comm": [_VP],

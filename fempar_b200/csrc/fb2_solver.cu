@@ -291,6 +291,60 @@ extern "C" int fb2_vec_dot(fb2_vector_t x, fb2_vector_t y, double* result) {
   FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
   return 0;
 }
+// vector_t%local_dot (vector.f90:41, par_scalar_array.f90:303-326): the weighted dot of this part without the all-reduce
+extern "C" int fb2_vec_local_dot(fb2_vector_t x, fb2_vector_t y, double* result) {
+  FB2_CHECK(x && y && result && x->n == y->n, "size mismatch");
+  double* d_res = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
+  const double* w = (x->s && x->s->imp) ? fb2_import_weight(x->s->imp) : nullptr;
+  FB2_TRY(fb2_dot_device(x->d, y->d, w, x->n, d_res));
+  FB2_CUDA(fb2_memcpy(result, d_res, sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+// vector_t%nullify_non_owned_dofs (par_scalar_array.f90): x_i <- 0 where this part does not own DOF i (weight 0)
+__global__ void k_nullify_non_owned(double* x, const double* __restrict__ w, i64 n) {
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x)
+    if (w[i] == 0.0) x[i] = 0.0;
+}
+extern "C" int fb2_vec_nullify_non_owned_dofs(fb2_vector_t x) {
+  FB2_CHECK(x, "null vector");
+  if (x->s && x->s->imp) k_nullify_non_owned<<<vec_grid(x->n), 256, 0, fb2_stream()>>>(x->d, fb2_import_weight(x->s->imp), x->n);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+// vector_t%extract_subvector / insert_subvector on an index subset (vector.f90:161-187; indices 1-based like the reference)
+__global__ void k_gather_idx(const double* __restrict__ x, const int* __restrict__ idx, int m, double* out) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < m) out[k] = x[idx[k] - 1];
+}
+__global__ void k_scatter_idx(double* x, const int* __restrict__ idx, int m, const double* __restrict__ in) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < m) x[idx[k] - 1] = in[k];
+}
+static int subvector(fb2_vector_t v, int32_t m, const int32_t* indices, double* values, bool extract) {
+  FB2_CHECK(v && m >= 0 && (m == 0 || (indices && values)), "bad argument");
+  if (m == 0) return 0;
+  for (int k = 0; k < m; ++k) FB2_CHECK(indices[k] >= 1 && indices[k] <= v->n, "subvector index out of range");
+  int* d_idx; double* d_val;
+  FB2_TRY(fb2_dalloc(&d_idx, (size_t)m)); FB2_TRY(fb2_dalloc(&d_val, (size_t)m));
+  FB2_CUDA(fb2_memcpy(d_idx, indices, sizeof(int) * (size_t)m, cudaMemcpyHostToDevice));
+  if (extract) {
+    k_gather_idx<<<(m + 255) / 256, 256, 0, fb2_stream()>>>(v->d, d_idx, m, d_val);
+    FB2_CUDA(fb2_memcpy(values, d_val, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost));
+  } else {
+    FB2_CUDA(fb2_memcpy(d_val, values, sizeof(double) * (size_t)m, cudaMemcpyHostToDevice));
+    k_scatter_idx<<<(m + 255) / 256, 256, 0, fb2_stream()>>>(v->d, d_idx, m, d_val);
+    FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
+  }
+  cudaFree(d_idx); cudaFree(d_val);
+  FB2_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int fb2_vec_extract_subvector(fb2_vector_t v, int32_t size_indices, const int32_t* indices, double* values) {
+  return subvector(v, size_indices, indices, values, true);
+}
+extern "C" int fb2_vec_insert_subvector(fb2_vector_t v, int32_t size_indices, const int32_t* indices, const double* values) {
+  return subvector(v, size_indices, indices, const_cast<double*>(values), false);
+}
 extern "C" int fb2_vec_nrm2(fb2_vector_t x, double* result) {
   FB2_TRY(fb2_vec_dot(x, x, result));
   *result = sqrt(*result);

@@ -70,13 +70,16 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // of its class and checks the segment bounds; everything else streams ja as before.  Products are formed in the same
 // order from the same operands, so y is bit-identical to the ja path (tests: test_midsize_spmv_variants_bitwise).
 struct SpmvClassDesc {
-  int nseg, idx_bytes, x_bytes, self_off;   // self_off: window position of the tile's own rows (the last segment)
+  int nseg, idx_bytes, x_bytes, pad;
   int delta[32];   // first column of the segment relative to the first row of the tile (even, so 16-byte aligned in x)
   int len[32];     // doubles, even
   int off[32];     // position of the segment in the window, doubles
 };
 #define SPMV_NOCLASS 0xFF
 
+// Tried and rejected in round 2 (profiles/r2_spmv_history.txt): consumers that stream the rows of a warp's range 32 entries at a
+// time (contiguous shared-memory reads, one xor tree per finished row).  It halves the shared-memory wavefronts per non-zero
+// but needs 107 instead of 54 instructions per 32 non-zeros (issue slots 82 % busy): 24.9 ms against 15.6 ms at config 2.
 // Persistent block over tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  Warp 8 is the TMA producer
 // (one elected lane): it runs STAGES tiles ahead, waiting on the per-stage "empty" mbarrier and arming
 // the "full" one with the byte count of the three bulk copies (val, ja, irp slice).  The 8 consumer
@@ -106,7 +109,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full_bar[SPMV_MAX_STAGES], empty_bar[SPMV_MAX_STAGES];
   __shared__ i64 s_e0a[SPMV_MAX_STAGES], s_r0[SPMV_MAX_STAGES];
-  __shared__ int s_nr[SPMV_MAX_STAGES], s_nd[SPMV_MAX_STAGES], s_cls[SPMV_MAX_STAGES], s_xoff[SPMV_MAX_STAGES], s_xself[SPMV_MAX_STAGES], s_lastcls[SPMV_MAX_STAGES];
+  __shared__ int s_nr[SPMV_MAX_STAGES], s_nd[SPMV_MAX_STAGES], s_cls[SPMV_MAX_STAGES], s_xoff[SPMV_MAX_STAGES], s_lastcls[SPMV_MAX_STAGES];
   __shared__ i64 s_d0[SPMV_MAX_STAGES];
   __shared__ double s_red[32];
   if (done_flag && *done_flag) return;
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
         s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0); s_d0[s] = d0; s_cls[s] = cls;
         if (!COMP && cls != SPMV_NOCLASS) {
           const SpmvClassDesc& D = cls_desc[cls];
-          s_xoff[s] = D.idx_bytes; s_xself[s] = D.self_off;
+          s_xoff[s] = D.idx_bytes;
           // consecutive tiles of an x-row of cells share their class: the index table this stage received two tiles ago is
           // still there (only index / ja copies write that region) and is not copied again
           const bool have_idx = s_lastcls[s] == cls;
@@ -202,6 +205,8 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     return;
   }
   // ---------------- consumer warps ----------------
+  const int TPR = NC / R;   // lanes per row: 4..32, power of two
+  const int row = tid / TPR, sub = tid - row * TPR;
   const int lane = tid & 31, w = tid >> 5;
   double dacc = 0.0;
   int it = 0;
@@ -243,93 +248,40 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       else return in_class ? sxw[sj16[k]] : x[sj[k] - 1];
     };
     const i64 e0a = s_e0a[s];
-    if constexpr (COMP) {
-      // (dictionary variant: lane groups of TPR lanes per row, as in round 1)
-      const int TPR = NC / R;
-      const int row = tid / TPR, sub = tid - row * TPR;
-      double acc = 0.0;
-      const bool live = row < s_nr[s];
-      double xrow = 0.0;
-      if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
-      if (live) {
-        const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
-        int k = b + sub;
-        for (; k + 3 * TPR < e; k += 4 * TPR) {
-          const double x0 = xat(k), x1 = xat(k + TPR), x2 = xat(k + 2 * TPR), x3 = xat(k + 3 * TPR);
-          acc += sv[k] * x0;
-          acc += sv[k + TPR] * x1;
-          acc += sv[k + 2 * TPR] * x2;
-          acc += sv[k + 3 * TPR] * x3;
-        }
-        if (k < e) {
-          const int k1 = k + TPR, k2 = k + 2 * TPR;
-          const bool p1 = k1 < e, p2 = k2 < e;
-          const double x0 = xat(k), x1 = p1 ? xat(k1) : 0.0, x2 = p2 ? xat(k2) : 0.0;
-          acc += sv[k] * x0;
-          if (p1) acc += sv[k1] * x1;
-          if (p2) acc += sv[k2] * x2;
-        }
+    double acc = 0.0;
+    const bool live = row < s_nr[s];
+    // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
+    double xrow = 0.0;
+    if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
+    if (live && in_class) {
+      // shared memory only: a plain strided loop (no gather latency to batch against)
+      const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
+#pragma unroll 4
+      for (int k = b + sub; k < e; k += TPR) acc += sv[k] * sxw[sj16[k]];
+    } else if (live) {
+      const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
+      int k = b + sub;
+      for (; k + 3 * TPR < e; k += 4 * TPR) {
+        const double x0 = xat(k), x1 = xat(k + TPR), x2 = xat(k + 2 * TPR), x3 = xat(k + 3 * TPR);
+        acc += sv[k] * x0;
+        acc += sv[k + TPR] * x1;
+        acc += sv[k + 2 * TPR] * x2;
+        acc += sv[k + 3 * TPR] * x3;
       }
-      for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
-      if (sub == 0 && live) {
-        y[r0 + row] = acc;
-        if (FUSE_DOT) dacc += acc * xrow;
+      if (k < e) {
+        // tail of up to 3 entries per lane as ONE masked batch, so that its gathers are in flight together
+        const int k1 = k + TPR, k2 = k + 2 * TPR;
+        const bool p1 = k1 < e, p2 = k2 < e;
+        const double x0 = xat(k), x1 = p1 ? xat(k1) : 0.0, x2 = p2 ? xat(k2) : 0.0;
+        acc += sv[k] * x0;
+        if (p1) acc += sv[k1] * x1;
+        if (p2) acc += sv[k2] * x2;
       }
-    } else {
-      // Warp-streamed rows.  Each warp owns a contiguous range of rows of the tile (balanced by entries) and walks the
-      // entries of that range 32 at a time, so every shared-memory read of val / index is one contiguous 256 / 64-byte
-      // access (the lane groups per row of round 1 cost 14.6 wavefronts per 32 non-zeros against ~6 here, and shared memory
-      // was the busiest unit of the pattern-class kernel: l1tex 87 %, profiles/r2_spmv_*).  Lane l accumulates the entries
-      // l, l+32, ... of the current row; when the row ends inside a chunk the lanes beyond the end start the next row and
-      // the finished row is summed over the warp with an xor tree.  Same code and order for class and ja tiles: bit-identical.
-      constexpr int NW = NC / 32;
-      const int nr = s_nr[s];
-      const int pl = lane < nr ? (int)(s_irp[lane] - e0a) : 0x7fffffff;   // first staged entry of row `lane` (R <= 32)
-      const int m0 = __shfl_sync(0xffffffffu, pl, 0), m1 = (int)(s_irp[nr] - e0a);
-      // rows whose first entry lies in [t_lo, t_hi)
-      const int t_lo = m0 + (int)(((i64)(m1 - m0) * w) / NW), t_hi = m0 + (int)(((i64)(m1 - m0) * (w + 1)) / NW);
-      const unsigned blo = __ballot_sync(0xffffffffu, pl >= t_lo), bhi = __ballot_sync(0xffffffffu, pl >= t_hi);
-      int w_lo = w == 0 ? 0 : (blo ? __ffs(blo) - 1 : nr), w_hi = w == NW - 1 ? nr : (bhi ? __ffs(bhi) - 1 : nr);
-      w_lo = min(w_lo, nr); w_hi = min(w_hi, nr);
-      const int kb_ = __shfl_sync(0xffffffffu, pl, w_lo & 31), ke_ = __shfl_sync(0xffffffffu, pl, w_hi & 31);
-      const int kb = w_lo < nr ? kb_ : m1, ke = w_hi < nr ? ke_ : m1;
-      // x of row `lane` for the fused <y,x> (class tiles: the tile's own rows are the last segment of the window)
-      double xr = 0.0;
-      if (FUSE_DOT && lane < nr) xr = in_class ? sxw[s_xself[s] + lane] : x[r0 + lane];
-      int row = w_lo;
-      int row_end = row < w_hi ? (int)(s_irp[row + 1] - e0a) : 0x7fffffff;
-      double acc = 0.0;
-      for (int kq = kb; kq < ke; kq += 128) {
-        double p[4];
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {       // the loads (and gathers) of four chunks in flight together
-          const int k = kq + 32 * c + lane;
-          p[c] = k < ke ? sv[k] * xat(k) : 0.0;
-        }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const int k0 = kq + 32 * c;
-          if (k0 < ke) {
-            int lo = 0;
-            while (row < w_hi && row_end <= k0 + 32) {     // the current row ends inside this chunk (or is empty)
-              const int e = row_end - k0;
-              double v = acc + ((lane >= lo && lane < e) ? p[c] : 0.0);
-#pragma unroll
-              for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-              const double xv = FUSE_DOT ? __shfl_sync(0xffffffffu, xr, row & 31) : 0.0;
-              if (lane == 0) {
-                y[r0 + row] = v;
-                if (FUSE_DOT) dacc += v * xv;
-              }
-              acc = 0.0; lo = e; ++row;
-              row_end = row < w_hi ? (int)(s_irp[row + 1] - e0a) : 0x7fffffff;
-            }
-            if (lane >= lo) acc += p[c];
-          }
-        }
-      }
-      for (; row < w_hi; ++row)            // rows without entries at the end of the range
-        if (lane == 0) y[r0 + row] = 0.0;
+    }
+    for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
+    if (sub == 0 && live) {
+      y[r0 + row] = acc;
+      if (FUSE_DOT) dacc += acc * xrow;
     }
     // COMP: the consumers wrote xs[] through the generic proxy into a region the producer's next bulk copy (async proxy)
     // overwrites: order the two proxies before releasing the stage
@@ -598,16 +550,12 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
       ++i;
       while (i < nu && su[i] - last <= SPMV_SEG_GAP) { last = su[i]; ++i; }
       const int len = (last - start + 2) & ~1;
-      if (nseg >= 30) { ok = 0; break; }
+      if (nseg >= 31) { ok = 0; break; }
       D.delta[nseg] = start; D.len[nseg] = len; D.off[nseg] = total;
       total += len; ++nseg;
     }
-    // the tile's own rows (x of the fused <y,x>) as one more segment
-    const int self_off = total, nrt = tile_nrows[t];
-    if (ok && nseg < 31) { D.delta[nseg] = 0; D.len[nseg] = (nrt + 1) & ~1; D.off[nseg] = total; total += D.len[nseg]; ++nseg; }
-    else ok = 0;
     if (total > xw_cap || total > 0xFFFF || idx_n > cap) ok = 0;
-    D.nseg = nseg; D.idx_bytes = idx_n * 2; D.x_bytes = total * 8; D.self_off = self_off;
+    D.nseg = nseg; D.idx_bytes = idx_n * 2; D.x_bytes = total * 8; D.pad = 0;
     for (int g = nseg; g < 32; ++g) { D.delta[g] = 0; D.len[g] = 0; D.off[g] = 0; }
     s_ok = ok;
   }
@@ -619,7 +567,7 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
     if (s_ok && k >= 0 && k < m) {
       const int d = ja[e0 + k] - 1 - (int)r0;
       int g = 0;
-      while (g + 2 < D.nseg && D.delta[g + 1] <= d) ++g;      // column segments only: the last segment is the tile's own rows
+      while (g + 1 < D.nseg && D.delta[g + 1] <= d) ++g;
       v = (unsigned short)(D.off[g] + d - D.delta[g]);
     }
     out[i] = v;
@@ -765,12 +713,12 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   // deeper pipelines.  R = the power of two whose average tile fills ~90 % of a stage; tiles that overflow are split.
   int cap = 2304, STAGES = 2;
   const double avg_row = (double)A->nnz / (double)A->n;
-  int R = 32;   // at most 32 rows per tile: the consumers keep one row pointer per lane
+  int R = 64;
   while (R > 8 && R * avg_row > 0.9 * cap) R >>= 1;
   if (getenv("FB2_SPMV_R")) R = atoi(getenv("FB2_SPMV_R"));
   if (getenv("FB2_SPMV_STAGES")) STAGES = atoi(getenv("FB2_SPMV_STAGES"));
   if (getenv("FB2_SPMV_CAP")) cap = atoi(getenv("FB2_SPMV_CAP"));
-  FB2_CHECK(R >= 8 && R <= 32 && (R & (R - 1)) == 0 && STAGES >= 2 && STAGES <= SPMV_MAX_STAGES && cap % 8 == 0, "bad SpMV tile parameters");
+  FB2_CHECK(R >= 8 && R <= 64 && (R & (R - 1)) == 0 && STAGES >= 2 && STAGES <= SPMV_MAX_STAGES && cap % 8 == 0, "bad SpMV tile parameters");
   const i64 nfixed = (A->n + R - 1) / R;
   int *pieces, *off, *d_flag, h_flag = 0, total = 0;
   FB2_TRY(fb2_dalloc(&pieces, (size_t)nfixed + 1)); FB2_TRY(fb2_dalloc(&off, (size_t)nfixed + 1)); FB2_TRY(fb2_dalloc(&d_flag, 1));

@@ -183,6 +183,11 @@ int fb2_vec_scal(fb2_vector_t dst, double alpha, fb2_vector_t src);      /* dst 
 int fb2_vec_axpby(fb2_vector_t op1, double alpha, fb2_vector_t op2, double beta); /* op1 = alpha*op2 + beta*op1 */
 int fb2_vec_dot(fb2_vector_t x, fb2_vector_t y, double* result);        /* par: weighted + all-reduce */
 int fb2_vec_nrm2(fb2_vector_t x, double* result);
+int fb2_vec_local_dot(fb2_vector_t x, fb2_vector_t y, double* result);  /* vector_t%local_dot: weighted, no all-reduce (vector.f90:41) */
+int fb2_vec_nullify_non_owned_dofs(fb2_vector_t x);                     /* vector_t%nullify_non_owned_dofs (vector.f90:52) */
+/* vector_t%extract_subvector / insert_subvector on a subset of 1-based indices (vector.f90:161-187) */
+int fb2_vec_extract_subvector(fb2_vector_t v, int32_t size_indices, const int32_t* indices, double* values);
+int fb2_vec_insert_subvector(fb2_vector_t v, int32_t size_indices, const int32_t* indices, const double* values);
 int fb2_vec_entrywise_product(fb2_vector_t z, fb2_vector_t x, fb2_vector_t y); /* z = x .* y */
 int fb2_vec_entrywise_invert(fb2_vector_t v);
 int fb2_vec_comm(fb2_vector_t v);                          /* par_scalar_array%comm, par_scalar_array.f90:498-533 */
