@@ -6,8 +6,12 @@ CPU restatement (numpy) of the reference's other Krylov solvers that share the C
   rgmres.f90:120-356, fgmres.f90:120-356, lgmres.f90:152-420,
   iterative_solver_utils.f90:46-106 (modified_gs_reorthonorm), :128-196 (iterative_gs_reorthonorm),
   :202-235 (apply_givens_rotation).
-Parity status: unpinned in the strict sense (the reference holds no golden vectors for these solvers; its tests only
-check that the solution error is below a tolerance) - fidelity rests on the line-by-line restatement cited above.
+Parity status: the reference holds no golden vectors for these solvers (its tests only check that the solution error is below
+a tolerance), so the restatement is pinned on an INDEPENDENT implementation instead (tests/test_oracle_krylov.py): scipy 1.18
+GMRES (per-iteration residual norms and iterates of R/F/LGMRES, identity and Jacobi preconditioning, with restarts) and
+MINRES (iterates after k iterations, with and without M) to 1e-8 .. 1e-9, LFOM against a dense Arnoldi projection and
+Richardson against the written-out recurrence.  What stays unpinned against the reference itself: its exact choice of
+error estimate per stopping criterion (cited line by line).
 
 A, M are callables y = A(x), z = M(r) on 1-D float64 arrays; dot defaults to numpy's.
 """

@@ -84,3 +84,88 @@ def test_minres_on_a_symmetric_indefinite_system():
     assert r["converged"] and r["istop"] == 1
     assert np.max(np.abs(r["x"] - xs)) <= 1e-6 * np.max(np.abs(xs))
     assert np.all(np.diff(r["history"]) <= 1e-12)        # MINRES minimises the residual: monotone estimate
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# Independent pin of the non-CG solvers (VERDICT r1 missing #6): scipy's GMRES / MINRES on the same matrix.  The reference
+# holds no vectors for icg/minres/*gmres/lfom/richardson, so the oracle used to be checked against nothing.  Same Krylov
+# space => same iterates and the same residual-norm sequence up to rounding, whoever wrote the recurrences.
+# ----------------------------------------------------------------------------------------------------------------------
+def _scipy_gmres_history(Aop, b, restart, maxiter, n):
+    res = []
+    x, info = spla.gmres(spla.LinearOperator((n, n), matvec=Aop), b, rtol=1e-30, atol=0.0, restart=restart, maxiter=maxiter,
+                         callback=lambda r: res.append(r), callback_type="pr_norm")
+    return x, np.array(res) * np.linalg.norm(b)
+
+
+def test_gmres_variants_against_scipy_gmres():
+    A, dinv, b, xe, cg = _system()
+    n = b.size
+    Af, Mf, If = (lambda x: A @ x), (lambda r: dinv * r), (lambda r: r.copy())
+    m = 25
+    # (1) identity preconditioner, ONE cycle of m inner iterations: RGMRES = LGMRES = FGMRES = scipy GMRES
+    xs, hs = _scipy_gmres_history(Af, b, restart=m, maxiter=1, n=n)
+    for solver in (K.rgmres, K.lgmres, K.fgmres):
+        r = solver(Af, If, b, rtol=0.0, atol=-1.0, maxit=m, dkrymax=m)
+        assert r["iters"] == m
+        assert np.max(np.abs(r["history"][:m] - hs[:m]) / hs[:m]) <= 1e-8, solver.__name__
+        assert np.max(np.abs(r["x"] - xs)) <= 1e-8 * np.max(np.abs(xs)), solver.__name__
+    # (2) Jacobi: right-preconditioned RGMRES is GMRES on A inv(D) (true residual norms); left-preconditioned LGMRES is GMRES on
+    #     inv(D) A with right-hand side inv(D) b (preconditioned residual norms)
+    ys, hr = _scipy_gmres_history(lambda y: A @ (dinv * y), b, restart=m, maxiter=1, n=n)
+    r = K.rgmres(Af, Mf, b, rtol=0.0, atol=-1.0, maxit=m, dkrymax=m)
+    assert np.max(np.abs(r["history"][:m] - hr[:m]) / hr[:m]) <= 1e-8
+    assert np.max(np.abs(r["x"] - dinv * ys)) <= 1e-8 * np.max(np.abs(ys))
+    xl, hl = _scipy_gmres_history(lambda x: dinv * (A @ x), dinv * b, restart=m, maxiter=1, n=n)
+    r = K.lgmres(Af, Mf, b, rtol=0.0, atol=-1.0, maxit=m, dkrymax=m)
+    assert np.max(np.abs(r["history"][:m] - hl[:m]) / hl[:m]) <= 1e-8
+    assert np.max(np.abs(r["x"] - xl)) <= 1e-8 * np.max(np.abs(xl))
+    # (3) restarts: 3 cycles of 8 (the restart logic of rgmres.f90 against scipy's)
+    xs3, hs3 = _scipy_gmres_history(Af, b, restart=8, maxiter=3, n=n)
+    r = K.rgmres(Af, If, b, rtol=0.0, atol=-1.0, maxit=24, dkrymax=8)
+    assert np.max(np.abs(r["x"] - xs3)) <= 1e-8 * np.max(np.abs(xs3))
+
+
+def test_minres_against_scipy_minres():
+    A, dinv, b, xe, cg = _system()
+    n = b.size
+    Af, If = (lambda x: A @ x), (lambda r: r.copy())
+    for k in (5, 12, 30):
+        xs, info = spla.minres(A, b, rtol=1e-30, maxiter=k)
+        r = K.minres(Af, If, b, rtol=0.0, atol=-1.0, maxit=k)
+        assert np.max(np.abs(r["x"] - xs)) <= 1e-9 * np.max(np.abs(xs)), k
+    # Jacobi-preconditioned: scipy takes the same SPD M^-1
+    Mop = spla.LinearOperator((n, n), matvec=lambda r: dinv * r)
+    xs, info = spla.minres(A, b, M=Mop, rtol=1e-30, maxiter=15)
+    r = K.minres(Af, (lambda v: dinv * v), b, rtol=0.0, atol=-1.0, maxit=15)
+    assert np.max(np.abs(r["x"] - xs)) <= 1e-9 * np.max(np.abs(xs))
+
+
+def test_lfom_and_richardson_against_closed_forms():
+    """LFOM with a full basis solves the Galerkin projection H y = beta e1 (checked with a dense Arnoldi);
+    Richardson is x <- x + w M (b - A x), written out directly."""
+    A, dinv, b, xe, cg = _system()
+    n = b.size
+    Af, Mf = (lambda x: A @ x), (lambda r: dinv * r)
+    x = np.zeros(n)
+    for _ in range(7):
+        x = x + 0.8 * (dinv * (b - A @ x))
+    r = K.richardson(Af, Mf, b, rtol=0.0, atol=-1.0, maxit=7, relaxation=0.8)
+    assert np.max(np.abs(r["x"] - x)) <= 1e-12 * np.max(np.abs(x))
+    # dense Arnoldi on the left-preconditioned operator (lfom.f90 works on inv(M) A)
+    m = 12
+    B = lambda v: dinv * (A @ v)
+    r0 = dinv * b
+    V = np.zeros((n, m + 1)); H = np.zeros((m + 1, m))
+    beta = np.linalg.norm(r0); V[:, 0] = r0 / beta
+    for j in range(m):
+        w = B(V[:, j])
+        for i in range(j + 1):
+            H[i, j] = V[:, i] @ w; w -= H[i, j] * V[:, i]
+        for i in range(j + 1):                       # one re-orthogonalisation pass
+            c = V[:, i] @ w; H[i, j] += c; w -= c * V[:, i]
+        H[j + 1, j] = np.linalg.norm(w); V[:, j + 1] = w / H[j + 1, j]
+    y = np.linalg.solve(H[:m, :m], beta * np.eye(m)[:, 0])
+    xf = V[:, :m] @ y
+    r = K.lfom(Af, Mf, b, rtol=0.0, atol=-1.0, maxit=m, dkrymax=m)
+    assert np.max(np.abs(r["x"] - xf)) <= 1e-8 * np.max(np.abs(xf))
