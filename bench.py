@@ -396,6 +396,7 @@ def main():
                  "pattern_classes": phase("spmv_classes"), "classes_setup_ms": phase("spmv_classes_ms")}
     asm_info = {"owner_cells_gather": phase("gather_fast_cells"), "cells_scatter": phase("gather_slow_cells"),
                 "rows_scatter": phase("gather_slow_rows")}
+    # per-rank timeline of the overlapped par apply (FB2_PAR_TIMELINE=1): gathered from every rank after the timed steps
     asm_ms, cg_ms, spmv_ms, jac_ms = [], [], [], []
     with ClockSampler(local) as clk:
         t0 = time.perf_counter()
@@ -504,6 +505,14 @@ def main():
                    "d2h_bytes_per_step": int(n_glob_rows * 8),
                    "what": "fb2_fe_space_set_source_values (H2D f(x_q) samples) + fb2_integrate_assemble + fb2_vec_get of the RHS"}
 
+    timeline = None
+    if world > 1 and os.environ.get("FB2_PAR_TIMELINE", "0") != "0":
+        names = ("par_itf_ms", "par_exchange_ms", "par_interior_ms", "par_exposed_wait_ms", "par_rest_ms")
+        mine = torch.tensor([phase(k) or 0.0 for k in names] + [float(np.mean(spmv_ms)) / a.cg_iters, float(np.mean(cg_ms)) / a.cg_iters],
+                            dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        timeline = {"columns": list(names) + ["spmv_apply_ms", "pcg_iteration_ms"], "per_rank": [[float(v) for v in t.cpu()] for t in allr]}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -570,7 +579,7 @@ def main():
             # kernels here 11 n (x/r update with four partial dots: 4 reads + 2 writes + dinv; p update: 3 reads + 1 write)
             "pcg_vector_bytes_per_iteration": {"reference_unfused": int(18 * 8 * n_glob_rows), "fused": int(11 * 8 * n_glob_rows),
                                                "measured_ms": (cg_t / a.cg_iters) - spmv_t},
-            "clocks": clk.summary(), "e2e": e2e, "e2e_assembly": e2e_asm,
+            "clocks": clk.summary(), "e2e": e2e, "e2e_assembly": e2e_asm, "par_timeline": timeline,
             # kernels of libfempar_b200.so per step: Dirichlet interpolation + memsets/assembly (4), Jacobi set-up (2), PCG set-up
             # (9), then per PCG iteration: serial 6 (SpMV, 2 partial reductions, x/r update, scalars, p update); par 14 (two
             # SpMV launches, 4 pack/unpack kernels, interface dot, reductions, updates; NCCL's own kernels not counted)

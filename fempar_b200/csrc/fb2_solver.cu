@@ -479,6 +479,49 @@ __global__ void k_cg_init_state(CgState* st, double rz, double tol, double tol_e
   st->iter = 0; st->converged = 0; st->done = 0; st->maxit = maxit; st->crit = crit;
 }
 
+// Per-rank timeline of the overlapped par apply (FB2_PAR_TIMELINE=1): events after the interface tiles, after the halo exchange
+// (comm stream), after the interior tiles and after the wait for the exchange, for every iteration of fb2_pcg_iterate[_multi];
+// averaged and published as phases par_itf_ms / par_exchange_ms / par_interior_ms / par_exposed_wait_ms / par_rest_ms.
+struct ParTimeline {
+  bool on = false;
+  std::vector<cudaEvent_t> ev;     // 6 per iteration: start, itf_done, halo_done (comm stream), interior_done, wait_done, iter_end
+  int iters = 0;
+  void begin(int n_iterations) {
+    on = n_iterations > 0 && getenv("FB2_PAR_TIMELINE") && atoi(getenv("FB2_PAR_TIMELINE")) != 0;
+    if (!on) return;
+    for (cudaEvent_t e : ev) cudaEventDestroy(e);
+    ev.assign((size_t)6 * n_iterations, nullptr);
+    for (auto& e : ev) cudaEventCreate(&e);
+    iters = 0;
+  }
+  cudaEvent_t at(int k) { return on && (size_t)(6 * iters + k) < ev.size() ? ev[6 * iters + k] : nullptr; }
+  void mark(int k, cudaStream_t st) {
+    cudaEvent_t e = at(k);
+    if (!e) return;
+    if (k == 0) marked = true;
+    if (marked) cudaEventRecord(e, st);      // iterations that do not take the overlapped branch are not counted
+  }
+  bool marked = false;
+  void next() { if (on && marked) ++iters; marked = false; }
+  void publish() {
+    if (!on || iters == 0) return;
+    double acc[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < iters; ++i) {
+      float t;
+      cudaEvent_t* e = &ev[6 * i];
+      cudaEventElapsedTime(&t, e[0], e[1]); acc[0] += t;     // interface tiles
+      cudaEventElapsedTime(&t, e[1], e[2]); acc[1] += t;     // halo exchange (pack, send/recv x2, unpack) on the comm stream
+      cudaEventElapsedTime(&t, e[1], e[3]); acc[2] += t;     // interior tiles
+      cudaEventElapsedTime(&t, e[3], e[4]); acc[3] += t;     // exchange not hidden behind the interior tiles
+      cudaEventElapsedTime(&t, e[4], e[5]); acc[4] += t;     // dots, all-reduces, vector updates
+    }
+    const char* names[5] = {"par_itf_ms", "par_exchange_ms", "par_interior_ms", "par_exposed_wait_ms", "par_rest_ms"};
+    for (int k = 0; k < 5; ++k) fb2_record_phase(names[k], acc[k] / iters);
+    on = false;
+  }
+};
+static ParTimeline g_tl;
+
 static int g_cg_icg = 0;   // 1 while fb2_ils_solve runs the ICG variant (icg.f90) through the fused CG kernels
 void fb2_cg_set_icg(int on) { g_cg_icg = on; }
 
@@ -560,13 +603,18 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
     static cudaEvent_t ev_itf = nullptr, ev_halo = nullptr;
     if (!ev_itf) { cudaEventCreateWithFlags(&ev_itf, cudaEventDisableTiming); cudaEventCreateWithFlags(&ev_halo, cudaEventDisableTiming); }
     cudaStream_t cs = fb2_comm_stream();
+    g_tl.mark(0, s);
     FB2_TRY(fb2_spmv_stream_range(A, W.p, W.Ap, false, &W.st->done, t_itf, A->spmv_ntiles, 0, nullptr, nullptr));
     FB2_CUDA(cudaEventRecord(ev_itf, s));
+    g_tl.mark(1, s);
     FB2_CUDA(cudaStreamWaitEvent(cs, ev_itf, 0));
     FB2_TRY(fb2_import_exchange_on(A->s->imp, W.Ap, cs));
     FB2_CUDA(cudaEventRecord(ev_halo, cs));
+    g_tl.mark(2, cs);
     FB2_TRY(fb2_spmv_stream_range(A, W.p, W.Ap, true, &W.st->done, 0, t_itf, g_par_chunk, part, &g));
+    g_tl.mark(3, s);
     FB2_CUDA(cudaStreamWaitEvent(s, ev_halo, 0));
+    g_tl.mark(4, s);
     if (ev_spmv1) cudaEventRecord(ev_spmv1, s);
     int gd = 0;
     if (row_itf < n) {
@@ -589,6 +637,7 @@ static int cg_enqueue_iteration(fb2_matrix_t A, const double* dinv, const double
   if (par) FB2_TRY(fb2_allreduce_sum(&W.st->rr, 4));
   k_cg_scalars<<<1, 1, 0, s>>>(W.st, hist, hist ? hist + W.hist_cap : nullptr);
   k_cg_update_p<<<vec_grid(n), 256, 0, s>>>(n, W.st, W.r, dinv, W.p);
+  g_tl.mark(5, s); g_tl.next();
   FB2_CUDA(cudaGetLastError());
   return 0;
 }
@@ -764,11 +813,14 @@ extern "C" int fb2_pcg_iterate(fb2_matrix_t A, fb2_vector_t dinv, fb2_vector_t b
   FB2_TRY(cg_setup(A, dinv ? dinv->d : nullptr, w, b->d, x->d, par, 0.0, -1.0, n_iterations + 1, FB2_STOP_RES_RES));
   std::vector<cudaEvent_t> ev(2 * (size_t)n_iterations + 2);
   for (auto& e : ev) cudaEventCreate(&e);
+  g_tl.begin(par ? n_iterations : 0);
   cudaEventRecord(ev[2 * n_iterations], s);
   for (int k = 0; k < n_iterations; ++k)
     FB2_TRY(cg_enqueue_iteration(A, dinv ? dinv->d : nullptr, w, x->d, par, nullptr, ev[2 * k], ev[2 * k + 1]));
   cudaEventRecord(ev[2 * n_iterations + 1], s);
   FB2_CUDA(cudaStreamSynchronize(s));
+  FB2_CUDA(cudaStreamSynchronize(fb2_comm_stream()));
+  g_tl.publish();
   float ms = 0, acc = 0;
   cudaEventElapsedTime(&ms, ev[2 * n_iterations], ev[2 * n_iterations + 1]);
   for (int k = 0; k < n_iterations; ++k) {
@@ -970,6 +1022,7 @@ static int multi_cg_iteration(const MultiCtx& C, MultiWork& M, fb2_vector_t* din
   static cudaEvent_t ev_itf = nullptr, ev_halo = nullptr;
   if (!ev_itf) { cudaEventCreateWithFlags(&ev_itf, cudaEventDisableTiming); cudaEventCreateWithFlags(&ev_halo, cudaEventDisableTiming); }
   if (ev0) cudaEventRecord(ev0, s);
+  g_tl.mark(0, s);
   std::vector<i64> t_itf(np), row_itf(np);
   std::vector<double*> aps(np);
   for (int i = 0; i < np; ++i) {
@@ -979,9 +1032,11 @@ static int multi_cg_iteration(const MultiCtx& C, MultiWork& M, fb2_vector_t* din
     aps[i] = W.Ap;
   }
   FB2_CUDA(cudaEventRecord(ev_itf, s));
+  g_tl.mark(1, s);
   FB2_CUDA(cudaStreamWaitEvent(cs, ev_itf, 0));
   FB2_TRY(exchange_multi(C, aps.data(), cs));
   FB2_CUDA(cudaEventRecord(ev_halo, cs));
+  g_tl.mark(2, cs);
   int off = 0;
   for (int i = 0; i < np; ++i) {
     CgWork& W = *M.parts[i];
@@ -989,7 +1044,9 @@ static int multi_cg_iteration(const MultiCtx& C, MultiWork& M, fb2_vector_t* din
     FB2_TRY(fb2_spmv_stream_range(C.A[i], W.p, W.Ap, true, &M.st->done, 0, t_itf[i], g_par_chunk, part + off, &g));
     off += g;
   }
+  g_tl.mark(3, s);
   FB2_CUDA(cudaStreamWaitEvent(s, ev_halo, 0));
+  g_tl.mark(4, s);
   if (ev1) cudaEventRecord(ev1, s);
   for (int i = 0; i < np; ++i) {
     CgWork& W = *M.parts[i];
@@ -1018,6 +1075,7 @@ static int multi_cg_iteration(const MultiCtx& C, MultiWork& M, fb2_vector_t* din
     CgWork& W = *M.parts[i];
     k_cg_update_p<<<vec_grid(W.n), 256, 0, s>>>(W.n, M.st, W.r, dinv ? dinv[i]->d : nullptr, W.p);
   }
+  g_tl.mark(5, s); g_tl.next();
   FB2_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1066,10 +1124,13 @@ extern "C" int fb2_pcg_iterate_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv
   FB2_TRY(multi_cg_setup(C, M, dinv, b, x, 0.0, -1.0, n_iterations + 1, FB2_STOP_RES_RES));
   std::vector<cudaEvent_t> ev(2 * (size_t)n_iterations + 2);
   for (auto& e : ev) cudaEventCreate(&e);
+  g_tl.begin(n_iterations);
   cudaEventRecord(ev[2 * n_iterations], s);
   for (int k = 0; k < n_iterations; ++k) FB2_TRY(multi_cg_iteration(C, M, dinv, x, nullptr, ev[2 * k], ev[2 * k + 1]));
   cudaEventRecord(ev[2 * n_iterations + 1], s);
   FB2_CUDA(cudaStreamSynchronize(s));
+  FB2_CUDA(cudaStreamSynchronize(fb2_comm_stream()));
+  g_tl.publish();
   float ms = 0, acc = 0;
   cudaEventElapsedTime(&ms, ev[2 * n_iterations], ev[2 * n_iterations + 1]);
   for (int k = 0; k < n_iterations; ++k) { float m1 = 0; cudaEventElapsedTime(&m1, ev[2 * k], ev[2 * k + 1]); acc += m1; }
