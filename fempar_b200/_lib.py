@@ -60,6 +60,8 @@ _SIGS = {
     "fb2_csr_get_values": [_VP, _VP],
     "fb2_csr_set_values": [_VP, _VP],
     "fb2_integrate_assemble": [_VP, _VP, C.c_int, C.c_int, _VP, _VP, C.c_int],
+    "fb2_integrate_residual": [_VP, _VP, C.c_int, _VP, C.c_double, _VP],
+    "fb2_integrate_tangent": [_VP, _VP, C.c_int, _VP, C.c_double],
     "fb2_spmv": [_VP, _VP, _VP],
     "fb2_extract_diagonal": [_VP, _VP],
     "fb2_set_spmv_variant": [C.c_int],

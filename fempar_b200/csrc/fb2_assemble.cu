@@ -487,3 +487,166 @@ extern "C" int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const do
   *l2_norm = all[2];
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// fe_operator_t residual / tangent at an evaluation point: what compute_internal_residual ->
+// discrete_integration%integrate_residual and compute_tangent -> integrate_tangent do for a non-linear operator
+// (sbm_fe_operator.i90:568-639; integrate_residual of test_transient_poisson_discrete_integration.f90:248-319 is the
+// beta = 0 case).  Device integrand: quasi-linear diffusion  -div(k(u) grad u) = f,  k(u) = 1 + beta u^2:
+//   residual_i = sum_K int  k(u_h) grad u_h . grad phi_i  -  f phi_i
+//   tangent_ij = sum_K int  k(u_h) grad phi_j . grad phi_i  +  k'(u_h) phi_j grad u_h . grad phi_i        (not symmetric)
+// u_h = the fe_function of the evaluation point: free DOF values from `u`, strong Dirichlet values from fixed_dof_values
+// (fe_cell_function_scalar_t%update, as the reference's u_h%update(fe, fe_function)).  Warp per cell, lanes over the quadrature
+// points for the geometry and u_h(q), grad u_h(q); then lanes over the rows (residual) or the (i, j) pairs (tangent).
+// ------------------------------------------------------------------------------------------
+template <bool TANGENT>
+__global__ void __launch_bounds__(128) k_integrate_nonlinear(AsmArgs A, const double* __restrict__ u, double beta, double* residual,
+                                                             int cells_in_launch) {
+  extern __shared__ double sm[];
+  const int nq = A.nq, nn = A.nn;
+  double* s_dphi = sm;                      // [nq][nn][3]
+  double* s_phi = s_dphi + nq * nn * 3;     // [nq][nn]
+  double* s_warp = s_phi + nq * nn;
+  const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per_warp = nq * 15 + nn + ((nn + 1) / 2);   // Jinv[9] wd uq gu[3] fw | u_local | gid(int)
+  double* w_Ji = s_warp + (size_t)w * per_warp;   // [nq][9]
+  double* w_wd = w_Ji + nq * 9;                   // [nq]
+  double* w_uq = w_wd + nq;                       // [nq]
+  double* w_gu = w_uq + nq;                       // [nq][3]
+  double* w_fw = w_gu + nq * 3;                   // [nq]
+  double* w_ul = w_fw + nq;                       // [nn]
+  int* w_gid = (int*)(w_ul + nn);                 // [nn]
+  for (int i = threadIdx.x; i < nq * nn * 3; i += blockDim.x) s_dphi[i] = A.dphi[i];
+  for (int i = threadIdx.x; i < nq * nn; i += blockDim.x) s_phi[i] = A.phi[i];
+  __syncthreads();
+  for (int ci = blockIdx.x * warps + w; ci < cells_in_launch; ci += gridDim.x * warps) {
+    int c;
+    double X[8][3];
+    if (A.coords) {
+      c = ci;
+      cell_vertices_from(A.coords, c, X);
+    } else {
+      int ijk[3] = {ci % A.g.nloc[0] + A.g.L[0], (ci / A.g.nloc[0]) % A.g.nloc[1] + A.g.L[1],
+                    ci / (A.g.nloc[0] * A.g.nloc[1]) + A.g.L[2]};
+      int lex = ijk[0] + A.g.ntot[0] * (ijk[1] + A.g.ntot[1] * ijk[2]);
+      c = A.perm ? A.perm[lex] : lex;
+      cell_vertices(A.g, ijk, X);
+    }
+    for (int l = lane; l < nn; l += 32) {
+      const int g = A.gids[(i64)c * A.nd + l];
+      w_gid[l] = g;
+      w_ul[l] = g > 0 ? u[g - 1] : (g < 0 ? A.fixed[-g - 1] : 0.0);
+    }
+    __syncwarp();
+    for (int q = lane; q < nq; q += 32) {
+      double inv[3][3], det;
+      jacobian_at(X, A.gdphi + q * 24, inv, det);
+      const double wd = det * A.qw[q];
+      double uq = 0.0, gr[3] = {0, 0, 0};
+      for (int a = 0; a < nn; ++a) {
+        uq += w_ul[a] * s_phi[q * nn + a];
+        for (int k = 0; k < 3; ++k) gr[k] += w_ul[a] * s_dphi[(q * nn + a) * 3 + k];
+      }
+      for (int i = 0; i < 3; ++i) {
+        for (int j = 0; j < 3; ++j) w_Ji[q * 9 + i * 3 + j] = inv[i][j];
+        w_gu[q * 3 + i] = inv[i][0] * gr[0] + inv[i][1] * gr[1] + inv[i][2] * gr[2];     // physical gradient of u_h
+      }
+      w_wd[q] = wd; w_uq[q] = uq;
+      double f;
+      if (A.src_qp) f = A.src_qp[(i64)c * nq + q];
+      else {
+        double xq[3] = {0, 0, 0};
+        for (int a = 0; a < 8; ++a)
+          for (int k = 0; k < 3; ++k) xq[k] += A.gphi[q * 8 + a] * X[a][k];
+        f = func_f(A.fn, xq);
+      }
+      w_fw[q] = wd * f;
+    }
+    __syncwarp();
+    if (!TANGENT) {
+      for (int i = lane; i < nn; i += 32) {
+        const int gi = w_gid[i];
+        if (gi <= 0 || gi > A.n_free) continue;
+        double r = 0.0;
+        for (int q = 0; q < nq; ++q) {
+          const double* ri = s_dphi + (q * nn + i) * 3;
+          const double* Ji = w_Ji + q * 9;
+          double d = 0.0;
+          for (int k = 0; k < 3; ++k) d += (Ji[k * 3] * ri[0] + Ji[k * 3 + 1] * ri[1] + Ji[k * 3 + 2] * ri[2]) * w_gu[q * 3 + k];
+          const double uq = w_uq[q];
+          r += w_wd[q] * (1.0 + beta * uq * uq) * d - w_fw[q] * s_phi[q * nn + i];
+        }
+        atomicAdd(&residual[gi - 1], r);
+      }
+    } else {
+      for (int e = lane; e < nn * nn; e += 32) {
+        const int ni = e % nn, nj = e / nn;
+        const int gi = w_gid[ni], gj = w_gid[nj];
+        if (gi <= 0 || gi > A.n_free || gj <= 0 || gj > A.n_free) continue;   // tangent with respect to the free DOFs
+        double s = 0.0;
+        for (int q = 0; q < nq; ++q) {
+          const double* ri = s_dphi + (q * nn + ni) * 3;
+          const double* rj = s_dphi + (q * nn + nj) * 3;
+          const double* Ji = w_Ji + q * 9;
+          double dij = 0.0, diu = 0.0;
+          for (int k = 0; k < 3; ++k) {
+            const double gik = Ji[k * 3] * ri[0] + Ji[k * 3 + 1] * ri[1] + Ji[k * 3 + 2] * ri[2];
+            const double gjk = Ji[k * 3] * rj[0] + Ji[k * 3 + 1] * rj[1] + Ji[k * 3 + 2] * rj[2];
+            dij += gik * gjk; diu += gik * w_gu[q * 3 + k];
+          }
+          const double uq = w_uq[q];
+          s += w_wd[q] * ((1.0 + beta * uq * uq) * dij + 2.0 * beta * uq * s_phi[q * nn + nj] * diu);
+        }
+        const i64 b = A.irp[gi - 1], end = A.irp[gi];
+        const i64 slot = find_slot(A.ja, b, end, gj);
+        if (slot < end && A.ja[slot] == gj) atomicAdd(&A.val[slot], s);
+      }
+    }
+    __syncwarp();
+  }
+}
+
+static int nonlinear_launch(fb2_matrix_t A, fb2_vector_t u, int func, const double* func_params, double beta, fb2_vector_t residual,
+                            bool tangent) {
+  FB2_CHECK(A && u && u->n == A->n, "evaluation point size mismatch");
+  fb2_space_s* s = A->s;
+  FB2_CHECK(s && s->d_gids && s->rt.ncomp == 1, "the non-linear integrand is defined for scalar spaces with cell DOF lists");
+  FB2_CHECK(!A->sym, "the tangent of the quasi-linear operator is not symmetric: full storage required");
+  AsmArgs a;
+  a.g = make_geom(s);
+  a.p = s->rt.p; a.nn = s->rt.nnode; a.ncomp = 1; a.nd = s->rt.ndofs; a.nq = s->rt.nq;
+  a.perm = s->d_perm; a.gids = s->d_gids; a.coords = s->d_coords; a.fixed = s->d_fixed; a.src_qp = s->d_src_qp;
+  a.qw = s->d_qw; a.phi = s->d_phi; a.dphi = s->d_dphi; a.gphi = s->d_gphi; a.gdphi = s->d_gdphi;
+  a.irp = A->d_irp; a.ja = A->d_ja; a.val = A->d_val; a.rhs = nullptr; a.n_free = A->n;
+  a.kind = FB2_KIND_POISSON; a.sym = 0; a.color = -1; a.fn = make_func(func, func_params); a.lambda = 0; a.mu = 0;
+  cudaStream_t st = fb2_stream();
+  const int warps = 4, nq = a.nq, nn = a.nn;
+  const size_t per_warp = (size_t)nq * 15 + nn + ((nn + 1) / 2);
+  const size_t smem = sizeof(double) * ((size_t)nq * nn * 4 + per_warp * warps);
+  FB2_CHECK(smem <= 227 * 1024, "reference tables do not fit in shared memory for this order");
+  int blocks = fb2_num_sms() * 4;
+  if ((i64)blocks * warps > s->m.n_local) blocks = (s->m.n_local + warps - 1) / warps;
+  if (blocks < 1) blocks = 1;
+  if (tangent) {
+    FB2_CUDA(cudaFuncSetAttribute(k_integrate_nonlinear<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    FB2_CUDA(cudaMemsetAsync(A->d_val, 0, sizeof(double) * (size_t)A->nnz, st));
+    k_integrate_nonlinear<true><<<blocks, warps * 32, smem, st>>>(a, u->d, beta, nullptr, s->m.n_local);
+  } else {
+    FB2_CHECK(residual && residual->n == A->n, "residual size mismatch");
+    FB2_CUDA(cudaFuncSetAttribute(k_integrate_nonlinear<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    FB2_CUDA(cudaMemsetAsync(residual->d, 0, sizeof(double) * (size_t)residual->n, st));
+    k_integrate_nonlinear<false><<<blocks, warps * 32, smem, st>>>(a, u->d, beta, residual->d, s->m.n_local);
+    // par: the residual is assembled across parts like the RHS (par_sparse_assembler.f90:171-176)
+    if (s->imp && fb2_comm_active() && fb2_comm_parts_per_rank() == 1) FB2_TRY(fb2_import_exchange(s->imp, residual->d));
+  }
+  FB2_CUDA(cudaGetLastError());
+  FB2_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+extern "C" int fb2_integrate_residual(fb2_matrix_t A, fb2_vector_t u, int func, const double* func_params, double beta,
+                                      fb2_vector_t residual) {
+  return nonlinear_launch(A, u, func, func_params, beta, residual, false);
+}
+extern "C" int fb2_integrate_tangent(fb2_matrix_t A, fb2_vector_t u, int func, const double* func_params, double beta) {
+  return nonlinear_launch(A, u, func, func_params, beta, nullptr, true);
+}

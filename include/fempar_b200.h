@@ -264,6 +264,18 @@ int fb2_pcg_solve_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv /*NULL = ide
 int fb2_pcg_iterate_multi(int np, fb2_matrix_t* A, fb2_vector_t* dinv, fb2_vector_t* b, fb2_vector_t* x, int n_iterations,
                           double* ms_total, double* ms_spmv);
 
+/* ---- fe_operator_t residual / tangent at an evaluation point -----------------------------------
+ * compute_internal_residual -> discrete_integration%integrate_residual and compute_tangent -> integrate_tangent
+ * (Integration/FEOperator/sbm_fe_operator.i90:568-639) for the quasi-linear diffusion operator -div(k(u) grad u) = f,
+ * k(u) = 1 + beta u^2 (beta = 0: integrate_residual of Tests/Serial/test_transient_poisson/modules/
+ * test_transient_poisson_discrete_integration.f90:248-319).  u = free DOF values of the evaluation point (strong Dirichlet
+ * values come from the space's fixed_dof_values); f = the analytic selector, or the user samples of
+ * fb2_fe_space_set_source_values.  residual: free rows, comm()'ed in par.  tangent: written into A's values (full storage;
+ * derivatives with respect to the free DOFs). */
+int fb2_integrate_residual(fb2_matrix_t A, fb2_vector_t u, int func, const double* func_params, double beta,
+                           fb2_vector_t residual);
+int fb2_integrate_tangent(fb2_matrix_t A, fb2_vector_t u, int func, const double* func_params, double beta);
+
 /* ---- error norms: sqrt(sum_K int |grad(u-u_h)|^2), sqrt(int (u-u_h)^2) ----- */
 int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double* h1_seminorm,
                     double* l2_norm);
