@@ -189,12 +189,15 @@ extern "C" int fb2_integrate_assemble(fb2_matrix_t A, fb2_vector_t rhs, int kind
   const bool host_built = s->d_coords != nullptr;   // no lattice: generic kernel, slots by binary search, atomic scatter
   FB2_CHECK(s->d_gids != nullptr, "this space has no cell DOF lists (bare space): use fb2_assemble_batch");
   if (host_built) scatter_variant = FB2_SCATTER_ATOMIC;
-  if (g_asm_variant != 1 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) FB2_TRY(fb2_build_scatter_map(A));
+
   // row-owner gather path (scalar Q2 Laplacian on structured parts): plan + verification are set-up as well
   bool rows_path = false;
-  if (g_asm_variant == 0 && scatter_variant == FB2_SCATTER_ATOMIC && !host_built) {
-    FB2_TRY(fb2_rows_prepare(A, kind));
-    rows_path = A->rows_state == 1 && A->map_state == 1;
+  if (g_asm_variant == 0 && scatter_variant == FB2_SCATTER_ATOMIC && !host_built) FB2_TRY(fb2_rows_prepare(A, kind));
+  // the scatter map is set-up too: with the row-owner plan only the cells left to the scatter kernel need verified tables
+  if (g_asm_variant != 1 && s->rt.p <= 3 && !(kind == FB2_KIND_ELASTICITY && s->rt.p > 2)) {
+    const bool rows_ok = g_asm_variant == 0 && scatter_variant == FB2_SCATTER_ATOMIC && A->rows_state == 1;
+    FB2_TRY(fb2_build_scatter_map(A, rows_ok ? A->d_slow_cells : nullptr, rows_ok ? A->n_slow_cells : 0));
+    rows_path = rows_ok && A->map_state == 1;
   }
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);

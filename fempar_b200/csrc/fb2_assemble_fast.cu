@@ -67,11 +67,14 @@ __global__ void k_map_build(const int* __restrict__ cells, int nd, const int* __
 }
 
 // warp per cell: does the table assigned to the cell reproduce the slots of this cell?
+// (list != nullptr: only the listed cells -- total-box lexicographic ids -- are verified: the cells the scatter kernel will visit)
 __global__ void k_map_verify(int n_local, int nd, const int* __restrict__ gids, const i64* __restrict__ irp,
                              const int* __restrict__ ja, i64 n_free, int sym, const int* __restrict__ cell_tab,
-                             const unsigned short* __restrict__ tabs, int* bad_list, int* n_bad) {
+                             const unsigned short* __restrict__ tabs, int* bad_list, int* n_bad, const int* __restrict__ list,
+                             const int* __restrict__ perm) {
   const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int c = blockIdx.x * warps + w; c < n_local; c += gridDim.x * warps) {
+  for (int k = blockIdx.x * warps + w; k < n_local; k += gridDim.x * warps) {
+    const int c = list ? (perm ? perm[list[k]] : list[k]) : k;
     const int* g = gids + (i64)c * nd;
     const unsigned short* tab = tabs + (size_t)cell_tab[c] * nd * nd;
     bool bad = false;
@@ -95,8 +98,15 @@ __global__ void k_map_assign(const int* __restrict__ bad_list, int n_bad, int fi
   if (k < n_bad) cell_tab[bad_list ? bad_list[k] : k] = first_tab + k;   // bad_list == nullptr: identity (every cell)
 }
 
-int fb2_build_scatter_map(fb2_matrix_s* A) {
+// only_cells / n_only: when the row-owner kernel owns most rows, only the cells the scatter kernel visits need a verified table
+int fb2_build_scatter_map(fb2_matrix_s* A, const int* only_cells, int n_only) {
+  if (A->map_state == 1 && A->map_partial && !only_cells) {
+    // a map verified for the scatter cells only is now needed for every cell (e.g. the colored or scatter-only variant): rebuild
+    cudaFree(A->d_cell_tab); cudaFree(A->d_tabs);
+    A->d_cell_tab = nullptr; A->d_tabs = nullptr; A->map_state = 0; A->map_partial = 0;
+  }
   if (A->map_state != 0) return 0;
+  A->map_partial = only_cells ? 1 : 0;
   fb2_space_s* s = A->s;
   const int nd = s->rt.ndofs, n_local = s->m.n_local;
   cudaStream_t st = fb2_stream();
@@ -153,8 +163,8 @@ int fb2_build_scatter_map(fb2_matrix_s* A) {
   const size_t tab_elems = (size_t)nd * nd;
   FB2_TRY(fb2_dalloc(&d_ctabs, tab_elems * ncls));
   k_map_build<<<ncls, 256, 0, st>>>(d_reps, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym, d_ctabs);
-  k_map_verify<<<fb2_num_sms() * 8, 256, 0, st>>>(n_local, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym, A->d_cell_tab,
-                                                   d_ctabs, d_bad, d_nbad);
+  k_map_verify<<<fb2_num_sms() * 8, 256, 0, st>>>(only_cells ? n_only : n_local, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym,
+                                                   A->d_cell_tab, d_ctabs, d_bad, d_nbad, only_cells, s->d_perm);
   int nbad = 0;
   FB2_CUDA(cudaMemcpyAsync(&nbad, d_nbad, sizeof(int), cudaMemcpyDeviceToHost, st));
   FB2_CUDA(cudaStreamSynchronize(st));
@@ -599,7 +609,7 @@ int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant,
   const fb2_space_s* s = A->s;
   if (s->rt.p > 3) return -1;
   if (args.kind == FB2_KIND_ELASTICITY && (s->rt.ncomp != 3 || s->rt.p > 2)) return -1;   // Q3 elasticity: generic kernel
-  FB2_TRY(fb2_build_scatter_map(A));
+  FB2_TRY(fb2_build_scatter_map(A, nullptr, 0));
   if (A->map_state != 1) return -1;
   FB2_TRY(load_const_tables(s));
   FastArgs F;

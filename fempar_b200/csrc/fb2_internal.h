@@ -117,6 +117,7 @@ struct fb2_matrix_s {
   unsigned short* d_tabs = nullptr;   // [n_tabs][nd*nd] relative slots, 0xFFFF = entry not stored
   int common_tab = -1;                // table id of the interior position class
   int n_tabs = 0, n_class_tabs = 0, map_state = 0;   // map_state: 0 not built, 1 built, -1 unavailable (search fallback)
+  int map_partial = 0;                // 1: tables verified only for the cells the scatter kernel visits (row-owner hybrid)
   // row-owner gather assembly (fb2_assemble_rows.cu): owner cells whose chunk of rows verified against the plan are written by
   // plain stores; the remaining ("slow") rows are zeroed and accumulated by the scatter kernel over the cells touching them
   int rows_state = 0;                     // 0 not built, 1 usable, -1 unavailable
@@ -164,7 +165,7 @@ int fb2_dot_device(const double* x, const double* y, const double* w, i64 n, dou
 double* fb2_scratch_partials();   // device buffer of FB2_MAX_PARTIALS doubles x 4
 #define FB2_MAX_PARTIALS 65536
 
-int fb2_build_scatter_map(fb2_matrix_s* A);
+int fb2_build_scatter_map(fb2_matrix_s* A, const int* only_cells, int n_only);
 int fb2_rows_prepare(fb2_matrix_s* A, int kind);     // fb2_assemble_rows.cu: plan + per-cell verification (set-up)
 int fb2_rows_zero_slow(fb2_matrix_s* A);
 int fb2_assembly_variant();

@@ -51,9 +51,15 @@ module b200_sparse_assembler_names
      real(c_double) :: material(2)    = [0.0_c_double, 1.0_c_double]      ! lambda, mu
      class(scalar_function_t), pointer :: source_term => null()           ! any user function: sampled on the host
      type(c_ptr) :: space = c_null_ptr
+     ! non-linear operator (fe_operator_t): conductivity k(u) = 1 + beta u^2 and the free DOF values of the evaluation point
+     real(c_double) :: beta = 0.0_c_double
+     type(b200_scalar_array_t), pointer :: evaluation_point => null()
    contains
-     procedure :: set_source_term    => b200_discrete_integration_set_source_term
-     procedure :: integrate_galerkin => b200_discrete_integration_integrate_galerkin
+     procedure :: set_source_term          => b200_discrete_integration_set_source_term
+     procedure :: set_device_evaluation_point => b200_discrete_integration_set_device_evaluation_point
+     procedure :: integrate_galerkin       => b200_discrete_integration_integrate_galerkin
+     procedure :: integrate_residual       => b200_discrete_integration_integrate_residual
+     procedure :: integrate_tangent        => b200_discrete_integration_integrate_tangent
   end type b200_discrete_integration_t
 
   public :: b200_sparse_assembler_t, b200_discrete_integration_t
@@ -181,4 +187,48 @@ contains
       p = c_loc(a)
     end function c_loc_or_null
   end subroutine b200_discrete_integration_integrate_galerkin
+
+  ! fe_operator_t%set_evaluation_point hands the fe_function of the current point to the discrete integration
+  ! (sbm_fe_operator.i90:524-541); on the device it is the scalar array of its free DOF values
+  subroutine b200_discrete_integration_set_device_evaluation_point(this, free_dof_values)
+    class(b200_discrete_integration_t), intent(inout) :: this
+    type(b200_scalar_array_t), target , intent(in)    :: free_dof_values
+    this%evaluation_point => free_dof_values
+  end subroutine b200_discrete_integration_set_device_evaluation_point
+
+  ! integrate_residual (discrete_integration.f90:44-75; cell loop of test_transient_poisson_discrete_integration.f90:248-319
+  ! with k(u_h)): residual_i = sum_K int k(u_h) grad u_h . grad phi_i - f phi_i, into the assembler's array
+  subroutine b200_discrete_integration_integrate_residual(this, fe_space, assembler)
+    class(b200_discrete_integration_t), intent(in)    :: this
+    class(serial_fe_space_t)          , intent(inout) :: fe_space
+    class(assembler_t)                , intent(inout) :: assembler
+    real(c_double), target :: prm(5)
+    assert(associated(this%evaluation_point))
+    prm = this%func_params
+    select type(assembler)
+    class is (b200_sparse_assembler_t)
+       call b200_check(fb2_integrate_residual(assembler%b200_matrix%handle, this%evaluation_point%handle, this%func, c_loc(prm), &
+            this%beta, assembler%b200_array%handle))
+    class default
+       check(.false.)
+    end select
+  end subroutine b200_discrete_integration_integrate_residual
+
+  ! integrate_tangent: tangent_ij = sum_K int k(u_h) grad phi_j . grad phi_i + k'(u_h) phi_j grad u_h . grad phi_i, into the
+  ! assembler's matrix (same CSR graph; not symmetric: full storage)
+  subroutine b200_discrete_integration_integrate_tangent(this, fe_space, assembler)
+    class(b200_discrete_integration_t), intent(in)    :: this
+    class(serial_fe_space_t)          , intent(inout) :: fe_space
+    class(assembler_t)                , intent(inout) :: assembler
+    real(c_double), target :: prm(5)
+    assert(associated(this%evaluation_point))
+    prm = this%func_params
+    select type(assembler)
+    class is (b200_sparse_assembler_t)
+       call b200_check(fb2_integrate_tangent(assembler%b200_matrix%handle, this%evaluation_point%handle, this%func, c_loc(prm), &
+            this%beta))
+    class default
+       check(.false.)
+    end select
+  end subroutine b200_discrete_integration_integrate_tangent
 end module b200_sparse_assembler_names
