@@ -560,6 +560,7 @@ def main():
             "setup_ms": {"fe_space": space_t, "csr_pattern": pattern_t, "scatter_map": t_map_ms, "gather_plan": t_gather_ms,
                          "spmv_pattern_classes": spmv_info["classes_setup_ms"]},
             "spmv_tiles": spmv_info, "assembly_cells": asm_info,
+            "peer_allreduce": bool(phase("peer_allreduce")) if world > 1 else None,
             # one-shot create -> compute -> solve (what every reference driver does): set-up + the first (cold) step
             "cold_start_ms": space_t + pattern_t + first_t,
             "wall_ms_per_step": wall_t, "checksum": checksum,

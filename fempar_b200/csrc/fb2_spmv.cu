@@ -74,6 +74,10 @@ struct SpmvClassDesc {
   int delta[32];   // first column of the segment relative to the first row of the tile (even, so 16-byte aligned in x)
   int len[32];     // doubles, even
   int off[32];     // position of the segment in the window, doubles
+  // row schedule: which row of the tile lane group g handles in round rd (sched[rd * G + g], 0xFF: none).  Rows are dealt out
+  // by length so that the four (two, one) rows a warp multiplies together have the same number of entries: with rows in
+  // their natural order a Q2 warp holds rows of 27..125 entries and every lane loops for the longest (62 % lane utilisation)
+  unsigned char sched[64];
 };
 #define SPMV_NOCLASS 0xFF
 
@@ -205,8 +209,11 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     return;
   }
   // ---------------- consumer warps ----------------
-  const int TPR = NC / R;   // lanes per row: 4..32, power of two
-  const int row = tid / TPR, sub = tid - row * TPR;
+  // lanes per row: a function of the tile height only, so that the summation order of a row (and with it y, bit for bit) does
+  // not depend on the number of consumer threads or on the row schedule; G rows per round
+  const int TPR = COMP ? NC / R : 256 / R;
+  const int G = NC / TPR, rounds = (R + G - 1) / G;
+  const int grp = tid / TPR, sub = tid - grp * TPR;
   const int lane = tid & 31, w = tid >> 5;
   double dacc = 0.0;
   int it = 0;
@@ -248,40 +255,46 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       else return in_class ? sxw[sj16[k]] : x[sj[k] - 1];
     };
     const i64 e0a = s_e0a[s];
-    double acc = 0.0;
-    const bool live = row < s_nr[s];
-    // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
-    double xrow = 0.0;
-    if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
-    if (live && in_class) {
-      // shared memory only: a plain strided loop (no gather latency to batch against)
-      const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
+    const int nr = s_nr[s];
+    const unsigned char* sched = in_class ? cls_desc[s_cls[s]].sched : nullptr;
+    for (int rd = 0; rd < rounds; ++rd) {
+      const int slot = rd * G + grp;
+      const int row = sched ? (int)sched[slot] : slot;
+      double acc = 0.0;
+      const bool live = row < nr;
+      // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
+      double xrow = 0.0;
+      if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
+      if (live && in_class) {
+        // shared memory only: a plain strided loop (no gather latency to batch against)
+        const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
 #pragma unroll 4
-      for (int k = b + sub; k < e; k += TPR) acc += sv[k] * sxw[sj16[k]];
-    } else if (live) {
-      const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
-      int k = b + sub;
-      for (; k + 3 * TPR < e; k += 4 * TPR) {
-        const double x0 = xat(k), x1 = xat(k + TPR), x2 = xat(k + 2 * TPR), x3 = xat(k + 3 * TPR);
-        acc += sv[k] * x0;
-        acc += sv[k + TPR] * x1;
-        acc += sv[k + 2 * TPR] * x2;
-        acc += sv[k + 3 * TPR] * x3;
+        for (int k = b + sub; k < e; k += TPR) acc += sv[k] * sxw[sj16[k]];
+      } else if (live) {
+        const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
+        int k = b + sub;
+        for (; k + 3 * TPR < e; k += 4 * TPR) {
+          const double x0 = xat(k), x1 = xat(k + TPR), x2 = xat(k + 2 * TPR), x3 = xat(k + 3 * TPR);
+          acc += sv[k] * x0;
+          acc += sv[k + TPR] * x1;
+          acc += sv[k + 2 * TPR] * x2;
+          acc += sv[k + 3 * TPR] * x3;
+        }
+        if (k < e) {
+          // tail of up to 3 entries per lane as ONE masked batch, so that its gathers are in flight together
+          const int k1 = k + TPR, k2 = k + 2 * TPR;
+          const bool p1 = k1 < e, p2 = k2 < e;
+          const double x0 = xat(k), x1 = p1 ? xat(k1) : 0.0, x2 = p2 ? xat(k2) : 0.0;
+          acc += sv[k] * x0;
+          if (p1) acc += sv[k1] * x1;
+          if (p2) acc += sv[k2] * x2;
+        }
       }
-      if (k < e) {
-        // tail of up to 3 entries per lane as ONE masked batch, so that its gathers are in flight together
-        const int k1 = k + TPR, k2 = k + 2 * TPR;
-        const bool p1 = k1 < e, p2 = k2 < e;
-        const double x0 = xat(k), x1 = p1 ? xat(k1) : 0.0, x2 = p2 ? xat(k2) : 0.0;
-        acc += sv[k] * x0;
-        if (p1) acc += sv[k1] * x1;
-        if (p2) acc += sv[k2] * x2;
+      for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
+      if (sub == 0 && live) {
+        y[r0 + row] = acc;
+        if (FUSE_DOT) dacc += acc * xrow;
       }
-    }
-    for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
-    if (sub == 0 && live) {
-      y[r0 + row] = acc;
-      if (FUSE_DOT) dacc += acc * xrow;
     }
     // COMP: the consumers wrote xs[] through the generic proxy into a region the producer's next bulk copy (async proxy)
     // overwrites: order the two proxies before releasing the stage
@@ -496,8 +509,8 @@ __global__ void k_tile_hash(i64 ntiles, const i64* __restrict__ irp, const int* 
 // block per class: segments of the representative tile's distinct columns and the window position of every entry
 __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp, const int* __restrict__ ja,
                                                      const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
-                                                     const int* __restrict__ rep, int cap, SpmvClassDesc* desc,
-                                                     unsigned short* cls_idx, int* valid) {
+                                                     const int* __restrict__ rep, int cap, int G, int rounds,
+                                                     SpmvClassDesc* desc, unsigned short* cls_idx, int* valid) {
   __shared__ int sb[DICT_SORT_MAX], su[DICT_SORT_MAX];
   __shared__ int s_scan[256];
   __shared__ SpmvClassDesc D;
@@ -556,6 +569,26 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
     }
     if (total > xw_cap || total > 0xFFFF || idx_n > cap) ok = 0;
     D.nseg = nseg; D.idx_bytes = idx_n * 2; D.x_bytes = total * 8; D.pad = 0;
+    // row schedule: rows by decreasing length; round 0 takes the G longest in order, round 1 the next G in reverse order (the
+    // group that got the longest row gets the shortest next), and so on
+    {
+      const int nrt = tile_nrows[t];
+      unsigned char order[64];
+      int len[64];
+      for (int r = 0; r < 64; ++r) { order[r] = (unsigned char)r; len[r] = r < nrt ? (int)(irp[r0 + r + 1] - irp[r0 + r]) : -1; }
+      for (int a = 1; a < nrt; ++a) {                 // insertion sort, stable
+        const unsigned char oa = order[a];
+        int b2 = a - 1;
+        while (b2 >= 0 && len[order[b2]] < len[oa]) { order[b2 + 1] = order[b2]; --b2; }
+        order[b2 + 1] = oa;
+      }
+      for (int k = 0; k < 64; ++k) D.sched[k] = (rounds == 0 && k < nrt) ? (unsigned char)k : 0xFF;   // rounds == 0: natural order
+      for (int rd = 0; rd < rounds; ++rd)
+        for (int g = 0; g < G; ++g) {
+          const int pos = rd * G + ((rd & 1) ? G - 1 - g : g);
+          if (rd * G + g < 64 && pos < nrt) D.sched[rd * G + g] = order[pos];
+        }
+    }
     for (int g = nseg; g < 32; ++g) { D.delta[g] = 0; D.len[g] = 0; D.off[g] = 0; }
     s_ok = ok;
   }
@@ -679,7 +712,10 @@ static int spmv_build_classes(fb2_matrix_s* A) {
     FB2_CUDA(fb2_memcpy(d_ch, h_ch.data(), sizeof(unsigned long long) * (size_t)ncls, cudaMemcpyHostToDevice));
     FB2_CUDA(fb2_memcpy(d_rep, h_rep.data(), sizeof(int) * (size_t)ncls, cudaMemcpyHostToDevice));
     FB2_CUDA(cudaMemsetAsync(d_nin, 0, sizeof(unsigned long long), st));
-    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap,
+    // FB2_SPMV_SCHED=0: rows in their natural order (A/B of the row schedule)
+    const bool sched_on = !(getenv("FB2_SPMV_SCHED") && atoi(getenv("FB2_SPMV_SCHED")) == 0);
+    const int tpr = 256 / A->spmv_R, G = A->spmv_nc / tpr, rounds = sched_on ? (A->spmv_R + G - 1) / G : 0;
+    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap, G, rounds,
                                         (SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, d_valid);
     k_tile_classify<<<fb2_num_sms() * 8, 256, 0, st>>>(nt, A->n, A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, hash, ncls, d_ch,
                                                         d_rep, d_valid, (const SpmvClassDesc*)A->d_cls_desc, A->d_tile_class, d_nin);
