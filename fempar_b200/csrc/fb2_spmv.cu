@@ -69,7 +69,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // The class of a tile is never assumed: fb2_spmv_build_classes compares every tile entry by entry with the representative
 // of its class and checks the segment bounds; everything else streams ja as before.  Products are formed in the same
 // order from the same operands, so y is bit-identical to the ja path (tests: test_midsize_spmv_variants_bitwise).
-struct SpmvClassDesc {
+struct __align__(16) SpmvClassDesc {
   int nseg, idx_bytes, x_bytes, pad;
   int delta[32];   // first column of the segment relative to the first row of the tile (even, so 16-byte aligned in x)
   int len[32];     // doubles, even
@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
   const size_t dict_off = xs_off + (size_t)SPMV_DS * 4;
   const size_t irp_off = xs_off + (COMP ? (size_t)SPMV_DS * 8 : 0);
   (void)dcap;
-  const size_t stage_bytes = irp_off + irp_bytes;
+  const size_t sched_off = irp_off + irp_bytes;       // 64 bytes: the row schedule of a class tile (copied with the tile)
+  const size_t stage_bytes = sched_off + 64;
   // tiles of this CTA: persistent (chunk == 0): blockIdx.x, blockIdx.x + gridDim.x, ... ; chunked: `chunk` consecutive tiles
   const i64 t_first = chunk ? (i64)blockIdx.x * chunk : (i64)blockIdx.x;
   const i64 t_step = chunk ? 1 : (i64)gridDim.x;
@@ -175,8 +176,9 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
           // still there (only index / ja copies write that region) and is not copied again
           const bool have_idx = s_lastcls[s] == cls;
           s_lastcls[s] = cls;
-          mbar_expect_tx(&full_bar[s], cnt4 * 8u + (have_idx ? 0u : (uint32_t)D.idx_bytes) + (uint32_t)D.x_bytes + (uint32_t)irp_bytes);
+          mbar_expect_tx(&full_bar[s], cnt4 * 8u + (have_idx ? 0u : (uint32_t)D.idx_bytes) + (uint32_t)D.x_bytes + (uint32_t)irp_bytes + 64u);
           bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
+          bulk_g2s(base + sched_off, D.sched, 64u, &full_bar[s]);
           if (cnt4) bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
           if (!have_idx) bulk_g2s(base + (size_t)cap * 8, cls_idx + (size_t)cls * cap, (uint32_t)D.idx_bytes, &full_bar[s]);
         } else {
@@ -256,7 +258,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     };
     const i64 e0a = s_e0a[s];
     const int nr = s_nr[s];
-    const unsigned char* sched = in_class ? cls_desc[s_cls[s]].sched : nullptr;
+    const unsigned char* sched = in_class ? base + sched_off : nullptr;
     for (int rd = 0; rd < rounds; ++rd) {
       const int slot = rd * G + grp;
       const int row = sched ? (int)sched[slot] : slot;
@@ -442,7 +444,7 @@ static int spmv_compress(fb2_matrix_s* A, int capbuf, int R, int STAGES) {
   FB2_CUDA(fb2_memcpy(&total, A->d_dict_ptr + nt, sizeof(i64), cudaMemcpyDeviceToHost));
   FB2_CUDA(fb2_memcpy(&dcap, d_max, sizeof(int), cudaMemcpyDeviceToHost));
   cudaFree(cnt); cudaFree(d_max);
-  const size_t smem = ((size_t)capbuf * 10 + (size_t)SPMV_DS * 8 + (size_t)(R + 2) * 8) * STAGES;
+  const size_t smem = ((size_t)capbuf * 10 + (size_t)SPMV_DS * 8 + (size_t)(R + 2) * 8 + 64) * STAGES;
   // worth it only when the dictionaries are small next to the 2 B per entry they save, and the stage still fits
   bool ok = dcap > 0 && smem <= 200 * 1024 && (double)total * 4.0 < 0.5 * 2.0 * (double)A->nnz;
   if (ok) {
@@ -777,7 +779,7 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   cudaFree(pieces); cudaFree(off); cudaFree(d_flag);
   const i64 ntiles = total;
   const int capbuf = cap + 8;
-  size_t stage = (size_t)capbuf * 12 + (size_t)(R + 2) * 8;
+  size_t stage = (size_t)capbuf * 12 + (size_t)(R + 2) * 8 + 64;     // val, ja | index table + x window, irp slice, row schedule
   size_t smem = stage * STAGES;
   FB2_CHECK(smem <= 200 * 1024, "SpMV tile does not fit in shared memory");
   A->spmv_R = R; A->spmv_cap = capbuf; A->spmv_ntiles = ntiles; A->spmv_smem = smem; A->spmv_stages = STAGES;
