@@ -69,21 +69,20 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // The class of a tile is never assumed: fb2_spmv_build_classes compares every tile entry by entry with the representative
 // of its class and checks the segment bounds; everything else streams ja as before.  Products are formed in the same
 // order from the same operands, so y is bit-identical to the ja path (tests: test_midsize_spmv_variants_bitwise).
-struct __align__(16) SpmvClassDesc {
+struct SpmvClassDesc {
   int nseg, idx_bytes, x_bytes, pad;
   int delta[32];   // first column of the segment relative to the first row of the tile (even, so 16-byte aligned in x)
   int len[32];     // doubles, even
   int off[32];     // position of the segment in the window, doubles
-  // row schedule: which row of the tile lane group g handles in round rd (sched[rd * G + g], 0xFF: none).  Rows are dealt out
-  // by length so that the four (two, one) rows a warp multiplies together have the same number of entries: with rows in
-  // their natural order a Q2 warp holds rows of 27..125 entries and every lane loops for the longest (62 % lane utilisation)
-  unsigned char sched[64];
 };
 #define SPMV_NOCLASS 0xFF
 
 // Tried and rejected in round 2 (profiles/r2_spmv_history.txt): consumers that stream the rows of a warp's range 32 entries at a
 // time (contiguous shared-memory reads, one xor tree per finished row).  It halves the shared-memory wavefronts per non-zero
 // but needs 107 instead of 54 instructions per 32 non-zeros (issue slots 82 % busy): 24.9 ms against 15.6 ms at config 2.
+// Also tried and dropped (same file, round 2): a per-class row schedule that deals rows to lane groups by length (62 % -> 95 %
+// lane utilisation, but equal-type rows of different chunks are 512 entries apart = the same banks: 4.0 instead of 2.5
+// wavefronts per LDS.64; 15.9 vs 16.2 ms with schedule, -5 % for Q3) and 16 / 4 lanes per row (18.8 / 17.5 ms).
 // Persistent block over tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  Warp 8 is the TMA producer
 // (one elected lane): it runs STAGES tiles ahead, waiting on the per-stage "empty" mbarrier and arming
 // the "full" one with the byte count of the three bulk copies (val, ja, irp slice).  The 8 consumer
@@ -125,8 +124,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
   const size_t dict_off = xs_off + (size_t)SPMV_DS * 4;
   const size_t irp_off = xs_off + (COMP ? (size_t)SPMV_DS * 8 : 0);
   (void)dcap;
-  const size_t sched_off = irp_off + irp_bytes;       // 64 bytes: the row schedule of a class tile (copied with the tile)
-  const size_t stage_bytes = sched_off + 64;
+  const size_t stage_bytes = irp_off + irp_bytes;
   // tiles of this CTA: persistent (chunk == 0): blockIdx.x, blockIdx.x + gridDim.x, ... ; chunked: `chunk` consecutive tiles
   const i64 t_first = chunk ? (i64)blockIdx.x * chunk : (i64)blockIdx.x;
   const i64 t_step = chunk ? 1 : (i64)gridDim.x;
@@ -176,9 +174,8 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
           // still there (only index / ja copies write that region) and is not copied again
           const bool have_idx = s_lastcls[s] == cls;
           s_lastcls[s] = cls;
-          mbar_expect_tx(&full_bar[s], cnt4 * 8u + (have_idx ? 0u : (uint32_t)D.idx_bytes) + (uint32_t)D.x_bytes + (uint32_t)irp_bytes + 64u);
+          mbar_expect_tx(&full_bar[s], cnt4 * 8u + (have_idx ? 0u : (uint32_t)D.idx_bytes) + (uint32_t)D.x_bytes + (uint32_t)irp_bytes);
           bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
-          bulk_g2s(base + sched_off, D.sched, 64u, &full_bar[s]);
           if (cnt4) bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
           if (!have_idx) bulk_g2s(base + (size_t)cap * 8, cls_idx + (size_t)cls * cap, (uint32_t)D.idx_bytes, &full_bar[s]);
         } else {
@@ -211,11 +208,8 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     return;
   }
   // ---------------- consumer warps ----------------
-  // lanes per row: a function of the tile height only, so that the summation order of a row (and with it y, bit for bit) does
-  // not depend on the number of consumer threads or on the row schedule; G rows per round
-  const int TPR = COMP ? NC / R : 256 / R;
-  const int G = NC / TPR, rounds = (R + G - 1) / G;
-  const int grp = tid / TPR, sub = tid - grp * TPR;
+  const int TPR = NC / R;   // lanes per row: 4..32, power of two
+  const int row = tid / TPR, sub = tid - row * TPR;
   const int lane = tid & 31, w = tid >> 5;
   double dacc = 0.0;
   int it = 0;
@@ -257,46 +251,40 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       else return in_class ? sxw[sj16[k]] : x[sj[k] - 1];
     };
     const i64 e0a = s_e0a[s];
-    const int nr = s_nr[s];
-    const unsigned char* sched = in_class ? base + sched_off : nullptr;
-    for (int rd = 0; rd < rounds; ++rd) {
-      const int slot = rd * G + grp;
-      const int row = sched ? (int)sched[slot] : slot;
-      double acc = 0.0;
-      const bool live = row < nr;
-      // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
-      double xrow = 0.0;
-      if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
-      if (live && in_class) {
-        // shared memory only: a plain strided loop (no gather latency to batch against)
-        const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
+    double acc = 0.0;
+    const bool live = row < s_nr[s];
+    // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
+    double xrow = 0.0;
+    if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
+    if (live && in_class) {
+      // shared memory only: a plain strided loop (no gather latency to batch against)
+      const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
 #pragma unroll 4
-        for (int k = b + sub; k < e; k += TPR) acc += sv[k] * sxw[sj16[k]];
-      } else if (live) {
-        const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
-        int k = b + sub;
-        for (; k + 3 * TPR < e; k += 4 * TPR) {
-          const double x0 = xat(k), x1 = xat(k + TPR), x2 = xat(k + 2 * TPR), x3 = xat(k + 3 * TPR);
-          acc += sv[k] * x0;
-          acc += sv[k + TPR] * x1;
-          acc += sv[k + 2 * TPR] * x2;
-          acc += sv[k + 3 * TPR] * x3;
-        }
-        if (k < e) {
-          // tail of up to 3 entries per lane as ONE masked batch, so that its gathers are in flight together
-          const int k1 = k + TPR, k2 = k + 2 * TPR;
-          const bool p1 = k1 < e, p2 = k2 < e;
-          const double x0 = xat(k), x1 = p1 ? xat(k1) : 0.0, x2 = p2 ? xat(k2) : 0.0;
-          acc += sv[k] * x0;
-          if (p1) acc += sv[k1] * x1;
-          if (p2) acc += sv[k2] * x2;
-        }
+      for (int k = b + sub; k < e; k += TPR) acc += sv[k] * sxw[sj16[k]];
+    } else if (live) {
+      const int b = (int)(s_irp[row] - e0a), e = (int)(s_irp[row + 1] - e0a);
+      int k = b + sub;
+      for (; k + 3 * TPR < e; k += 4 * TPR) {
+        const double x0 = xat(k), x1 = xat(k + TPR), x2 = xat(k + 2 * TPR), x3 = xat(k + 3 * TPR);
+        acc += sv[k] * x0;
+        acc += sv[k + TPR] * x1;
+        acc += sv[k + 2 * TPR] * x2;
+        acc += sv[k + 3 * TPR] * x3;
       }
-      for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
-      if (sub == 0 && live) {
-        y[r0 + row] = acc;
-        if (FUSE_DOT) dacc += acc * xrow;
+      if (k < e) {
+        // tail of up to 3 entries per lane as ONE masked batch, so that its gathers are in flight together
+        const int k1 = k + TPR, k2 = k + 2 * TPR;
+        const bool p1 = k1 < e, p2 = k2 < e;
+        const double x0 = xat(k), x1 = p1 ? xat(k1) : 0.0, x2 = p2 ? xat(k2) : 0.0;
+        acc += sv[k] * x0;
+        if (p1) acc += sv[k1] * x1;
+        if (p2) acc += sv[k2] * x2;
       }
+    }
+    for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
+    if (sub == 0 && live) {
+      y[r0 + row] = acc;
+      if (FUSE_DOT) dacc += acc * xrow;
     }
     // COMP: the consumers wrote xs[] through the generic proxy into a region the producer's next bulk copy (async proxy)
     // overwrites: order the two proxies before releasing the stage
@@ -444,7 +432,7 @@ static int spmv_compress(fb2_matrix_s* A, int capbuf, int R, int STAGES) {
   FB2_CUDA(fb2_memcpy(&total, A->d_dict_ptr + nt, sizeof(i64), cudaMemcpyDeviceToHost));
   FB2_CUDA(fb2_memcpy(&dcap, d_max, sizeof(int), cudaMemcpyDeviceToHost));
   cudaFree(cnt); cudaFree(d_max);
-  const size_t smem = ((size_t)capbuf * 10 + (size_t)SPMV_DS * 8 + (size_t)(R + 2) * 8 + 64) * STAGES;
+  const size_t smem = ((size_t)capbuf * 10 + (size_t)SPMV_DS * 8 + (size_t)(R + 2) * 8) * STAGES;
   // worth it only when the dictionaries are small next to the 2 B per entry they save, and the stage still fits
   bool ok = dcap > 0 && smem <= 200 * 1024 && (double)total * 4.0 < 0.5 * 2.0 * (double)A->nnz;
   if (ok) {
@@ -511,8 +499,8 @@ __global__ void k_tile_hash(i64 ntiles, const i64* __restrict__ irp, const int* 
 // block per class: segments of the representative tile's distinct columns and the window position of every entry
 __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp, const int* __restrict__ ja,
                                                      const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
-                                                     const int* __restrict__ rep, int cap, int G, int rounds,
-                                                     SpmvClassDesc* desc, unsigned short* cls_idx, int* valid) {
+                                                     const int* __restrict__ rep, int cap, SpmvClassDesc* desc,
+                                                     unsigned short* cls_idx, int* valid) {
   __shared__ int sb[DICT_SORT_MAX], su[DICT_SORT_MAX];
   __shared__ int s_scan[256];
   __shared__ SpmvClassDesc D;
@@ -571,26 +559,6 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
     }
     if (total > xw_cap || total > 0xFFFF || idx_n > cap) ok = 0;
     D.nseg = nseg; D.idx_bytes = idx_n * 2; D.x_bytes = total * 8; D.pad = 0;
-    // row schedule: rows by decreasing length; round 0 takes the G longest in order, round 1 the next G in reverse order (the
-    // group that got the longest row gets the shortest next), and so on
-    {
-      const int nrt = tile_nrows[t];
-      unsigned char order[64];
-      int len[64];
-      for (int r = 0; r < 64; ++r) { order[r] = (unsigned char)r; len[r] = r < nrt ? (int)(irp[r0 + r + 1] - irp[r0 + r]) : -1; }
-      for (int a = 1; a < nrt; ++a) {                 // insertion sort, stable
-        const unsigned char oa = order[a];
-        int b2 = a - 1;
-        while (b2 >= 0 && len[order[b2]] < len[oa]) { order[b2 + 1] = order[b2]; --b2; }
-        order[b2 + 1] = oa;
-      }
-      for (int k = 0; k < 64; ++k) D.sched[k] = (rounds == 0 && k < nrt) ? (unsigned char)k : 0xFF;   // rounds == 0: natural order
-      for (int rd = 0; rd < rounds; ++rd)
-        for (int g = 0; g < G; ++g) {
-          const int pos = rd * G + ((rd & 1) ? G - 1 - g : g);
-          if (rd * G + g < 64 && pos < nrt) D.sched[rd * G + g] = order[pos];
-        }
-    }
     for (int g = nseg; g < 32; ++g) { D.delta[g] = 0; D.len[g] = 0; D.off[g] = 0; }
     s_ok = ok;
   }
@@ -714,10 +682,7 @@ static int spmv_build_classes(fb2_matrix_s* A) {
     FB2_CUDA(fb2_memcpy(d_ch, h_ch.data(), sizeof(unsigned long long) * (size_t)ncls, cudaMemcpyHostToDevice));
     FB2_CUDA(fb2_memcpy(d_rep, h_rep.data(), sizeof(int) * (size_t)ncls, cudaMemcpyHostToDevice));
     FB2_CUDA(cudaMemsetAsync(d_nin, 0, sizeof(unsigned long long), st));
-    // FB2_SPMV_SCHED=0: rows in their natural order (A/B of the row schedule)
-    const bool sched_on = !(getenv("FB2_SPMV_SCHED") && atoi(getenv("FB2_SPMV_SCHED")) == 0);
-    const int tpr = 256 / A->spmv_R, G = A->spmv_nc / tpr, rounds = sched_on ? (A->spmv_R + G - 1) / G : 0;
-    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap, G, rounds,
+    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap,
                                         (SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, d_valid);
     k_tile_classify<<<fb2_num_sms() * 8, 256, 0, st>>>(nt, A->n, A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, hash, ncls, d_ch,
                                                         d_rep, d_valid, (const SpmvClassDesc*)A->d_cls_desc, A->d_tile_class, d_nin);
@@ -779,12 +744,14 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   cudaFree(pieces); cudaFree(off); cudaFree(d_flag);
   const i64 ntiles = total;
   const int capbuf = cap + 8;
-  size_t stage = (size_t)capbuf * 12 + (size_t)(R + 2) * 8 + 64;     // val, ja | index table + x window, irp slice, row schedule
+  size_t stage = (size_t)capbuf * 12 + (size_t)(R + 2) * 8;
   size_t smem = stage * STAGES;
   FB2_CHECK(smem <= 200 * 1024, "SpMV tile does not fit in shared memory");
   A->spmv_R = R; A->spmv_cap = capbuf; A->spmv_ntiles = ntiles; A->spmv_smem = smem; A->spmv_stages = STAGES;
   // consumer threads: 128 (4 warps) when R rows leave at least 4 lanes per row, else 256; FB2_SPMV_CONSUMERS overrides
-  int nc = 256;
+  // 8 lanes per row measured best (profiles/r2_spmv_history.txt): 256 consumer threads for 32-row tiles, 128 for <= 16-row tiles
+  // (Q3: 13.5 vs 14.1 ms; 16 lanes per row 18.8-19.2 ms, 4 lanes 17.5-18.7 ms at config 2)
+  int nc = R <= 16 ? 128 : 256;
   if (getenv("FB2_SPMV_CONSUMERS")) nc = atoi(getenv("FB2_SPMV_CONSUMERS"));
   if (g_compress) nc = 256;   // the dictionary variant stages two entries per consumer thread
   FB2_CHECK((nc == 128 || nc == 256) && nc / R >= 1 && nc / R <= 32, "bad FB2_SPMV_CONSUMERS");

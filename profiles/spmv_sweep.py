@@ -24,7 +24,7 @@ bytes_alg = A.nnz * 12 + A.num_rows * 24
 combos = [(32, 2, 2304, 32, 256), (32, 2, 2304, 32, 128), (32, 2, 2304, 64, 128), (32, 2, 2304, 32, 256)]
 if order != 2:
     combos = [(16, 2, 2304, 32, 256), (16, 2, 2304, 32, 128), (16, 2, 2304, 64, 128)]
-sched = os.environ.get("FB2_SPMV_SCHED", "1")
+sched = os.environ.get("FB2_SPMV_SCHED", "1") + " tprbase=" + os.environ.get("FB2_SPMV_TPR_BASE", "256")
 for R, st, cap, chunk, nc in combos:
     os.environ["FB2_SPMV_R"], os.environ["FB2_SPMV_STAGES"], os.environ["FB2_SPMV_CAP"], os.environ["FB2_SPMV_CHUNK"] = \
         str(R), str(st), str(cap), str(chunk)
