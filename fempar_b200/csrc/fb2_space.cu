@@ -646,17 +646,20 @@ __global__ void __launch_bounds__(128) k_row_fill_reg(int p, int ncomp, int M0, 
     const int b0 = hi[0] - lo[0] + 1, b1 = hi[1] - lo[1] + 1, b2 = hi[2] - lo[2] + 1;
     const int nb = b0 * b1 * b2, ncand = nb * ncomp;
     int v[KPL];
+    // candidate e = lane * KPL + i  <->  (component, box position): decoded once per lane (integer divisions by run-time
+    // box sizes), then advanced with carries for the lane's other KPL - 1 candidates
+    int e = lane * KPL;
+    int comp = e / nb, q = e - comp * nb;
+    int o0 = q % b0, o1 = (q / b0) % b1, o2 = q / (b0 * b1);
 #pragma unroll
-    for (int i = 0; i < KPL; ++i) {
-      const int e = lane * KPL + i;
+    for (int i = 0; i < KPL; ++i, ++e) {
       int g = 0x7fffffff;
       if (e < ncand) {
-        const int comp = e / nb, q = e - comp * nb;
-        const int a0 = lo[0] + q % b0, a1 = lo[1] + (q / b0) % b1, a2 = lo[2] + q / (b0 * b1);
-        const int c = node_dof[comp * lat_size + a0 + (i64)M0 * (a1 + (i64)M1 * a2)];
+        const int c = node_dof[comp * lat_size + (lo[0] + o0) + (i64)M0 * ((lo[1] + o1) + (i64)M1 * (lo[2] + o2))];
         if (c > 0 && c <= n && (!sym || c >= r + 1)) g = c;
       }
       v[i] = g;
+      if (++o0 == b0) { o0 = 0; if (++o1 == b1) { o1 = 0; if (++o2 == b2) { o2 = 0; ++comp; } } }
     }
 #pragma unroll
     for (int k = 2; k <= SORT_N; k <<= 1) {
