@@ -68,6 +68,7 @@ _SIGS = {
     "fb2_csr_set_initial_solution": [_VP, _VP],
     "fb2_csr_free_solver_workspace": [_VP],
     "fb2_csr_spmv_reset": [_VP],
+    "fb2_peer_allreduce_selftest": [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)],
     "fb2_csr_get_convergence_data": [_VP, _VP, _VP],
     "fb2_set_assembly_variant": [C.c_int],
     "fb2_vec_create": [C.POINTER(_VP), _VP],

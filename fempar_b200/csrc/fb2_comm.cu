@@ -1,6 +1,7 @@
 // Distributed layer: execution_context_t on NCCL (mpi_context.f90:384-474,522-639) and the device
 // dof_import_t (dof_import.f90:49-213) used by par_scalar_array%comm() (par_scalar_array.f90:498-533).
 #include <nccl.h>
+#include <math.h>
 #include <string.h>
 #include <unistd.h>
 #include <algorithm>
@@ -61,8 +62,9 @@ struct PeerAllreduce {
 };
 static PeerAllreduce g_peer;
 
-__global__ void k_peer_allreduce(double* buf, int count, double* const* peers, double* local, int me, int nranks,
-                                 unsigned long long epoch) {
+// one rank's part of the exchange: executed by the first 32 threads of a block
+__device__ __forceinline__ void peer_allreduce_body(double* buf, int count, double* const* peers, double* local, int me, int nranks,
+                                                    unsigned long long epoch) {
   const int r = threadIdx.x;
   const size_t par = (size_t)(epoch & 1ULL) * nranks * PEER_SLOT;
   if (r < nranks) {
@@ -80,6 +82,57 @@ __global__ void k_peer_allreduce(double* buf, int count, double* const* peers, d
     for (int q = 0; q < nranks; ++q) acc += ((const volatile double*)(local + par + (size_t)q * PEER_SLOT))[r];
     buf[r] = acc;
   }
+  __syncthreads();
+}
+__global__ void k_peer_allreduce(double* buf, int count, double* const* peers, double* local, int me, int nranks,
+                                 unsigned long long epoch) {
+  peer_allreduce_body(buf, count, peers, local, me, nranks, epoch);
+}
+// The same protocol with every rank played by one block of ONE cooperative launch (all blocks co-resident, so the waits cannot
+// deadlock): lets a single-GPU box exercise the mailbox / epoch-parity logic over many consecutive all-reduces.
+__global__ void k_peer_allreduce_emulated(double* bufs /*[nranks][PEER_SLOT]*/, int count, double* const* peers, int nranks,
+                                          int epochs, double* sums_out /*[epochs][nranks][count]*/) {
+  const int me = blockIdx.x;
+  double* buf = bufs + (size_t)me * PEER_SLOT;
+  for (int e = 1; e <= epochs; ++e) {
+    if (threadIdx.x < count) buf[threadIdx.x] = (double)(me + 1) * 0.125 + (double)e + 1000.0 * threadIdx.x;   // this rank's contribution
+    __syncthreads();
+    peer_allreduce_body(buf, count, peers, peers[me], me, nranks, (unsigned long long)e);
+    if (threadIdx.x < count) sums_out[((size_t)(e - 1) * nranks + me) * count + threadIdx.x] = buf[threadIdx.x];
+    __syncthreads();
+  }
+}
+extern "C" int fb2_peer_allreduce_selftest(int nranks, int count, int epochs, double* max_abs_error) {
+  FB2_CHECK(nranks >= 2 && nranks <= 16 && count >= 1 && count <= PEER_SLOT - 1 && epochs >= 1 && max_abs_error, "bad argument");
+  int dev = 0, coop = 0;
+  FB2_CUDA(cudaGetDevice(&dev));
+  FB2_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+  FB2_CHECK(coop, "cooperative launch not supported");
+  cudaStream_t st = fb2_stream();
+  const size_t box = (size_t)2 * nranks * PEER_SLOT;
+  double *d_boxes, *d_bufs, *d_out;
+  double** d_peers;
+  FB2_TRY(fb2_dalloc(&d_boxes, box * nranks)); FB2_TRY(fb2_dalloc(&d_bufs, (size_t)nranks * PEER_SLOT));
+  FB2_TRY(fb2_dalloc(&d_out, (size_t)epochs * nranks * count)); FB2_TRY(fb2_dalloc(&d_peers, (size_t)nranks));
+  FB2_CUDA(cudaMemsetAsync(d_boxes, 0, box * nranks * sizeof(double), st));
+  std::vector<double*> peers((size_t)nranks);
+  for (int r = 0; r < nranks; ++r) peers[r] = d_boxes + box * r;
+  FB2_CUDA(fb2_memcpy(d_peers, peers.data(), sizeof(double*) * (size_t)nranks, cudaMemcpyHostToDevice));
+  double* const* peers_arg = d_peers;
+  void* args[] = {(void*)&d_bufs, (void*)&count, (void*)&peers_arg, (void*)&nranks, (void*)&epochs, (void*)&d_out};
+  FB2_CUDA(cudaLaunchCooperativeKernel((const void*)k_peer_allreduce_emulated, dim3(nranks), dim3(32), args, 0, st));
+  std::vector<double> out((size_t)epochs * nranks * count);
+  FB2_CUDA(fb2_memcpy(out.data(), d_out, sizeof(double) * out.size(), cudaMemcpyDeviceToHost));
+  double err = 0.0;
+  for (int e = 1; e <= epochs; ++e)
+    for (int k = 0; k < count; ++k) {
+      double want = 0.0;
+      for (int q = 0; q < nranks; ++q) want += (double)(q + 1) * 0.125 + (double)e + 1000.0 * k;     // rank order, like the kernel
+      for (int me = 0; me < nranks; ++me) err = std::max(err, fabs(out[((size_t)(e - 1) * nranks + me) * count + k] - want));
+    }
+  *max_abs_error = err;
+  cudaFree(d_boxes); cudaFree(d_bufs); cudaFree(d_out); cudaFree(d_peers);
+  return 0;
 }
 
 static void peer_allreduce_teardown() {

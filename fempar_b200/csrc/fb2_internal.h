@@ -131,6 +131,7 @@ struct fb2_matrix_s {
   int n_slow_cells = 0;
   // SpMV tile geometry (fb2_spmv.cu)
   int spmv_R = 0, spmv_cap = 0, spmv_grid = 0, spmv_stages = 0, spmv_nc = 0;   // nc: consumer threads per CTA
+  int spmv_tr = 0;                          // 1: rows dealt transposed to the lane groups, chunks staggered in the stage
   i64 spmv_ntiles = 0;
   i64* d_tile_row = nullptr;              // first row of every tile
   unsigned char* d_tile_nrows = nullptr;  // rows in the tile (<= spmv_R)

@@ -76,6 +76,11 @@ struct SpmvClassDesc {
   int off[32];     // position of the segment in the window, doubles
 };
 #define SPMV_NOCLASS 0xFF
+// transposed rows: stagger (entries) of chunk g in the stage, per stream.  val: 8 x 8 B = half of the 32 banks, so that the four
+// 8-lane groups of a warp pair up into two conflict-free wavefronts; ja: 8 x 4 B and class index table: 16 x 2 B = 8 banks each
+#define SPMV_STAG_VAL 8
+#define SPMV_STAG_JA 8
+#define SPMV_STAG_IDX 16
 
 // Tried and rejected in round 2 (profiles/r2_spmv_history.txt): consumers that stream the rows of a warp's range 32 entries at a
 // time (contiguous shared-memory reads, one xor tree per finished row).  It halves the shared-memory wavefronts per non-zero
@@ -104,7 +109,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
                                                              int chunk, const int* __restrict__ dict, const i64* __restrict__ dict_ptr,
                                                              int dcap, const unsigned char* __restrict__ tile_class,
                                                              const SpmvClassDesc* __restrict__ cls_desc,
-                                                             const unsigned short* __restrict__ cls_idx) {
+                                                             const unsigned short* __restrict__ cls_idx, int tr) {
   constexpr int IB = COMP ? 2 : 4;                       // bytes per streamed column index
   constexpr i64 AL = COMP ? 7 : 3;                       // element-range alignment mask
   const int* ja = (const int*)ja_any;
@@ -137,80 +142,98 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
 
   if (tid >= NC) {
     // ---------------- producer warp ----------------
-    // lane 0 keeps the tile bookkeeping and issues the val / ja (or class index table) / irp copies; for a class tile the
-    // other lanes issue one x-segment copy each
+    // Every lane keeps the header of the tile; lane 0 waits for the stage, arms the barrier and issues the irp copy.  The
+    // entries are copied in `nch` chunks (1, or one per lane group of a consumer warp when the rows are dealt transposed, see
+    // the consumer side): lane g copies chunk g of val and of ja (or of the class index table); for a class tile lane l also
+    // copies x segment l - 1.
     const int plane = tid - NC;
+    const int TPRP = (R <= 16 ? 128 : 256) / R;
+    const int nch = tr ? 32 / TPRP : 1;                  // chunks per tile
+    const int CW = tr ? NC / 32 : R;                     // rows per chunk
+    const i64 CA = tr ? (i64)7 : AL;                     // chunk alignment (entries, relative to the aligned tile start)
     i64 t = t_first;
-    i64 e0 = 0, e1 = 0, r0 = 0, d0 = 0, d1 = 0;
+    i64 e0 = 0, r0 = 0, d0 = 0, d1 = 0, cb = 0, ce = 0;
     int nr = 0, cls = SPMV_NOCLASS;
-    if (plane == 0 && t < t_end) {
-      r0 = tile_row[t]; nr = tile_nrows[t]; e0 = irp[r0]; e1 = irp[r0 + nr];
-      if (COMP) { d0 = dict_ptr[t]; d1 = dict_ptr[t + 1]; }
-      if (!COMP && tile_class) cls = tile_class[t];
-    }
+    auto load_tile = [&](i64 tt, i64& R0, int& NR, i64& E0, i64& CB, i64& CE, i64& D0, i64& D1, int& CLS) {
+      R0 = tile_row[tt]; NR = tile_nrows[tt]; E0 = irp[R0];
+      CB = CE = 0;
+      if (plane < nch) { CB = irp[R0 + min(plane * CW, NR)]; CE = irp[R0 + min((plane + 1) * CW, NR)]; }
+      if (COMP) { D0 = dict_ptr[tt]; D1 = dict_ptr[tt + 1]; }
+      CLS = (!COMP && tile_class) ? tile_class[tt] : SPMV_NOCLASS;
+    };
+    if (t < t_end) load_tile(t, r0, nr, e0, cb, ce, d0, d1, cls);
     for (int it = 0; t < t_end; t += t_step, ++it) {
       const int s = it % STAGES;
       unsigned char* base = smem_raw + s * stage_bytes;
-      i64 ne0 = 0, ne1 = 0, nr0 = 0, nd0 = 0, nd1 = 0;
+      i64 ne0 = 0, nr0 = 0, nd0 = 0, nd1 = 0, ncb = 0, nce = 0;
       int nnr = 0, ncls = SPMV_NOCLASS;
+      // prefetch the header of the next tile before blocking on the empty barrier
+      const i64 tn = t + t_step;
+      if (tn < t_end) load_tile(tn, nr0, nnr, ne0, ncb, nce, nd0, nd1, ncls);
+      const i64 e0a = e0 & ~AL;
+      const i64 ca = e0a + ((cb - e0a) & ~CA);                                    // aligned start of this lane's chunk
+      const uint32_t cn = (plane < nch && ce > cb) ? (uint32_t)((ce - ca + CA) & ~CA) : 0u;   // its entries
+      const uint32_t cnt_all = __reduce_add_sync(0xffffffffu, cn);
+      const bool is_cls = !COMP && cls != SPMV_NOCLASS;
+      // consecutive tiles of an x-row of cells share their class: the index table this stage received two tiles ago is still
+      // there (only index / ja copies write that region) and is not copied again
+      const bool have_idx = is_cls && s_lastcls[s] == cls;
+      __syncwarp();
       if (plane == 0) {
-        // prefetch the row / element range of the next tile before blocking on the empty barrier
-        const i64 tn = t + t_step;
-        if (tn < t_end) {
-          nr0 = tile_row[tn]; nnr = tile_nrows[tn]; ne0 = irp[nr0]; ne1 = irp[nr0 + nnr];
-          if (COMP) { nd0 = dict_ptr[tn]; nd1 = dict_ptr[tn + 1]; }
-          if (!COMP && tile_class) ncls = tile_class[tn];
-        }
         mbar_wait_parked(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
-        const i64 e0a = e0 & ~AL;
-        const uint32_t cnt4 = (uint32_t)((e1 - e0a + AL) & ~AL);
         // a dictionary that does not fit the region is not staged: the consumers then go through it in global memory
         const uint32_t dbytes = (COMP && d1 - d0 <= SPMV_DS) ? (uint32_t)(d1 - d0) * 4u : 0u;
         s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0); s_d0[s] = d0; s_cls[s] = cls;
-        if (!COMP && cls != SPMV_NOCLASS) {
+        s_lastcls[s] = is_cls ? cls : SPMV_NOCLASS;
+        if (is_cls) {
           const SpmvClassDesc& D = cls_desc[cls];
           s_xoff[s] = D.idx_bytes;
-          // consecutive tiles of an x-row of cells share their class: the index table this stage received two tiles ago is
-          // still there (only index / ja copies write that region) and is not copied again
-          const bool have_idx = s_lastcls[s] == cls;
-          s_lastcls[s] = cls;
-          mbar_expect_tx(&full_bar[s], cnt4 * 8u + (have_idx ? 0u : (uint32_t)D.idx_bytes) + (uint32_t)D.x_bytes + (uint32_t)irp_bytes);
-          bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
-          if (cnt4) bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
-          if (!have_idx) bulk_g2s(base + (size_t)cap * 8, cls_idx + (size_t)cls * cap, (uint32_t)D.idx_bytes, &full_bar[s]);
+          const uint32_t ib = have_idx ? 0u : (tr ? cnt_all * 2u : (uint32_t)D.idx_bytes);
+          mbar_expect_tx(&full_bar[s], cnt_all * 8u + ib + (uint32_t)D.x_bytes + (uint32_t)irp_bytes);
+          if (!have_idx && !tr) bulk_g2s(base + (size_t)cap * 8, cls_idx + (size_t)cls * cap, (uint32_t)D.idx_bytes, &full_bar[s]);
         } else {
-          s_lastcls[s] = SPMV_NOCLASS;
-          mbar_expect_tx(&full_bar[s], cnt4 * (uint32_t)(8 + IB) + dbytes + (uint32_t)irp_bytes);
-          bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
-          if (cnt4) {
-            bulk_g2s(base, val + e0a, cnt4 * 8u, &full_bar[s]);
-            if (COMP) bulk_g2s(base + (size_t)cap * 8, ja16 + e0a, cnt4 * 2u, &full_bar[s]);
-            else bulk_g2s(base + (size_t)cap * 8, ja + e0a, cnt4 * 4u, &full_bar[s]);
-          }
+          mbar_expect_tx(&full_bar[s], cnt_all * (uint32_t)(8 + IB) + dbytes + (uint32_t)irp_bytes);
           if (COMP && dbytes) bulk_g2s(base + dict_off, dict + d0, dbytes, &full_bar[s]);
         }
+        bulk_g2s(base + irp_off, irp + r0, (uint32_t)irp_bytes, &full_bar[s]);
       }
-      if (!COMP && tile_class) {
-        // x window of a class tile: lane l copies segment l - 1 (the barrier was armed by lane 0 above)
-        const int c_now = __shfl_sync(0xffffffffu, cls, 0);
-        if (c_now != SPMV_NOCLASS) {
-          const i64 r_now = __shfl_sync(0xffffffffu, r0, 0);
-          const SpmvClassDesc& D = cls_desc[c_now];
-          if (plane >= 1 && plane <= D.nseg) {
-            const int g = plane - 1;
-            bulk_g2s(base + (size_t)cap * 8 + (size_t)D.idx_bytes + (size_t)D.off[g] * 8, x + (r_now + D.delta[g]), (uint32_t)D.len[g] * 8u,
-                     &full_bar[s]);
-          }
+      __syncwarp();   // the barrier is armed and the stage is free: the other lanes may copy into it
+      if (cn) {
+        // chunk g lands SPMV_STAG_* x g entries behind its natural place (transposed rows only): the lane groups of a consumer
+        // warp then read different shared-memory banks although their rows start a multiple of 128 bytes apart
+        const size_t de = (size_t)(ca - e0a);
+        const size_t g = tr ? (size_t)plane : 0;
+        bulk_g2s(base + (de + SPMV_STAG_VAL * g) * 8, val + ca, cn * 8u, &full_bar[s]);
+        if (is_cls) {
+          if (!have_idx && tr)
+            bulk_g2s(base + (size_t)cap * 8 + (de + SPMV_STAG_IDX * g) * 2, cls_idx + (size_t)cls * cap + de, cn * 2u, &full_bar[s]);
+        } else if (COMP) bulk_g2s(base + (size_t)cap * 8 + de * 2, ja16 + ca, cn * 2u, &full_bar[s]);
+        else bulk_g2s(base + (size_t)cap * 8 + (de + SPMV_STAG_JA * g) * 4, ja + ca, cn * 4u, &full_bar[s]);
+      }
+      if (is_cls) {
+        // x window of a class tile: lane l copies segment l - 1
+        const SpmvClassDesc& D = cls_desc[cls];
+        if (plane >= 1 && plane <= D.nseg) {
+          const int g = plane - 1;
+          bulk_g2s(base + (size_t)cap * 8 + (size_t)D.idx_bytes + (size_t)D.off[g] * 8, x + (r0 + D.delta[g]), (uint32_t)D.len[g] * 8u,
+                   &full_bar[s]);
         }
       }
-      e0 = ne0; e1 = ne1; r0 = nr0; nr = nnr; d0 = nd0; d1 = nd1; cls = ncls;
+      e0 = ne0; r0 = nr0; nr = nnr; d0 = nd0; d1 = nd1; cls = ncls; cb = ncb; ce = nce;
     }
     return;
   }
   // ---------------- consumer warps ----------------
-  const int TPR = NC / R;   // lanes per row: 4..32, power of two
-  const int row = tid / TPR, sub = tid - row * TPR;
+  // lanes per row: a function of the tile height only (8 for R = 32 and 16, 16 for R = 8, 4 for R = 64), so that the summation
+  // order of a row -- and y, bit for bit -- is the same for every kernel variant and consumer count (groups beyond R idle)
+  const int TPR = (R <= 16 ? 128 : 256) / R;
   const int lane = tid & 31, w = tid >> 5;
+  // tr (transposed rows): lane group g of warp w owns row g * (NC / 32) + w instead of w * (32 / TPR) + g.  Where the row
+  // lengths repeat with the period of a cell's created DOFs (8 for Q2) the groups of a warp then hold rows of equal length
+  // and finish together; chunk g of the tile (the rows of group g) is staged SPMV_STAG_* x g entries behind its natural place
+  const int grp = tr ? lane / TPR : 0;
+  const int row = tr ? grp * (NC / 32) + w : tid / TPR;
+  const int sub = tid & (TPR - 1);
   double dacc = 0.0;
   int it = 0;
   for (i64 t = t_first; t < t_end; t += t_step, ++it) {
@@ -218,9 +241,9 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     mbar_wait(&full_bar[s], (it / STAGES) & 1);
     const i64 r0 = s_r0[s];
     const unsigned char* base = smem_raw + s * stage_bytes;
-    const double* sv = (const double*)base;
-    const int* sj = (const int*)(base + (size_t)cap * 8);
-    const unsigned short* sj16 = (const unsigned short*)(base + (size_t)cap * 8);
+    const double* sv = (const double*)base + SPMV_STAG_VAL * grp;
+    const int* sj = (const int*)(base + (size_t)cap * 8) + SPMV_STAG_JA * grp;
+    const unsigned short* sj16 = (const unsigned short*)(base + (size_t)cap * 8) + (COMP ? 0 : SPMV_STAG_IDX * grp);
     const int* sd = (const int*)(base + dict_off);
     const i64* s_irp = (const i64*)(base + irp_off);
     // COMP: the consumer warps gather x once per DISTINCT column of the tile into shared memory (7-9x fewer gathers than
@@ -499,7 +522,7 @@ __global__ void k_tile_hash(i64 ntiles, const i64* __restrict__ irp, const int* 
 // block per class: segments of the representative tile's distinct columns and the window position of every entry
 __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp, const int* __restrict__ ja,
                                                      const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
-                                                     const int* __restrict__ rep, int cap, SpmvClassDesc* desc,
+                                                     const int* __restrict__ rep, int cap, int idx_extra, SpmvClassDesc* desc,
                                                      unsigned short* cls_idx, int* valid) {
   __shared__ int sb[DICT_SORT_MAX], su[DICT_SORT_MAX];
   __shared__ int s_scan[256];
@@ -544,8 +567,9 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
   if (tid == 0) {
     // greedy runs of the sorted distinct deltas; starts rounded down and lengths rounded up to even (16-byte bulk copies)
     int nseg = 0, total = 0, ok = m > 0;
+    // idx_extra: room behind the table for the staggered chunks of the transposed row layout (the x window starts behind it)
     const int idx_n = (shift + m + 7) & ~7;
-    const int xw_cap = (cap * 4 - idx_n * 2) / 8;
+    const int xw_cap = (cap * 4 - (idx_n + idx_extra) * 2) / 8;
     int i = 0;
     while (ok && i < nu) {
       const int start = su[i] & ~1;
@@ -557,8 +581,8 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
       D.delta[nseg] = start; D.len[nseg] = len; D.off[nseg] = total;
       total += len; ++nseg;
     }
-    if (total > xw_cap || total > 0xFFFF || idx_n > cap) ok = 0;
-    D.nseg = nseg; D.idx_bytes = idx_n * 2; D.x_bytes = total * 8; D.pad = 0;
+    if (total > xw_cap || total > 0xFFFF || idx_n + idx_extra > cap) ok = 0;
+    D.nseg = nseg; D.idx_bytes = (idx_n + idx_extra) * 2; D.x_bytes = total * 8; D.pad = 0;
     for (int g = nseg; g < 32; ++g) { D.delta[g] = 0; D.len[g] = 0; D.off[g] = 0; }
     s_ok = ok;
   }
@@ -682,7 +706,9 @@ static int spmv_build_classes(fb2_matrix_s* A) {
     FB2_CUDA(fb2_memcpy(d_ch, h_ch.data(), sizeof(unsigned long long) * (size_t)ncls, cudaMemcpyHostToDevice));
     FB2_CUDA(fb2_memcpy(d_rep, h_rep.data(), sizeof(int) * (size_t)ncls, cudaMemcpyHostToDevice));
     FB2_CUDA(cudaMemsetAsync(d_nin, 0, sizeof(unsigned long long), st));
-    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap,
+    const int tpr = (A->spmv_R <= 16 ? 128 : 256) / A->spmv_R;
+    const int idx_extra = A->spmv_tr ? SPMV_STAG_IDX * (32 / tpr - 1) : 0;
+    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap, idx_extra,
                                         (SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, d_valid);
     k_tile_classify<<<fb2_num_sms() * 8, 256, 0, st>>>(nt, A->n, A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, hash, ncls, d_ch,
                                                         d_rep, d_valid, (const SpmvClassDesc*)A->d_cls_desc, A->d_tile_class, d_nin);
@@ -708,6 +734,29 @@ static int spmv_build_classes(fb2_matrix_s* A) {
   return 0;
 }
 
+// lane-group iterations of the consumer warps over the fixed tiles for the two row maps: a warp advances its G rows together,
+// so a tile costs sum over warps of max over the warp's rows of ceil(len / TPR).  [0] natural (warp w: rows w G .. w G + G - 1),
+// [1] transposed (rows w, w + W, ...)
+__global__ void k_row_map_cost(i64 n, const i64* __restrict__ irp, int R, int TPR, int W, int G, i64 nfixed,
+                               unsigned long long* cost) {
+  const i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long c0 = 0, c1 = 0;
+  if (t < nfixed) {
+    const i64 r0 = t * R;
+    for (int w = 0; w < W; ++w) {
+      int m0 = 0, m1 = 0;
+      for (int g = 0; g < G; ++g) {
+        const i64 a = r0 + w * G + g, b = r0 + g * W + w;
+        if (a < n) m0 = max(m0, (int)((irp[a + 1] - irp[a] + TPR - 1) / TPR));
+        if (b < n) m1 = max(m1, (int)((irp[b + 1] - irp[b] + TPR - 1) / TPR));
+      }
+      c0 += m0; c1 += m1;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) { c0 += __shfl_down_sync(0xffffffffu, c0, o); c1 += __shfl_down_sync(0xffffffffu, c1, o); }
+  if ((threadIdx.x & 31) == 0) { atomicAdd(&cost[0], c0); atomicAdd(&cost[1], c1); }
+}
+
 // choose the tile geometry once per matrix
 int fb2_spmv_prepare(fb2_matrix_s* A) {
   if (A->spmv_cap > 0 || A->n == 0) return 0;
@@ -723,10 +772,40 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   if (getenv("FB2_SPMV_CAP")) cap = atoi(getenv("FB2_SPMV_CAP"));
   FB2_CHECK(R >= 8 && R <= 64 && (R & (R - 1)) == 0 && STAGES >= 2 && STAGES <= SPMV_MAX_STAGES && cap % 8 == 0, "bad SpMV tile parameters");
   const i64 nfixed = (A->n + R - 1) / R;
+  // consumer threads: 8 lanes per row measured best (profiles/r2_spmv_history.txt): 256 consumer threads for 32-row tiles, 128 for
+  // <= 16-row tiles (Q3: 13.5 vs 14.1 ms; 16 lanes per row 18.8-19.2 ms, 4 lanes 17.5-18.7 ms at config 2)
+  int nc = R <= 16 ? 128 : 256;
+  if (getenv("FB2_SPMV_CONSUMERS")) nc = atoi(getenv("FB2_SPMV_CONSUMERS"));
+  if (g_compress) nc = 256;   // the dictionary variant stages two entries per consumer thread
+  FB2_CHECK((nc == 128 || nc == 256) && nc >= (R <= 16 ? 128 : 256), "bad FB2_SPMV_CONSUMERS: too few lane groups for the tile height");
+  A->spmv_nc = nc;
+  // row map: transposed when it saves >= 10 % of the lane-group iterations (rows of equal length meet in one warp);
+  // FB2_SPMV_TRANSPOSE=0/1 overrides.  Needs 8 lanes per row and as many lane groups as rows.
+  {
+    const int tpr = (R <= 16 ? 128 : 256) / R, W = nc / 32, G = 32 / tpr;
+    int tr = 0;
+    if (tpr == 8 && W * G == R && !g_compress) {
+      unsigned long long *d_cost, h_cost[2] = {0, 0};
+      FB2_TRY(fb2_dalloc(&d_cost, 2));
+      FB2_CUDA(cudaMemsetAsync(d_cost, 0, 2 * sizeof(unsigned long long), st));
+      k_row_map_cost<<<(unsigned)((nfixed + 255) / 256), 256, 0, st>>>(A->n, A->d_irp, R, tpr, W, G, nfixed, d_cost);
+      FB2_CUDA(cudaMemcpyAsync(h_cost, d_cost, sizeof(h_cost), cudaMemcpyDeviceToHost, st));
+      FB2_CUDA(cudaStreamSynchronize(st));
+      cudaFree(d_cost);
+      tr = (double)h_cost[1] < 0.9 * (double)h_cost[0] ? 1 : 0;
+      if (getenv("FB2_SPMV_TRANSPOSE")) tr = atoi(getenv("FB2_SPMV_TRANSPOSE")) ? 1 : 0;
+      fb2_record_phase("spmv_row_map_cost_natural", (double)h_cost[0]);
+      fb2_record_phase("spmv_row_map_cost_transposed", (double)h_cost[1]);
+    }
+    A->spmv_tr = tr;
+    fb2_record_phase("spmv_transposed_rows", tr);
+  }
+  // transposed rows: the chunks are staged up to 3 x 8 entries behind their place and aligned to 8 entries
+  const int cap_fit = A->spmv_tr ? cap - 32 : cap;
   int *pieces, *off, *d_flag, h_flag = 0, total = 0;
   FB2_TRY(fb2_dalloc(&pieces, (size_t)nfixed + 1)); FB2_TRY(fb2_dalloc(&off, (size_t)nfixed + 1)); FB2_TRY(fb2_dalloc(&d_flag, 1));
   FB2_CUDA(cudaMemsetAsync(d_flag, 0, sizeof(int), st));
-  k_tile_pieces<<<(unsigned)((nfixed + 256) / 256), 256, 0, st>>>(A->n, A->d_irp, R, cap, nfixed, pieces, d_flag);
+  k_tile_pieces<<<(unsigned)((nfixed + 256) / 256), 256, 0, st>>>(A->n, A->d_irp, R, cap_fit, nfixed, pieces, d_flag);
   {
     void* tmp = nullptr; size_t bytes = 0;
     FB2_CUDA(cub::DeviceScan::ExclusiveSum(tmp, bytes, pieces, off, nfixed + 1, st));
@@ -739,7 +818,7 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   FB2_CUDA(fb2_memcpy(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost));
   FB2_CHECK(h_flag == 0, "a pair of rows exceeds the SpMV stage buffer: use fb2_set_spmv_variant(1)");
   FB2_TRY(fb2_dalloc(&A->d_tile_row, (size_t)total)); FB2_TRY(fb2_dalloc(&A->d_tile_nrows, (size_t)total));
-  k_tile_fill<<<(unsigned)((nfixed + 255) / 256), 256, 0, st>>>(A->n, A->d_irp, R, cap, nfixed, off, A->d_tile_row, A->d_tile_nrows);
+  k_tile_fill<<<(unsigned)((nfixed + 255) / 256), 256, 0, st>>>(A->n, A->d_irp, R, cap_fit, nfixed, off, A->d_tile_row, A->d_tile_nrows);
   FB2_CUDA(cudaStreamSynchronize(st));
   cudaFree(pieces); cudaFree(off); cudaFree(d_flag);
   const i64 ntiles = total;
@@ -748,14 +827,6 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   size_t smem = stage * STAGES;
   FB2_CHECK(smem <= 200 * 1024, "SpMV tile does not fit in shared memory");
   A->spmv_R = R; A->spmv_cap = capbuf; A->spmv_ntiles = ntiles; A->spmv_smem = smem; A->spmv_stages = STAGES;
-  // consumer threads: 128 (4 warps) when R rows leave at least 4 lanes per row, else 256; FB2_SPMV_CONSUMERS overrides
-  // 8 lanes per row measured best (profiles/r2_spmv_history.txt): 256 consumer threads for 32-row tiles, 128 for <= 16-row tiles
-  // (Q3: 13.5 vs 14.1 ms; 16 lanes per row 18.8-19.2 ms, 4 lanes 17.5-18.7 ms at config 2)
-  int nc = R <= 16 ? 128 : 256;
-  if (getenv("FB2_SPMV_CONSUMERS")) nc = atoi(getenv("FB2_SPMV_CONSUMERS"));
-  if (g_compress) nc = 256;   // the dictionary variant stages two entries per consumer thread
-  FB2_CHECK((nc == 128 || nc == 256) && nc / R >= 1 && nc / R <= 32, "bad FB2_SPMV_CONSUMERS");
-  A->spmv_nc = nc;
   // the attribute is per kernel, not per matrix (two matrices with different R must not lower each other's limit)
   FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<true, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   FB2_CUDA(cudaFuncSetAttribute(k_spmv_stream<false, false, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -785,7 +856,7 @@ extern "C" int fb2_csr_spmv_reset(fb2_matrix_t A) {
   A->d_tile_row = nullptr; A->d_tile_nrows = nullptr; A->d_tile_class = nullptr; A->d_cls_desc = nullptr; A->d_cls_idx = nullptr;
   A->d_idx16 = nullptr; A->d_dict = nullptr; A->d_dict_ptr = nullptr;
   A->spmv_R = A->spmv_cap = A->spmv_grid = A->spmv_stages = 0; A->spmv_ntiles = 0; A->spmv_smem = 0;
-  A->spmv_nc = 0; A->spmv_comp = 0; A->spmv_cls = 0; A->spmv_ncls = 0; A->spmv_tiles_in_class = 0; A->spmv_t_itf = -1; A->spmv_row_itf = -1;
+  A->spmv_nc = 0; A->spmv_tr = 0; A->spmv_comp = 0; A->spmv_cls = 0; A->spmv_ncls = 0; A->spmv_tiles_in_class = 0; A->spmv_t_itf = -1; A->spmv_row_itf = -1;
   return 0;
 }
 
@@ -803,7 +874,7 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
   k_spmv_stream<FD, CP, NCT><<<(unsigned)grid, NCT + 32, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
                                                                     done_flag, A->spmv_R, A->spmv_cap, nt, A->spmv_stages,   \
                                                                     A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP, \
-                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx)
+                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, CP ? 0 : A->spmv_tr)
 #define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                   \
   do {                                                                                                    \
     if (!CP && A->spmv_nc == 128) SPMV_LAUNCH_NC(FD, false, 128, JA, SMEM, DICT, DPTR, DCAP);             \

@@ -212,6 +212,10 @@ int fb2_csr_set_initial_solution(fb2_matrix_t A, fb2_vector_t x0);
  * (NULL, or num_iterations doubles; needs a solve with history != NULL) = the estimate of the second criterion per iteration
  * for the four DELTA_*_AND_RES_* criteria. */
 int fb2_csr_get_convergence_data(fb2_matrix_t A, double out[4], double* history_extra);
+/* Self-test of the NVLink peer-memory scalar all-reduce protocol (fb2_comm.cu) on ONE device: every rank is played by one block
+ * of a cooperative launch over `epochs` consecutive all-reduces of `count` (<= 7) doubles; returns the largest deviation from
+ * the rank-ordered sum (0 when every rank holds the bit-identical result). */
+int fb2_peer_allreduce_selftest(int nranks, int count, int epochs, double* max_abs_error);
 /* drops the SpMV tile table / pattern classes of the matrix; the next apply prepares them again (tuning sweeps) */
 int fb2_csr_spmv_reset(fb2_matrix_t A);
 /* releases the solver workspace of the operator early (fb2_csr_destroy does it too) */

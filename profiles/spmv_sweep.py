@@ -20,23 +20,26 @@ M = fb.JacobiPreconditioner(); M.create(op); M.numerical_setup()
 ils = fb.IterativeLinearSolver(); ils.set_type_from_string("CG"); ils.set_operators(A, M)
 x = s.create_dof_values()
 bytes_alg = A.nnz * 12 + A.num_rows * 24
-# (R, STAGES, CAP, CHUNK, CONSUMERS); round-2 call 4 showed 2 stages x 4 CTAs/SM ahead of deeper rings and smaller tiles
-combos = [(32, 2, 2304, 32, 256), (32, 2, 2304, 32, 128), (32, 2, 2304, 64, 128), (32, 2, 2304, 32, 256)]
+# (R, STAGES, CAP, CHUNK, CONSUMERS, TRANSPOSE); round-2 call 4 showed 2 stages x 4 CTAs/SM ahead of deeper rings and smaller tiles;
+# TRANSPOSE: row map of the consumer lane groups (0 natural, 1 transposed + staggered chunks), A/B/A/B against box drift
+combos = [(32, 2, 2304, 32, 256, 0), (32, 2, 2304, 32, 256, 1), (32, 2, 2304, 32, 256, 0), (32, 2, 2304, 32, 256, 1)]
 if order != 2:
-    combos = [(16, 2, 2304, 32, 256), (16, 2, 2304, 32, 128), (16, 2, 2304, 64, 128)]
-sched = os.environ.get("FB2_SPMV_SCHED", "1") + " tprbase=" + os.environ.get("FB2_SPMV_TPR_BASE", "256")
-for R, st, cap, chunk, nc in combos:
+    combos = [(16, 2, 2304, 32, 128, 0), (16, 2, 2304, 32, 128, 1), (16, 2, 2304, 32, 128, 0), (16, 2, 2304, 32, 128, 1)]
+for R, st, cap, chunk, nc, tr in combos:
     os.environ["FB2_SPMV_R"], os.environ["FB2_SPMV_STAGES"], os.environ["FB2_SPMV_CAP"], os.environ["FB2_SPMV_CHUNK"] = \
         str(R), str(st), str(cap), str(chunk)
     os.environ["FB2_SPMV_CONSUMERS"] = str(nc)
+    os.environ["FB2_SPMV_TRANSPOSE"] = str(tr)
     try:
         fb._lib.check(L.fb2_csr_spmv_reset(A.h))
         ils.iterate(op.get_translation(), x, 3)
         t, ts = ils.iterate(op.get_translation(), x, 12)
         ms = ts / 12
-        print("sched=%s nc=%d " % (sched, nc), end="")
-        print("R=%-3d stages=%d cap=%-5d chunk=%-4d  spmv %.3f ms  %.0f GB/s algorithmic  tiles_in_class %.0f / %.0f  ctas/sm %.0f" % (
-            R, st, cap, chunk, ms, bytes_alg / ms / 1e6, op.last_phase_ms("spmv_tiles_in_class"), op.last_phase_ms("spmv_tiles"),
-            op.last_phase_ms("spmv_ctas_per_sm")), flush=True)
+        print("transpose=%d nc=%d " % (tr, nc), end="")
+        print("R=%-3d stages=%d cap=%-5d chunk=%-4d  spmv %.3f ms  %.0f GB/s algorithmic  tiles_in_class %.0f / %.0f  ctas/sm %.0f  "
+              "row-map cost natural %.4g transposed %.4g" % (
+                  R, st, cap, chunk, ms, bytes_alg / ms / 1e6, op.last_phase_ms("spmv_tiles_in_class"), op.last_phase_ms("spmv_tiles"),
+                  op.last_phase_ms("spmv_ctas_per_sm"), op.last_phase_ms("spmv_row_map_cost_natural"),
+                  op.last_phase_ms("spmv_row_map_cost_transposed")), flush=True)
     except Exception as e:   # a geometry that does not fit is reported, not fatal
-        print("R=%d stages=%d cap=%d chunk=%d: %s" % (R, st, cap, chunk, e), flush=True)
+        print("R=%d stages=%d cap=%d chunk=%d transpose=%d: %s" % (R, st, cap, chunk, tr, e), flush=True)

@@ -86,3 +86,13 @@ def test_element_wise_assembler_batches(fb2, N, p, ncomp, kind, mat, device_bc, 
     assert _close(rhs.get_entries(), o.rhs())
     A.assembly(gids[:0].reshape(0, nd), None, None, rhs)  # empty batch is a no-op
     assert _close(rhs.get_entries(), o.rhs())
+
+
+@pytest.mark.parametrize("nranks,count", [(2, 1), (8, 4), (8, 7), (16, 4)])
+def test_peer_allreduce_protocol_on_one_device(fb2, nranks, count):
+    """The NVLink peer-memory scalar all-reduce (mailboxes, epoch flags, parity double-buffering) with every rank played by one
+    block of a cooperative launch: 200 consecutive all-reduces, every rank must hold the bit-identical rank-ordered sum."""
+    import ctypes as C
+    err = C.c_double(-1.0)
+    fb2._lib.check(fb2._lib.lib().fb2_peer_allreduce_selftest(nranks, count, 200, C.byref(err)))
+    assert err.value == 0.0

@@ -77,30 +77,45 @@ def test_midsize_serial_entrywise(fb2, asm_variant, N, p, func, prm):
     assert np.max(np.abs(xs.get_entries() - r["x"])) <= 1e-9 * np.max(np.abs(r["x"]))
 
 
-def test_midsize_spmv_variants_bitwise(fb2):
+def test_midsize_spmv_variants_bitwise(fb2, monkeypatch):
     """the same values (the atomic scatter of the boundary rows is not order-deterministic, so they are copied) through every
-    SpMV kernel variant: class-table columns must reproduce the ja stream bit for bit"""
+    SpMV kernel variant and both row maps of the consumer lane groups (natural / transposed with staggered chunks): class-table
+    columns must reproduce the ja stream bit for bit, and the row map must not change a bit of y"""
+    import ctypes as C
     N, p = (32, 32, 32), 2
     s, op = _operator(fb2, N, p, 1, fb2.poisson, FUNC_SHARP_WAVE, WAVE, None)
     v = op.get_matrix().get_values()
     x = np.random.default_rng(3).standard_normal(s.num_free_dofs)
     L = fb2._lib.lib()
-    ys = []
+    ys, seen_tr = {}, set()
     try:
-        for variant in (0, 3, 1):                      # 3 = TMA tiles streaming ja for every tile (no pattern classes)
+        for variant, tr in ((0, "0"), (0, "1"), (3, "0"), (3, "1"), (0, None), (1, None)):   # 3 = ja streamed for every tile
+            if tr is None:
+                monkeypatch.delenv("FB2_SPMV_TRANSPOSE", raising=False)
+            else:
+                monkeypatch.setenv("FB2_SPMV_TRANSPOSE", tr)
             fb2._lib.check(L.fb2_set_spmv_variant(variant))
             A2 = fb2.SparseMatrix(s)                   # the variant binds when the matrix is first applied
             A2.set_values(v)
             vx2, vy2 = s.create_dof_values(), s.create_dof_values()
             vx2.set_entries(x)
             A2.apply(vx2, vy2)
-            ys.append(vy2.get_entries())
+            ys[(variant, tr)] = vy2.get_entries()
             A2.apply(vx2, vy2)
-            assert np.array_equal(ys[-1], vy2.get_entries()), "SpMV is not run-to-run deterministic"
+            assert np.array_equal(ys[(variant, tr)], vy2.get_entries()), "SpMV is not run-to-run deterministic"
+            if variant != 1:
+                ms = C.c_double(0)
+                fb2._lib.check(L.fb2_last_phase_ms(b"spmv_transposed_rows", C.byref(ms)))
+                seen_tr.add(int(ms.value))
+                if tr is not None:
+                    assert int(ms.value) == int(tr)
     finally:
         fb2._lib.check(L.fb2_set_spmv_variant(0))
-    assert np.array_equal(ys[0], ys[1]), "class-table SpMV differs bitwise from the ja-streaming SpMV"
-    assert np.max(np.abs(ys[0] - ys[2])) <= 1e-13 * np.max(np.abs(ys[2]))
+    assert seen_tr == {0, 1}
+    ref = ys[(3, "0")]
+    for key in ((0, "0"), (0, "1"), (3, "1"), (0, None)):
+        assert np.array_equal(ys[key], ref), ("SpMV differs bitwise from the natural-map ja-streaming SpMV", key)
+    assert np.max(np.abs(ref - ys[(1, None)])) <= 1e-13 * np.max(np.abs(ys[(1, None)]))
 
 
 @pytest.mark.parametrize("N,p,parts", [((32, 32, 32), 2, (2, 2, 2)), ((24, 24, 24), 1, (2, 2, 1))])

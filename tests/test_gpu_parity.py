@@ -317,9 +317,12 @@ def test_determinism_of_reductions_and_colored_scatter(fb2):
 
 
 @pytest.mark.parametrize("N,p", [((9, 8, 7), 2), ((12, 12, 12), 1), ((5, 5, 4), 3)])
-def test_spmv_kernel_variants_agree(fb2, N, p):
+def test_spmv_kernel_variants_agree(fb2, N, p, monkeypatch):
     """variant 0 = TMA-streamed tiles, 1 = warp per row, 2 = streamed tiles with dictionary-compressed uint16 column indices:
-    2 forms the same products in the same order (bit-identical y and fused <Ap,p>, same PCG history), 1 agrees to rounding."""
+    2 forms the same products in the same order (bit-identical y and fused <Ap,p>, same PCG history), 1 agrees to rounding.
+    (natural row map for both: the transposed map of variant 0 keeps y bit for bit but sums the fused <Ap,p> partials in
+    another order -- tests/test_gpu_midsize.py::test_midsize_spmv_variants_bitwise covers it)"""
+    monkeypatch.setenv("FB2_SPMV_TRANSPOSE", "0")
     ys, hist = {}, {}
     lib = fb2._lib.lib()
     try:
