@@ -37,7 +37,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
 }
 // wait with a suspend-time hint: the thread may be parked by the hardware instead of spinning through the issue slots
-__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
   asm volatile(
       "{\n"
       ".reg .pred P1;\n"
@@ -47,7 +47,7 @@ __device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity)
       "bra LAB_WAITP;\n"
       "DONEP:\n"
       "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity), "r"(20000u)
+      "r"(parity), "r"(hint_ns)
       : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -81,6 +81,7 @@ struct SpmvClassDesc {
 #define SPMV_STAG_VAL 8
 #define SPMV_STAG_JA 8
 #define SPMV_STAG_IDX 16
+#define SPMV_WAIT_NS_DEFAULT 0u
 
 // Tried and rejected in round 2 (profiles/r2_spmv_history.txt): consumers that stream the rows of a warp's range 32 entries at a
 // time (contiguous shared-memory reads, one xor tree per finished row).  It halves the shared-memory wavefronts per non-zero
@@ -109,7 +110,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
                                                              int chunk, const int* __restrict__ dict, const i64* __restrict__ dict_ptr,
                                                              int dcap, const unsigned char* __restrict__ tile_class,
                                                              const SpmvClassDesc* __restrict__ cls_desc,
-                                                             const unsigned short* __restrict__ cls_idx, int tr) {
+                                                             const unsigned short* __restrict__ cls_idx, int tr, uint32_t wait_hint) {
   constexpr int IB = COMP ? 2 : 4;                       // bytes per streamed column index
   constexpr i64 AL = COMP ? 7 : 3;                       // element-range alignment mask
   const int* ja = (const int*)ja_any;
@@ -149,7 +150,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     const int plane = tid - NC;
     const int TPRP = (R <= 16 ? 128 : 256) / R;
     const int nch = tr ? 32 / TPRP : 1;                  // chunks per tile
-    const int CW = tr ? NC / 32 : R;                     // rows per chunk
+    const int CW = tr ? R / nch : R;                     // rows per chunk
     const i64 CA = tr ? (i64)7 : AL;                     // chunk alignment (entries, relative to the aligned tile start)
     i64 t = t_first;
     i64 e0 = 0, r0 = 0, d0 = 0, d1 = 0, cb = 0, ce = 0;
@@ -162,8 +163,10 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       CLS = (!COMP && tile_class) ? tile_class[tt] : SPMV_NOCLASS;
     };
     if (t < t_end) load_tile(t, r0, nr, e0, cb, ce, d0, d1, cls);
-    for (int it = 0; t < t_end; t += t_step, ++it) {
-      const int s = it % STAGES;
+    // stage index and ring phase advance incrementally (STAGES is a run-time value: no division per tile)
+    int s = 0;
+    uint32_t ph = 0;
+    for (; t < t_end; t += t_step) {
       unsigned char* base = smem_raw + s * stage_bytes;
       i64 ne0 = 0, nr0 = 0, nd0 = 0, nd1 = 0, ncb = 0, nce = 0;
       int nnr = 0, ncls = SPMV_NOCLASS;
@@ -180,7 +183,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       const bool have_idx = is_cls && s_lastcls[s] == cls;
       __syncwarp();
       if (plane == 0) {
-        mbar_wait_parked(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+        mbar_wait_parked(&empty_bar[s], ph ^ 1u, 20000u);
         // a dictionary that does not fit the region is not staged: the consumers then go through it in global memory
         const uint32_t dbytes = (COMP && d1 - d0 <= SPMV_DS) ? (uint32_t)(d1 - d0) * 4u : 0u;
         s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0); s_d0[s] = d0; s_cls[s] = cls;
@@ -220,6 +223,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
         }
       }
       e0 = ne0; r0 = nr0; nr = nnr; d0 = nd0; d1 = nd1; cls = ncls; cb = ncb; ce = nce;
+      if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
     return;
   }
@@ -231,14 +235,18 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
   // tr (transposed rows): lane group g of warp w owns row g * (NC / 32) + w instead of w * (32 / TPR) + g.  Where the row
   // lengths repeat with the period of a cell's created DOFs (8 for Q2) the groups of a warp then hold rows of equal length
   // and finish together; chunk g of the tile (the rows of group g) is staged SPMV_STAG_* x g entries behind its natural place
+  // With fewer lane groups than rows the warps go over the tile in passes (NC = 128 and R = 32: two).
+  const int GPW = 32 / TPR, rows_pp = (NC / 32) * GPW, NP = (R + rows_pp - 1) / rows_pp;
   const int grp = tr ? lane / TPR : 0;
-  const int row = tr ? grp * (NC / 32) + w : tid / TPR;
+  const int row0 = tr ? grp * (R / GPW) + w : tid / TPR;
+  const int row_step = tr ? NC / 32 : rows_pp;
   const int sub = tid & (TPR - 1);
   double dacc = 0.0;
-  int it = 0;
-  for (i64 t = t_first; t < t_end; t += t_step, ++it) {
-    const int s = it % STAGES;
-    mbar_wait(&full_bar[s], (it / STAGES) & 1);
+  int s = 0;
+  uint32_t ph = 0;
+  for (i64 t = t_first; t < t_end; t += t_step) {
+    if (wait_hint) mbar_wait_parked(&full_bar[s], ph, wait_hint);
+    else mbar_wait(&full_bar[s], ph);
     const i64 r0 = s_r0[s];
     const unsigned char* base = smem_raw + s * stage_bytes;
     const double* sv = (const double*)base + SPMV_STAG_VAL * grp;
@@ -274,8 +282,10 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       else return in_class ? sxw[sj16[k]] : x[sj[k] - 1];
     };
     const i64 e0a = s_e0a[s];
+    const int nr_t = s_nr[s];
+    for (int pass = 0, row = row0; pass < NP; ++pass, row += row_step) {
     double acc = 0.0;
-    const bool live = row < s_nr[s];
+    const bool live = row < nr_t;
     // the row's own x for the fused <y,x>: issued before the entry loop so that its latency is hidden behind it
     double xrow = 0.0;
     if (FUSE_DOT && sub == 0 && live) xrow = x[r0 + row];
@@ -304,16 +314,24 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
         if (p2) acc += sv[k2] * x2;
       }
     }
-    for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
+    if (TPR == 8) {   // the usual group width, unrolled
+      acc += __shfl_down_sync(0xffffffffu, acc, 4, 8);
+      acc += __shfl_down_sync(0xffffffffu, acc, 2, 8);
+      acc += __shfl_down_sync(0xffffffffu, acc, 1, 8);
+    } else {
+      for (int o = TPR >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, TPR);
+    }
     if (sub == 0 && live) {
       y[r0 + row] = acc;
       if (FUSE_DOT) dacc += acc * xrow;
     }
+    }   // passes
     // COMP: the consumers wrote xs[] through the generic proxy into a region the producer's next bulk copy (async proxy)
     // overwrites: order the two proxies before releasing the stage
     if (COMP) fence_proxy_async();
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty_bar[s]);
+    if (++s == STAGES) { s = 0; ph ^= 1u; }
   }
   if (FUSE_DOT) {
     // deterministic block sum over the consumer warps (named barrier 1: the producer warp has exited)
@@ -743,15 +761,17 @@ __global__ void k_row_map_cost(i64 n, const i64* __restrict__ irp, int R, int TP
   unsigned long long c0 = 0, c1 = 0;
   if (t < nfixed) {
     const i64 r0 = t * R;
-    for (int w = 0; w < W; ++w) {
-      int m0 = 0, m1 = 0;
-      for (int g = 0; g < G; ++g) {
-        const i64 a = r0 + w * G + g, b = r0 + g * W + w;
-        if (a < n) m0 = max(m0, (int)((irp[a + 1] - irp[a] + TPR - 1) / TPR));
-        if (b < n) m1 = max(m1, (int)((irp[b + 1] - irp[b] + TPR - 1) / TPR));
+    const int NP = R / (W * G);
+    for (int p = 0; p < NP; ++p)
+      for (int w = 0; w < W; ++w) {
+        int m0 = 0, m1 = 0;
+        for (int g = 0; g < G; ++g) {
+          const i64 a = r0 + (p * W + w) * G + g, b = r0 + g * (R / G) + p * W + w;
+          if (a < n) m0 = max(m0, (int)((irp[a + 1] - irp[a] + TPR - 1) / TPR));
+          if (b < n) m1 = max(m1, (int)((irp[b + 1] - irp[b] + TPR - 1) / TPR));
+        }
+        c0 += m0; c1 += m1;
       }
-      c0 += m0; c1 += m1;
-    }
   }
   for (int o = 16; o > 0; o >>= 1) { c0 += __shfl_down_sync(0xffffffffu, c0, o); c1 += __shfl_down_sync(0xffffffffu, c1, o); }
   if ((threadIdx.x & 31) == 0) { atomicAdd(&cost[0], c0); atomicAdd(&cost[1], c1); }
@@ -777,14 +797,14 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
   int nc = R <= 16 ? 128 : 256;
   if (getenv("FB2_SPMV_CONSUMERS")) nc = atoi(getenv("FB2_SPMV_CONSUMERS"));
   if (g_compress) nc = 256;   // the dictionary variant stages two entries per consumer thread
-  FB2_CHECK((nc == 128 || nc == 256) && nc >= (R <= 16 ? 128 : 256), "bad FB2_SPMV_CONSUMERS: too few lane groups for the tile height");
+  FB2_CHECK(nc == 128 || nc == 256, "bad FB2_SPMV_CONSUMERS");
   A->spmv_nc = nc;
   // row map: transposed when it saves >= 10 % of the lane-group iterations (rows of equal length meet in one warp);
-  // FB2_SPMV_TRANSPOSE=0/1 overrides.  Needs 8 lanes per row and as many lane groups as rows.
+  // FB2_SPMV_TRANSPOSE=0/1 overrides.  Needs 8 lanes per row and whole passes of the lane groups over the tile.
   {
     const int tpr = (R <= 16 ? 128 : 256) / R, W = nc / 32, G = 32 / tpr;
     int tr = 0;
-    if (tpr == 8 && W * G == R && !g_compress) {
+    if (tpr == 8 && R % (W * G) == 0 && !g_compress) {
       unsigned long long *d_cost, h_cost[2] = {0, 0};
       FB2_TRY(fb2_dalloc(&d_cost, 2));
       FB2_CUDA(cudaMemsetAsync(d_cost, 0, 2 * sizeof(unsigned long long), st));
@@ -870,11 +890,13 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
   i64 grid = chunk ? (nt + chunk - 1) / chunk : (nt < A->spmv_grid ? nt : (i64)A->spmv_grid);
   // class tiles bulk-copy segments of x: they need a 16-byte aligned x (always true for library vectors, not for views)
   const unsigned char* tcls = (A->spmv_cls == 1 && (((uintptr_t)x) & 15) == 0) ? A->d_tile_class + t0 : nullptr;
+  // suspend-time hint (ns) of the consumers' wait for a full stage; 0 = plain try_wait spin
+  const uint32_t wait_hint = getenv("FB2_SPMV_WAIT_NS") ? (uint32_t)atoi(getenv("FB2_SPMV_WAIT_NS")) : SPMV_WAIT_NS_DEFAULT;
 #define SPMV_LAUNCH_NC(FD, CP, NCT, JA, SMEM, DICT, DPTR, DCAP)                                                                   \
   k_spmv_stream<FD, CP, NCT><<<(unsigned)grid, NCT + 32, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
                                                                     done_flag, A->spmv_R, A->spmv_cap, nt, A->spmv_stages,   \
                                                                     A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP, \
-                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, CP ? 0 : A->spmv_tr)
+                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, CP ? 0 : A->spmv_tr, wait_hint)
 #define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                   \
   do {                                                                                                    \
     if (!CP && A->spmv_nc == 128) SPMV_LAUNCH_NC(FD, false, 128, JA, SMEM, DICT, DPTR, DCAP);             \
