@@ -571,6 +571,9 @@ def main():
                          # tiles of a verified pattern class stream no column indices: what the kernel actually has to move
                          "streamed_bytes_per_launch_estimate": per_gpu_bytes - 4.0 * nnz_loc * class_share,
                          "streamed_GBps": (per_gpu_bytes - 4.0 * nnz_loc * class_share) / (np.mean(spmv_ms) / a.cg_iters * 1e-3) / 1e9,
+                         # DRAM bytes of the ncu capture over this run's launch time: the physical bandwidth the kernel draws
+                         "traffic_GBps": (traffic / (np.mean(spmv_ms) / a.cg_iters * 1e-3) / 1e9) if traffic else None,
+                         "traffic_frac_of_peak": (traffic / (np.mean(spmv_ms) / a.cg_iters * 1e-3) / 1e9 / peak) if traffic else None,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650"},
             "roofline_assembly": {"bound": "hbm", "kernel": asm_kernel_label(a, ncomp),
                                   "achieved": asm_bytes / (np.mean(asm_ms) * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",

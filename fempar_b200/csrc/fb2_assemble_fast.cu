@@ -40,7 +40,8 @@ __global__ void k_map_keys(CellGeom g, const int* __restrict__ perm, int n_local
   int c = perm ? perm[lex] : lex;
   int key = cell_class_key(g, cl);
   cell_tab[c] = key;
-  atomicMin(&rep[key], c);
+  // the interior key is shared by almost every cell: look before the atomic (an out-of-date larger value only costs an atomic)
+  if (((volatile int*)rep)[key] > c) atomicMin(&rep[key], c);
 }
 __global__ void k_map_remap(int n_local, const int* __restrict__ class_of_key, int* cell_tab) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -71,7 +72,7 @@ __global__ void k_map_build(const int* __restrict__ cells, int nd, const int* __
 __global__ void k_map_verify(int n_local, int nd, const int* __restrict__ gids, const i64* __restrict__ irp,
                              const int* __restrict__ ja, i64 n_free, int sym, const int* __restrict__ cell_tab,
                              const unsigned short* __restrict__ tabs, int* bad_list, int* n_bad, const int* __restrict__ list,
-                             const int* __restrict__ perm) {
+                             const int* __restrict__ perm, const unsigned* __restrict__ row_fast) {
   const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int k = blockIdx.x * warps + w; k < n_local; k += gridDim.x * warps) {
     const int c = list ? (perm ? perm[list[k]] : list[k]) : k;
@@ -82,6 +83,8 @@ __global__ void k_map_verify(int n_local, int nd, const int* __restrict__ gids, 
       int i = e / nd, j = e - i * nd;
       int gi = g[i], gj = g[j];
       bool valid = gi > 0 && gi <= n_free && gj > 0 && gj <= n_free && !(sym && gi > gj);
+      // rows the gather kernel writes are never scattered through this table (same filter as k_assemble_fast)
+      if (row_fast && gi > 0 && gi <= n_free && ((row_fast[(gi - 1) >> 5] >> ((gi - 1) & 31)) & 1u)) continue;
       unsigned short rel = tab[e];
       if (valid) {
         i64 s = irp[gi - 1] + rel;
@@ -164,7 +167,8 @@ int fb2_build_scatter_map(fb2_matrix_s* A, const int* only_cells, int n_only) {
   FB2_TRY(fb2_dalloc(&d_ctabs, tab_elems * ncls));
   k_map_build<<<ncls, 256, 0, st>>>(d_reps, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym, d_ctabs);
   k_map_verify<<<fb2_num_sms() * 8, 256, 0, st>>>(only_cells ? n_only : n_local, nd, s->d_gids, A->d_irp, A->d_ja, A->n, A->sym,
-                                                   A->d_cell_tab, d_ctabs, d_bad, d_nbad, only_cells, s->d_perm);
+                                                   A->d_cell_tab, d_ctabs, d_bad, d_nbad, only_cells, s->d_perm,
+                                                   only_cells ? A->d_row_fast : nullptr);
   int nbad = 0;
   FB2_CUDA(cudaMemcpyAsync(&nbad, d_nbad, sizeof(int), cudaMemcpyDeviceToHost, st));
   FB2_CUDA(cudaStreamSynchronize(st));
@@ -609,7 +613,9 @@ int fb2_assemble_fast(fb2_matrix_s* A, const AsmArgs& args, int scatter_variant,
   const fb2_space_s* s = A->s;
   if (s->rt.p > 3) return -1;
   if (args.kind == FB2_KIND_ELASTICITY && (s->rt.ncomp != 3 || s->rt.p > 2)) return -1;   // Q3 elasticity: generic kernel
-  FB2_TRY(fb2_build_scatter_map(A, nullptr, 0));
+  // rows_path: the caller built the map for the cells the scatter kernel visits (asking for the full map here would throw that
+  // partial map away and verify every cell after all)
+  if (!rows_path) FB2_TRY(fb2_build_scatter_map(A, nullptr, 0));
   if (A->map_state != 1) return -1;
   FB2_TRY(load_const_tables(s));
   FastArgs F;

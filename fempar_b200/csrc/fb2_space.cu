@@ -697,6 +697,130 @@ __global__ void __launch_bounds__(128) k_row_fill_reg(int p, int ncomp, int M0, 
   }
 }
 
+// Same rows again, the sort replaced by a learned permutation wherever it repeats.  A warp walks rows r, r + D, r + 2 D, ...
+// (D = DOFs an interior cell creates: rows D apart sit on the same kind of n-face one cell further, so their candidate box has
+// the same shape and -- away from the boundary -- the same order of DOF ids).  It keeps, per sorted slot, the lattice offset
+// (relative to the box origin) of the candidate that landed there when it last sorted a row; for the next row it gathers the
+// candidates straight into that order and checks: same box shape, same row length, every gathered id a free DOF (and in the
+// stored triangle), ids strictly increasing.  irp already holds the exact number of admissible candidates of the row, the
+// offsets are distinct positions of the box, so a strictly increasing admissible sequence of that length IS the sorted row.
+// Any failed check falls back to the sort (64-bit keys: id, offset) and re-learns.  ~60 instead of ~1000 instructions per row.
+template <int KPL>
+__global__ void __launch_bounds__(128) k_row_fill_perm(int p, int ncomp, int M0, int M1, int M2, int lat_size, i64 n, int sym,
+                                                       const int* __restrict__ dof_node, const int* __restrict__ node_dof,
+                                                       const i64* __restrict__ irp, int* __restrict__ ja, int D, int J,
+                                                       unsigned long long* n_sorted) {
+  constexpr int SORT_N = 32 * KPL;
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const i64 gw = (i64)blockIdx.x * warps + (threadIdx.x >> 5), nw = (i64)gridDim.x * warps;
+  const i64 span = (i64)D * J;
+  const i64 ntask = ((n + span - 1) / span) * D;
+  unsigned long long sorted_here = 0;
+  for (i64 task = gw; task < ntask; task += nw) {
+    const i64 blk = task / D;
+    const int c = (int)(task - blk * D);
+    int off[KPL];
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) off[i] = 0;
+    int pb0 = -1, pb1 = -1, pb2 = -1, pcnt = -1;
+    for (int j = 0; j < J; ++j) {
+      const i64 r = blk * span + (i64)j * D + c;
+      if (r >= n) break;
+      const unsigned lat = (unsigned)dof_node[r] % (unsigned)lat_size;
+      const int a0 = (int)(lat % (unsigned)M0), a12 = (int)(lat / (unsigned)M0);
+      const int a1 = a12 % M1, a2 = a12 / M1;
+      int lo0, lo1, lo2, b0, b1, b2;
+      {
+        int hi;
+        if (a0 % p == 0) { lo0 = max(a0 - p, 0); hi = min(a0 + p, M0 - 1); } else { lo0 = (a0 / p) * p; hi = lo0 + p; }
+        b0 = hi - lo0 + 1;
+        if (a1 % p == 0) { lo1 = max(a1 - p, 0); hi = min(a1 + p, M1 - 1); } else { lo1 = (a1 / p) * p; hi = lo1 + p; }
+        b1 = hi - lo1 + 1;
+        if (a2 % p == 0) { lo2 = max(a2 - p, 0); hi = min(a2 + p, M2 - 1); } else { lo2 = (a2 / p) * p; hi = lo2 + p; }
+        b2 = hi - lo2 + 1;
+      }
+      const int base = lo0 + M0 * (lo1 + M1 * lo2);
+      const i64 start = irp[r];
+      const int cnt = (int)(irp[r + 1] - start);
+      int v[KPL];
+      bool ok = b0 == pb0 && b1 == pb1 && b2 == pb2 && cnt == pcnt;
+      if (ok) {
+        bool good = true;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) {
+          const int slot = lane * KPL + i;
+          v[i] = 0x7fffffff;
+          if (slot < cnt) {
+            const int g = node_dof[base + off[i]];
+            good = good && g > 0 && g <= n && (!sym || g >= r + 1);
+            v[i] = g;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i + 1 < KPL; ++i) good = good && (lane * KPL + i + 1 >= cnt || v[i] < v[i + 1]);
+        const int nxt = __shfl_down_sync(0xffffffffu, v[0], 1);
+        good = good && (lane == 31 || lane * KPL + KPL >= cnt || v[KPL - 1] < nxt);
+        ok = __all_sync(0xffffffffu, good);
+      }
+      if (!ok) {
+        // sort (id, offset) pairs and learn the permutation
+        ++sorted_here;
+        const int nb = b0 * b1 * b2, ncand = nb * ncomp;
+        unsigned long long key[KPL];
+        int e = lane * KPL;
+        int comp = e / nb, q = e - comp * nb;
+        int o0 = q % b0, o1 = (q / b0) % b1, o2 = q / (b0 * b1);
+#pragma unroll
+        for (int i = 0; i < KPL; ++i, ++e) {
+          unsigned long long k = ((unsigned long long)0x7fffffffu << 32) | (unsigned)e;
+          if (e < ncand) {
+            const int o = comp * lat_size + o0 + M0 * (o1 + M1 * o2);
+            const int g = node_dof[base + o];
+            if (g > 0 && g <= n && (!sym || g >= r + 1)) k = ((unsigned long long)(unsigned)g << 32) | (unsigned)o;
+          }
+          key[i] = k;
+          if (++o0 == b0) { o0 = 0; if (++o1 == b1) { o1 = 0; if (++o2 == b2) { o2 = 0; ++comp; } } }
+        }
+#pragma unroll
+        for (int k = 2; k <= SORT_N; k <<= 1) {
+#pragma unroll
+          for (int jj = k >> 1; jj > 0; jj >>= 1) {
+            if (jj >= KPL) {
+              const int lj = jj / KPL;
+#pragma unroll
+              for (int i = 0; i < KPL; ++i) {
+                const int idx = lane * KPL + i;
+                const unsigned long long other = __shfl_xor_sync(0xffffffffu, key[i], lj);
+                const bool up = (idx & k) == 0, lower = (idx & jj) == 0;
+                key[i] = (lower == up) ? min(key[i], other) : max(key[i], other);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < KPL; ++i) {
+                if ((i & jj) == 0) {
+                  const int i2 = i | jj;
+                  const bool up = ((lane * KPL + i) & k) == 0;
+                  const unsigned long long a = key[i], b = key[i2];
+                  if ((a > b) == up) { key[i] = b; key[i2] = a; }
+                }
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) { v[i] = (int)(key[i] >> 32); off[i] = (int)(unsigned)key[i]; }
+        pb0 = b0; pb1 = b1; pb2 = b2; pcnt = cnt;
+      }
+#pragma unroll
+      for (int i = 0; i < KPL; ++i) {
+        const int slot = lane * KPL + i;
+        if (slot < cnt) ja[start + slot] = v[i];
+      }
+    }
+  }
+  if (lane == 0 && sorted_here) atomicAdd(n_sorted, sorted_here);
+}
+
 extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_storage) {
   FB2_CHECK(s != nullptr, "null space");
   fb2_matrix_s* A = new fb2_matrix_s();
@@ -739,11 +863,33 @@ extern "C" int fb2_csr_create(fb2_matrix_t* out, fb2_space_t s, int symmetric_st
   k_row_fill<SN><<<blocks, threads, (threads / 32) * SN * sizeof(int), st>>>(p, ncomp, s->Mlat[0], s->Mlat[1], s->Mlat[2], \
                                                                              s->lat_size, n, A->sym, s->d_dof_node,      \
                                                                              s->d_node_dof, A->d_irp, A->d_ja)
-    static const int fill_variant = getenv("FB2_ROW_FILL") ? atoi(getenv("FB2_ROW_FILL")) : 1;   // 0: shared-memory sort
+    const int fill_variant = getenv("FB2_ROW_FILL") ? atoi(getenv("FB2_ROW_FILL")) : 2;
 #define LAUNCH_FILL_REG(K)                                                                                               \
   k_row_fill_reg<K><<<fb2_num_sms() * 16, 128, 0, st>>>(p, ncomp, s->Mlat[0], s->Mlat[1], s->Mlat[2], s->lat_size, n, A->sym, \
                                                         s->d_dof_node, s->d_node_dof, A->d_irp, A->d_ja)
-    if (fill_variant && maxrow <= 32) LAUNCH_FILL_REG(1);
+    // 2 (default): learned permutation, needs 32-bit lattice offsets; 1: register sort of every row; 0: shared-memory sort
+    const bool perm_ok = fill_variant >= 2 && maxrow <= 512 && s->lat_size * ncomp < 0x7fffffffLL;
+    if (perm_ok) {
+      unsigned long long* d_ns;
+      FB2_TRY(fb2_dalloc(&d_ns, 1));
+      FB2_CUDA(cudaMemsetAsync(d_ns, 0, sizeof(unsigned long long), st));
+      int D = ncomp;
+      for (int k = 0; k < 3; ++k) D *= p;                  // DOFs created by an interior cell
+      if (getenv("FB2_ROW_FILL_STRIDE")) D = std::max(1, atoi(getenv("FB2_ROW_FILL_STRIDE")));
+      const int J = 32;
+#define LAUNCH_FILL_PERM(K)                                                                                              \
+  k_row_fill_perm<K><<<fb2_num_sms() * 16, 128, 0, st>>>(p, ncomp, s->Mlat[0], s->Mlat[1], s->Mlat[2], (int)s->lat_size, n, A->sym, \
+                                                         s->d_dof_node, s->d_node_dof, A->d_irp, A->d_ja, D, J, d_ns)
+      if (maxrow <= 32) LAUNCH_FILL_PERM(1);
+      else if (maxrow <= 128) LAUNCH_FILL_PERM(4);
+      else LAUNCH_FILL_PERM(16);
+#undef LAUNCH_FILL_PERM
+      unsigned long long h_ns = 0;
+      FB2_CUDA(cudaMemcpyAsync(&h_ns, d_ns, sizeof(h_ns), cudaMemcpyDeviceToHost, st));
+      FB2_CUDA(cudaStreamSynchronize(st));
+      cudaFree(d_ns);
+      fb2_record_phase("pattern_rows_sorted", (double)h_ns);
+    } else if (fill_variant && maxrow <= 32) LAUNCH_FILL_REG(1);
     else if (fill_variant && maxrow <= 128) LAUNCH_FILL_REG(4);
     else if (fill_variant && maxrow <= 512) LAUNCH_FILL_REG(16);
     else if (maxrow <= 32) LAUNCH_FILL(32);
