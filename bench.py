@@ -393,6 +393,7 @@ def main():
             return None
     t_map_ms, t_gather_ms = phase("scatter_map"), phase("gather_plan")
     spmv_info = {"tiles": phase("spmv_tiles"), "tiles_in_pattern_class": phase("spmv_tiles_in_class"),
+                 "tiles_private_descriptor": phase("spmv_tiles_private"), "transposed_rows": phase("spmv_transposed_rows"),
                  "pattern_classes": phase("spmv_classes"), "classes_setup_ms": phase("spmv_classes_ms")}
     asm_info = {"owner_cells_gather": phase("gather_fast_cells"), "cells_scatter": phase("gather_slow_cells"),
                 "rows_scatter": phase("gather_slow_rows")}
@@ -536,6 +537,8 @@ def main():
     class_share = 0.0
     if a.spmv_variant == 0 and spmv_info["tiles"] and spmv_info["tiles_in_pattern_class"] is not None and ppr == 1:
         class_share = spmv_info["tiles_in_pattern_class"] / spmv_info["tiles"]
+        # tiles with a private descriptor stream a uint16 index instead of ja: 10 instead of 12 B per non-zero
+        class_share += 0.5 * (spmv_info.get("tiles_private_descriptor") or 0.0) / spmv_info["tiles"]
     achieved = per_gpu_bytes / (np.mean(spmv_ms) / a.cg_iters * 1e-3) / 1e9
     asm_bytes = nnz_loc * 8 + n_loc * 8
     try:

@@ -148,7 +148,9 @@ struct fb2_matrix_s {
   int spmv_cls = 0;                         // 0 not built, 1 in use, -1 unavailable / switched off
   int spmv_ncls = 0;
   i64 spmv_tiles_in_class = 0;
-  unsigned char* d_tile_class = nullptr;    // [ntiles] class id, 0xFF: none
+  unsigned char* d_tile_class = nullptr;    // [ntiles] class id, 0xFF: none, 0xFE: private descriptor (d_tile_priv)
+  int* d_tile_priv = nullptr;               // [ntiles] descriptor index of a private tile (behind the classes in d_cls_desc / d_cls_idx)
+  i64 spmv_tiles_private = 0;
   void* d_cls_desc = nullptr;               // SpmvClassDesc[ncls]
   unsigned short* d_cls_idx = nullptr;      // [ncls][spmv_cap] x-window position of every staged entry
   int owns_space = 0;                       // matrix created from host arrays without a space: it owns a bare one

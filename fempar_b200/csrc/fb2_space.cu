@@ -915,7 +915,7 @@ extern "C" int fb2_csr_destroy(fb2_matrix_t A) {
   fb2_solver_ws_free(A);
   cudaFree(A->d_irp); cudaFree(A->d_ja); cudaFree(A->d_val); cudaFree(A->d_cell_tab); cudaFree(A->d_tabs); cudaFree(A->d_tile_row); cudaFree(A->d_tile_nrows);
   cudaFree(A->d_idx16); cudaFree(A->d_dict); cudaFree(A->d_dict_ptr);
-  cudaFree(A->d_tile_class); cudaFree(A->d_cls_desc); cudaFree(A->d_cls_idx);
+  cudaFree(A->d_tile_class); cudaFree(A->d_cls_desc); cudaFree(A->d_cls_idx); cudaFree(A->d_tile_priv);
   cudaFree(A->d_rows_plan); cudaFree(A->d_chunk_base); cudaFree(A->d_row_fast); cudaFree(A->d_slow_rows); cudaFree(A->d_slow_cells);
   if (A->owns_space) fb2_fe_space_destroy(A->s);
   delete A;

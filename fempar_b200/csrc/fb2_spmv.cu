@@ -76,6 +76,10 @@ struct SpmvClassDesc {
   int off[32];     // position of the segment in the window, doubles
 };
 #define SPMV_NOCLASS 0xFF
+// 0xFE in the tile table: a tile with its own descriptor and index table (no class mates, but its columns still form <= 31
+// segments of x: index-free like a class tile, 10 B per non-zero); its descriptor index is in tile_priv[]
+#define SPMV_PRIVATE 0xFE
+#define SPMV_NONE (-1)
 // transposed rows: stagger (entries) of chunk g in the stage, per stream.  val: 8 x 8 B = half of the 32 banks, so that the four
 // 8-lane groups of a warp pair up into two conflict-free wavefronts; ja: 8 x 4 B and class index table: 16 x 2 B = 8 banks each
 #define SPMV_STAG_VAL 8
@@ -110,7 +114,8 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
                                                              int chunk, const int* __restrict__ dict, const i64* __restrict__ dict_ptr,
                                                              int dcap, const unsigned char* __restrict__ tile_class,
                                                              const SpmvClassDesc* __restrict__ cls_desc,
-                                                             const unsigned short* __restrict__ cls_idx, int tr, uint32_t wait_hint) {
+                                                             const unsigned short* __restrict__ cls_idx, int tr, uint32_t wait_hint,
+                                                             const int* __restrict__ tile_priv) {
   constexpr int IB = COMP ? 2 : 4;                       // bytes per streamed column index
   constexpr i64 AL = COMP ? 7 : 3;                       // element-range alignment mask
   const int* ja = (const int*)ja_any;
@@ -136,7 +141,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
   const i64 t_step = chunk ? 1 : (i64)gridDim.x;
   const i64 t_end = chunk ? min(t_first + chunk, ntiles) : ntiles;
   if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NC / 32); s_lastcls[s] = SPMV_NOCLASS; }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], NC / 32); s_lastcls[s] = SPMV_NONE; }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -154,13 +159,17 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     const i64 CA = tr ? (i64)7 : AL;                     // chunk alignment (entries, relative to the aligned tile start)
     i64 t = t_first;
     i64 e0 = 0, r0 = 0, d0 = 0, d1 = 0, cb = 0, ce = 0;
-    int nr = 0, cls = SPMV_NOCLASS;
+    int nr = 0, cls = SPMV_NONE;
     auto load_tile = [&](i64 tt, i64& R0, int& NR, i64& E0, i64& CB, i64& CE, i64& D0, i64& D1, int& CLS) {
       R0 = tile_row[tt]; NR = tile_nrows[tt]; E0 = irp[R0];
       CB = CE = 0;
       if (plane < nch) { CB = irp[R0 + min(plane * CW, NR)]; CE = irp[R0 + min((plane + 1) * CW, NR)]; }
       if (COMP) { D0 = dict_ptr[tt]; D1 = dict_ptr[tt + 1]; }
-      CLS = (!COMP && tile_class) ? tile_class[tt] : SPMV_NOCLASS;
+      CLS = SPMV_NONE;
+      if (!COMP && tile_class) {
+        const int c8 = tile_class[tt];
+        CLS = c8 == SPMV_NOCLASS ? SPMV_NONE : c8 == SPMV_PRIVATE ? tile_priv[tt] : c8;
+      }
     };
     if (t < t_end) load_tile(t, r0, nr, e0, cb, ce, d0, d1, cls);
     // stage index and ring phase advance incrementally (STAGES is a run-time value: no division per tile)
@@ -169,7 +178,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     for (; t < t_end; t += t_step) {
       unsigned char* base = smem_raw + s * stage_bytes;
       i64 ne0 = 0, nr0 = 0, nd0 = 0, nd1 = 0, ncb = 0, nce = 0;
-      int nnr = 0, ncls = SPMV_NOCLASS;
+      int nnr = 0, ncls = SPMV_NONE;
       // prefetch the header of the next tile before blocking on the empty barrier
       const i64 tn = t + t_step;
       if (tn < t_end) load_tile(tn, nr0, nnr, ne0, ncb, nce, nd0, nd1, ncls);
@@ -177,7 +186,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       const i64 ca = e0a + ((cb - e0a) & ~CA);                                    // aligned start of this lane's chunk
       const uint32_t cn = (plane < nch && ce > cb) ? (uint32_t)((ce - ca + CA) & ~CA) : 0u;   // its entries
       const uint32_t cnt_all = __reduce_add_sync(0xffffffffu, cn);
-      const bool is_cls = !COMP && cls != SPMV_NOCLASS;
+      const bool is_cls = !COMP && cls != SPMV_NONE;
       // consecutive tiles of an x-row of cells share their class: the index table this stage received two tiles ago is still
       // there (only index / ja copies write that region) and is not copied again
       const bool have_idx = is_cls && s_lastcls[s] == cls;
@@ -187,7 +196,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
         // a dictionary that does not fit the region is not staged: the consumers then go through it in global memory
         const uint32_t dbytes = (COMP && d1 - d0 <= SPMV_DS) ? (uint32_t)(d1 - d0) * 4u : 0u;
         s_e0a[s] = e0a; s_r0[s] = r0; s_nr[s] = nr; s_nd[s] = (int)(d1 - d0); s_d0[s] = d0; s_cls[s] = cls;
-        s_lastcls[s] = is_cls ? cls : SPMV_NOCLASS;
+        s_lastcls[s] = is_cls ? cls : SPMV_NONE;
         if (is_cls) {
           const SpmvClassDesc& D = cls_desc[cls];
           s_xoff[s] = D.idx_bytes;
@@ -274,7 +283,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
       }
     }
     // class tile: uint16 window positions where ja would be, the x window right behind them
-    const bool in_class = !COMP && tile_class && s_cls[s] != SPMV_NOCLASS;
+    const bool in_class = !COMP && tile_class && s_cls[s] != SPMV_NONE;
     const double* sxw = (const double*)(base + (size_t)cap * 8 + (in_class ? s_xoff[s] : 0));
     // x value of the k-th staged entry
     auto xat = [&](int k) -> double {
@@ -655,6 +664,29 @@ __global__ void k_tile_classify(i64 ntiles, i64 n, const i64* __restrict__ irp, 
   }
 }
 
+// tiles left without class, in tile order of discovery (the descriptor index of a private tile carries no meaning)
+__global__ void k_list_unclassified(i64 ntiles, const unsigned char* __restrict__ tile_class, int* list, int* count, int limit) {
+  const i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ntiles || tile_class[t] != SPMV_NOCLASS) return;
+  const int k = atomicAdd(count, 1);
+  if (k < limit) list[k] = (int)t;
+}
+// a private descriptor is used when it was built (valid) and every x segment lies inside the vector
+__global__ void k_private_assign(int n_priv, const int* __restrict__ list, const int* __restrict__ valid,
+                                 const SpmvClassDesc* __restrict__ desc, const i64* __restrict__ tile_row, i64 n, int first,
+                                 unsigned char* tile_class, int* tile_priv, unsigned long long* n_used) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_priv) return;
+  const int t = list[k];
+  bool ok = valid[k] != 0;
+  if (ok) {
+    const SpmvClassDesc& D = desc[k];
+    const i64 r0 = tile_row[t];
+    for (int g = 0; g < D.nseg; ++g) ok = ok && r0 + D.delta[g] >= 0 && r0 + D.delta[g] + D.len[g] <= n;
+  }
+  if (ok) { tile_class[t] = (unsigned char)SPMV_PRIVATE; tile_priv[t] = first + k; atomicAdd(n_used, 1ULL); }
+}
+
 static int g_spmv_classes = getenv("FB2_SPMV_CLASSES") ? atoi(getenv("FB2_SPMV_CLASSES")) : 1;
 void fb2_spmv_set_classes(bool on) { g_spmv_classes = on ? 1 : 0; }
 
@@ -736,6 +768,43 @@ static int spmv_build_classes(fb2_matrix_s* A) {
     if (cudaGetLastError() != cudaSuccess) rc = 1;
     A->spmv_ncls = ncls; A->spmv_tiles_in_class = (i64)h_nin;
     if (rc == 0 && h_nin * 4 >= (unsigned long long)nt) A->spmv_cls = 1;   // worth the extra branch: a quarter of the tiles or more
+    // Private descriptors for the tiles without class mates (next to sub-domain interfaces and mesh boundaries their columns
+    // still form a few segments of x): the same index-free consumer path, 10 B per non-zero instead of 12 B + gathers.
+    // Only when classes are in use and the rest is small (<= a quarter of the tiles, <= 1 GiB of tables).
+    A->spmv_tiles_private = 0;
+    const i64 n_rest = nt - (i64)h_nin;
+    static const int use_private = getenv("FB2_SPMV_PRIVATE") ? atoi(getenv("FB2_SPMV_PRIVATE")) : 1;
+    if (A->spmv_cls == 1 && use_private && n_rest > 0 && n_rest * 4 <= nt &&
+        (size_t)n_rest * ((size_t)A->spmv_cap * 2 + sizeof(SpmvClassDesc)) <= ((size_t)1 << 30)) {
+      int *d_list, *d_cnt, *d_valid2;
+      unsigned long long* d_used;
+      FB2_TRY(fb2_dalloc(&d_list, (size_t)n_rest)); FB2_TRY(fb2_dalloc(&d_cnt, 1)); FB2_TRY(fb2_dalloc(&d_valid2, (size_t)n_rest));
+      FB2_TRY(fb2_dalloc(&d_used, 1));
+      FB2_CUDA(cudaMemsetAsync(d_cnt, 0, sizeof(int), st));
+      FB2_CUDA(cudaMemsetAsync(d_used, 0, sizeof(unsigned long long), st));
+      k_list_unclassified<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(nt, A->d_tile_class, d_list, d_cnt, (int)n_rest);
+      // grow the descriptor and index tables: classes first, private tiles behind them
+      void* desc2; unsigned short* idx2;
+      FB2_TRY(fb2_dalloc((char**)&desc2, ((size_t)ncls + n_rest) * sizeof(SpmvClassDesc)));
+      FB2_TRY(fb2_dalloc(&idx2, ((size_t)ncls + n_rest) * A->spmv_cap + 8));
+      FB2_CUDA(cudaMemcpyAsync(desc2, A->d_cls_desc, (size_t)ncls * sizeof(SpmvClassDesc), cudaMemcpyDeviceToDevice, st));
+      FB2_CUDA(cudaMemcpyAsync(idx2, A->d_cls_idx, (size_t)ncls * A->spmv_cap * sizeof(unsigned short), cudaMemcpyDeviceToDevice, st));
+      FB2_TRY(fb2_dalloc(&A->d_tile_priv, (size_t)nt));
+      FB2_CUDA(cudaMemsetAsync(A->d_tile_priv, 0xff, sizeof(int) * (size_t)nt, st));
+      SpmvClassDesc* pdesc = (SpmvClassDesc*)desc2 + ncls;
+      k_class_build<<<(unsigned)n_rest, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_list, A->spmv_cap, idx_extra,
+                                                     pdesc, idx2 + (size_t)ncls * A->spmv_cap, d_valid2);
+      k_private_assign<<<(unsigned)((n_rest + 255) / 256), 256, 0, st>>>((int)n_rest, d_list, d_valid2, pdesc, A->d_tile_row, A->n, ncls,
+                                                                          A->d_tile_class, A->d_tile_priv, d_used);
+      unsigned long long h_used = 0;
+      FB2_CUDA(cudaMemcpyAsync(&h_used, d_used, sizeof(h_used), cudaMemcpyDeviceToHost, st));
+      FB2_CUDA(cudaStreamSynchronize(st));
+      if (cudaGetLastError() != cudaSuccess) rc = 1;
+      cudaFree(A->d_cls_desc); cudaFree(A->d_cls_idx);
+      A->d_cls_desc = desc2; A->d_cls_idx = idx2;
+      A->spmv_tiles_private = (i64)h_used;
+      cudaFree(d_list); cudaFree(d_cnt); cudaFree(d_valid2); cudaFree(d_used);
+    }
     cudaFree(d_ch); cudaFree(d_rep); cudaFree(d_valid); cudaFree(d_nin);
   }
   cudaFree(hash); cudaFree(hash_s); cudaFree(uniq); cudaFree(tid); cudaFree(tid_s); cudaFree(counts); cudaFree(d_nruns);
@@ -747,6 +816,7 @@ static int spmv_build_classes(fb2_matrix_s* A) {
   fb2_record_phase("spmv_classes_ms", ms);
   fb2_record_phase("spmv_classes", (double)A->spmv_ncls);
   fb2_record_phase("spmv_tiles_in_class", (double)A->spmv_tiles_in_class);
+  fb2_record_phase("spmv_tiles_private", (double)A->spmv_tiles_private);
   fb2_record_phase("spmv_signatures", (double)nruns);
   if (rc) { fb2_set_error("SpMV class construction failed"); return 1; }
   return 0;
@@ -871,12 +941,12 @@ int fb2_spmv_prepare(fb2_matrix_s* A) {
 extern "C" int fb2_csr_spmv_reset(fb2_matrix_t A) {
   FB2_CHECK(A, "null matrix");
   FB2_CUDA(cudaStreamSynchronize(fb2_stream()));
-  cudaFree(A->d_tile_row); cudaFree(A->d_tile_nrows); cudaFree(A->d_tile_class); cudaFree(A->d_cls_desc); cudaFree(A->d_cls_idx);
+  cudaFree(A->d_tile_row); cudaFree(A->d_tile_nrows); cudaFree(A->d_tile_class); cudaFree(A->d_cls_desc); cudaFree(A->d_cls_idx); cudaFree(A->d_tile_priv);
   cudaFree(A->d_idx16); cudaFree(A->d_dict); cudaFree(A->d_dict_ptr);
-  A->d_tile_row = nullptr; A->d_tile_nrows = nullptr; A->d_tile_class = nullptr; A->d_cls_desc = nullptr; A->d_cls_idx = nullptr;
+  A->d_tile_row = nullptr; A->d_tile_nrows = nullptr; A->d_tile_class = nullptr; A->d_cls_desc = nullptr; A->d_cls_idx = nullptr; A->d_tile_priv = nullptr;
   A->d_idx16 = nullptr; A->d_dict = nullptr; A->d_dict_ptr = nullptr;
   A->spmv_R = A->spmv_cap = A->spmv_grid = A->spmv_stages = 0; A->spmv_ntiles = 0; A->spmv_smem = 0;
-  A->spmv_nc = 0; A->spmv_tr = 0; A->spmv_comp = 0; A->spmv_cls = 0; A->spmv_ncls = 0; A->spmv_tiles_in_class = 0; A->spmv_t_itf = -1; A->spmv_row_itf = -1;
+  A->spmv_nc = 0; A->spmv_tr = 0; A->spmv_comp = 0; A->spmv_cls = 0; A->spmv_ncls = 0; A->spmv_tiles_in_class = 0; A->spmv_tiles_private = 0; A->spmv_t_itf = -1; A->spmv_row_itf = -1;
   return 0;
 }
 
@@ -896,7 +966,7 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
   k_spmv_stream<FD, CP, NCT><<<(unsigned)grid, NCT + 32, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
                                                                     done_flag, A->spmv_R, A->spmv_cap, nt, A->spmv_stages,   \
                                                                     A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP, \
-                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, CP ? 0 : A->spmv_tr, wait_hint)
+                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, CP ? 0 : A->spmv_tr, wait_hint, A->d_tile_priv ? A->d_tile_priv + t0 : nullptr)
 #define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                   \
   do {                                                                                                    \
     if (!CP && A->spmv_nc == 128) SPMV_LAUNCH_NC(FD, false, 128, JA, SMEM, DICT, DPTR, DCAP);             \
