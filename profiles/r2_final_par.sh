@@ -1,6 +1,15 @@
 # Final multi-GPU evidence on N GPUs of one box: NCCL / peer-memory parity tests, bench lines (plain, with the per-rank timeline,
-# and with the peer-memory all-reduce switched off for the A/B).   usage: bash profiles/r2_final_par.sh N
+# and with the peer-memory all-reduce switched off for the A/B).   usage: bash profiles/r2_final_par.sh N [short]
+# short: the parity tests of tests/test_gpu_par.py and ONE bench line (with the per-rank timeline) only
 N=$1
+if [ "$2" = "short" ]; then
+set -x
+timeout 900 python -m pytest tests/test_gpu_par.py -m gpu -q > gpurun_out/fp_pytest_par_n$N.log 2>&1; echo "rc=$?" >> gpurun_out/fp_pytest_par_n$N.log
+tail -3 gpurun_out/fp_pytest_par_n$N.log
+FB2_PAR_TIMELINE=1 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29812 bench.py --gpus $N > gpurun_out/fp_bench_n${N}_timeline.json 2> gpurun_out/fp_bench_n${N}_timeline.err
+tail -c 1500 gpurun_out/fp_bench_n${N}_timeline.json
+exit 0
+fi
 set -x
 timeout 900 python -m pytest tests/test_gpu_par.py tests/test_gpu_boundary.py -m gpu -q > gpurun_out/fp_pytest_par_n$N.log 2>&1; echo "rc=$?" >> gpurun_out/fp_pytest_par_n$N.log
 tail -3 gpurun_out/fp_pytest_par_n$N.log
