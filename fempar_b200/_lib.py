@@ -84,6 +84,7 @@ _SIGS = {
     "fb2_vec_dot": [_VP, _VP, C.POINTER(C.c_double)],
     "fb2_vec_nrm2": [_VP, C.POINTER(C.c_double)],
     "fb2_vec_local_dot": [_VP, _VP, C.POINTER(C.c_double)],
+    "fb2_vec_dot_no_alloc": [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_double)],
     "fb2_vec_nullify_non_owned_dofs": [_VP],
     "fb2_vec_extract_subvector": [_VP, C.c_int32, _VP, _VP],
     "fb2_vec_insert_subvector": [_VP, C.c_int32, _VP, _VP],

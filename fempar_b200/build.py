@@ -7,7 +7,7 @@ import sysconfig
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfempar_b200.so")
-SOURCES = ["fb2_space.cu", "fb2_assemble.cu", "fb2_assemble_fast.cu", "fb2_assemble_rows.cu", "fb2_solver.cu", "fb2_spmv.cu", "fb2_comm.cu", "fb2_par.cu", "fb2_boundary.cu", "fb2_krylov.cu", "fb2_unstructured.cu"]
+SOURCES = ["fb2_space.cu", "fb2_assemble.cu", "fb2_assemble_fast.cu", "fb2_assemble_rows.cu", "fb2_solver.cu", "fb2_spmv.cu", "fb2_comm.cu", "fb2_par.cu", "fb2_boundary.cu", "fb2_krylov.cu", "fb2_unstructured.cu", "fb2_no_alloc.cu"]
 
 
 def nccl_dirs():

@@ -27,6 +27,8 @@ STRUCTS = {"fb2_ils_params_t", "fb2_ils_ext_params_t"}
 # pointer arguments the header documents as "may be NULL": type(c_ptr), value (pass c_loc(array) or c_null_ptr)
 NULLABLE = {"history", "history_extra", "func_params", "mat_params", "fixed_dof_values", "elmat", "elvec", "val", "weight",
             "host_in", "ms_total", "ms_spmv", "irp_host", "ja_host", "gid_out", "part_out", "dinv"}
+# DEVICE pointers (what fb2_vec_device_ptr returns): a Fortran array dummy would pass a host address, so type(c_ptr), value too
+DEVICE_PTRS = {"x_dev", "y_dev"}
 
 
 def strip_comments(txt):
@@ -69,7 +71,7 @@ def fortran_decl(a, fname=""):
             return "type(c_ptr), value :: %s" % name
         # handle*: the new handle of a create call (scalar by reference), or the handle list of a *_multi call (array)
         return "type(c_ptr) :: %s%s" % (name, "(*)" if fname.endswith("_multi") else "")
-    if (b == "void" and n >= 1) or (n >= 1 and name in NULLABLE and b in SCALARS):
+    if (b == "void" and n >= 1) or (n >= 1 and (name in NULLABLE or name in DEVICE_PTRS) and b in SCALARS):
         return "type(c_ptr), value :: %s" % name
     if b == "char" and n == 1:
         return "character(kind=c_char), %s :: %s(*)" % (intent, name)

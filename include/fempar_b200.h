@@ -300,6 +300,18 @@ int fb2_error_norms(fb2_space_t s, fb2_vector_t x, int func, const double* func_
 #define FB2_NORM_W1INFTY 10
 int fb2_error_norms_all(fb2_space_t s, fb2_vector_t x, int func, const double* func_params, double exponent, double norms[11]);
 
+/* ---- allocation-free dot product ------------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  result_host <- sum_i x_dev[i] * y_dev[i], i < n
+ * (the plain local dot: no sub-domain weights, no all-reduce).  x_dev / y_dev are device pointers (fb2_vec_device_ptr),
+ * result_host a host pointer; the call blocks until the result is there.  The block partials live in a file-scope __device__
+ * array of 65 568 doubles (512 KiB + 256 B per GPU that loads the library, held until exit) instead of the library's
+ * cudaMalloc'ed scratch; one partial per 4 096 elements bounds the length: n > FB2_NO_ALLOC_MAX_N returns 2 with
+ * fb2_last_error_string() set.  No cudaMalloc, cudaFree or allocating routine is called.  Every call shares the array
+ * (nothing in it has to start at zero: each slot read was written earlier in the same call): calls that overlap on the GPU race. */
+#define FB2_NO_ALLOC_MAX_N 268435456LL
+int fb2_vec_dot_no_alloc(const double* x_dev, const double* y_dev, int64_t n, double* result_host);
+
 #ifdef __cplusplus
 }
 #endif
