@@ -670,6 +670,25 @@ int fb2_ils_load_initial_solution(fb2_matrix_t A, double* x) {
   return 0;
 }
 
+// PCG set-up from the zero initial solution in ONE pass over b (and dinv): x <- 0, r <- b, p <- M^-1 b, and the block partials
+// of <r,p>, <r,r> (= <b,b>) -- same thread/block mapping and summation order as k_dot, so the sums are the bits the separate
+// kernels gave.  partials: [2][gridDim.x]
+__global__ void k_cg_setup_zero_x0(const double* __restrict__ b, const double* __restrict__ dinv, const double* __restrict__ w,
+                                   i64 n, double* __restrict__ x, double* __restrict__ r, double* __restrict__ p, double* partials) {
+  __shared__ double s_red[32];
+  double a_rp = 0.0, a_rr = 0.0;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) {
+    const double bi = b[i], pi = dinv ? dinv[i] * bi : bi, wi = w ? w[i] : 1.0;
+    x[i] = 0.0; r[i] = bi; p[i] = pi;
+    a_rp += wi * bi * pi;
+    a_rr += wi * bi * bi;
+  }
+  const double s0 = block_sum(a_rp, s_red);
+  __syncthreads();
+  const double s1 = block_sum(a_rr, s_red);
+  if (threadIdx.x == 0) { partials[blockIdx.x] = s0; partials[gridDim.x + blockIdx.x] = s1; }
+}
+
 static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const double* b, double* x, bool par, double rtol,
                     double atol, int maxit, int stop) {
   cudaStream_t s = fb2_stream();
@@ -678,21 +697,26 @@ static int cg_setup(fb2_matrix_t A, const double* dinv, const double* w, const d
   // x <- 0 ; r = A x ; r = b - r   (cg.f90:142,158-162)
   // The initial solution is zero (base_iterative_linear_solver.f90:281-282), so r = b - A*0 = b bit for bit: the
   // reference's initial SpMV and its halo exchange are skipped.
+  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
   if (fb2_ils_has_initial_solution(A)) {   // user-selected initial solution: the full r = b - A x (cg.f90:158-162)
     FB2_TRY(fb2_ils_load_initial_solution(A, x));
     FB2_TRY(fb2_op_apply(A, x, W.r));
     FB2_TRY(fb2_dev_axpby(W.r, 1.0, b, -1.0, n));
+    // z = M^-1 r ; p = z ; r_z = <r,z>
+    if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, dinv, W.r, n);
+    else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    FB2_TRY(fb2_dot_device(W.r, W.p, w, n, d_tmp));          // r_z
+    FB2_TRY(fb2_dot_device(W.r, W.r, w, n, d_tmp + 1));      // ||r(0)||^2
+    FB2_TRY(fb2_dot_device(b, b, w, n, d_tmp + 2));          // ||b||^2
   } else {
-    k_init<<<vec_grid(n), 256, 0, s>>>(x, 0.0, n);
-    FB2_CUDA(cudaMemcpyAsync(W.r, b, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    // zero initial solution: one fused pass (x, r, p, <r,p>, <r,r> = <b,b>) instead of 3 fills and 3 dots
+    const int g = reduce_grid(n);
+    double* part = fb2_scratch_partials();
+    k_cg_setup_zero_x0<<<g, 256, 0, s>>>(b, dinv, w, n, x, W.r, W.p, part);
+    k_reduce_partials<<<1, 256, 0, s>>>(part, g, g, 2, d_tmp);
+    FB2_CUDA(cudaMemcpyAsync(d_tmp + 2, d_tmp + 1, sizeof(double), cudaMemcpyDeviceToDevice, s));   // ||b||^2 = ||r(0)||^2
+    FB2_CUDA(cudaGetLastError());
   }
-  // z = M^-1 r ; p = z ; r_z = <r,z>
-  if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.p, dinv, W.r, n);
-  else FB2_CUDA(cudaMemcpyAsync(W.p, W.r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
-  double* d_tmp = fb2_scratch_partials() + FB2_MAX_PARTIALS * 4;
-  FB2_TRY(fb2_dot_device(W.r, W.p, w, n, d_tmp));          // r_z
-  FB2_TRY(fb2_dot_device(W.r, W.r, w, n, d_tmp + 1));      // ||r(0)||^2
-  FB2_TRY(fb2_dot_device(b, b, w, n, d_tmp + 2));          // ||b||^2
   if (stop == FB2_STOP_RES_NRMGIVEN_RHS_NRMGIVEN) {        // |b|_inv(M): r = inv(M) b ; b.r   (cg.f90:144-154), Ap is free here
     if (dinv) k_ew_product<<<vec_grid(n), 256, 0, s>>>(W.Ap, dinv, b, n);
     FB2_TRY(fb2_dot_device(b, dinv ? W.Ap : b, w, n, d_tmp + 3));
