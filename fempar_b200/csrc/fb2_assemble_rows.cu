@@ -51,6 +51,7 @@ struct RowsArgs {
   FuncPrm fn;
   int nseg, seg_len;          // x-segments per pencil, owner cells per segment
   int npy, npz;               // pencils per direction
+  unsigned char stage_swz[32];     // chunk-image swizzle, see h_stage_swz (zeros = identity, FB2_ASM_SWIZZLE=0)
   unsigned char row_of_node[27];   // chunk row (0..P^3-1) of the owner cell's node (a1-1) + P (a2-1) + P^2 (a3-1)
 };
 
@@ -63,6 +64,14 @@ template <int P> __device__ __forceinline__ int unit_a(int t) { return t == P ? 
 // ------------------------------------------------------------------------------------------
 // the gather kernel (Q2: 27 units = 27 lanes, one owner cell per warp pass)
 // ------------------------------------------------------------------------------------------
+// Chunk image in shared memory: slot s lives at s ^ stage_swz[s >> 4], a permutation inside every aligned group of 16 doubles
+// (= the 16 eight-byte banks; table passed in RowsArgs::stage_swz), so the coalesced read-out of 32 consecutive slots stays conflict-free whatever the table holds.
+// The table was searched offline against the scatter of the interior Q2 plan (27 lanes store column j of their row: 112
+// wavefronts per owner cell with the identity, 76 with this table, 51 if conflict-free; ncu had 19 % of the kernel's
+// shared-memory wavefronts on that store).  Any table is correct; this one is only tuned for the interior plan.
+static const unsigned char h_stage_swz[32] = {4, 8, 1, 15, 0, 2, 13, 14, 1, 4, 4, 6, 4, 1, 3, 2,
+                                              4, 8, 1, 9, 5, 12, 13, 12, 4, 9, 7, 9, 1, 10, 11, 0};
+
 template <int P, bool SRC, bool ZSKIP>
 __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
   static_assert(P == 2, "row-owner kernel: Q2 (27 units per owner cell = one warp pass)");
@@ -85,13 +94,17 @@ __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
   double* s_qw = s_gp + (SRC ? NQ * 10 : 0);                    // [NQ]
   double* s_B = s_qw + NQ;                                     // [N1*N1]
   double* s_C = s_B + N1 * N1;
-  unsigned short* s_plan = (unsigned short*)(s_C + N1 * N1);   // [NN][NN]
+  unsigned short* s_plan = (unsigned short*)(s_C + N1 * N1);   // [NN columns][32 lanes]: swizzled image position of (unit, column)
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   for (int e = tid; e < NQ * 24; e += blockDim.x) s_gd[(e / 24) * 26 + e % 24] = R.gdphi[e];
   if (SRC) for (int e = tid; e < NQ * 8; e += blockDim.x) s_gp[(e / 8) * 10 + e % 8] = R.gphi[e];
   for (int e = tid; e < NQ; e += blockDim.x) s_qw[e] = R.qw[e];
   if (tid < N1 * N1) { s_B[tid] = c_B1[P - 1][tid]; s_C[tid] = c_C1[P - 1][tid]; }
-  for (int e = tid; e < NN * NN; e += blockDim.x) s_plan[e] = R.plan[e];
+  static_assert(CH <= 512, "stage_swz covers 32 groups of 16 slots");
+  for (int e = tid; e < NN * NN; e += blockDim.x) {   // transposed: the lanes of a warp read consecutive uint16 (one wavefront)
+    const unsigned short slot = R.plan[e];
+    s_plan[(e % NN) * 32 + e / NN] = slot == 0xFFFF ? slot : (unsigned short)(slot ^ R.stage_swz[slot >> 4]);
+  }
 
   // pencil and x-segment of this CTA (local-box cell coordinates)
   int b = blockIdx.x;
@@ -164,7 +177,7 @@ __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
   const bool rcv0 = unit_on && t0 == P - 1, rcv1 = unit_on && t1 == P - 1, rcv2 = unit_on && t2 == P - 1;
   const bool owner_lane = unit_on && d0 == 0 && d1 == 0 && d2 == 0;
   double* stage = s_stage + w * CH;
-  const unsigned short* myplan = s_plan + (unit_on ? lane : 0) * NN;
+  const unsigned short* myplan = s_plan + (unit_on ? lane : 0);
 
   __syncthreads();
   slab_geometry(x_begin);
@@ -249,14 +262,14 @@ __global__ void __launch_bounds__(256, 2) k_assemble_rows(RowsArgs R) {
       if (unit_on) {
 #pragma unroll
         for (int j = 0; j < NN; ++j) {
-          const unsigned short slot = myplan[j];
+          const unsigned short slot = myplan[j * 32];
           if (slot != 0xFFFF) stage[slot] = acc[j];
         }
       }
       __syncwarp();
       double* dst = R.val + cbase[h];
 #pragma unroll
-      for (int e = 0; e < CH; e += 32) dst[e + lane] = stage[e + lane];
+      for (int e = 0; e < CH; e += 32) dst[e + lane] = stage[(e + lane) ^ R.stage_swz[(e + lane) >> 4]];
       __syncwarp();
     }
     __syncthreads();      // the next step's geometry overwrites the slab of this step
@@ -407,7 +420,7 @@ size_t rows_smem_bytes(bool src) {
   constexpr int N1 = P + 1, NN = N1 * N1 * N1, NQ = NN, CH = rows_chunk(P);
   constexpr int SC = NQ * 6, SB = GZ * SC + 10, SA = GY * SB + 4;
   size_t d = 2 * (size_t)SA + 8 * (size_t)CH + (src ? 2 * GY * GZ * NQ + NQ * 10 : 0) + NQ * 26 + NQ + 2 * N1 * N1;
-  return d * sizeof(double) + (size_t)NN * NN * sizeof(unsigned short) + 16;
+  return d * sizeof(double) + (size_t)NN * 32 * sizeof(unsigned short) + 16;
 }
 
 }  // namespace
@@ -537,6 +550,8 @@ int fb2_rows_launch(fb2_matrix_s* A, const AsmArgs& a) {
   const bool zskip = tables_have_centre_zeros(s);
   RowsArgs R;
   R.g = a.g; R.perm = a.perm; R.chunk_base = A->d_chunk_base; R.gids = a.gids; R.plan = A->d_rows_plan;
+  static const int use_swz = getenv("FB2_ASM_SWIZZLE") ? atoi(getenv("FB2_ASM_SWIZZLE")) : 1;
+  for (int k = 0; k < 32; ++k) R.stage_swz[k] = use_swz ? h_stage_swz[k] : 0;
   R.qw = a.qw; R.gphi = a.gphi; R.gdphi = a.gdphi; R.src_qp = a.src_qp; R.val = a.val; R.rhs = a.rhs; R.fn = a.fn;
   for (int k = 0; k < 27; ++k) R.row_of_node[k] = k < P * P * P ? A->rows_row_of_node[k] : 0;
   R.npy = (s->m.nloc[1] + TY - 1) / TY; R.npz = (s->m.nloc[2] + TZ - 1) / TZ;
