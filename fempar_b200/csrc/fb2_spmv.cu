@@ -23,6 +23,24 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// the same copy with an L2 eviction policy: the once-read streams (val, ja) are marked evict_first so that they do not push the
+// re-used data (x segments, class index tables: L2-resident across neighbouring tiles) out of the 126 MB L2
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+               : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n"
@@ -86,6 +104,7 @@ struct SpmvClassDesc {
 #define SPMV_STAG_JA 8
 #define SPMV_STAG_IDX 16
 #define SPMV_WAIT_NS_DEFAULT 0u
+#define SPMV_L2HINT_DEFAULT 1
 
 // Tried and rejected in round 2 (profiles/r2_spmv_history.txt): consumers that stream the rows of a warp's range 32 entries at a
 // time (contiguous shared-memory reads, one xor tree per finished row).  It halves the shared-memory wavefronts per non-zero
@@ -115,7 +134,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
                                                              int dcap, const unsigned char* __restrict__ tile_class,
                                                              const SpmvClassDesc* __restrict__ cls_desc,
                                                              const unsigned short* __restrict__ cls_idx, int tr, uint32_t wait_hint,
-                                                             const int* __restrict__ tile_priv) {
+                                                             const int* __restrict__ tile_priv, int l2hint) {
   constexpr int IB = COMP ? 2 : 4;                       // bytes per streamed column index
   constexpr i64 AL = COMP ? 7 : 3;                       // element-range alignment mask
   const int* ja = (const int*)ja_any;
@@ -153,6 +172,7 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
     // the consumer side): lane g copies chunk g of val and of ja (or of the class index table); for a class tile lane l also
     // copies x segment l - 1.
     const int plane = tid - NC;
+    const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
     const int TPRP = (R <= 16 ? 128 : 256) / R;
     const int nch = tr ? 32 / TPRP : 1;                  // chunks per tile
     const int CW = tr ? R / nch : R;                     // rows per chunk
@@ -215,11 +235,13 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
         // warp then read different shared-memory banks although their rows start a multiple of 128 bytes apart
         const size_t de = (size_t)(ca - e0a);
         const size_t g = tr ? (size_t)plane : 0;
-        bulk_g2s(base + (de + SPMV_STAG_VAL * g) * 8, val + ca, cn * 8u, &full_bar[s]);
+        if (l2hint & 1) bulk_g2s_hint(base + (de + SPMV_STAG_VAL * g) * 8, val + ca, cn * 8u, &full_bar[s], pol_stream);
+        else bulk_g2s(base + (de + SPMV_STAG_VAL * g) * 8, val + ca, cn * 8u, &full_bar[s]);
         if (is_cls) {
           if (!have_idx && tr)
             bulk_g2s(base + (size_t)cap * 8 + (de + SPMV_STAG_IDX * g) * 2, cls_idx + (size_t)cls * cap + de, cn * 2u, &full_bar[s]);
         } else if (COMP) bulk_g2s(base + (size_t)cap * 8 + de * 2, ja16 + ca, cn * 2u, &full_bar[s]);
+        else if (l2hint & 1) bulk_g2s_hint(base + (size_t)cap * 8 + (de + SPMV_STAG_JA * g) * 4, ja + ca, cn * 4u, &full_bar[s], pol_stream);
         else bulk_g2s(base + (size_t)cap * 8 + (de + SPMV_STAG_JA * g) * 4, ja + ca, cn * 4u, &full_bar[s]);
       }
       if (is_cls) {
@@ -227,8 +249,12 @@ __global__ void __launch_bounds__(NC + 32, 4) k_spmv_stream(i64 n, const i64* __
         const SpmvClassDesc& D = cls_desc[cls];
         if (plane >= 1 && plane <= D.nseg) {
           const int g = plane - 1;
-          bulk_g2s(base + (size_t)cap * 8 + (size_t)D.idx_bytes + (size_t)D.off[g] * 8, x + (r0 + D.delta[g]), (uint32_t)D.len[g] * 8u,
-                   &full_bar[s]);
+          if (l2hint & 2)
+            bulk_g2s_hint(base + (size_t)cap * 8 + (size_t)D.idx_bytes + (size_t)D.off[g] * 8, x + (r0 + D.delta[g]),
+                          (uint32_t)D.len[g] * 8u, &full_bar[s], pol_keep);
+          else
+            bulk_g2s(base + (size_t)cap * 8 + (size_t)D.idx_bytes + (size_t)D.off[g] * 8, x + (r0 + D.delta[g]), (uint32_t)D.len[g] * 8u,
+                     &full_bar[s]);
         }
       }
       e0 = ne0; r0 = nr0; nr = nnr; d0 = nd0; d1 = nd1; cls = ncls; cb = ncb; ce = nce;
@@ -960,13 +986,15 @@ int fb2_spmv_stream_range(fb2_matrix_s* A, const double* x, double* y, bool fuse
   i64 grid = chunk ? (nt + chunk - 1) / chunk : (nt < A->spmv_grid ? nt : (i64)A->spmv_grid);
   // class tiles bulk-copy segments of x: they need a 16-byte aligned x (always true for library vectors, not for views)
   const unsigned char* tcls = (A->spmv_cls == 1 && (((uintptr_t)x) & 15) == 0) ? A->d_tile_class + t0 : nullptr;
+  // L2 eviction hints of the bulk copies: bit 0 = val / ja streams evict_first, bit 1 = x segments evict_last (FB2_SPMV_L2HINT)
+  const int l2hint = getenv("FB2_SPMV_L2HINT") ? atoi(getenv("FB2_SPMV_L2HINT")) : SPMV_L2HINT_DEFAULT;
   // suspend-time hint (ns) of the consumers' wait for a full stage; 0 = plain try_wait spin
   const uint32_t wait_hint = getenv("FB2_SPMV_WAIT_NS") ? (uint32_t)atoi(getenv("FB2_SPMV_WAIT_NS")) : SPMV_WAIT_NS_DEFAULT;
 #define SPMV_LAUNCH_NC(FD, CP, NCT, JA, SMEM, DICT, DPTR, DCAP)                                                                   \
   k_spmv_stream<FD, CP, NCT><<<(unsigned)grid, NCT + 32, SMEM, st>>>(A->n, A->d_irp, JA, A->d_val, x, y, FD ? partials : nullptr, \
                                                                     done_flag, A->spmv_R, A->spmv_cap, nt, A->spmv_stages,   \
                                                                     A->d_tile_row + t0, A->d_tile_nrows + t0, chunk, DICT, DPTR, DCAP, \
-                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, CP ? 0 : A->spmv_tr, wait_hint, A->d_tile_priv ? A->d_tile_priv + t0 : nullptr)
+                                                                    CP ? nullptr : tcls, (const SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, CP ? 0 : A->spmv_tr, wait_hint, A->d_tile_priv ? A->d_tile_priv + t0 : nullptr, l2hint)
 #define SPMV_LAUNCH(FD, CP, JA, SMEM, DICT, DPTR, DCAP)                                                   \
   do {                                                                                                    \
     if (!CP && A->spmv_nc == 128) SPMV_LAUNCH_NC(FD, false, 128, JA, SMEM, DICT, DPTR, DCAP);             \
