@@ -575,7 +575,7 @@ __global__ void k_tile_hash(i64 ntiles, const i64* __restrict__ irp, const int* 
 // block per class: segments of the representative tile's distinct columns and the window position of every entry
 __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp, const int* __restrict__ ja,
                                                      const i64* __restrict__ tile_row, const unsigned char* __restrict__ tile_nrows,
-                                                     const int* __restrict__ rep, int cap, int idx_extra, SpmvClassDesc* desc,
+                                                     const int* __restrict__ rep, int cap, int idx_extra, int x_align, SpmvClassDesc* desc,
                                                      unsigned short* cls_idx, int* valid) {
   __shared__ int sb[DICT_SORT_MAX], su[DICT_SORT_MAX];
   __shared__ int s_scan[256];
@@ -618,24 +618,36 @@ __global__ void __launch_bounds__(256) k_class_build(const i64* __restrict__ irp
     if (i < m && (i == 0 || sb[i] != sb[i - 1])) su[pos++] = sb[i];
   __syncthreads();
   if (tid == 0) {
-    // greedy runs of the sorted distinct deltas; starts rounded down and lengths rounded up to even (16-byte bulk copies)
-    int nseg = 0, total = 0, ok = m > 0;
+    // greedy runs of the sorted distinct deltas; starts rounded down and lengths rounded up to even (16-byte bulk copies).
+    // x_align: every segment starts at a window position congruent to its first column modulo 16 doubles (= the 32 banks), so
+    // that window position == column (mod 16) across ALL segments.  The four lane groups of a consumer warp read columns that
+    // differ by multiples of 8 (the same kind of row in consecutive cells) and the 8 lanes of a group read 8 consecutive
+    // entries, whose columns are distinct modulo 8 even where they straddle two segments: with packed segments those residues
+    // were scrambled (ncu: 3.5 instead of 2 wavefronts per x-window LDS.64).  Falls back to packed segments when the padding
+    // does not fit the stage.
+    int nseg = 0, total = 0, extent = 0, ok = m > 0;
     // idx_extra: room behind the table for the staggered chunks of the transposed row layout (the x window starts behind it)
     const int idx_n = (shift + m + 7) & ~7;
     const int xw_cap = (cap * 4 - (idx_n + idx_extra) * 2) / 8;
-    int i = 0;
-    while (ok && i < nu) {
-      const int start = su[i] & ~1;
-      int last = su[i];
-      ++i;
-      while (i < nu && su[i] - last <= SPMV_SEG_GAP) { last = su[i]; ++i; }
-      const int len = (last - start + 2) & ~1;
-      if (nseg >= 31) { ok = 0; break; }
-      D.delta[nseg] = start; D.len[nseg] = len; D.off[nseg] = total;
-      total += len; ++nseg;
+    for (int mode = x_align ? 1 : 0; mode >= 0; --mode) {
+      nseg = 0; total = 0; extent = 0; ok = m > 0;
+      int i = 0;
+      while (ok && i < nu) {
+        const int start = su[i] & ~1;
+        int last = su[i];
+        ++i;
+        while (i < nu && su[i] - last <= SPMV_SEG_GAP) { last = su[i]; ++i; }
+        const int len = (last - start + 2) & ~1;
+        if (nseg >= 31) { ok = 0; break; }
+        int off = extent;
+        if (mode) off += (((start - off) % 16) + 16) % 16;
+        D.delta[nseg] = start; D.len[nseg] = len; D.off[nseg] = off;
+        extent = off + len; total += len; ++nseg;
+      }
+      if (extent > xw_cap || extent > 0xFFFF || idx_n + idx_extra > cap) ok = 0;
+      if (ok || nseg >= 31) break;
     }
-    if (total > xw_cap || total > 0xFFFF || idx_n + idx_extra > cap) ok = 0;
-    D.nseg = nseg; D.idx_bytes = (idx_n + idx_extra) * 2; D.x_bytes = total * 8; D.pad = 0;
+    D.nseg = nseg; D.idx_bytes = (idx_n + idx_extra) * 2; D.x_bytes = total * 8; D.pad = extent;
     for (int g = nseg; g < 32; ++g) { D.delta[g] = 0; D.len[g] = 0; D.off[g] = 0; }
     s_ok = ok;
   }
@@ -784,7 +796,8 @@ static int spmv_build_classes(fb2_matrix_s* A) {
     FB2_CUDA(cudaMemsetAsync(d_nin, 0, sizeof(unsigned long long), st));
     const int tpr = (A->spmv_R <= 16 ? 128 : 256) / A->spmv_R;
     const int idx_extra = A->spmv_tr ? SPMV_STAG_IDX * (32 / tpr - 1) : 0;
-    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap, idx_extra,
+    const int x_align = getenv("FB2_SPMV_XALIGN") ? atoi(getenv("FB2_SPMV_XALIGN")) : 0;   // bank-preserving x windows: measured, no gain (profiles/r2_spmv_history.txt)
+    k_class_build<<<ncls, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_rep, A->spmv_cap, idx_extra, x_align,
                                         (SpmvClassDesc*)A->d_cls_desc, A->d_cls_idx, d_valid);
     k_tile_classify<<<fb2_num_sms() * 8, 256, 0, st>>>(nt, A->n, A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, hash, ncls, d_ch,
                                                         d_rep, d_valid, (const SpmvClassDesc*)A->d_cls_desc, A->d_tile_class, d_nin);
@@ -818,7 +831,7 @@ static int spmv_build_classes(fb2_matrix_s* A) {
       FB2_TRY(fb2_dalloc(&A->d_tile_priv, (size_t)nt));
       FB2_CUDA(cudaMemsetAsync(A->d_tile_priv, 0xff, sizeof(int) * (size_t)nt, st));
       SpmvClassDesc* pdesc = (SpmvClassDesc*)desc2 + ncls;
-      k_class_build<<<(unsigned)n_rest, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_list, A->spmv_cap, idx_extra,
+      k_class_build<<<(unsigned)n_rest, 256, 0, st>>>(A->d_irp, A->d_ja, A->d_tile_row, A->d_tile_nrows, d_list, A->spmv_cap, idx_extra, x_align,
                                                      pdesc, idx2 + (size_t)ncls * A->spmv_cap, d_valid2);
       k_private_assign<<<(unsigned)((n_rest + 255) / 256), 256, 0, st>>>((int)n_rest, d_list, d_valid2, pdesc, A->d_tile_row, A->n, ncls,
                                                                           A->d_tile_class, A->d_tile_priv, d_used);

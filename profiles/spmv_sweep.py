@@ -23,13 +23,15 @@ bytes_alg = A.nnz * 12 + A.num_rows * 24
 # (R, STAGES, CAP, CHUNK, CONSUMERS, TRANSPOSE); round-2 call 4 showed 2 stages x 4 CTAs/SM ahead of deeper rings and smaller tiles;
 # TRANSPOSE: row map of the consumer lane groups (0 natural, 1 transposed + staggered chunks), A/B/A/B against box drift
 # WAIT_NS: suspend-time hint of the consumers' mbarrier wait (0 = plain try_wait spin)
-# last column here: FB2_SPMV_L2HINT (bit 0: val / ja copies evict_first, bit 1: x segments evict_last)
-combos = [(32, 2, 2304, 32, 256, 1, 0, 0), (32, 2, 2304, 32, 256, 1, 0, 1), (32, 2, 2304, 32, 256, 1, 0, 2), (32, 2, 2304, 32, 256, 1, 0, 3),
-          (32, 2, 2304, 32, 256, 1, 0, 0), (32, 2, 2304, 32, 256, 1, 0, 1), (32, 2, 2304, 32, 256, 1, 0, 3)]
+# last columns: FB2_SPMV_L2HINT (bit 0: val / ja copies evict_first, bit 1: x segments evict_last), FB2_SPMV_XALIGN (x-window
+# segments placed so that window position == column modulo 16 doubles)
+combos = [(32, 2, 2304, 32, 256, 1, 0, 1, 1), (32, 2, 2304, 32, 256, 1, 0, 1, 0), (32, 2, 2304, 32, 256, 1, 0, 1, 1), (32, 2, 2304, 32, 256, 1, 0, 1, 0),
+          (32, 2, 2304, 32, 256, 0, 0, 1, 1), (32, 2, 2304, 32, 256, 0, 0, 1, 0)]
 if order != 2:
-    combos = [(16, 2, 2304, 32, 128, 0, 0, 0), (16, 2, 2304, 32, 128, 0, 0, 1), (16, 2, 2304, 32, 128, 0, 0, 3), (16, 2, 2304, 32, 128, 0, 0, 0)]
-for R, st, cap, chunk, nc, tr, wait_ns, l2hint in combos:
+    combos = [(16, 2, 2304, 32, 128, 0, 0, 1, 1), (16, 2, 2304, 32, 128, 0, 0, 1, 0), (16, 2, 2304, 32, 128, 0, 0, 1, 1), (16, 2, 2304, 32, 128, 0, 0, 1, 0)]
+for R, st, cap, chunk, nc, tr, wait_ns, l2hint, xalign in combos:
     os.environ["FB2_SPMV_L2HINT"] = str(l2hint)
+    os.environ["FB2_SPMV_XALIGN"] = str(xalign)
     os.environ["FB2_SPMV_R"], os.environ["FB2_SPMV_STAGES"], os.environ["FB2_SPMV_CAP"], os.environ["FB2_SPMV_CHUNK"] = \
         str(R), str(st), str(cap), str(chunk)
     os.environ["FB2_SPMV_CONSUMERS"] = str(nc)
@@ -40,7 +42,7 @@ for R, st, cap, chunk, nc, tr, wait_ns, l2hint in combos:
         ils.iterate(op.get_translation(), x, 3)
         t, ts = ils.iterate(op.get_translation(), x, 12)
         ms = ts / 12
-        print("transpose=%d wait_ns=%-5d l2hint=%d nc=%d " % (tr, wait_ns, l2hint, nc), end="")
+        print("transpose=%d l2hint=%d xalign=%d nc=%d " % (tr, l2hint, xalign, nc), end="")
         print("R=%-3d stages=%d cap=%-5d chunk=%-4d  spmv %.3f ms  %.0f GB/s algorithmic  tiles_in_class %.0f / %.0f  ctas/sm %.0f  "
               "row-map cost natural %.4g transposed %.4g" % (
                   R, st, cap, chunk, ms, bytes_alg / ms / 1e6, op.last_phase_ms("spmv_tiles_in_class"), op.last_phase_ms("spmv_tiles"),
